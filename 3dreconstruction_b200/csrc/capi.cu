@@ -1,0 +1,208 @@
+// capi.cu — the extern "C" boundary declared in include/b200match.h.  Host-side planning only:
+// carve the caller's workspace, copy the pair table, enqueue the kernels.  No allocation, no
+// exceptions, no CPU compute path.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "common.cuh"
+
+static std::atomic<long long> g_launches{0};
+static thread_local char g_cuda_err[256] = "";
+
+void b200m_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int b200m_set_cuda_error(cudaError_t e, const char* where) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", where, cudaGetErrorString(e));
+    return B200M_ECUDA;
+}
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+static inline int pow2ceil(int n) { int p = 1; while (p < n) p <<= 1; return p; }
+
+static int choose_splits(int num_pairs, int max_n, int max_m, int mode, int sm_count) {
+    // Enough CTAs for ~2 per SM; a single image pair has only ceil(n/128) row tiles.
+    long long tiles = (long long)num_pairs * ((max_n + 127) / 128);
+    if (mode == B200M_MODE_CROSS) tiles += (long long)num_pairs * ((max_m + 127) / 128);
+    long long want = 2LL * sm_count;
+    int S = (int)((want + tiles - 1) / (tiles > 0 ? tiles : 1));
+    int max_split = (((max_n < max_m ? max_n : max_m) + 255) / 256);   // keep >= 256 columns per split
+    if (S > max_split) S = max_split;
+    if (S > 8) S = 8;
+    if (S < 1) S = 1;
+    return S;
+}
+
+static int g_sm_count = 0;
+static int device_sm_count() {
+    if (g_sm_count == 0) {
+        int dev = 0, sm = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+        if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        g_sm_count = sm;
+    }
+    return g_sm_count;
+}
+
+// Lay the workspace out.  base may be null (size query).
+static void make_plan(MatchPlan& pl, char* base, int mode, int num_pairs, long long total_n, long long total_m,
+                      long long total_pad, int S, bool need_bwd) {
+    size_t off = 0;
+    pl.S = S; pl.total_n = total_n; pl.total_m = total_m; pl.total_pad = total_pad;
+    pl.pairs = (DevPair*)(base + off); off = align_up(off + sizeof(DevPair) * (size_t)num_pairs, 256);
+    pl.fwd = (Top2*)(base + off);      off = align_up(off + sizeof(Top2) * (size_t)S * total_n, 256);
+    pl.bwd = (Top2*)(base + off);      off = align_up(off + (need_bwd ? sizeof(Top2) * (size_t)S * total_m : 0), 256);
+    pl.sortbuf = (u64*)(base + off);   off = align_up(off + sizeof(u64) * (size_t)total_pad, 256);
+    pl.tbest = (int32_t*)(base + off); off = align_up(off + sizeof(int32_t) * (size_t)total_n, 256);
+    pl.bytes = off;
+    (void)mode;
+}
+
+extern "C" {
+
+int b200m_version(void) { return B200M_VERSION; }
+
+const char* b200m_error_string(int code) {
+    switch (code) {
+        case B200M_OK: return "ok";
+        case B200M_EINVAL: return "invalid argument";
+        case B200M_EWORKSPACE: return "workspace too small";
+        case B200M_ECUDA: return "CUDA error";
+        case B200M_ENODEVICE: return "no sm_100 device (this library has no CPU path)";
+        case B200M_EUNSUPPORTED: return "unsupported shape";
+        default: return "unknown error";
+    }
+}
+
+const char* b200m_last_cuda_error(void) { return g_cuda_err; }
+
+int b200m_device_info(int* sm_count, int* cc_major, int* cc_minor) {
+    int dev = 0, n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return B200M_ENODEVICE;
+    if (cudaGetDevice(&dev) != cudaSuccess) return B200M_ENODEVICE;
+    int sm = 0, ma = 0, mi = 0;
+    cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&ma, cudaDevAttrComputeCapabilityMajor, dev);
+    cudaDeviceGetAttribute(&mi, cudaDevAttrComputeCapabilityMinor, dev);
+    if (sm_count) *sm_count = sm;
+    if (cc_major) *cc_major = ma;
+    if (cc_minor) *cc_minor = mi;
+    return ma == 10 ? B200M_OK : B200M_ENODEVICE;
+}
+
+int64_t b200m_launch_count(void) { return g_launches.load(); }
+void b200m_reset_launch_count(void) { g_launches.store(0); }
+
+int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t total_n, int64_t total_m,
+                          int max_n, int max_m, int D, size_t* bytes) {
+    (void)kind; (void)D;
+    if (!bytes || num_pairs < 0 || total_n < 0 || total_m < 0) return B200M_EINVAL;
+    // Upper bounds that do not depend on the device: S <= 8, sum pow2ceil(n) <= 2 * total_n + P.
+    MatchPlan pl;
+    make_plan(pl, nullptr, mode, num_pairs, total_n, total_m, 2 * total_n + num_pairs, 8,
+              mode == B200M_MODE_CROSS);
+    (void)max_n; (void)max_m;
+    *bytes = pl.bytes;
+    return B200M_OK;
+}
+
+}  // extern "C"
+
+// Shared front half of match_pairs / knn2_pairs: validate, plan, upload pair table, run knn stage.
+static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64_t q_rows, const void* t_desc,
+                         const void* t_norm, int64_t t_rows, int D, const b200m_pair* pairs_host,
+                         int num_pairs, int mode, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                         MatchPlan& pl, int& max_n, int& max_npad) {
+    if (num_pairs < 0 || D <= 0 || (num_pairs > 0 && (!pairs_host || !q_desc || !t_desc || !workspace)))
+        return B200M_EINVAL;
+    if (kind != B200M_KIND_HAMMING && kind != B200M_KIND_L2_I8 && kind != B200M_KIND_L2_F32) return B200M_EINVAL;
+    if (kind != B200M_KIND_HAMMING && (!q_norm || !t_norm) && num_pairs > 0) return B200M_EINVAL;
+    int sm = device_sm_count();
+    if (sm == 0) return B200M_ENODEVICE;
+
+    long long total_n = 0, total_m = 0, total_pad = 0;
+    int max_m = 0;
+    max_n = 0; max_npad = 1;
+    std::vector<DevPair> dp((size_t)num_pairs);
+    for (int p = 0; p < num_pairs; ++p) {
+        const b200m_pair& s = pairs_host[p];
+        if (s.n < 0 || s.m < 0 || s.q_off < 0 || s.t_off < 0 || s.out_off < 0) return B200M_EINVAL;
+        if ((int64_t)s.q_off + s.n > q_rows || (int64_t)s.t_off + s.m > t_rows) return B200M_EINVAL;
+        DevPair& d = dp[p];
+        d.q_off = s.q_off; d.n = s.n; d.t_off = s.t_off; d.m = s.m; d.out_off = s.out_off;
+        d.fwd_off = total_n; d.bwd_off = total_m; d.sort_off = total_pad;
+        d.npad = pow2ceil(s.n > 0 ? s.n : 1); d._pad = 0;
+        total_n += s.n; total_m += s.m; total_pad += d.npad;
+        if (s.n > max_n) max_n = s.n;
+        if (s.m > max_m) max_m = s.m;
+        if (d.npad > max_npad) max_npad = d.npad;
+    }
+    const bool need_bwd = mode == B200M_MODE_CROSS;
+    int S = choose_splits(num_pairs, max_n, max_m, mode, sm);
+    make_plan(pl, (char*)workspace, mode, num_pairs, total_n, total_m, total_pad, S, need_bwd);
+    if (pl.bytes > workspace_bytes) return B200M_EWORKSPACE;
+    if (num_pairs == 0 || total_n == 0) return B200M_OK;
+    B200M_CUDA_CHECK(cudaMemcpyAsync(pl.pairs, dp.data(), sizeof(DevPair) * (size_t)num_pairs,
+                                     cudaMemcpyHostToDevice, st), "pair table upload");
+    // pageable source: the copy is staged before the call returns, so `dp` may go out of scope.
+    for (int dir = 0; dir < (need_bwd ? 2 : 1); ++dir) {
+        bool back = dir == 1;
+        Top2* out = back ? pl.bwd : pl.fwd;
+        long long rows = back ? total_m : total_n;
+        int rc;
+        if (kind == B200M_KIND_HAMMING)
+            rc = launch_hamming_top2((const uint8_t*)q_desc, (const uint8_t*)t_desc, D, pl.pairs, num_pairs,
+                                     max_n, max_m, S, back, out, rows, st);
+        else if (kind == B200M_KIND_L2_I8)
+            rc = launch_l2_i8_top2((const int8_t*)q_desc, (const int32_t*)q_norm, q_rows, (const int8_t*)t_desc,
+                                   (const int32_t*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
+                                   back, out, rows, st);
+        else
+            rc = launch_l2_f32_top2((const float*)q_desc, (const float*)q_norm, q_rows, (const float*)t_desc,
+                                    (const float*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
+                                    back, out, rows, st);
+        if (rc != B200M_OK) return rc;
+    }
+    return B200M_OK;
+}
+
+extern "C" {
+
+int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                      const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                      const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                      int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    if (mode != B200M_MODE_RATIO && mode != B200M_MODE_CROSS && mode != B200M_MODE_NN) return B200M_EINVAL;
+    if (num_pairs > 0 && (!out_q || !out_t || !out_d || !out_count)) return B200M_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    MatchPlan pl; int max_n = 0, max_npad = 1;
+    int rc = run_knn_stage(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs,
+                           mode, workspace, workspace_bytes, st, pl, max_n, max_npad);
+    if (rc != B200M_OK) return rc;
+    if (num_pairs == 0) return B200M_OK;
+    if (pl.total_n == 0) {
+        B200M_CUDA_CHECK(cudaMemsetAsync(out_count, 0, sizeof(int32_t) * (size_t)num_pairs, st), "count memset");
+        return B200M_OK;
+    }
+    rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, st);
+    if (rc != B200M_OK) return rc;
+    return launch_sort_emit(kind, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, st);
+}
+
+int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                     const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                     const b200m_pair* pairs_host, int num_pairs,
+                     int32_t* idx1, int32_t* idx2, float* d1, float* d2,
+                     void* workspace, size_t workspace_bytes, void* stream) {
+    if (num_pairs > 0 && (!idx1 || !idx2 || !d1 || !d2)) return B200M_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    MatchPlan pl; int max_n = 0, max_npad = 1;
+    int rc = run_knn_stage(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs,
+                           B200M_MODE_NN, workspace, workspace_bytes, st, pl, max_n, max_npad);
+    if (rc != B200M_OK) return rc;
+    if (num_pairs == 0 || pl.total_n == 0) return B200M_OK;
+    return launch_knn2_emit(kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,75 @@
+// common.cuh — shared device/host definitions for the b200match kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/b200match.h"
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+// Per-row result of the knn stage.  key = (value << 32) | train_index, so that u64 `min`
+// orders by (value asc, index asc) == cv2's "ties -> lowest trainIdx" (SURVEY F8-i).
+// value: HAMMING -> bit count; L2_I8 -> exact integer squared distance;
+//        L2_F32  -> IEEE bits of the (non-negative) fp32 squared distance.
+struct Top2 { u64 k1, k2; };
+#define B200M_SENTINEL 0xFFFFFFFFFFFFFFFFull
+
+// Device-side pair record (host b200m_pair + offsets into the per-row workspaces).
+struct DevPair {
+    int q_off, n, t_off, m;
+    long long out_off;   // first output slot (capacity n)
+    long long fwd_off;   // first row of this pair in the forward Top2 array (prefix sum of n)
+    long long bwd_off;   // first row in the backward Top2 array (prefix sum of m), MODE_CROSS only
+    long long sort_off;  // first slot in the padded sort buffer (prefix sum of pow2ceil(n))
+    int npad;            // pow2ceil(n)
+    int _pad;
+};
+
+struct MatchPlan {       // host-side carve-up of the caller's workspace
+    DevPair* pairs;      // [P]
+    Top2* fwd;           // [S][total_n]
+    Top2* bwd;           // [S][total_m]   (MODE_CROSS)
+    u64* sortbuf;        // [sum npad]
+    int32_t* tbest;      // [total_n]
+    int S;               // column splits per direction
+    long long total_n, total_m, total_pad;
+    size_t bytes;
+};
+
+__device__ __forceinline__ void top2_insert(u64& k1, u64& k2, u64 k) {
+    u64 hi = k1 > k ? k1 : k;
+    k1 = k1 < k ? k1 : k;
+    k2 = k2 < hi ? k2 : hi;
+}
+__device__ __forceinline__ void top2_insert32(u32& k1, u32& k2, u32 k) {
+    k2 = min(k2, max(k1, k));
+    k1 = min(k1, k);
+}
+
+// host helpers implemented in capi.cu
+void b200m_count_launch(int n = 1);
+int b200m_set_cuda_error(cudaError_t e, const char* where);
+#define B200M_CUDA_CHECK(expr, where)                                   \
+    do {                                                                \
+        cudaError_t _e = (expr);                                        \
+        if (_e != cudaSuccess) return b200m_set_cuda_error(_e, where);  \
+    } while (0)
+
+// kernel launchers (one per .cu)
+int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, const DevPair* pairs,
+                        int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
+                        long long total_rows, cudaStream_t st);
+int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows,
+                      const int8_t* t_desc, const int32_t* t_norm, int64_t t_rows, int D,
+                      const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
+                      Top2* out, long long total_rows, cudaStream_t st);
+int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
+                       const float* t_desc, const float* t_norm, int64_t t_rows, int D,
+                       const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
+                       Top2* out, long long total_rows, cudaStream_t st);
+int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
+                    cudaStream_t st);
+int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
+                     int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st);
+int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
+                     float* d1, float* d2, cudaStream_t st);

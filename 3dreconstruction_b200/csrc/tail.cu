@@ -1,0 +1,175 @@
+// tail.cu — everything after the knn stage, on the device:
+//   finalize : merge column-split partial top-2s, convert to cv2's float32 distance, apply the
+//              mode test of EnhancedBFMatcher.match
+//              (/root/reference/FeatureMatchingExtraction/feature_matchers.py:212-224 ratio test in
+//              fp64 as Python evaluates `m.distance < ratio * n.distance`; :225-238 cross-check ==
+//              strict mutual first-argmin; or plain 1-NN)
+//   sort_emit: the reference's stable `sort(key=score)` (:241) == order by (distance, queryIdx);
+//              one CTA per pair runs a bitonic network over 64-bit keys
+//              (float32 distance bits << 32 | queryIdx); rejected rows carry a sentinel and sink.
+//   knn2_emit: raw k=2 neighbours for knnMatch-level parity checks.
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float value_to_distance(int kind, u32 v) {
+    if (kind == B200M_KIND_HAMMING) return (float)v;                     // exact integer as float
+    if (kind == B200M_KIND_L2_I8) return __fsqrt_rn((float)v);          // v < 2^24: exact -> IEEE sqrt
+    return __fsqrt_rn(__uint_as_float(v));                              // fp32 squared distance bits
+}
+
+__device__ __forceinline__ Top2 merge_splits(const Top2* __restrict__ arr, long long total, int S, long long row) {
+    Top2 r = arr[row];
+    for (int s = 1; s < S; ++s) {
+        Top2 o = arr[(long long)s * total + row];
+        top2_insert(r.k1, r.k2, o.k1);
+        top2_insert(r.k1, r.k2, o.k2);
+    }
+    return r;
+}
+
+__global__ void __launch_bounds__(256)
+finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
+                const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
+                long long total_m, int S, u64* __restrict__ sortbuf, int32_t* __restrict__ tbest) {
+    int p = blockIdx.x / blocks_per_pair;
+    int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
+    DevPair pr = pairs[p];
+    if (i >= pr.n) return;
+    Top2 t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
+    u64 key = B200M_SENTINEL;
+    int32_t tb = -1;
+    if (t.k1 != B200M_SENTINEL) {
+        u32 j1 = (u32)t.k1;
+        float d1 = value_to_distance(kind, (u32)(t.k1 >> 32));
+        bool keep;
+        if (mode == B200M_MODE_RATIO) {
+            keep = false;
+            if (t.k2 != B200M_SENTINEL) {            // cv2 returns a single neighbour when m == 1
+                float d2 = value_to_distance(kind, (u32)(t.k2 >> 32));
+                keep = (double)d1 < ratio * (double)d2;
+            }
+        } else if (mode == B200M_MODE_CROSS) {
+            Top2 b = merge_splits(bwd, total_m, S, pr.bwd_off + j1);
+            keep = (u32)b.k1 == (u32)i;
+        } else {
+            keep = true;
+        }
+        tb = (int32_t)j1;
+        if (keep) key = ((u64)__float_as_uint(d1) << 32) | (u64)(u32)i;
+    }
+    sortbuf[pr.sort_off + i] = key;
+    tbest[pr.fwd_off + i] = tb;
+}
+
+__device__ __forceinline__ void bitonic(u64* a, int npad) {
+    for (int k = 2; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < (npad >> 1); t += blockDim.x) {
+                int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));   // index with bit j clear
+                int hi = lo | j;
+                u64 x = a[lo], y = a[hi];
+                bool up = (lo & k) == 0;
+                if ((x > y) == up) { a[lo] = y; a[hi] = x; }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
+                 const int32_t* __restrict__ tbest, int smem_keys, int32_t* __restrict__ out_q,
+                 int32_t* __restrict__ out_t, float* __restrict__ out_d, int32_t* __restrict__ out_count) {
+    extern __shared__ u64 skeys[];
+    __shared__ int s_count;
+    DevPair pr = pairs[blockIdx.x];
+    u64* g = sortbuf + pr.sort_off;
+    const int n = pr.n, npad = pr.npad;
+    if (threadIdx.x == 0) s_count = 0;
+    u64* a = npad <= smem_keys ? skeys : g;
+    int local = 0;
+    for (int t = threadIdx.x; t < npad; t += blockDim.x) {
+        u64 k = t < n ? g[t] : B200M_SENTINEL;
+        local += (k != B200M_SENTINEL);
+        if (a != g || t >= n) a[t] = k;
+    }
+    __syncthreads();
+    if (local) atomicAdd(&s_count, local);
+    if (npad > 1) bitonic(a, npad);
+    __syncthreads();
+    const int cnt = s_count;
+    for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
+        u64 k = a[t];
+        int q = (int)(u32)k;
+        out_q[pr.out_off + t] = q;
+        out_t[pr.out_off + t] = tbest[pr.fwd_off + q];
+        out_d[pr.out_off + t] = __uint_as_float((u32)(k >> 32));
+    }
+    if (threadIdx.x == 0) out_count[blockIdx.x] = cnt;
+}
+
+__global__ void __launch_bounds__(256)
+knn2_emit_kernel(int kind, const DevPair* __restrict__ pairs, int blocks_per_pair,
+                 const Top2* __restrict__ fwd, long long total_n, int S, int32_t* __restrict__ idx1,
+                 int32_t* __restrict__ idx2, float* __restrict__ d1, float* __restrict__ d2) {
+    int p = blockIdx.x / blocks_per_pair;
+    int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
+    DevPair pr = pairs[p];
+    if (i >= pr.n) return;
+    Top2 t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
+    long long o = pr.out_off + i;
+    bool h1 = t.k1 != B200M_SENTINEL, h2 = t.k2 != B200M_SENTINEL;
+    idx1[o] = h1 ? (int32_t)(u32)t.k1 : -1;
+    idx2[o] = h2 ? (int32_t)(u32)t.k2 : -1;
+    d1[o] = h1 ? value_to_distance(kind, (u32)(t.k1 >> 32)) : -1.0f;
+    d2[o] = h2 ? value_to_distance(kind, (u32)(t.k2 >> 32)) : -1.0f;
+}
+
+}  // namespace
+
+int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
+                    cudaStream_t st) {
+    int bpp = (max_n + 255) / 256;
+    long long grid = (long long)num_pairs * bpp;
+    if (grid <= 0) return B200M_OK;
+    if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    finalize_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
+                                                    plan.bwd, plan.total_m, plan.S, plan.sortbuf, plan.tbest);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "finalize_kernel launch");
+    return B200M_OK;
+}
+
+int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
+                     int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st) {
+    (void)kind;
+    if (num_pairs <= 0) return B200M_OK;
+    static bool attr_set = false;
+    const int kMaxSmemKeys = 16384;                       // 128 KiB of 64-bit keys
+    if (!attr_set) {
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(sort_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              kMaxSmemKeys * (int)sizeof(u64)), "sort_emit smem attr");
+        attr_set = true;
+    }
+    int smem_keys = max_npad <= kMaxSmemKeys ? max_npad : kMaxSmemKeys;
+    int threads = max_npad >= 2048 ? 1024 : (max_npad >= 512 ? 256 : 64);
+    sort_emit_kernel<<<num_pairs, threads, (size_t)smem_keys * sizeof(u64), st>>>(
+        plan.pairs, plan.sortbuf, plan.tbest, smem_keys, out_q, out_t, out_d, out_count);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "sort_emit_kernel launch");
+    return B200M_OK;
+}
+
+int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
+                     float* d1, float* d2, cudaStream_t st) {
+    int bpp = (max_n + 255) / 256;
+    long long grid = (long long)num_pairs * bpp;
+    if (grid <= 0) return B200M_OK;
+    if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    knn2_emit_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, plan.pairs, bpp, plan.fwd, plan.total_n, plan.S,
+                                                     idx1, idx2, d1, d2);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "knn2_emit_kernel launch");
+    return B200M_OK;
+}

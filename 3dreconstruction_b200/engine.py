@@ -1,0 +1,207 @@
+"""Array-first host side of the matcher: owns device buffers (torch = plumbing only) and calls the
+C-ABI in include/b200match.h.  Everything that computes runs in libb200match.so on the GPU; a
+missing library or device raises — there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import NamedTuple, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+NORM_L2, NORM_HAMMING = 4, 6      # cv2.NORM_L2, cv2.NORM_HAMMING
+
+
+class MatchArrays(NamedTuple):
+    query_idx: np.ndarray    # int32 [K]
+    train_idx: np.ndarray    # int32 [K]
+    distance: np.ndarray     # float32 [K]   sorted by (distance, query_idx)
+
+
+class Knn2Arrays(NamedTuple):
+    idx1: np.ndarray
+    idx2: np.ndarray
+    d1: np.ndarray
+    d2: np.ndarray
+
+
+class DeviceDescriptors(NamedTuple):
+    """One descriptor store resident in HBM, already in the layout its kernel wants."""
+    kind: int
+    desc: torch.Tensor                 # uint8 [rows, D] | int8 [rows, Dpad] | float32 [rows, Dpad]
+    norm: Optional[torch.Tensor]       # int32 [rows] | float32 [rows] | None
+    rows: int
+    width: int                         # D as passed to the C-ABI
+
+
+def mode_of(cross_check: bool, ratio_threshold: Optional[float]) -> int:
+    """EnhancedBFMatcher.match's branch (feature_matchers.py:208 vs :225)."""
+    if ratio_threshold is not None and not cross_check:
+        return L.MODE_RATIO
+    return L.MODE_CROSS if cross_check else L.MODE_NN
+
+
+def _ptr(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+class Engine:
+    def __init__(self, device: Optional[torch.device | str | int] = None):
+        self.lib = L.load()
+        if not torch.cuda.is_available():
+            raise L.B200MatchError(L.ENODEVICE, "Engine", "no CUDA device: the matcher has no CPU fallback")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        with torch.cuda.device(self.device):
+            L.check(self.lib.b200m_device_info(None, None, None), "b200m_device_info")
+        self._ws: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------------ memory helpers
+    def _workspace(self, nbytes: int) -> torch.Tensor:
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def to_device(self, a: np.ndarray) -> torch.Tensor:
+        return torch.from_numpy(np.ascontiguousarray(a)).to(self.device, non_blocking=True)
+
+    # ------------------------------------------------------------------ descriptor upload / prep
+    def prepare(self, desc, norm_type: int, force_kind: Optional[int] = None) -> DeviceDescriptors:
+        """Upload (if needed) and re-encode one descriptor matrix [rows, D]."""
+        t = desc if isinstance(desc, torch.Tensor) else self.to_device(desc)
+        if t.dim() != 2:
+            raise ValueError("descriptors must be [rows, D]")
+        t = t.contiguous()
+        rows, D = int(t.shape[0]), int(t.shape[1])
+        if norm_type == NORM_HAMMING:
+            if t.dtype != torch.uint8:
+                raise ValueError("NORM_HAMMING needs uint8 descriptors")      # cv2.error in the reference
+            return DeviceDescriptors(L.KIND_HAMMING, t, None, rows, D)
+        if norm_type != NORM_L2:
+            raise ValueError(f"unsupported norm_type {norm_type}")
+        if t.dtype == torch.uint8:
+            t = t.to(torch.float32)
+        if t.dtype != torch.float32:
+            raise ValueError("NORM_L2 needs float32 (or uint8) descriptors")
+        with torch.cuda.device(self.device):
+            if force_kind != L.KIND_L2_F32:
+                Dpad = (D + 127) // 128 * 128
+                d8 = torch.empty((rows, Dpad), dtype=torch.int8, device=self.device)
+                nrm = torch.empty((rows,), dtype=torch.int32, device=self.device)
+                flag = torch.zeros((1,), dtype=torch.int32, device=self.device)
+                L.check(self.lib.b200m_prep_l2_i8(t.data_ptr(), rows, D, d8.data_ptr(), Dpad, nrm.data_ptr(),
+                                                  flag.data_ptr(), self._stream()), "b200m_prep_l2_i8")
+                if force_kind == L.KIND_L2_I8 or int(flag.item()) == 0:
+                    return DeviceDescriptors(L.KIND_L2_I8, d8, nrm, rows, Dpad)
+            Dpad = (D + 31) // 32 * 32
+            if Dpad != D:
+                t = torch.nn.functional.pad(t, (0, Dpad - D))
+            nrm = torch.empty((rows,), dtype=torch.float32, device=self.device)
+            L.check(self.lib.b200m_prep_l2_f32(t.data_ptr(), rows, Dpad, nrm.data_ptr(), self._stream()),
+                    "b200m_prep_l2_f32")
+            return DeviceDescriptors(L.KIND_L2_F32, t, nrm, rows, Dpad)
+
+    # ------------------------------------------------------------------ pair tables
+    @staticmethod
+    def make_pairs(spec: Sequence[Sequence[int]]):
+        """spec rows: (q_off, n, t_off, m).  Returns (ctypes array, out offsets, total_n, total_m, max_n, max_m)."""
+        arr = (L.Pair * max(len(spec), 1))()
+        off = 0
+        tn = tm = mn = mm = 0
+        offs = np.zeros(len(spec) + 1, np.int64)
+        for p, (q_off, n, t_off, m) in enumerate(spec):
+            arr[p] = L.Pair(int(q_off), int(n), int(t_off), int(m), off)
+            off += int(n)
+            offs[p + 1] = off
+            tn += int(n); tm += int(m); mn = max(mn, int(n)); mm = max(mm, int(m))
+        return arr, offs, tn, tm, mn, mm
+
+    # ------------------------------------------------------------------ the hot path (device in, device out)
+    def match_device(self, q: DeviceDescriptors, t: DeviceDescriptors, spec, mode: int, ratio: float = 0.0):
+        """Enqueue matching for the pairs in `spec`; returns device tensors
+        (out_q, out_t, out_d, out_count, out_offsets[np])."""
+        if q.kind != t.kind or q.width != t.width:
+            raise ValueError("descriptor kind/width mismatch")
+        pairs, offs, tn, tm, mn, mm = self.make_pairs(spec)
+        P = len(spec)
+        nbytes = ctypes.c_size_t(0)
+        L.check(self.lib.b200m_workspace_bytes(q.kind, mode, P, tn, tm, mn, mm, q.width, ctypes.byref(nbytes)),
+                "b200m_workspace_bytes")
+        ws = self._workspace(nbytes.value)
+        cap = max(tn, 1)
+        out_q = torch.empty(cap, dtype=torch.int32, device=self.device)
+        out_t = torch.empty(cap, dtype=torch.int32, device=self.device)
+        out_d = torch.empty(cap, dtype=torch.float32, device=self.device)
+        out_c = torch.zeros(max(P, 1), dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self.lib.b200m_match_pairs(q.kind, q.desc.data_ptr(), _ptr(q.norm), q.rows, t.desc.data_ptr(),
+                                            _ptr(t.norm), t.rows, q.width, pairs, P, mode, float(ratio),
+                                            out_q.data_ptr(), out_t.data_ptr(), out_d.data_ptr(), out_c.data_ptr(),
+                                            ws.data_ptr(), ws.numel(), self._stream())
+        L.check(rc, "b200m_match_pairs")
+        return out_q, out_t, out_d, out_c, offs
+
+    def knn2_device(self, q: DeviceDescriptors, t: DeviceDescriptors, spec):
+        if q.kind != t.kind or q.width != t.width:
+            raise ValueError("descriptor kind/width mismatch")
+        pairs, offs, tn, tm, mn, mm = self.make_pairs(spec)
+        P = len(spec)
+        nbytes = ctypes.c_size_t(0)
+        L.check(self.lib.b200m_workspace_bytes(q.kind, L.MODE_NN, P, tn, tm, mn, mm, q.width, ctypes.byref(nbytes)),
+                "b200m_workspace_bytes")
+        ws = self._workspace(nbytes.value)
+        cap = max(tn, 1)
+        i1 = torch.empty(cap, dtype=torch.int32, device=self.device)
+        i2 = torch.empty(cap, dtype=torch.int32, device=self.device)
+        d1 = torch.empty(cap, dtype=torch.float32, device=self.device)
+        d2 = torch.empty(cap, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self.lib.b200m_knn2_pairs(q.kind, q.desc.data_ptr(), _ptr(q.norm), q.rows, t.desc.data_ptr(),
+                                           _ptr(t.norm), t.rows, q.width, pairs, P, i1.data_ptr(), i2.data_ptr(),
+                                           d1.data_ptr(), d2.data_ptr(), ws.data_ptr(), ws.numel(), self._stream())
+        L.check(rc, "b200m_knn2_pairs")
+        return i1, i2, d1, d2, offs
+
+    # ------------------------------------------------------------------ host-array convenience (one pair)
+    def _prepare_pair(self, desc1, desc2, norm_type):
+        a = self.prepare(desc1, norm_type)
+        b = self.prepare(desc2, norm_type)
+        if a.kind != b.kind:      # one side integer-valued, the other not: both go the fp32 way
+            a = self.prepare(desc1, norm_type, force_kind=L.KIND_L2_F32)
+            b = self.prepare(desc2, norm_type, force_kind=L.KIND_L2_F32)
+        return a, b
+
+    def match_arrays(self, desc1: np.ndarray, desc2: np.ndarray, norm_type: int = NORM_L2,
+                     cross_check: bool = False, ratio_threshold: Optional[float] = None) -> MatchArrays:
+        """One image pair, host arrays in, host arrays out (H2D + kernels + D2H)."""
+        if desc1.ndim != 2 or desc2.ndim != 2 or desc1.shape[1] != desc2.shape[1]:
+            raise ValueError("descriptor width mismatch")
+        if desc1.dtype != desc2.dtype:
+            raise ValueError("descriptor dtype mismatch")
+        a, b = self._prepare_pair(desc1, desc2, norm_type)
+        mode = mode_of(cross_check, ratio_threshold)
+        oq, ot, od, oc, _ = self.match_device(a, b, [(0, a.rows, 0, b.rows)], mode, ratio_threshold or 0.0)
+        k = int(oc[0].item())
+        return MatchArrays(oq[:k].cpu().numpy(), ot[:k].cpu().numpy(), od[:k].cpu().numpy())
+
+    def knn2_arrays(self, desc1: np.ndarray, desc2: np.ndarray, norm_type: int = NORM_L2) -> Knn2Arrays:
+        a, b = self._prepare_pair(desc1, desc2, norm_type)
+        i1, i2, d1, d2, _ = self.knn2_device(a, b, [(0, a.rows, 0, b.rows)])
+        n = a.rows
+        return Knn2Arrays(i1[:n].cpu().numpy(), i2[:n].cpu().numpy(), d1[:n].cpu().numpy(), d2[:n].cpu().numpy())
+
+
+_default_engine: Optional[Engine] = None
+
+
+def default_engine() -> Engine:
+    global _default_engine
+    if _default_engine is None:
+        _default_engine = Engine()
+    return _default_engine

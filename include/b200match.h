@@ -1,0 +1,134 @@
+/*
+ * b200match.h — C-ABI of the B200-native exhaustive descriptor matcher.
+ *
+ * Drop-in boundary for ONE hot path of Tarboucha/3DReconstruction: `EnhancedBFMatcher`
+ * (/root/reference/FeatureMatchingExtraction/feature_matchers.py:184-252), i.e. the arithmetic the
+ * reference delegates to cv2.BFMatcher at :197 (construct), :210 (knnMatch k=2) and :227 (match),
+ * plus the ratio test (:212-224), the cross-check semantics of `crossCheck=True` (:225-238) and
+ * the final stable sort by distance (:241).
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, no C++/torch types.  `stream` is a cudaStream_t passed as void*.
+ *   - every data pointer is a DEVICE pointer owned by the caller unless the name ends in `_host`.
+ *   - no allocation inside, no exceptions: each entry point returns B200M_OK (0) or a negative
+ *     B200M_E* code; b200m_error_string() names it; b200m_last_cuda_error() returns the CUDA
+ *     error text of the last failing call on this thread.
+ *   - work is enqueued on `stream` and is asynchronous; outputs are valid once the stream syncs.
+ *   - there is NO CPU fallback: without an sm_100 device the compute entry points return
+ *     B200M_ENODEVICE.
+ */
+#ifndef B200MATCH_H
+#define B200MATCH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200M_VERSION 100
+
+#if defined(__GNUC__)
+#define B200M_API __attribute__((visibility("default")))
+#else
+#define B200M_API
+#endif
+
+/* error codes */
+#define B200M_OK          0
+#define B200M_EINVAL     -1   /* bad argument (null pointer, negative size, width 0, ...)      */
+#define B200M_EWORKSPACE -2   /* workspace too small: query b200m_workspace_bytes()             */
+#define B200M_ECUDA      -3   /* a CUDA runtime call / launch failed                            */
+#define B200M_ENODEVICE  -4   /* no sm_100 device: this library has no CPU path                 */
+#define B200M_EUNSUPPORTED -5 /* shape outside what the kernels implement (stated per call)     */
+
+/* The three behaviours of EnhancedBFMatcher.match. */
+#define B200M_MODE_RATIO  0   /* feature_matchers.py:208-224: knn k=2 + `d1 < ratio*d2` in fp64 */
+#define B200M_MODE_CROSS  1   /* :225-238 with crossCheck=True: strict mutual first-argmin      */
+#define B200M_MODE_NN     2   /* :225-238 with crossCheck=False, ratio None: plain 1-NN         */
+
+/* Descriptor kinds (what cv2.BFMatcher's normType + dtype select, feature_matchers.py:197). */
+#define B200M_KIND_HAMMING 0  /* uint8 rows, NORM_HAMMING: __popc INT-pipe kernel               */
+#define B200M_KIND_L2_I8   1  /* int8 rows (= integer-valued 0..255 float descriptors shifted by
+                                 -128) + int32 row norms: tcgen05 kind::i8, exact              */
+#define B200M_KIND_L2_F32  2  /* float32 rows: tcgen05 kind::tf32 candidates + fp32 re-rank     */
+
+/* One image pair of a batch: rows [q_off, q_off+n) of the query store against rows
+ * [t_off, t_off+m) of the train store; its matches are written at out_off.. (capacity n). */
+typedef struct b200m_pair {
+    int32_t q_off, n;
+    int32_t t_off, m;
+    int64_t out_off;
+} b200m_pair;
+
+B200M_API int         b200m_version(void);
+B200M_API const char* b200m_error_string(int code);
+B200M_API const char* b200m_last_cuda_error(void);
+/* sm count / compute capability of the current device; B200M_ENODEVICE when none. */
+B200M_API int         b200m_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ------------------------------------------------------------------------------------------
+ * Descriptor preparation (replaces nothing in the reference: cv2 consumes float32 directly;
+ * this is the exact re-encoding SURVEY §7.1 step 4 calls the pre-pass).
+ *   src   float32 [rows, D] row-major
+ *   dst   int8    [rows, Dpad]  (Dpad = D rounded up to 128, zero padded), value = src - 128
+ *   norms int32   [rows]        sum over D of (src-128)^2
+ *   not_integer  int32[1]       set to 1 if any element is not an integer in 0..255
+ *                               (caller must then use the F32 kind); caller zeroes it first.
+ */
+B200M_API int b200m_prep_l2_i8(const float* src, int64_t rows, int D, int8_t* dst, int Dpad,
+                     int32_t* norms, int32_t* not_integer, void* stream);
+
+/* Row squared norms for the F32 kind: norms[r] = sum_k src[r,k]^2 (fp32). */
+B200M_API int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Workspace query for b200m_match_pairs / b200m_knn2_pairs.
+ *   total_n = sum of pair.n, total_m = sum of pair.m, max_n/max_m = largest single pair.
+ */
+B200M_API int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t total_n, int64_t total_m,
+                          int max_n, int max_m, int D, size_t* bytes);
+
+/* ------------------------------------------------------------------------------------------
+ * The hot path, batched over image pairs (a single pair is num_pairs == 1).
+ * Replaces, per pair, cv2.BFMatcher.knnMatch/match + ratio/cross-check + sort
+ * (feature_matchers.py:208-241).
+ *
+ *   kind           B200M_KIND_*
+ *   q_desc/t_desc  descriptor stores (may be the same pointer for all-pairs over one store):
+ *                    HAMMING: uint8 [rows, D]      (D = bytes per descriptor, any D >= 1)
+ *                    L2_I8  : int8  [rows, D]      (D multiple of 128, from b200m_prep_l2_i8)
+ *                    L2_F32 : float [rows, D]      (D multiple of 32 floats)
+ *   q_norm/t_norm  L2_I8: int32 [rows]; L2_F32: float [rows]; HAMMING: NULL
+ *   q_rows/t_rows  number of rows in each store (bounds for TMA maps)
+ *   pairs_host     HOST array of num_pairs descriptors (copied to the device workspace)
+ *   mode, ratio    B200M_MODE_*; ratio used by MODE_RATIO only (fp64, as Python does at :216)
+ *   out_q/out_t/out_d  int32/int32/float32 arrays, capacity = max(pair.out_off + pair.n):
+ *                  pair p's matches occupy [out_off, out_off + out_count[p]) sorted by
+ *                  (distance asc, queryIdx asc) — the reference's stable sort (:241)
+ *   out_count      int32 [num_pairs]
+ */
+B200M_API int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                      const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                      const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                      int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* Raw k=2 neighbours per query row (what cv2.BFMatcher.knnMatch(k=2) returns at :210), for
+ * parity checks of the knn stage itself.  Arrays of length sum(pair.n), pair p at out_off:
+ * idx2 = -1 / d2 = -1 when the pair has a single train row (cv2 returns a length-1 list). */
+B200M_API int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                     const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                     const b200m_pair* pairs_host, int num_pairs,
+                     int32_t* idx1, int32_t* idx2, float* d1, float* d2,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* Counters for bench.py's `gpu_launches`: kernels launched by this library since the last reset. */
+B200M_API int64_t b200m_launch_count(void);
+B200M_API void    b200m_reset_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MATCH_H */

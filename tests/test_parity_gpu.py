@@ -1,0 +1,215 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the oracle on the same seeded
+inputs, against the committed golden vectors produced by the reference's own EnhancedBFMatcher,
+and — at BASELINE.json's full sizes — through size-independent properties.
+
+Bar: bit-exact (indices, float32 distance bits, order) for Hamming and integer-valued L2;
+relative distance error <= 1e-5 for non-integer float descriptors, near-tie index differences
+counted and bounded."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import is_integer_valued, pkg
+from oracle import bf_oracle as O
+
+pytestmark = pytest.mark.gpu
+b = pkg()
+synth = b.synth
+RTOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def eng():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return b.Engine()
+
+
+def assert_exact(got, want, what=""):
+    assert len(got.query_idx) == len(want.query_idx), f"{what}: count {len(got.query_idx)} != {len(want.query_idx)}"
+    assert np.array_equal(got.query_idx, want.query_idx), what
+    assert np.array_equal(got.train_idx, want.train_idx), what
+    assert np.array_equal(got.distance.view(np.uint32), want.distance.view(np.uint32)), what
+
+
+def assert_close_float(got, want, what="", max_flip_frac=0.01):
+    """Non-integer float descriptors: compare as sets keyed by query; distances within RTOL; index
+    differences only allowed where the oracle's own distance gap is inside the tolerance."""
+    g = {int(q): (int(t), float(d)) for q, t, d in zip(got.query_idx, got.train_idx, got.distance)}
+    w = {int(q): (int(t), float(d)) for q, t, d in zip(want.query_idx, want.train_idx, want.distance)}
+    flips = len(set(g) ^ set(w))
+    for q in set(g) & set(w):
+        if g[q][0] != w[q][0]:
+            flips += 1
+        assert abs(g[q][1] - w[q][1]) <= RTOL * max(abs(w[q][1]), 1e-6) + 1e-7, f"{what}: q={q} {g[q]} vs {w[q]}"
+    assert flips <= max(1, int(max_flip_frac * max(len(w), 1))), f"{what}: {flips} near-tie flips of {len(w)}"
+    return flips
+
+
+MODES = [(False, None), (False, 0.7), (False, 0.75), (True, None)]
+
+
+# ------------------------------------------------------------------ golden vectors from the reference
+def test_golden_vectors(eng, golden):
+    for name, g in golden.items():
+        if name.startswith("err_"):
+            with pytest.raises(Exception):
+                eng.match_arrays(g["desc1"], g["desc2"], g["norm"], g["cross_check"], g["ratio"])
+            continue
+        got = eng.match_arrays(g["desc1"], g["desc2"], g["norm"], g["cross_check"], g["ratio"])
+        want = O.Matches(g["q"], g["t"], g["d"])
+        if is_integer_valued(g["desc1"]) and is_integer_valued(g["desc2"]):
+            assert_exact(got, want, name)
+        else:
+            assert_close_float(got, want, name)
+
+
+# ------------------------------------------------------------------ Hamming
+@pytest.mark.parametrize("nbytes", [1, 5, 32, 61, 64, 128, 200])
+@pytest.mark.parametrize("mode", MODES)
+def test_hamming_vs_oracle(eng, nbytes, mode):
+    for seed, (n, m) in enumerate([(1, 1), (1, 7), (9, 1), (2, 2), (130, 127), (257, 513), (1000, 777)]):
+        a, c = synth.binary_pair(seed=100 + seed, n=max(n, m), nbytes=nbytes)
+        a, c = a[:n], c[:m]
+        assert_exact(eng.match_arrays(a, c, b.NORM_HAMMING, *mode), O.reference_match(a, c, O.NORM_HAMMING, *mode),
+                     f"hamming D={nbytes} n={n} m={m} mode={mode}")
+
+
+def test_hamming_heavy_ties(eng):
+    rng = np.random.default_rng(7)
+    for nbytes, hi in [(1, 2), (1, 4), (2, 3), (32, 2)]:
+        a = rng.integers(0, hi, size=(300, nbytes), dtype=np.uint8)
+        c = np.concatenate([a[:100], a[:100], np.zeros((10, nbytes), np.uint8),
+                            rng.integers(0, hi, size=(211, nbytes), dtype=np.uint8)])
+        for mode in MODES:
+            assert_exact(eng.match_arrays(a, c, b.NORM_HAMMING, *mode),
+                         O.reference_match(a, c, O.NORM_HAMMING, *mode), f"ties D={nbytes} hi={hi} {mode}")
+
+
+def test_hamming_knn2_raw(eng):
+    a, c = synth.binary_pair(seed=5, n=700, m=650, nbytes=32)
+    got = eng.knn2_arrays(a, c, b.NORM_HAMMING)
+    want = O.knn2_c(a, c, O.NORM_HAMMING)
+    for x, y in zip(got, want):
+        assert np.array_equal(x, y)
+    got = eng.knn2_arrays(a, c[:1], b.NORM_HAMMING)          # M == 1: second neighbour absent
+    assert np.all(got.idx2 == -1) and np.all(got.d2 == -1)
+
+
+def test_hamming_config2_full_size(eng):
+    """BASELINE config 2: ORB 256-bit, 10k x 10k, cross-check.  Oracle finishes in seconds here."""
+    a, c = synth.binary_pair(seed=1, n=10000, nbytes=32)
+    got = eng.match_arrays(a, c, b.NORM_HAMMING, True, None)
+    assert_exact(got, O.reference_match(a, c, O.NORM_HAMMING, True, None), "config2")
+    assert len(got.query_idx) > 5000
+    # properties: sorted by (distance, queryIdx); mutual (swap roles -> same pair set)
+    key = got.distance.astype(np.float64) * 1e6 + got.query_idx
+    assert np.all(np.diff(key) > 0)
+    rev = eng.match_arrays(c, a, b.NORM_HAMMING, True, None)
+    assert set(zip(got.query_idx.tolist(), got.train_idx.tolist())) == set(zip(rev.train_idx.tolist(), rev.query_idx.tolist()))
+
+
+def test_hamming_batched_pairs_equal_single(eng):
+    """Several pairs with ragged sizes in one C-ABI call == the same pairs one by one."""
+    sets = [synth.binary_pair(seed=40 + i, n=n, nbytes=32)[0] for i, n in enumerate([300, 129, 1, 640, 77])]
+    store = np.concatenate(sets)
+    offs = np.cumsum([0] + [len(s) for s in sets])
+    dd = eng.prepare(store, b.NORM_HAMMING)
+    spec, pairs = [], [(0, 1), (0, 3), (2, 4), (3, 1), (4, 2), (1, 1)]
+    for i, j in pairs:
+        spec.append((offs[i], len(sets[i]), offs[j], len(sets[j])))
+    for mode in MODES:
+        oq, ot, od, oc, ooff = eng.match_device(dd, dd, spec, b.mode_of(*mode), mode[1] or 0.0)
+        oq, ot, od, oc = oq.cpu().numpy(), ot.cpu().numpy(), od.cpu().numpy(), oc.cpu().numpy()
+        for p, (i, j) in enumerate(pairs):
+            want = O.reference_match(sets[i], sets[j], O.NORM_HAMMING, *mode)
+            s = slice(int(ooff[p]), int(ooff[p]) + int(oc[p]))
+            assert_exact(O.Matches(oq[s], ot[s], od[s]), want, f"batched pair {p} mode {mode}")
+
+
+# ------------------------------------------------------------------ integer-valued L2 (SIFT) — tcgen05 kind::i8
+@pytest.mark.parametrize("mode", MODES)
+def test_l2_i8_vs_oracle(eng, mode):
+    for seed, (n, m, d) in enumerate([(1, 1, 128), (1, 9, 128), (9, 1, 128), (2, 2, 128), (130, 127, 128),
+                                      (300, 513, 128), (1000, 777, 128), (200, 300, 64), (150, 150, 8),
+                                      (260, 140, 200), (500, 400, 256)]):
+        a, c = synth.sift_pair(seed=200 + seed, n=max(n, m), d=d)
+        a, c = a[:n], np.ascontiguousarray(c[:m])
+        assert_exact(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode),
+                     f"l2_i8 n={n} m={m} d={d} mode={mode}")
+
+
+def test_l2_i8_extremes_and_ties(eng):
+    rng = np.random.default_rng(9)
+    a = rng.choice([0.0, 255.0], size=(200, 128)).astype(np.float32)     # largest possible distances
+    c = rng.choice([0.0, 255.0], size=(180, 128)).astype(np.float32)
+    c[:50] = a[:50]
+    c[50:60] = 0
+    for mode in MODES:
+        assert_exact(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"extreme {mode}")
+    a = rng.integers(0, 3, size=(300, 128)).astype(np.float32)           # heavy ties
+    c = np.concatenate([a[:100], a[:100], rng.integers(0, 3, size=(150, 128)).astype(np.float32)])
+    for mode in MODES:
+        assert_exact(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"ties {mode}")
+
+
+def test_l2_i8_knn2_raw(eng):
+    a, c = synth.sift_pair(seed=6, n=900, m=800)
+    got = eng.knn2_arrays(a, c, b.NORM_L2)
+    want = O.knn2_c(a, c, O.NORM_L2)
+    assert np.array_equal(got.idx1, want.idx1) and np.array_equal(got.idx2, want.idx2)
+    assert np.array_equal(got.d1.view(np.uint32), want.d1.view(np.uint32))
+    assert np.array_equal(got.d2.view(np.uint32), want.d2.view(np.uint32))
+
+
+def test_l2_i8_config1_full_size(eng):
+    """BASELINE config 1: SIFT 8192 x 8192 x 128, ratio 0.75."""
+    a, c = synth.sift_pair(seed=0, n=8192)
+    got = eng.match_arrays(a, c, b.NORM_L2, False, 0.75)
+    assert_exact(got, O.reference_match(a, c, O.NORM_L2, False, 0.75), "config1")
+    assert 3500 < len(got.query_idx) < 4700
+    assert np.all(np.diff(got.distance) >= 0)
+
+
+def test_l2_uint8_descriptors(eng):
+    """cv2 accepts CV_8U with NORM_L2 (integer sum, float sqrt)."""
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, size=(300, 128), dtype=np.uint8)
+    c = rng.integers(0, 256, size=(200, 128), dtype=np.uint8)
+    got = eng.match_arrays(a, c, b.NORM_L2, False, None)
+    want = O.reference_match(a.astype(np.float32), c.astype(np.float32), O.NORM_L2, False, None)
+    assert_exact(got, want, "u8 L2")
+
+
+# ------------------------------------------------------------------ non-integer float L2 (SuperPoint) — TF32 + fp32 re-rank
+@pytest.mark.parametrize("mode", [(True, None), (False, 0.8), (False, None)])
+def test_l2_f32_vs_oracle(eng, mode):
+    s = synth.superpoint_set(seed=21, images=2, n=1500, d=256, pool=2500)
+    flips = assert_close_float(eng.match_arrays(s[0], s[1], b.NORM_L2, *mode),
+                               O.reference_match(s[0], s[1], O.NORM_L2, *mode), f"f32 {mode}")
+    print(f"f32 mode={mode}: near-tie flips={flips}")
+    rng = np.random.default_rng(4)
+    a = rng.normal(size=(333, 100)).astype(np.float32) * 3.0          # not unit norm, D not a multiple of 32
+    c = (a[rng.permutation(333)[:290]] + rng.normal(size=(290, 100)).astype(np.float32) * 0.05).astype(np.float32)
+    assert_close_float(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"f32 generic {mode}")
+
+
+# ------------------------------------------------------------------ plugin level
+def test_plugin_match_returns_matchdata(eng):
+    a, c = synth.binary_pair(seed=1, n=500, nbytes=32)
+    F = b.contracts.FeatureData
+    f1 = F(keypoints=list(range(len(a))), descriptors=a, method="ORB")
+    f2 = F(keypoints=list(range(len(c))), descriptors=c, method="ORB")
+    m = b.B200BFMatcher(norm_type=b.NORM_HAMMING, cross_check=False, ratio_threshold=0.7, engine=eng)
+    md = m.match(f1, f2)
+    want = O.reference_match(a, c, O.NORM_HAMMING, False, 0.7)
+    assert md.method == "BF" and md.score_type == b.contracts.ScoreType.DISTANCE and isinstance(md.matches, list)
+    assert [x.queryIdx for x in md.matches] == want.query_idx.tolist()
+    assert [x.trainIdx for x in md.matches] == want.train_idx.tolist()
+    assert [x.score for x in md.matches] == [float(v) for v in want.distance]
+    assert md.matching_time > 0
+    # error convention: width mismatch -> printed, empty MatchData (feature_matchers.py:250-252)
+    bad = F(keypoints=list(range(4)), descriptors=np.zeros((4, 16), np.uint8), method="ORB")
+    assert m.match(f1, bad).matches == []
+    # downstream helpers keep working on our MatchData
+    assert len(md.filter_by_score(40.0).filtered_matches) <= len(md.matches)

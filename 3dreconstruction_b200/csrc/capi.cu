@@ -185,6 +185,11 @@ int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t 
         B200M_CUDA_CHECK(cudaMemsetAsync(out_count, 0, sizeof(int32_t) * (size_t)num_pairs, st), "count memset");
         return B200M_OK;
     }
+    if (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) {
+        rc = launch_refine_i8(false, ratio, pl, num_pairs, max_n, (const int8_t*)q_desc, (const int32_t*)q_norm,
+                              (const int8_t*)t_desc, (const int32_t*)t_norm, D, st);
+        if (rc != B200M_OK) return rc;
+    }
     rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, st);
     if (rc != B200M_OK) return rc;
     return launch_sort_emit(kind, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, st);
@@ -202,6 +207,11 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
                            B200M_MODE_NN, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
     if (num_pairs == 0 || pl.total_n == 0) return B200M_OK;
+    if (kind == B200M_KIND_L2_I8) {
+        rc = launch_refine_i8(true, 0.0, pl, num_pairs, max_n, (const int8_t*)q_desc, (const int32_t*)q_norm,
+                              (const int8_t*)t_desc, (const int32_t*)t_norm, D, st);
+        if (rc != B200M_OK) return rc;
+    }
     return launch_knn2_emit(kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, st);
 }
 

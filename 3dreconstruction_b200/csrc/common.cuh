@@ -67,6 +67,8 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
                        const float* t_desc, const float* t_norm, int64_t t_rows, int D,
                        const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
                        Top2* out, long long total_rows, cudaStream_t st);
+int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_pairs, int max_n, const int8_t* q_desc,
+                     const int32_t* q_norm, const int8_t* t_desc, const int32_t* t_norm, int D, cudaStream_t st);
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
                     cudaStream_t st);
 int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,

@@ -1,6 +1,340 @@
-// l2_i8.cu — placeholder until the tcgen05 kind::i8 kernel lands.
+// l2_i8.cu — exact integer L2 knn (k=2) for SIFT-style descriptors on the 5th-gen tensor cores.
+// Replaces cv2.BFMatcher(NORM_L2).knnMatch(k=2)/match as called at
+// /root/reference/FeatureMatchingExtraction/feature_matchers.py:210,227 for integer-valued 0..255
+// float32 descriptors (traditional_detectors.py:42), bit-exactly:
+//   d^2(i,j) = ||a'_i||^2 + ||b'_j||^2 - 2 a'_i . b'_j   with a' = a-128, b' = b-128 (int8),
+// the dot product from tcgen05.mma kind::i8 (int32 accumulators in TMEM), all terms exact integers.
+//
+// Persistent, warp-specialised CTA (one per SM), 320 threads:
+//   warps 0-7  epilogue : tcgen05.ld 32 columns at a time, key = (||b'||^2*32 + c) - 64*acc (one
+//                         IMAD), 3-input-min tree per 32-column chunk, running top-2 of chunk minima
+//   warp  8    producer : TMA (cp.async.bulk.tensor, SWIZZLE_128B) query tile (kept for the whole
+//                         work item, double buffered across items) and a ring of train tiles
+//   warp  9    MMA      : one thread issues tcgen05.mma M=128 N=256 K=32 x 4 per 128-byte K block
+//                         into a double-buffered TMEM accumulator (2 x 256 columns = all 512)
+// No N x M matrix reaches HBM: per query row only {best, runner-up candidate} leave the SM.
+//
+// Exactness of the runner-up: the running top-2 is over CHUNK MINIMA (32 consecutive train
+// columns), so k1 is the exact best (ties -> lowest column: the column sits in the low key bits and
+// chunks are visited in ascending order with a strict compare) and k2 is the best among all OTHER
+// chunks.  The true runner-up is min(k2, runner-up inside the winner's chunk); tail.cu recomputes
+// those <= 31 distances exactly where the result depends on it (refine_second_i8).
 #include "common.cuh"
-int launch_l2_i8_top2(const int8_t*, const int32_t*, int64_t, const int8_t*, const int32_t*, int64_t, int,
-                      const DevPair*, int, int, int, int, bool, Top2*, long long, cudaStream_t) {
-    return B200M_EUNSUPPORTED;
+#include "sm100.cuh"
+
+namespace {
+
+constexpr int TM = 128;            // query rows per tile  (UMMA M)
+constexpr int TN = 256;            // train columns per tile (UMMA N)
+constexpr int KB_BYTES = 128;      // one swizzle-128B K block
+constexpr int A_KB_BYTES = TM * KB_BYTES;   // 16 KiB
+constexpr int B_KB_BYTES = TN * KB_BYTES;   // 32 KiB
+constexpr int NABUF = 2;
+constexpr int EPI_THREADS = 256;
+constexpr int THREADS = EPI_THREADS + 64;
+constexpr int MASK_CB = 1 << 30;   // column-constant of a masked (out of range) column
+constexpr int INVALID_VAL = 1 << 24;
+
+struct Item {
+    int q_off, n, t_off, m, r0, c_begin, c_end, split;
+    long long row_base;
+    bool valid;
+};
+
+__device__ __forceinline__ Item decode_item(long long item, const DevPair* __restrict__ pairs, int tiles_max, int S,
+                                            int backward) {
+    Item it;
+    int tile = (int)(item % tiles_max); item /= tiles_max;
+    it.split = (int)(item % S);
+    int p = (int)(item / S);
+    DevPair pr = pairs[p];
+    if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
+    else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
+    it.r0 = tile * TM;
+    int cols_per = ((it.m + S - 1) / S + TN - 1) / TN * TN;
+    it.c_begin = it.split * cols_per;
+    it.c_end = min(it.m, it.c_begin + cols_per);
+    it.valid = it.r0 < it.n;
+    return it;
+}
+
+__device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b), c); }
+
+struct SmemLayout {
+    uint8_t* a;        // [NABUF][nkb][16 KiB]
+    uint8_t* b;        // [NB][32 KiB]
+    int* cb;           // [2][256]
+    int* exch;         // [128][4]
+    uint64_t* a_full;  // [NABUF]
+    uint64_t* a_empty; // [NABUF]
+    uint64_t* b_full;  // [NB]
+    uint64_t* b_empty; // [NB]
+    uint64_t* acc_full;   // [2]
+    uint64_t* acc_empty;  // [2]
+    uint32_t* tmem_ptr;
+};
+
+__device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb, int NB) {
+    SmemLayout s;
+    s.a = base;
+    s.b = s.a + NABUF * nkb * A_KB_BYTES;
+    uint8_t* p = s.b + NB * B_KB_BYTES;
+    s.cb = (int*)p; p += 2 * TN * sizeof(int);
+    s.exch = (int*)p; p += TM * 4 * sizeof(int);
+    s.a_full = (uint64_t*)p; p += NABUF * 8;
+    s.a_empty = (uint64_t*)p; p += NABUF * 8;
+    s.b_full = (uint64_t*)p; p += NB * 8;
+    s.b_empty = (uint64_t*)p; p += NB * 8;
+    s.acc_full = (uint64_t*)p; p += 2 * 8;
+    s.acc_empty = (uint64_t*)p; p += 2 * 8;
+    s.tmem_ptr = (uint32_t*)p;
+    return s;
+}
+
+__host__ __device__ constexpr size_t smem_bytes(int nkb, int NB) {
+    return 1024 /*alignment slack*/ + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)NB * B_KB_BYTES +
+           2 * TN * sizeof(int) + TM * 4 * sizeof(int) + (2 * NABUF + 2 * 8 /*NB<=8*/ + 4) * 8 + 16;
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
+                  const int32_t* __restrict__ q_norm, const int32_t* __restrict__ t_norm,
+                  const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
+                  int nkb, int NB, Top2* __restrict__ out, long long total_rows) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1 KiB alignment
+    const SmemLayout sm = carve(smem, nkb, NB);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 8 && lane == 0) {
+        sm100::tma_prefetch_desc(&tmap_q);
+        sm100::tma_prefetch_desc(&tmap_t);
+        for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
+        for (int i = 0; i < NB; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_THREADS / 32); }
+        sm100::fence_barrier_init();
+    }
+    if (warp == 9) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    sm100::tc_fence_before();
+    __syncthreads();
+    sm100::tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr;
+
+    if (warp == 8) {
+        // ===================== TMA producer (one thread) =====================
+        if (lane == 0) {
+            uint32_t a_cnt = 0, b_cnt = 0;
+            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+                Item it = decode_item(item, pairs, tiles_max, S, backward);
+                if (!it.valid) continue;
+                const uint32_t ab = a_cnt & 1;
+                sm100::mbar_wait(&sm.a_empty[ab], ((a_cnt >> 1) & 1) ^ 1);
+                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
+                for (int kb = 0; kb < nkb; ++kb)
+                    sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                       kb * KB_BYTES, it.q_off + it.r0);
+                ++a_cnt;
+                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        const uint32_t s = b_cnt % NB;
+                        sm100::mbar_wait(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[s], (uint32_t)B_KB_BYTES);
+                        sm100::tma_load_2d(sm.b + (size_t)s * B_KB_BYTES, &tmap_t, &sm.b_full[s], kb * KB_BYTES,
+                                           it.t_off + c0);
+                        ++b_cnt;
+                    }
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer (one thread) =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
+            uint32_t a_cnt = 0, b_cnt = 0, acc_cnt = 0;
+            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+                Item it = decode_item(item, pairs, tiles_max, S, backward);
+                if (!it.valid) continue;
+                const uint32_t ab = a_cnt & 1;
+                sm100::mbar_wait(&sm.a_full[ab], (a_cnt >> 1) & 1);
+                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                    const uint32_t as = acc_cnt & 1;
+                    sm100::mbar_wait(&sm.acc_empty[as], ((acc_cnt >> 1) & 1) ^ 1);
+                    sm100::tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + as * TN;
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        const uint32_t s = b_cnt % NB;
+                        sm100::mbar_wait(&sm.b_full[s], (b_cnt / NB) & 1);
+                        sm100::tc_fence_after();
+                        const uint64_t adesc = sm100::make_smem_desc_sw128(
+                            sm100::smem_u32(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES));
+                        const uint64_t bdesc = sm100::make_smem_desc_sw128(sm100::smem_u32(sm.b + (size_t)s * B_KB_BYTES));
+#pragma unroll
+                        for (int k = 0; k < KB_BYTES / 32; ++k)      // UMMA K = 32 bytes of int8; +2 = 32 B >> 4
+                            sm100::mma_i8(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        sm100::mma_commit(&sm.b_empty[s]);           // smem stage free once these MMAs retire
+                        ++b_cnt;
+                    }
+                    sm100::mma_commit(&sm.acc_full[as]);
+                    ++acc_cnt;
+                }
+                sm100::mma_commit(&sm.a_empty[ab]);
+                ++a_cnt;
+            }
+        }
+    } else {
+        // ===================== epilogue: 8 warps, lane quarter = warp % 4, column half = warp / 4 =====================
+        const int e = threadIdx.x;                 // 0..255: owns column e of every tile's norm vector
+        const int quarter = warp & 3, half = warp >> 2;
+        const int row_in_tile = quarter * 32 + lane;
+        uint32_t acc_cnt = 0;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            int v1 = 0x7fffffff, v2 = 0x7fffffff, i1 = -1, i2 = -1;
+            auto load_cb = [&](int c0) -> int {
+                int col = c0 + e;
+                return col < it.c_end ? __ldg(t_norm + it.t_off + col) * 32 + (e & 31) : MASK_CB;
+            };
+            int cb_next = it.c_begin < it.c_end ? load_cb(it.c_begin) : MASK_CB;
+            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                const uint32_t as = acc_cnt & 1;
+                sm.cb[as * TN + e] = cb_next;
+                if (c0 + TN < it.c_end) cb_next = load_cb(c0 + TN);
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
+                sm100::tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * TN + half * 128;
+                const int4* cbv = reinterpret_cast<const int4*>(sm.cb + as * TN + half * 128);
+#pragma unroll 1
+                for (int ch = 0; ch < 4; ++ch) {
+                    uint32_t acc[32];
+                    sm100::tmem_ld32(taddr + ch * 32, acc);
+                    sm100::tmem_ld_wait();
+                    int key[32];
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) {
+                        int4 c4 = cbv[ch * 8 + g];                       // warp-uniform address: broadcast
+                        key[4 * g + 0] = c4.x - 64 * (int)acc[4 * g + 0];
+                        key[4 * g + 1] = c4.y - 64 * (int)acc[4 * g + 1];
+                        key[4 * g + 2] = c4.z - 64 * (int)acc[4 * g + 2];
+                        key[4 * g + 3] = c4.w - 64 * (int)acc[4 * g + 3];
+                    }
+                    int a[11];
+#pragma unroll
+                    for (int k = 0; k < 10; ++k) a[k] = min3(key[3 * k], key[3 * k + 1], key[3 * k + 2]);
+                    a[10] = min(key[30], key[31]);
+                    int cm = min(min3(min3(a[0], a[1], a[2]), min3(a[3], a[4], a[5]), min3(a[6], a[7], a[8])),
+                                 min(a[9], a[10]));
+                    // insert the chunk minimum; later chunks have larger columns, so strict '<' keeps the lowest
+                    int val = cm >> 5;
+                    int col = c0 + half * 128 + ch * 32 + (cm & 31);
+                    bool lt1 = val < v1, lt2 = val < v2;
+                    v2 = lt1 ? v1 : (lt2 ? val : v2);
+                    i2 = lt1 ? i1 : (lt2 ? col : i2);
+                    v1 = lt1 ? val : v1;
+                    i1 = lt1 ? col : i1;
+                }
+                sm100::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
+                ++acc_cnt;
+            }
+            // merge the two column halves of each row (warp w and w+4), then publish
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (half == 1) {
+                sm.exch[row_in_tile * 4 + 0] = v1; sm.exch[row_in_tile * 4 + 1] = i1;
+                sm.exch[row_in_tile * 4 + 2] = v2; sm.exch[row_in_tile * 4 + 3] = i2;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (half == 0) {
+                int row = it.r0 + row_in_tile;
+                if (row < it.n) {
+                    int nq = __ldg(q_norm + it.q_off + row);
+                    auto mk = [&](int v, int i) -> u64 {
+                        return (i < 0 || v >= INVALID_VAL) ? B200M_SENTINEL : (((u64)(u32)(v + nq)) << 32) | (u64)(u32)i;
+                    };
+                    u64 k1 = mk(v1, i1), k2 = mk(v2, i2);
+                    top2_insert(k1, k2, mk(sm.exch[row_in_tile * 4 + 0], sm.exch[row_in_tile * 4 + 1]));
+                    top2_insert(k1, k2, mk(sm.exch[row_in_tile * 4 + 2], sm.exch[row_in_tile * 4 + 3]));
+                    Top2 t; t.k1 = k1; t.k2 = k2;
+                    out[(long long)it.split * total_rows + it.row_base + row] = t;
+                }
+            }
+        }
+    }
+
+    sm100::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) sm100::tmem_dealloc<512>(tmem_base);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+static b200m_encode_tiled_fn get_encode_fn() {
+    static b200m_encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (b200m_encode_tiled_fn)p;
+    }
+    return fn;
+}
+
+int b200m_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_bytes, uint32_t box_rows,
+                       CUtensorMapDataType dtype, uint32_t elem_bytes) {
+    b200m_encode_tiled_fn enc = get_encode_fn();
+    if (!enc) return b200m_set_cuda_error(cudaErrorNotSupported, "cuTensorMapEncodeTiled entry point");
+    if (((uintptr_t)base & 15) || (row_bytes & 15) || rows == 0) return B200M_EINVAL;
+    cuuint64_t gdim[2] = {row_bytes / elem_bytes, rows};
+    cuuint64_t gstride[1] = {row_bytes};
+    cuuint32_t box[2] = {128u / elem_bytes, box_rows};        // inner box = one 128-byte swizzle span
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, dtype, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return b200m_set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    return B200M_OK;
+}
+
+int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows, const int8_t* t_desc,
+                      const int32_t* t_norm, int64_t t_rows, int D, const DevPair* pairs, int num_pairs, int max_n,
+                      int max_m, int S, bool backward, Top2* out, long long total_rows, cudaStream_t st) {
+    if (D % KB_BYTES != 0) return B200M_EINVAL;
+    const int nkb = D / KB_BYTES;
+    if (nkb > 2) return B200M_EUNSUPPORTED;      // d^2 must stay < 2^24 (exact in fp32, as in cv2) and keys in int32
+    if (backward) {                              // roles swapped: train rows look for their best query row
+        const int8_t* d = q_desc; q_desc = t_desc; t_desc = d;
+        const int32_t* nn = q_norm; q_norm = t_norm; t_norm = nn;
+        int64_t r = q_rows; q_rows = t_rows; t_rows = r;
+        int mx = max_n; max_n = max_m; max_m = mx;
+    }
+    CUtensorMap tq, tt;
+    int rc = b200m_make_tmap_2d(&tq, q_desc, (uint64_t)q_rows, (uint64_t)D, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+    if (rc != B200M_OK) return rc;
+    rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D, TN, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+    if (rc != B200M_OK) return rc;
+    const int NB = nkb == 1 ? 5 : 4;
+    const size_t smem = smem_bytes(nkb, NB);
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(2, 4) > (int)smem_bytes(1, 5) ? (int)smem_bytes(2, 4)
+                                                                                            : (int)smem_bytes(1, 5)),
+                         "l2_i8 smem attr");
+        attr_set = true;
+    }
+    int tiles_max = (max_n + TM - 1) / TM;
+    long long total_items = (long long)num_pairs * S * tiles_max;
+    if (total_items <= 0) return B200M_OK;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
+    l2_i8_top2_kernel<<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
+                                                   backward ? 1 : 0, nkb, NB, out, total_rows);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_top2_kernel launch");
+    return B200M_OK;
 }

@@ -28,6 +28,62 @@ __device__ __forceinline__ Top2 merge_splits(const Top2* __restrict__ arr, long 
     return r;
 }
 
+
+// Exact runner-up for the tensor-core L2_I8 kernel (see l2_i8.cu header): k2 so far is the best
+// among all chunks other than the winner's 32-column chunk; recompute the winner's chunk exactly
+// (int8 dp4a, one warp per query row, one lane per column) and fold it in.  In MODE_RATIO a row is
+// refined only if it passes the ratio test with the candidate (the true runner-up is never larger,
+// so a row that fails with the candidate fails anyway).  The merged result is written to split 0.
+__global__ void __launch_bounds__(256)
+refine_i8_kernel(int always, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
+                 Top2* __restrict__ fwd, long long total_n, int S, const int8_t* __restrict__ q_desc,
+                 const int32_t* __restrict__ q_norm, const int8_t* __restrict__ t_desc,
+                 const int32_t* __restrict__ t_norm, int D) {
+    const int lane = threadIdx.x & 31;
+    int p = blockIdx.x / blocks_per_pair;
+    int i = (blockIdx.x - p * blocks_per_pair) * 8 + (threadIdx.x >> 5);
+    DevPair pr = pairs[p];
+    if (i >= pr.n) return;
+    const long long row = pr.fwd_off + i;
+    Top2 t = merge_splits(fwd, total_n, S, row);
+    if (t.k1 != B200M_SENTINEL) {
+        bool need = always || ratio <= 0.0 || t.k2 == B200M_SENTINEL;
+        if (!need) {
+            float d1 = value_to_distance(B200M_KIND_L2_I8, (u32)(t.k1 >> 32));
+            float d2 = value_to_distance(B200M_KIND_L2_I8, (u32)(t.k2 >> 32));
+            need = (double)d1 < ratio * (double)d2;
+        }
+        if (need) {
+            const int j1 = (int)(u32)t.k1;
+            const int col = (j1 & ~31) + lane;
+            u64 key = B200M_SENTINEL;
+            if (col < pr.m && col != j1) {
+                const int4* a = reinterpret_cast<const int4*>(q_desc + (long long)(pr.q_off + i) * D);
+                const int4* b = reinterpret_cast<const int4*>(t_desc + (long long)(pr.t_off + col) * D);
+                int dot = 0;
+                for (int k = 0; k < D / 16; ++k) {
+                    int4 x = __ldg(a + k), y = __ldg(b + k);
+                    dot = __dp4a(x.x, y.x, dot); dot = __dp4a(x.y, y.y, dot);
+                    dot = __dp4a(x.z, y.z, dot); dot = __dp4a(x.w, y.w, dot);
+                }
+                int d2i = __ldg(q_norm + pr.q_off + i) + __ldg(t_norm + pr.t_off + col) - 2 * dot;
+                key = ((u64)(u32)d2i << 32) | (u64)(u32)col;
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                u64 o = __shfl_xor_sync(0xffffffffu, key, off);
+                key = o < key ? o : key;
+            }
+            if (key < t.k2) t.k2 = key;
+        }
+    }
+    if (lane == 0) {
+        fwd[row] = t;
+        Top2 none; none.k1 = B200M_SENTINEL; none.k2 = B200M_SENTINEL;
+        for (int s = 1; s < S; ++s) fwd[(long long)s * total_n + row] = none;
+    }
+}
+
 __global__ void __launch_bounds__(256)
 finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
                 const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
@@ -127,6 +183,20 @@ knn2_emit_kernel(int kind, const DevPair* __restrict__ pairs, int blocks_per_pai
 }
 
 }  // namespace
+
+
+int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_pairs, int max_n, const int8_t* q_desc,
+                     const int32_t* q_norm, const int8_t* t_desc, const int32_t* t_norm, int D, cudaStream_t st) {
+    int bpp = (max_n + 7) / 8;
+    long long grid = (long long)num_pairs * bpp;
+    if (grid <= 0) return B200M_OK;
+    if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    refine_i8_kernel<<<(unsigned)grid, 256, 0, st>>>(always ? 1 : 0, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
+                                                     plan.S, q_desc, q_norm, t_desc, t_norm, D);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "refine_i8_kernel launch");
+    return B200M_OK;
+}
 
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
                     cudaStream_t st) {

@@ -1,0 +1,211 @@
+"""All-pairs (i<j) exhaustive matching over a descriptor store resident in HBM — the batched form of
+the per-pair loop in the reference's `match_folder`
+(/root/reference/FeatureMatchingExtraction/pipeline.py:538-606; pair list = itertools.combinations,
+image_manager.py:491-494), with detection hoisted out: descriptors are uploaded once, every pair is a
+work item of one C-ABI call, and results come back as a CSR (pair_ptr, query_idx, train_idx, distance).
+
+Multi-GPU: pairs are independent, so the (i<j) list is cut into balanced contiguous
+blocks, one per rank; the packed store is broadcast once from rank 0 (NCCL over NVLink) and the
+per-pair match lists return to rank 0 by a variable-length gather.  No collective sits inside the
+matching itself.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, NamedTuple, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from .engine import DeviceDescriptors, Engine, NORM_HAMMING, NORM_L2, mode_of
+
+
+_PAIR_DTYPE = np.dtype([("q_off", "<i4"), ("n", "<i4"), ("t_off", "<i4"), ("m", "<i4"), ("out_off", "<i8")])
+assert _PAIR_DTYPE.itemsize == ctypes.sizeof(L.Pair)
+
+
+class Store(NamedTuple):
+    dd: DeviceDescriptors            # all images' rows, concatenated
+    offsets: np.ndarray              # int64 [I+1] first row of each image
+    norm_type: int
+
+
+class PairCSR(NamedTuple):
+    pairs: np.ndarray                # int32 [P, 2] image indices (i, j)
+    ptr: "torch.Tensor | np.ndarray"     # int64 [P+1]
+    query_idx: "torch.Tensor | np.ndarray"
+    train_idx: "torch.Tensor | np.ndarray"
+    distance: "torch.Tensor | np.ndarray"
+
+    def pair(self, p: int):
+        s, e = int(self.ptr[p]), int(self.ptr[p + 1])
+        return self.query_idx[s:e], self.train_idx[s:e], self.distance[s:e]
+
+    def to_host(self) -> "PairCSR":
+        f = lambda x: x.cpu().numpy() if isinstance(x, torch.Tensor) else x   # noqa: E731
+        return PairCSR(self.pairs, f(self.ptr), f(self.query_idx), f(self.train_idx), f(self.distance))
+
+
+def build_store(engine: Engine, images: Sequence[np.ndarray] | np.ndarray | torch.Tensor, norm_type: int,
+                counts: Optional[Sequence[int]] = None) -> Store:
+    """Upload and re-encode all images' descriptors.  `images` is a list of [n_i, D] arrays, an
+    [I, n, D] array, or an already concatenated [rows, D] tensor plus `counts`."""
+    if counts is not None:
+        cat = images
+        counts = list(counts)
+    elif isinstance(images, np.ndarray) and images.ndim == 3:
+        counts = [images.shape[1]] * images.shape[0]
+        cat = images.reshape(-1, images.shape[2])
+    else:
+        counts = [len(x) for x in images]
+        cat = np.concatenate(list(images), axis=0)
+    if norm_type == NORM_HAMMING and not isinstance(cat, torch.Tensor) and cat.shape[1] % 16 != 0:
+        # AKAZE's 61-byte rows: zero-pad to a 16-byte multiple once (adds 0 to every Hamming distance)
+        pad = (-cat.shape[1]) % 16
+        cat = np.pad(cat, ((0, 0), (0, pad)))
+    offsets = np.zeros(len(counts) + 1, np.int64)
+    np.cumsum(counts, out=offsets[1:])
+    return Store(engine.prepare(cat, norm_type), offsets, norm_type)
+
+
+def all_pairs(num_images: int) -> np.ndarray:
+    i, j = np.triu_indices(num_images, k=1)
+    return np.stack([i, j], axis=1).astype(np.int32)
+
+
+def partition_pairs(pairs: np.ndarray, offsets: np.ndarray, world: int) -> List[np.ndarray]:
+    """Balanced contiguous blocks of the pair list: block boundaries are placed on the prefix sum of
+    per-pair work n_i * n_j, so every rank gets ~1/world of the distance evaluations while keeping
+    the (i<j) order (consecutive pairs share image i: L2 locality)."""
+    if len(pairs) == 0:
+        return [pairs[:0] for _ in range(world)]
+    n = np.diff(offsets)
+    w = n[pairs[:, 0]].astype(np.float64) * n[pairs[:, 1]].astype(np.float64)
+    cum = np.concatenate([[0.0], np.cumsum(w)])
+    cuts = np.searchsorted(cum, np.linspace(0.0, cum[-1], world + 1)[1:-1], side="left")
+    bounds = np.concatenate([[0], cuts, [len(pairs)]]).astype(np.int64)
+    return [pairs[bounds[r]:bounds[r + 1]] for r in range(world)]
+
+
+class AllPairsMatcher:
+    """Chunked CSR matching of an arbitrary pair list over one Store (single GPU)."""
+
+    def __init__(self, engine: Engine, chunk_pairs: int = 2048):
+        self.engine = engine
+        self.chunk_pairs = int(chunk_pairs)
+        self._bufs = {}
+
+    def _buf(self, name: str, numel: int, dtype) -> torch.Tensor:
+        t = self._bufs.get(name)
+        if t is None or t.numel() < numel or t.dtype != dtype:
+            t = torch.empty(max(numel, 1), dtype=dtype, device=self.engine.device)
+            self._bufs[name] = t
+        return t
+
+    def match(self, store: Store, pairs: np.ndarray, cross_check: bool = False,
+              ratio_threshold: Optional[float] = None) -> PairCSR:
+        """Returns a device-resident CSR over `pairs` (order preserved)."""
+        eng, lib, dd = self.engine, self.engine.lib, store.dd
+        mode = mode_of(cross_check, ratio_threshold)
+        ratio = float(ratio_threshold or 0.0)
+        n_of = np.diff(store.offsets)
+        P = len(pairs)
+        outs_q, outs_t, outs_d, ptrs = [], [], [], []
+        base = 0
+        dev = eng.device
+        for c0 in range(0, P, self.chunk_pairs):
+            chunk = pairs[c0:c0 + self.chunk_pairs]
+            C = len(chunk)
+            rec = np.zeros(C, dtype=_PAIR_DTYPE)
+            rec["q_off"] = store.offsets[chunk[:, 0]]; rec["n"] = n_of[chunk[:, 0]]
+            rec["t_off"] = store.offsets[chunk[:, 1]]; rec["m"] = n_of[chunk[:, 1]]
+            arr = rec.ctypes.data_as(ctypes.POINTER(L.Pair))
+            tn, tm = int(rec["n"].sum(dtype=np.int64)), int(rec["m"].sum(dtype=np.int64))
+            mn, mm = int(rec["n"].max()), int(rec["m"].max())
+            nbytes = ctypes.c_size_t(0)
+            L.check(lib.b200m_workspace_bytes(dd.kind, mode, C, tn, tm, mn, mm, dd.width, ctypes.byref(nbytes)),
+                    "b200m_workspace_bytes")
+            ws = eng._workspace(nbytes.value)
+            oq = self._buf("q", tn, torch.int32); ot = self._buf("t", tn, torch.int32)
+            od = self._buf("d", tn, torch.float32); oc = self._buf("c", C, torch.int32)
+            optr = self._buf("p", C + 1, torch.int64)
+            with torch.cuda.device(dev):
+                rc = lib.b200m_match_pairs_csr(dd.kind, dd.desc.data_ptr(), 0 if dd.norm is None else dd.norm.data_ptr(),
+                                               dd.rows, dd.desc.data_ptr(), 0 if dd.norm is None else dd.norm.data_ptr(),
+                                               dd.rows, dd.width, arr, C, mode, ratio, oq.data_ptr(), ot.data_ptr(),
+                                               od.data_ptr(), oc.data_ptr(), optr.data_ptr(), ws.data_ptr(), ws.numel(),
+                                               eng._stream())
+            L.check(rc, "b200m_match_pairs_csr")
+            if P <= self.chunk_pairs:          # single chunk: hand the buffers out without a copy
+                total = int(optr[C].item())
+                return PairCSR(pairs, optr[:C + 1].clone(), oq[:total].clone(), ot[:total].clone(), od[:total].clone())
+            total = int(optr[C].item())        # sync: the tight size of this chunk
+            outs_q.append(oq[:total].clone()); outs_t.append(ot[:total].clone()); outs_d.append(od[:total].clone())
+            ptrs.append(optr[:C] + base)
+            base += total
+        if P == 0:
+            z = torch.zeros(1, dtype=torch.int64, device=dev)
+            e = torch.empty(0, dtype=torch.int32, device=dev)
+            return PairCSR(pairs, z, e, e.clone(), torch.empty(0, dtype=torch.float32, device=dev))
+        ptrs.append(torch.tensor([base], dtype=torch.int64, device=dev))
+        return PairCSR(pairs, torch.cat(ptrs), torch.cat(outs_q), torch.cat(outs_t), torch.cat(outs_d))
+
+
+# ---------------------------------------------------------------------------------- multi-GPU
+def broadcast_store(store: Optional[Store], norm_type: int, device: torch.device, src: int = 0) -> Store:
+    """Broadcast the packed store (descriptors, norms, offsets) from `src` to every rank."""
+    import torch.distributed as dist
+    rank = dist.get_rank()
+    meta = [None]
+    if rank == src:
+        dd = store.dd
+        meta = [(dd.kind, tuple(dd.desc.shape), str(dd.desc.dtype), None if dd.norm is None else str(dd.norm.dtype),
+                 dd.rows, dd.width, store.offsets.tolist())]
+    dist.broadcast_object_list(meta, src=src)
+    kind, shape, dt, ndt, rows, width, offsets = meta[0]
+    tdt = getattr(torch, dt.split(".")[-1])
+    desc = store.dd.desc if rank == src else torch.empty(shape, dtype=tdt, device=device)
+    dist.broadcast(desc, src=src)
+    norm = None
+    if ndt is not None:
+        norm = store.dd.norm if rank == src else torch.empty((rows,), dtype=getattr(torch, ndt.split(".")[-1]), device=device)
+        dist.broadcast(norm, src=src)
+    return Store(DeviceDescriptors(kind, desc, norm, rows, width), np.asarray(offsets, np.int64), norm_type)
+
+
+def gather_csr(local: PairCSR, device: torch.device, dst: int = 0) -> Optional[PairCSR]:
+    """Variable-length gather of every rank's CSR to `dst` (all_gather of sizes, then send/recv)."""
+    import torch.distributed as dist
+    rank, world = dist.get_rank(), dist.get_world_size()
+    P = len(local.pairs)
+    sizes = torch.tensor([P, int(local.query_idx.numel())], dtype=torch.int64, device=device)
+    all_sizes = [torch.zeros_like(sizes) for _ in range(world)]
+    dist.all_gather(all_sizes, sizes)
+    all_sizes = [tuple(int(v) for v in s.tolist()) for s in all_sizes]
+    pairs_dev = torch.from_numpy(np.ascontiguousarray(local.pairs)).to(device)
+    if rank != dst:
+        for t in (pairs_dev, local.ptr, local.query_idx, local.train_idx, local.distance):
+            if t.numel():
+                dist.send(t.contiguous(), dst=dst)
+        return None
+    parts_pairs, parts_ptr, parts_q, parts_t, parts_d = [], [], [], [], []
+    base = 0
+    for r in range(world):
+        Pr, Kr = all_sizes[r]
+        if r == dst:
+            pr, ptr, q, t, d = pairs_dev, local.ptr, local.query_idx, local.train_idx, local.distance
+        else:
+            pr = torch.empty((Pr, 2), dtype=torch.int32, device=device)
+            ptr = torch.empty(Pr + 1, dtype=torch.int64, device=device)
+            q = torch.empty(Kr, dtype=torch.int32, device=device)
+            t = torch.empty(Kr, dtype=torch.int32, device=device)
+            d = torch.empty(Kr, dtype=torch.float32, device=device)
+            for buf in (pr, ptr, q, t, d):
+                if buf.numel():
+                    dist.recv(buf, src=r)
+        parts_pairs.append(pr); parts_ptr.append(ptr[:Pr] + base); parts_q.append(q); parts_t.append(t); parts_d.append(d)
+        base += Kr
+    parts_ptr.append(torch.tensor([base], dtype=torch.int64, device=device))
+    return PairCSR(torch.cat(parts_pairs).cpu().numpy(), torch.cat(parts_ptr), torch.cat(parts_q), torch.cat(parts_t),
+                   torch.cat(parts_d))

@@ -33,6 +33,12 @@ static int choose_splits(int num_pairs, int max_n, int max_m, int mode, int sm_c
     return S;
 }
 
+// Optional device timing of the dominant (knn) kernels for bench.py's roofline: CUDA events recorded on
+// the launching stream around each knn launch, summed by b200m_timing_collect().
+static bool g_timing = false;
+static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
+static size_t g_events_used = 0;
+
 static int g_sm_count = 0;
 static int device_sm_count() {
     if (g_sm_count == 0) {
@@ -88,6 +94,26 @@ int b200m_device_info(int* sm_count, int* cc_major, int* cc_minor) {
     if (cc_major) *cc_major = ma;
     if (cc_minor) *cc_minor = mi;
     return ma == 10 ? B200M_OK : B200M_ENODEVICE;
+}
+
+int b200m_timing_enable(int on) {
+    g_timing = on != 0;
+    g_events_used = 0;
+    return B200M_OK;
+}
+
+int b200m_timing_collect(double* knn_ms, int* knn_launches) {
+    double total = 0.0;
+    for (size_t i = 0; i < g_events_used; ++i) {
+        float ms = 0.f;
+        B200M_CUDA_CHECK(cudaEventSynchronize(g_events[i].second), "event sync");
+        B200M_CUDA_CHECK(cudaEventElapsedTime(&ms, g_events[i].first, g_events[i].second), "event elapsed");
+        total += ms;
+    }
+    if (knn_ms) *knn_ms = total;
+    if (knn_launches) *knn_launches = (int)g_events_used;
+    g_events_used = 0;
+    return B200M_OK;
 }
 
 int64_t b200m_launch_count(void) { return g_launches.load(); }
@@ -150,6 +176,18 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         Top2* out = back ? pl.bwd : pl.fwd;
         long long rows = back ? total_m : total_n;
         int rc;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (g_timing) {
+            if (g_events_used == g_events.size()) {
+                cudaEvent_t a, b;
+                B200M_CUDA_CHECK(cudaEventCreate(&a), "event create");
+                B200M_CUDA_CHECK(cudaEventCreate(&b), "event create");
+                g_events.emplace_back(a, b);
+            }
+            e0 = g_events[g_events_used].first; e1 = g_events[g_events_used].second;
+            ++g_events_used;
+            cudaEventRecord(e0, st);
+        }
         if (kind == B200M_KIND_HAMMING)
             rc = launch_hamming_top2((const uint8_t*)q_desc, (const uint8_t*)t_desc, D, pl.pairs, num_pairs,
                                      max_n, max_m, S, back, out, rows, st);
@@ -161,6 +199,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
             rc = launch_l2_f32_top2((const float*)q_desc, (const float*)q_norm, q_rows, (const float*)t_desc,
                                     (const float*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
                                     back, out, rows, st);
+        if (e1) cudaEventRecord(e1, st);
         if (rc != B200M_OK) return rc;
     }
     return B200M_OK;
@@ -168,11 +207,11 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
 
 extern "C" {
 
-int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
-                      const void* t_desc, const void* t_norm, int64_t t_rows, int D,
-                      const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
-                      int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
-                      void* workspace, size_t workspace_bytes, void* stream) {
+static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                            const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                            const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                            int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count, int64_t* out_ptr,
+                            void* workspace, size_t workspace_bytes, void* stream) {
     if (mode != B200M_MODE_RATIO && mode != B200M_MODE_CROSS && mode != B200M_MODE_NN) return B200M_EINVAL;
     if (num_pairs > 0 && (!out_q || !out_t || !out_d || !out_count)) return B200M_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
@@ -180,9 +219,13 @@ int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t 
     int rc = run_knn_stage(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs,
                            mode, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
-    if (num_pairs == 0) return B200M_OK;
+    if (num_pairs == 0) {
+        if (out_ptr) B200M_CUDA_CHECK(cudaMemsetAsync(out_ptr, 0, sizeof(int64_t), st), "ptr memset");
+        return B200M_OK;
+    }
+    B200M_CUDA_CHECK(cudaMemsetAsync(out_count, 0, sizeof(int32_t) * (size_t)num_pairs, st), "count memset");
     if (pl.total_n == 0) {
-        B200M_CUDA_CHECK(cudaMemsetAsync(out_count, 0, sizeof(int32_t) * (size_t)num_pairs, st), "count memset");
+        if (out_ptr) B200M_CUDA_CHECK(cudaMemsetAsync(out_ptr, 0, sizeof(int64_t) * ((size_t)num_pairs + 1), st), "ptr memset");
         return B200M_OK;
     }
     if (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) {
@@ -190,9 +233,33 @@ int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t 
                               (const int8_t*)t_desc, (const int32_t*)t_norm, D, st);
         if (rc != B200M_OK) return rc;
     }
-    rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, st);
+    // CSR mode counts survivors in finalize (into out_count), scans them into tight offsets, then emits.
+    rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, out_ptr ? out_count : nullptr, st);
     if (rc != B200M_OK) return rc;
+    if (out_ptr) {
+        rc = launch_scan_offsets(pl, out_count, num_pairs, (long long*)out_ptr, st);
+        if (rc != B200M_OK) return rc;
+    }
     return launch_sort_emit(kind, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, st);
+}
+
+int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                      const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                      const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                      int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
+                      void* workspace, size_t workspace_bytes, void* stream) {
+    return match_pairs_impl(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs, mode,
+                            ratio, out_q, out_t, out_d, out_count, nullptr, workspace, workspace_bytes, stream);
+}
+
+int b200m_match_pairs_csr(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                          const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                          const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                          int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count, int64_t* out_ptr,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+    if (num_pairs >= 0 && !out_ptr) return B200M_EINVAL;
+    return match_pairs_impl(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs, mode,
+                            ratio, out_q, out_t, out_d, out_count, out_ptr, workspace, workspace_bytes, stream);
 }
 
 int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,

@@ -70,7 +70,9 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
 int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_pairs, int max_n, const int8_t* q_desc,
                      const int32_t* q_norm, const int8_t* t_desc, const int32_t* t_norm, int D, cudaStream_t st);
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
-                    cudaStream_t st);
+                    int32_t* counts, cudaStream_t st);
+int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
+                        cudaStream_t st);
 int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
                      int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st);
 int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,

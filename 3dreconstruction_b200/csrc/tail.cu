@@ -87,12 +87,14 @@ refine_i8_kernel(int always, double ratio, const DevPair* __restrict__ pairs, in
 __global__ void __launch_bounds__(256)
 finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
                 const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
-                long long total_m, int S, u64* __restrict__ sortbuf, int32_t* __restrict__ tbest) {
+                long long total_m, int S, u64* __restrict__ sortbuf, int32_t* __restrict__ tbest,
+                int32_t* __restrict__ counts) {
     int p = blockIdx.x / blocks_per_pair;
     int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
     DevPair pr = pairs[p];
-    if (i >= pr.n) return;
-    Top2 t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
+    const bool active = i < pr.n;
+    Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
+    if (active) t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
     u64 key = B200M_SENTINEL;
     int32_t tb = -1;
     if (t.k1 != B200M_SENTINEL) {
@@ -114,8 +116,52 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
         tb = (int32_t)j1;
         if (keep) key = ((u64)__float_as_uint(d1) << 32) | (u64)(u32)i;
     }
-    sortbuf[pr.sort_off + i] = key;
-    tbest[pr.fwd_off + i] = tb;
+    if (active) {
+        sortbuf[pr.sort_off + i] = key;
+        tbest[pr.fwd_off + i] = tb;
+    }
+    if (counts) {                                   // CSR mode: survivors per pair (block = one pair)
+        int c = __syncthreads_count(key != B200M_SENTINEL);
+        if (threadIdx.x == 0 && c) atomicAdd(&counts[p], c);
+    }
+}
+
+// CSR mode: exclusive scan of the per-pair survivor counts -> tight output offsets.
+__global__ void __launch_bounds__(1024)
+scan_offsets_kernel(DevPair* __restrict__ pairs, const int32_t* __restrict__ counts, int num_pairs,
+                    long long* __restrict__ out_ptr) {
+    __shared__ long long warp_sums[32];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int base = 0; base < num_pairs; base += 1024) {
+        int p = base + threadIdx.x;
+        long long v = p < num_pairs ? counts[p] : 0, x = v;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            long long o = __shfl_up_sync(0xffffffffu, x, off);
+            if (lane >= off) x += o;
+        }
+        if (lane == 31) warp_sums[w] = x;
+        __syncthreads();
+        if (w == 0) {
+            long long y = warp_sums[lane];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                long long o = __shfl_up_sync(0xffffffffu, y, off);
+                if (lane >= off) y += o;
+            }
+            warp_sums[lane] = y;
+        }
+        __syncthreads();
+        long long excl = carry + (w ? warp_sums[w - 1] : 0) + x - v;
+        if (p < num_pairs) { pairs[p].out_off = excl; out_ptr[p] = excl; }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out_ptr[num_pairs] = carry;
 }
 
 __device__ __forceinline__ void bitonic(u64* a, int npad) {
@@ -198,14 +244,22 @@ int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_p
     return B200M_OK;
 }
 
+int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
+                        cudaStream_t st) {
+    scan_offsets_kernel<<<1, 1024, 0, st>>>(plan.pairs, counts, num_pairs, out_ptr);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "scan_offsets_kernel launch");
+    return B200M_OK;
+}
+
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
-                    cudaStream_t st) {
+                    int32_t* counts, cudaStream_t st) {
     int bpp = (max_n + 255) / 256;
     long long grid = (long long)num_pairs * bpp;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
     finalize_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
-                                                    plan.bwd, plan.total_m, plan.S, plan.sortbuf, plan.tbest);
+                                                    plan.bwd, plan.total_m, plan.S, plan.sortbuf, plan.tbest, counts);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "finalize_kernel launch");
     return B200M_OK;

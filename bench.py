@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the brute-force matching hot path (BASELINE.json metric:
+image pairs/s and Gdist/s, SIFT-L2 / ORB-Hamming, 1/2/4/8 B200 vs CPU cv2).
+
+    python bench.py --gpus N --steps K --warmup W                 # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W  # reference CPU arm (cv2.BFMatcher)
+
+Workload (config.workload): BASELINE configs[3] — SIFT all-pairs exhaustive matching, 200 images x
+8192 keypoints x 128-d (19,900 pairs), knnMatch k=2 + ratio 0.75, sharded over the N ranks by
+balanced contiguous pair blocks (strong scaling: the pair list is fixed).  One "step" = one pass over
+all pairs.  The int8 store (210 MB) is larger than L2 (126 MB), so no L2 flush is needed between steps.
+`also` carries single-pair numbers for configs[0] (SIFT 8k x 8k) and configs[1] (ORB 10k x 10k cross-check).
+Prints exactly ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+RATIO = 0.75
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--images", type=int, default=200)
+    ap.add_argument("--keypoints", type=int, default=8192)
+    ap.add_argument("--chunk-pairs", type=int, default=2048)
+    ap.add_argument("--cpu-sample-pairs", type=int, default=24)
+    ap.add_argument("--no-also", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [x for x in sm if x > 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- synthetic data on the device
+def sift_set_gpu(torch, device, images, n, seed=3, d=128, shared=0.3, sigma=6.0):
+    """Same recipe as 3dreconstruction_b200.synth.sift_set, generated on the GPU (840 MB of float32)."""
+    g = torch.Generator(device=device); g.manual_seed(seed)
+
+    def sift_like(rows):
+        x = torch._standard_gamma(torch.full((rows, d), 0.6, device=device), generator=g)
+        x = x / (x.norm(dim=1, keepdim=True) + 1e-12)
+        x = torch.clamp(x, max=0.2)
+        x = x / (x.norm(dim=1, keepdim=True) + 1e-12)
+        return torch.clamp(torch.round(512.0 * x), 0, 255)
+
+    pool = sift_like(2 * n)
+    k = int(n * shared)
+    out = torch.empty((images, n, d), dtype=torch.float32, device=device)
+    for i in range(images):
+        pick = torch.randperm(2 * n, device=device, generator=g)[:k]
+        out[i, :k] = torch.clamp(torch.round(pool[pick] + sigma * torch.randn((k, d), device=device, generator=g)), 0, 255)
+        out[i, k:] = sift_like(n - k)
+        out[i] = out[i][torch.randperm(n, device=device, generator=g)]
+    return out
+
+
+# --------------------------------------------------------------------------- CPU arm (reference's own engine)
+def cpu_match_fn():
+    """cv2.BFMatcher driven exactly as EnhancedBFMatcher.match drives it (oracle/bf_oracle.cv2_match);
+    falls back to the C restatement (OpenMP) when cv2 is not importable on this box."""
+    from oracle import bf_oracle as O
+    try:
+        import cv2
+        threads = os.cpu_count() or 1
+        cv2.setNumThreads(threads)
+        return (lambda a, b: O.cv2_match(a, b, O.NORM_L2, False, RATIO)), cv2.getNumThreads(), f"cv2.BFMatcher {cv2.__version__}"
+    except ImportError:
+        O.set_threads(os.cpu_count() or 1)
+        return (lambda a, b: O.reference_match(a, b, O.NORM_L2, False, RATIO)), O.num_threads(), "oracle/bf_oracle.c (OpenMP)"
+
+
+def cpu_time_pairs(host_images, pair_list):
+    fn, cores, engine = cpu_match_fn()
+    fn(host_images[0][:512], host_images[1][:512])          # warm the thread pool
+    t0 = time.perf_counter()
+    for i, j in pair_list:
+        fn(host_images[i], host_images[j])
+    return time.perf_counter() - t0, cores, engine
+
+
+def host_sample_images(args, count):
+    synth = importlib.import_module("3dreconstruction_b200.synth")
+    return synth.sift_set(seed=3, images=count, n=args.keypoints)
+
+
+def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path (cv2.BFMatcher, all host threads) on a
+    bounded sample of the same workload per step.  Rank 0 only; other ranks exit 0 without work."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    n_img = 5
+    imgs = host_sample_images(args, n_img)
+    sample = [(0, 1), (0, 2), (1, 2), (3, 4)]                  # 4 pairs per step  (~2 s of 8-thread cv2)
+    for _ in range(args.warmup):
+        cpu_time_pairs(imgs, sample[:1])
+    t_total, cores, engine = 0.0, 1, ""
+    for _ in range(args.steps):
+        t, cores, engine = cpu_time_pairs(imgs, sample)
+        t_total += t
+    pairs_s = len(sample) * args.steps / t_total
+    gdist = pairs_s * args.keypoints * args.keypoints / 1e9
+    line = {"impl": "reference", "metric": "image pairs/s (SIFT-L2 all-pairs, knn k=2 + ratio 0.75)", "value": pairs_s,
+            "unit": "pairs/s", "gdist_per_s": gdist, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * t_total / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args),
+            "cpu_baseline": {"value": pairs_s, "unit": "pairs/s", "cores": cores, "kind": "port",
+                             "sample": f"{len(sample)} pairs/step of the {args.keypoints}x{args.keypoints}x128 workload, {engine} "
+                                       "driven by oracle/bf_oracle.cv2_match (restates EnhancedBFMatcher.match)"},
+            "e2e": {"value": pairs_s, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def workload_config(args):
+    P = args.images * (args.images - 1) // 2
+    return {"workload": f"SIFT all-pairs: {args.images} images x {args.keypoints} keypoints x 128-d, {P} pairs, "
+                        f"knnMatch k=2 + ratio {RATIO} (BASELINE configs[3])",
+            "pairs": P, "l2_flush": "inputs larger than L2 (int8 store > 126 MB)" if args.images * args.keypoints * 128 > 126e6
+            else "store fits L2 (reduced size run)", "parallelism": f"pair-list sharding x{args.gpus}"}
+
+
+# --------------------------------------------------------------------------- the B200 arm
+def single_pair_extras(torch, b, eng, pk):
+    """configs[0] and configs[1]: one pair, device-resident, kernels only (CUDA events, 20 reps)."""
+    L = b._lib
+    out = {}
+
+    def timed(fn, reps=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    a, c = b.synth.sift_pair(seed=0, n=8192)
+    da, dc = eng.prepare(a, b.NORM_L2), eng.prepare(c, b.NORM_L2)
+    ms = timed(lambda: eng.match_device(da, dc, [(0, 8192, 0, 8192)], L.MODE_RATIO, RATIO))
+    gd = 8192 * 8192 / 1e9 / (ms / 1e3)
+    out["sift_pair_8192x8192_ratio0.75"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": gd,
+                                            "note": "one pair cannot fill 148 SMs x tensor pipe; latency-bound"}
+    a, c = b.synth.binary_pair(seed=1, n=10000, nbytes=32)
+    da, dc = eng.prepare(a, b.NORM_HAMMING), eng.prepare(c, b.NORM_HAMMING)
+    ms = timed(lambda: eng.match_device(da, dc, [(0, 10000, 0, 10000)], L.MODE_CROSS))
+    gd = 1e8 / 1e9 / (ms / 1e3)
+    popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 8 / 1e9       # Gdist/s, 256-bit, at max clock
+    out["orb_pair_10000x10000_crosscheck"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": gd,
+                                              "gdist_both_directions_per_s": 2 * gd,
+                                              "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": 2 * gd / popc_peak}
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    b = importlib.import_module("3dreconstruction_b200")
+    ap = importlib.import_module("3dreconstruction_b200.allpairs")
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    eng = b.Engine(device)
+    lib = eng.lib
+    pk, pk_src = peaks()
+    I, n, D = args.images, args.keypoints, 128
+    pairs = ap.all_pairs(I)
+    P = len(pairs)
+
+    # ---- inputs: rank 0 synthesises float32 SIFT-like descriptors, prepares the int8 store, broadcasts it
+    host_pinned = None
+    store = None
+    if rank == 0:
+        desc = sift_set_gpu(torch, device, I, n)                       # [I, n, 128] float32 on the device
+        host_pinned = torch.empty((I * n, D), dtype=torch.float32, pin_memory=True)
+        host_pinned.copy_(desc.view(I * n, D))                          # the e2e arm starts from HOST buffers
+        store = ap.build_store(eng, desc.view(I * n, D), b.NORM_L2, counts=[n] * I)
+        del desc
+    if world > 1:
+        store = ap.broadcast_store(store, b.NORM_L2, device)
+    assert store.dd.kind == b._lib.KIND_L2_I8
+    shards = ap.partition_pairs(pairs, store.offsets, world)
+    mine = shards[rank]
+    matcher = ap.AllPairsMatcher(eng, chunk_pairs=args.chunk_pairs)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def step():
+        return matcher.match(store, mine, cross_check=False, ratio_threshold=RATIO)
+
+    for _ in range(max(args.warmup, 3)):
+        res = step()
+    matches_total = int(res.query_idx.numel())
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.b200m_reset_launch_count()
+    lib.b200m_timing_enable(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        res = step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    launches = torch.tensor([lib.b200m_launch_count()], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(launches, op=dist.ReduceOp.SUM)
+    import ctypes
+    knn_ms, knn_launches = ctypes.c_double(0), ctypes.c_int(0)
+    lib.b200m_timing_collect(ctypes.byref(knn_ms), ctypes.byref(knn_launches))
+    lib.b200m_timing_enable(0)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = float(ms.item())
+    value = P * args.steps / (ms_total / 1e3)
+
+    # ---- end to end: HOST float32 descriptors -> H2D -> prep -> (broadcast) -> match -> (gather) -> D2H CSR
+    def e2e_step():
+        st = None
+        if rank == 0:
+            dev_desc = host_pinned.to(device, non_blocking=True)
+            st = ap.build_store(eng, dev_desc, b.NORM_L2, counts=[n] * I)
+        if world > 1:
+            st = ap.broadcast_store(st, b.NORM_L2, device)
+        r = matcher.match(st, mine, cross_check=False, ratio_threshold=RATIO)
+        if world > 1:
+            r = ap.gather_csr(r, device)
+        if rank == 0:
+            h = r.to_host()
+            return h.ptr.nbytes + h.query_idx.nbytes + h.train_idx.nbytes + h.distance.nbytes
+        return 0
+
+    e2e_step()
+    barrier()
+    e2e_steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        d2h = e2e_step()
+    barrier()
+    t_e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_value = P * e2e_steps / float(t_e2e.item())
+
+    if rank == 0:
+        my_pairs = len(mine)
+        ops = 2.0 * n * n * D * my_pairs * args.steps                 # int8 MACs x2, rank 0's share
+        achieved = ops / (knn_ms.value / 1e3) / 1e12 if knn_ms.value > 0 else None
+        peak = 2.0 * pk["bf16_tflops_sustained"]
+        line = {"metric": "image pairs/s (SIFT-L2 all-pairs, knn k=2 + ratio 0.75)", "value": value, "unit": "pairs/s",
+                "gdist_per_s": value * n * n / 1e9, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "int8 (exact; int32 accumulate)", "data": "synthetic", "config": workload_config(args),
+                "matches_per_step": matches_total if world == 1 else None,
+                "roofline": {"bound": "tensor", "kernel": "l2_i8_top2_kernel (tcgen05 kind::i8)", "achieved": achieved,
+                             "peak": peak, "unit": "TOP/s int8 (TFLOP/s-equivalent)", "frac": achieved / peak if achieved else None,
+                             "peak_source": f"2 x bf16_tflops_sustained of {pk_src} MEASURED_PEAKS.json (int8 peak not measured by the driver)",
+                             "kernel_ms_per_step": knn_ms.value / args.steps, "kernel_launches": knn_launches.value,
+                             "kernel_share_of_step": knn_ms.value / ms_total if world == 1 else None,
+                             "algorithmic_ops_per_pair": 2.0 * n * n * D, "algorithmic_hbm_bytes_per_pair": 2 * n * D + 12 * n,
+                             "traffic": None},
+                "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel() * 4),
+                        "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                        "path": "pinned host float32 descriptors -> H2D -> b200m_prep_l2_i8 -> b200m_match_pairs_csr -> D2H CSR"},
+                "gpu_launches": int(launches.item()), "clocks": clocks}
+        if world == 1:
+            imgs = host_sample_images(args, 4)
+            sample = [(0, 1), (0, 2), (0, 3), (1, 2), (1, 3), (2, 3)] * max(1, args.cpu_sample_pairs // 6)
+            t, cores, engine = cpu_time_pairs(imgs, sample)
+            line["cpu_baseline"] = {"value": len(sample) / t, "unit": "pairs/s", "cores": cores, "kind": "port",
+                                    "sample": f"{len(sample)} pairs of {n}x{n}x128 on this host, {engine} driven by "
+                                              "oracle/bf_oracle.cv2_match (restates EnhancedBFMatcher.match)"}
+            if not args.no_also:
+                line["also"] = single_pair_extras(torch, b, eng, pk)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -115,6 +115,16 @@ B200M_API int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm
                       int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
                       void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same as b200m_match_pairs but with a TIGHT CSR result: pair.out_off is ignored; pair p's matches
+ * occupy [out_ptr[p], out_ptr[p+1]) of out_q/out_t/out_d (capacity sum(pair.n)); out_ptr is
+ * int64 [num_pairs + 1] on the device.  Used by the all-pairs driver so that only real matches
+ * cross PCIe / NVLink. */
+B200M_API int b200m_match_pairs_csr(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                          const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                          const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                          int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
+                          int64_t* out_ptr, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Raw k=2 neighbours per query row (what cv2.BFMatcher.knnMatch(k=2) returns at :210), for
  * parity checks of the knn stage itself.  Arrays of length sum(pair.n), pair p at out_off:
  * idx2 = -1 / d2 = -1 when the pair has a single train row (cv2 returns a length-1 list). */
@@ -123,6 +133,12 @@ B200M_API int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm,
                      const b200m_pair* pairs_host, int num_pairs,
                      int32_t* idx1, int32_t* idx2, float* d1, float* d2,
                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* Measurement hooks for bench.py's roofline: when enabled, CUDA events are recorded on the
+ * launching stream around every knn-stage kernel; collect() synchronises them and returns the summed
+ * device time (ms) and the number of knn launches since the last collect/enable. */
+B200M_API int b200m_timing_enable(int on);
+B200M_API int b200m_timing_collect(double* knn_ms, int* knn_launches);
 
 /* Counters for bench.py's `gpu_launches`: kernels launched by this library since the last reset. */
 B200M_API int64_t b200m_launch_count(void);

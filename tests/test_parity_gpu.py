@@ -213,3 +213,31 @@ def test_plugin_match_returns_matchdata(eng):
     assert m.match(f1, bad).matches == []
     # downstream helpers keep working on our MatchData
     assert len(md.filter_by_score(40.0).filtered_matches) <= len(md.matches)
+
+
+# ------------------------------------------------------------------ all-pairs CSR driver (single GPU)
+@pytest.mark.parametrize("kind", ["sift", "orb", "akaze61"])
+@pytest.mark.parametrize("mode", [(False, 0.75), (True, None)])
+def test_all_pairs_csr_equals_per_pair_oracle(eng, kind, mode):
+    ap = pkg("allpairs")
+    sizes = [300, 129, 1, 640, 77, 256]
+    if kind == "sift":
+        imgs = [synth.sift_pair(seed=60 + i, n=max(s, 2))[0][:s] for i, s in enumerate(sizes)]
+        # plant overlap so the ratio test has survivors
+        imgs[3][:200] = np.clip(imgs[0][:200] + np.random.default_rng(1).integers(-4, 5, size=(200, 128)), 0, 255)
+        norm = b.NORM_L2
+    else:
+        nb = 32 if kind == "orb" else 61
+        imgs = [synth.binary_pair(seed=70 + i, n=max(s, 2), nbytes=nb)[0][:s] for i, s in enumerate(sizes)]
+        imgs[3][:200] = imgs[0][:200]
+        imgs[3][:200, 0] ^= 1
+        norm = b.NORM_HAMMING
+    store = ap.build_store(eng, imgs, norm)
+    pairs = ap.all_pairs(len(imgs))
+    for chunk in (4, 1000):                       # multi-chunk and single-chunk code paths
+        res = ap.AllPairsMatcher(eng, chunk_pairs=chunk).match(store, pairs, *mode).to_host()
+        assert res.ptr[0] == 0 and len(res.ptr) == len(pairs) + 1 and res.ptr[-1] == len(res.query_idx)
+        for p, (i, j) in enumerate(pairs):
+            q, t, d = res.pair(p)
+            want = O.reference_match(imgs[i], imgs[j], norm, *mode)
+            assert_exact(O.Matches(q, t, d), want, f"{kind} pair {i},{j} chunk={chunk} mode={mode}")

@@ -128,7 +128,7 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 Item it = decode_item(item, pairs, tiles_max, S, backward);
                 if (!it.valid) continue;
                 const uint32_t ab = a_cnt & 1;
-                sm100::mbar_wait(&sm.a_empty[ab], ((a_cnt >> 1) & 1) ^ 1);
+                sm100::mbar_wait_suspend(&sm.a_empty[ab], ((a_cnt >> 1) & 1) ^ 1);
                 sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
                 for (int kb = 0; kb < nkb; ++kb)
                     sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
@@ -137,7 +137,7 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                     for (int kb = 0; kb < nkb; ++kb) {
                         const uint32_t s = b_cnt % NB;
-                        sm100::mbar_wait(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
+                        sm100::mbar_wait_suspend(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
                         sm100::mbar_arrive_expect_tx(&sm.b_full[s], (uint32_t)B_KB_BYTES);
                         sm100::tma_load_2d(sm.b + (size_t)s * B_KB_BYTES, &tmap_t, &sm.b_full[s], kb * KB_BYTES,
                                            it.t_off + c0);
@@ -155,15 +155,15 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 Item it = decode_item(item, pairs, tiles_max, S, backward);
                 if (!it.valid) continue;
                 const uint32_t ab = a_cnt & 1;
-                sm100::mbar_wait(&sm.a_full[ab], (a_cnt >> 1) & 1);
+                sm100::mbar_wait_suspend(&sm.a_full[ab], (a_cnt >> 1) & 1);
                 for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                     const uint32_t as = acc_cnt & 1;
-                    sm100::mbar_wait(&sm.acc_empty[as], ((acc_cnt >> 1) & 1) ^ 1);
+                    sm100::mbar_wait_suspend(&sm.acc_empty[as], ((acc_cnt >> 1) & 1) ^ 1);
                     sm100::tc_fence_after();
                     const uint32_t d_tmem = tmem_base + as * TN;
                     for (int kb = 0; kb < nkb; ++kb) {
                         const uint32_t s = b_cnt % NB;
-                        sm100::mbar_wait(&sm.b_full[s], (b_cnt / NB) & 1);
+                        sm100::mbar_wait_suspend(&sm.b_full[s], (b_cnt / NB) & 1);
                         sm100::tc_fence_after();
                         const uint64_t adesc = sm100::make_smem_desc_sw128(
                             sm100::smem_u32(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES));
@@ -191,33 +191,43 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
             int v1 = 0x7fffffff, v2 = 0x7fffffff, i1 = -1, i2 = -1;
-            auto load_cb = [&](int c0) -> int {
+            // raw norm of this thread's column of the NEXT tile: loaded early, consumed one tile later
+            auto load_nt = [&](int c0) -> int {
                 int col = c0 + e;
-                return col < it.c_end ? __ldg(t_norm + it.t_off + col) * 32 + (e & 31) : MASK_CB;
+                return col < it.c_end ? __ldg(t_norm + it.t_off + col) : -1;
             };
-            int cb_next = it.c_begin < it.c_end ? load_cb(it.c_begin) : MASK_CB;
+            int nt_next = it.c_begin < it.c_end ? load_nt(it.c_begin) : -1;
+            const uint32_t cb_s = sm100::smem_u32(sm.cb);
             for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                 const uint32_t as = acc_cnt & 1;
-                sm.cb[as * TN + e] = cb_next;
-                if (c0 + TN < it.c_end) cb_next = load_cb(c0 + TN);
+                sm100::sts32(cb_s + (as * TN + e) * 4, nt_next >= 0 ? nt_next * 32 + (e & 31) : MASK_CB);
+                if (c0 + TN < it.c_end) nt_next = load_nt(c0 + TN);
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
                 sm100::tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * TN + half * 128;
-                const int4* cbv = reinterpret_cast<const int4*>(sm.cb + as * TN + half * 128);
-#pragma unroll 1
+                const uint32_t cbv = cb_s + (as * TN + half * 128) * 4;
+                uint32_t acc[2][32];
+                sm100::tmem_ld32(taddr, acc[0]);
+#pragma unroll
                 for (int ch = 0; ch < 4; ++ch) {
-                    uint32_t acc[32];
-                    sm100::tmem_ld32(taddr + ch * 32, acc);
-                    sm100::tmem_ld_wait();
+                    sm100::tmem_ld_wait();                                   // chunk ch is in registers
+                    if (ch + 1 < 4) {
+                        sm100::tmem_ld32(taddr + (ch + 1) * 32, acc[(ch + 1) & 1]);   // overlaps the math below
+                    } else {
+                        sm100::tc_fence_before();                            // whole tile read: free the TMEM stage early
+                        __syncwarp();
+                        if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
+                    }
+                    const uint32_t(&a32)[32] = acc[ch & 1];
                     int key[32];
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
-                        int4 c4 = cbv[ch * 8 + g];                       // warp-uniform address: broadcast
-                        key[4 * g + 0] = c4.x - 64 * (int)acc[4 * g + 0];
-                        key[4 * g + 1] = c4.y - 64 * (int)acc[4 * g + 1];
-                        key[4 * g + 2] = c4.z - 64 * (int)acc[4 * g + 2];
-                        key[4 * g + 3] = c4.w - 64 * (int)acc[4 * g + 3];
+                        int4 c4 = sm100::lds128(cbv + (ch * 32 + g * 4) * 4);   // warp-uniform address: broadcast
+                        key[4 * g + 0] = c4.x - 64 * (int)a32[4 * g + 0];
+                        key[4 * g + 1] = c4.y - 64 * (int)a32[4 * g + 1];
+                        key[4 * g + 2] = c4.z - 64 * (int)a32[4 * g + 2];
+                        key[4 * g + 3] = c4.w - 64 * (int)a32[4 * g + 3];
                     }
                     int a[11];
 #pragma unroll
@@ -234,9 +244,6 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     v1 = lt1 ? val : v1;
                     i1 = lt1 ? col : i1;
                 }
-                sm100::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
                 ++acc_cnt;
             }
             // merge the two column halves of each row (warp w and w+4), then publish

@@ -1,0 +1,85 @@
+// tools/mma_peak.cu — microbenchmark: raw tcgen05.mma issue rate per .kind on this GPU (no epilogue, no TMA).
+// One CTA per SM; one thread issues back-to-back M=128 N=256 K=32-byte MMAs on (uninitialised) smem operands
+// into two TMEM accumulators.  Prints TOP/s per kind: the honest tensor-pipe roofline for each data type.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/mma_peak tools/mma_peak.cu && tools/mma_peak
+#include <cstdio>
+#include <cuda_runtime.h>
+#include "../3dreconstruction_b200/csrc/sm100.cuh"
+
+#define MMA_KIND(NAME, KINDSTR)                                                                          \
+    __device__ __forceinline__ void NAME(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { \
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"                                   \
+                     "tcgen05.mma.cta_group::1.kind::" KINDSTR " [%0], %1, %2, %3, p;\n\t}" ::"r"(d),    \
+                     "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");                                   \
+    }
+MMA_KIND(mma_k_i8, "i8")
+MMA_KIND(mma_k_f16, "f16")
+MMA_KIND(mma_k_tf32, "tf32")
+MMA_KIND(mma_k_f8, "f8f6f4")
+
+template <int KIND>
+__global__ void __launch_bounds__(128, 1) peak_kernel(int iters, uint32_t idesc, long long* cycles) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tptr;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x3c003c00u;  // benign values
+    if (threadIdx.x == 0) { sm100::mbar_init(&bar, 1); sm100::fence_barrier_init(); }
+    if (warp == 0) sm100::tmem_alloc<512>(&tptr);
+    sm100::fence_proxy_async();
+    sm100::tc_fence_before(); __syncthreads(); sm100::tc_fence_after();
+    uint32_t tbase = tptr;
+    if (threadIdx.x == 32) {
+        uint64_t ad = sm100::make_smem_desc_sw128(sm100::smem_u32(smem));
+        uint64_t bd = sm100::make_smem_desc_sw128(sm100::smem_u32(smem + 16384));
+        long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                uint32_t d = tbase + ((it & 1) ? 256 : 0);
+                if (KIND == 0) mma_k_i8(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+                if (KIND == 1) mma_k_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+                if (KIND == 2) mma_k_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+                if (KIND == 3) mma_k_f8(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+            }
+        }
+        sm100::mma_commit(&bar);
+        sm100::mbar_wait(&bar, 0);
+        long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    }
+    sm100::tc_fence_before(); __syncthreads();
+    if (warp == 0) sm100::tmem_dealloc<512>(tbase);
+}
+
+template <int KIND>
+void run(const char* name, uint32_t idesc, int k_elems_per_mma, int sms) {
+    long long* dcyc; cudaMalloc(&dcyc, 8);
+    cudaFuncSetAttribute(peak_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const int iters = 20000;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    peak_kernel<KIND><<<sms, 128, 64 * 1024>>>(200, idesc, dcyc);
+    cudaEventRecord(e0);
+    peak_kernel<KIND><<<sms, 128, 64 * 1024>>>(iters, idesc, dcyc);
+    cudaEventRecord(e1);
+    cudaError_t err = cudaDeviceSynchronize();
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    long long cyc = 0; cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+    double macs = (double)sms * iters * 4.0 * 128 * 256 * k_elems_per_mma;
+    printf("%-8s %s: %.3f ms, %.1f TOP/s, %.1f cycles per MMA (M128 N256 K=%d), %.0f MAC/clk/SM\n", name,
+           cudaGetErrorString(err), ms, 2 * macs / (ms * 1e-3) / 1e12, (double)cyc / (iters * 4.0), k_elems_per_mma,
+           128.0 * 256 * k_elems_per_mma / ((double)cyc / (iters * 4.0)));
+    cudaFree(dcyc);
+}
+
+int main() {
+    int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    printf("SMs: %d\n", sms);
+    run<0>("i8", sm100::make_idesc(2, 1, 1, 128, 256), 32, sms);
+    run<1>("f16", sm100::make_idesc(1, 0, 0, 128, 256), 16, sms);
+    run<1>("bf16", sm100::make_idesc(1, 1, 1, 128, 256), 16, sms);
+    run<2>("tf32", sm100::make_idesc(1, 2, 2, 128, 256), 8, sms);
+    run<3>("e4m3", sm100::make_idesc(1, 0, 0, 128, 256), 32, sms);
+    return 0;
+}

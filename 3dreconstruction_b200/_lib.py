@@ -19,7 +19,7 @@ KIND_HAMMING, KIND_L2_I8, KIND_L2_F32 = 0, 1, 2
 EXPORTS = ["b200m_version", "b200m_error_string", "b200m_last_cuda_error", "b200m_device_info",
            "b200m_prep_l2_i8", "b200m_prep_l2_f32", "b200m_workspace_bytes", "b200m_match_pairs",
            "b200m_knn2_pairs", "b200m_launch_count", "b200m_reset_launch_count", "b200m_match_pairs_csr",
-           "b200m_timing_enable", "b200m_timing_collect"]
+           "b200m_timing_enable", "b200m_timing_collect", "b200m_f32_stats"]
 
 
 class Pair(ctypes.Structure):
@@ -62,6 +62,7 @@ def load() -> ctypes.CDLL:
                                           vp, vp, vp, vp, vp, vp, ctypes.c_size_t, vp]
     lib.b200m_timing_enable.argtypes = [i32]
     lib.b200m_timing_collect.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i32)]
+    lib.b200m_f32_stats.argtypes = [ctypes.POINTER(i64), ctypes.POINTER(i64), i32]
     lib.b200m_launch_count.restype = i64
     lib.b200m_reset_launch_count.restype = None
     _lib = lib

@@ -51,8 +51,8 @@ static int device_sm_count() {
 }
 
 // Lay the workspace out.  base may be null (size query).
-static void make_plan(MatchPlan& pl, char* base, int mode, int num_pairs, long long total_n, long long total_m,
-                      long long total_pad, int S, bool need_bwd) {
+static void make_plan(MatchPlan& pl, char* base, int kind, int mode, int num_pairs, long long total_n,
+                      long long total_m, long long total_pad, int S, bool need_bwd) {
     size_t off = 0;
     pl.S = S; pl.total_n = total_n; pl.total_m = total_m; pl.total_pad = total_pad;
     pl.pairs = (DevPair*)(base + off); off = align_up(off + sizeof(DevPair) * (size_t)num_pairs, 256);
@@ -60,6 +60,12 @@ static void make_plan(MatchPlan& pl, char* base, int mode, int num_pairs, long l
     pl.bwd = (Top2*)(base + off);      off = align_up(off + (need_bwd ? sizeof(Top2) * (size_t)S * total_m : 0), 256);
     pl.sortbuf = (u64*)(base + off);   off = align_up(off + sizeof(u64) * (size_t)total_pad, 256);
     pl.tbest = (int32_t*)(base + off); off = align_up(off + sizeof(int32_t) * (size_t)total_n, 256);
+    pl.cand = nullptr; pl.pmax = nullptr;
+    if (kind == B200M_KIND_L2_F32) {
+        long long rows = need_bwd && total_m > total_n ? total_m : total_n;
+        pl.cand = (void*)(base + off);  off = align_up(off + 8ull * B200M_F32_CAND * (size_t)S * rows, 256);
+        pl.pmax = (float*)(base + off); off = align_up(off + sizeof(float) * (size_t)num_pairs, 256);
+    }
     pl.bytes = off;
     (void)mode;
 }
@@ -116,18 +122,27 @@ int b200m_timing_collect(double* knn_ms, int* knn_launches) {
     return B200M_OK;
 }
 
+int b200m_f32_stats(int64_t* fallback_rows, int64_t* fallback_evals, int reset) {
+    unsigned long long v[2] = {0, 0};
+    int rc = b200m_f32_stats_read(v, reset != 0);
+    if (rc != B200M_OK) return rc;
+    if (fallback_rows) *fallback_rows = (int64_t)v[0];
+    if (fallback_evals) *fallback_evals = (int64_t)v[1];
+    return B200M_OK;
+}
+
 int64_t b200m_launch_count(void) { return g_launches.load(); }
 void b200m_reset_launch_count(void) { g_launches.store(0); }
 
 int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t total_n, int64_t total_m,
                           int max_n, int max_m, int D, size_t* bytes) {
-    (void)kind; (void)D;
+    (void)D;
     if (!bytes || num_pairs < 0 || total_n < 0 || total_m < 0) return B200M_EINVAL;
-    // Upper bounds that do not depend on the device: S <= 8, sum pow2ceil(n) <= 2 * total_n + P.
+    // Upper bounds that do not depend on the device: choose_splits is monotone in the SM count (<= 256
+    // assumed), sum pow2ceil(n) <= 2 * total_n + P.
     MatchPlan pl;
-    make_plan(pl, nullptr, mode, num_pairs, total_n, total_m, 2 * total_n + num_pairs, 8,
-              mode == B200M_MODE_CROSS);
-    (void)max_n; (void)max_m;
+    make_plan(pl, nullptr, kind, mode, num_pairs, total_n, total_m, 2 * total_n + num_pairs,
+              choose_splits(num_pairs, max_n, max_m, mode, 256), mode == B200M_MODE_CROSS);
     *bytes = pl.bytes;
     return B200M_OK;
 }
@@ -137,8 +152,8 @@ int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t total_n, in
 // Shared front half of match_pairs / knn2_pairs: validate, plan, upload pair table, run knn stage.
 static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64_t q_rows, const void* t_desc,
                          const void* t_norm, int64_t t_rows, int D, const b200m_pair* pairs_host,
-                         int num_pairs, int mode, void* workspace, size_t workspace_bytes, cudaStream_t st,
-                         MatchPlan& pl, int& max_n, int& max_npad) {
+                         int num_pairs, int mode, bool need2, void* workspace, size_t workspace_bytes,
+                         cudaStream_t st, MatchPlan& pl, int& max_n, int& max_npad) {
     if (num_pairs < 0 || D <= 0 || (num_pairs > 0 && (!pairs_host || !q_desc || !t_desc || !workspace)))
         return B200M_EINVAL;
     if (kind != B200M_KIND_HAMMING && kind != B200M_KIND_L2_I8 && kind != B200M_KIND_L2_F32) return B200M_EINVAL;
@@ -165,7 +180,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
     }
     const bool need_bwd = mode == B200M_MODE_CROSS;
     int S = choose_splits(num_pairs, max_n, max_m, mode, sm);
-    make_plan(pl, (char*)workspace, mode, num_pairs, total_n, total_m, total_pad, S, need_bwd);
+    make_plan(pl, (char*)workspace, kind, mode, num_pairs, total_n, total_m, total_pad, S, need_bwd);
     if (pl.bytes > workspace_bytes) return B200M_EWORKSPACE;
     if (num_pairs == 0 || total_n == 0) return B200M_OK;
     B200M_CUDA_CHECK(cudaMemcpyAsync(pl.pairs, dp.data(), sizeof(DevPair) * (size_t)num_pairs,
@@ -198,7 +213,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         else
             rc = launch_l2_f32_top2((const float*)q_desc, (const float*)q_norm, q_rows, (const float*)t_desc,
                                     (const float*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
-                                    back, out, rows, st);
+                                    back, need2, pl.cand, pl.pmax, out, rows, st);
         if (e1) cudaEventRecord(e1, st);
         if (rc != B200M_OK) return rc;
     }
@@ -217,7 +232,7 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
     cudaStream_t st = (cudaStream_t)stream;
     MatchPlan pl; int max_n = 0, max_npad = 1;
     int rc = run_knn_stage(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs,
-                           mode, workspace, workspace_bytes, st, pl, max_n, max_npad);
+                           mode, mode == B200M_MODE_RATIO, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
     if (num_pairs == 0) {
         if (out_ptr) B200M_CUDA_CHECK(cudaMemsetAsync(out_ptr, 0, sizeof(int64_t), st), "ptr memset");
@@ -271,7 +286,7 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
     cudaStream_t st = (cudaStream_t)stream;
     MatchPlan pl; int max_n = 0, max_npad = 1;
     int rc = run_knn_stage(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs,
-                           B200M_MODE_NN, workspace, workspace_bytes, st, pl, max_n, max_npad);
+                           B200M_MODE_NN, true, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
     if (num_pairs == 0 || pl.total_n == 0) return B200M_OK;
     if (kind == B200M_KIND_L2_I8) {

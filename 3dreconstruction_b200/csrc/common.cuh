@@ -13,6 +13,7 @@ typedef unsigned int u32;
 //        L2_F32  -> IEEE bits of the (non-negative) fp32 squared distance.
 struct Top2 { u64 k1, k2; };
 #define B200M_SENTINEL 0xFFFFFFFFFFFFFFFFull
+#define B200M_F32_CAND 8     // TF32 candidates kept per query row and column split (l2_f32.cu)
 
 // Device-side pair record (host b200m_pair + offsets into the per-row workspaces).
 struct DevPair {
@@ -31,6 +32,8 @@ struct MatchPlan {       // host-side carve-up of the caller's workspace
     Top2* bwd;           // [S][total_m]   (MODE_CROSS)
     u64* sortbuf;        // [sum npad]
     int32_t* tbest;      // [total_n]
+    void* cand;          // L2_F32: [S][max(total_n, total_m)][B200M_F32_CAND] (estimate, column)
+    float* pmax;         // L2_F32: [P] max train-row norm of the direction being processed
     int S;               // column splits per direction
     long long total_n, total_m, total_pad;
     size_t bytes;
@@ -66,7 +69,8 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
 int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
                        const float* t_desc, const float* t_norm, int64_t t_rows, int D,
                        const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
-                       Top2* out, long long total_rows, cudaStream_t st);
+                       bool need2, void* cand_ws, float* pmax, Top2* out, long long total_rows, cudaStream_t st);
+int b200m_f32_stats_read(unsigned long long out[2], bool reset);
 int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_pairs, int max_n, const int8_t* q_desc,
                      const int32_t* q_norm, const int8_t* t_desc, const int32_t* t_norm, int D, cudaStream_t st);
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,

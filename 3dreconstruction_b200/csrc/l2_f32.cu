@@ -1,6 +1,456 @@
-// l2_f32.cu — placeholder until the TF32 candidate + fp32 re-rank kernel lands.
+// l2_f32.cu — L2 knn (k=2) for non-integer float32 descriptors (SuperPoint 256-d, DISK/ALIKED 128-d;
+// /root/reference/FeatureMatchingExtraction/deep_learning_detectors.py:124,202,282) replacing
+// cv2.BFMatcher(NORM_L2).knnMatch(k=2)/match as called at feature_matchers.py:210,227.
+//
+// Two stages:
+//   1. l2_f32_cand_kernel — TF32 CANDIDATES on the tensor cores.  Same persistent, warp-specialised
+//      pipeline as l2_i8.cu (TMA SWIZZLE_128B -> tcgen05.mma kind::tf32 M128 x N128 x K8, fp32
+//      accumulators double-buffered in TMEM) with an epilogue that keeps, per query row, the
+//      KC = 8 smallest estimates e_j = ||b_j||^2 - 2 a.b_j  (+ column) in registers.
+//   2. refine_f32_kernel — exact fp32 RE-RANK.  The TF32 estimate of d^2 is off by at most
+//      eps = C_EPS * ||a|| * max_j ||b_j||  (operands truncated to 10 mantissa bits: relative 2^-10
+//      each, |sum a_k b_k| <= ||a|| ||b||, d^2 carries 2x the dot error; C_EPS = 0.0042 > 2^-8 covers
+//      the fp32 accumulation and norm rounding as well).  The true top-2 therefore lie among the
+//      columns with e <= e_min2 + 2 eps; the kept list provably contains all of them when its
+//      worst entry is above that bound (every dropped column has a larger estimate).  Those few
+//      candidates get the direct fp32 sum (a-b)^2 — what cv2 computes — and rows whose list is not
+//      provably sufficient are re-scanned exhaustively in fp32 (rare; counted).
+// Result: Top2 keys (IEEE bits of the exact fp32 d^2 << 32 | column), ties -> lowest column.
+#include <math_constants.h>
 #include "common.cuh"
-int launch_l2_f32_top2(const float*, const float*, int64_t, const float*, const float*, int64_t, int,
-                       const DevPair*, int, int, int, int, bool, Top2*, long long, cudaStream_t) {
-    return B200M_EUNSUPPORTED;
+#include "sm100.cuh"
+
+namespace {
+
+constexpr int TM = 128;            // query rows per tile  (UMMA M)
+constexpr int TN = 128;            // train columns per tile (UMMA N)
+constexpr int KB_BYTES = 128;      // one swizzle-128B K block = 32 floats
+constexpr int A_KB_BYTES = TM * KB_BYTES;   // 16 KiB
+constexpr int B_KB_BYTES = TN * KB_BYTES;   // 16 KiB
+constexpr int MAX_NKB = 8;         // D <= 256 floats: the whole query tile stays resident (128 KiB)
+constexpr int NB = 5;              // train K-block ring
+constexpr int EPI_THREADS = 256;
+constexpr int THREADS = EPI_THREADS + 64;
+constexpr int KC = B200M_F32_CAND; // candidates kept per row
+constexpr float C_EPS = 0.0042f;
+
+struct Item {
+    int q_off, n, t_off, m, r0, c_begin, c_end, split;
+    long long row_base;
+    bool valid;
+};
+
+__device__ __forceinline__ Item decode_item(long long item, const DevPair* __restrict__ pairs, int tiles_max, int S,
+                                            int backward) {
+    Item it;
+    int tile = (int)(item % tiles_max); item /= tiles_max;
+    it.split = (int)(item % S);
+    int p = (int)(item / S);
+    DevPair pr = pairs[p];
+    if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
+    else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
+    it.r0 = tile * TM;
+    int cols_per = ((it.m + S - 1) / S + TN - 1) / TN * TN;
+    it.c_begin = it.split * cols_per;
+    it.c_end = min(it.m, it.c_begin + cols_per);
+    it.valid = it.r0 < it.n;
+    return it;
+}
+
+struct SmemLayout {
+    uint8_t* a;        // [nabuf][nkb][16 KiB]
+    uint8_t* b;        // [NB][16 KiB]
+    float* cb;         // [2][TN]   ||b||^2 of the tile's columns (+inf when masked)
+    float2* exch;      // [TM][KC]  column-half exchange
+    uint64_t* a_full; uint64_t* a_empty;   // [2]
+    uint64_t* b_full; uint64_t* b_empty;   // [NB]
+    uint64_t* acc_full; uint64_t* acc_empty;   // [2]
+    uint32_t* tmem_ptr;
+};
+
+__host__ __device__ constexpr int nabuf_of(int nkb) { return nkb <= MAX_NKB / 2 ? 2 : 1; }
+
+__device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
+    SmemLayout s;
+    s.a = base;
+    s.b = s.a + nabuf_of(nkb) * nkb * A_KB_BYTES;
+    uint8_t* p = s.b + NB * B_KB_BYTES;
+    s.cb = (float*)p; p += 2 * TN * sizeof(float);
+    s.exch = (float2*)p; p += TM * KC * sizeof(float2);
+    s.a_full = (uint64_t*)p; p += 2 * 8;
+    s.a_empty = (uint64_t*)p; p += 2 * 8;
+    s.b_full = (uint64_t*)p; p += NB * 8;
+    s.b_empty = (uint64_t*)p; p += NB * 8;
+    s.acc_full = (uint64_t*)p; p += 2 * 8;
+    s.acc_empty = (uint64_t*)p; p += 2 * 8;
+    s.tmem_ptr = (uint32_t*)p;
+    return s;
+}
+
+__host__ __device__ constexpr size_t smem_bytes(int nkb) {
+    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NB * B_KB_BYTES + 2 * TN * sizeof(float) +
+           TM * KC * sizeof(float2) + (8 + 2 * NB) * 8 + 16;
+}
+
+// Sorted (ascending) list of the KC smallest (estimate, column); strict '<' keeps the earlier column on ties.
+struct CandList {
+    float v[KC];
+    int c[KC];
+    __device__ __forceinline__ void init() {
+#pragma unroll
+        for (int k = 0; k < KC; ++k) { v[k] = CUDART_INF_F; c[k] = -1; }
+    }
+    __device__ __forceinline__ void insert(float x, int col) {   // caller checked x < v[KC-1]
+        v[KC - 1] = x; c[KC - 1] = col;
+#pragma unroll
+        for (int k = KC - 1; k > 0; --k) {
+            bool sw = v[k] < v[k - 1];
+            float tv = v[k - 1]; int tc = c[k - 1];
+            v[k - 1] = sw ? v[k] : tv; c[k - 1] = sw ? c[k] : tc;
+            v[k] = sw ? tv : v[k];     c[k] = sw ? tc : c[k];
+        }
+    }
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
+                   const float* __restrict__ t_norm, const DevPair* __restrict__ pairs, long long total_items,
+                   int tiles_max, int S, int backward, int nkb, float2* __restrict__ cand, long long total_rows) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const SmemLayout sm = carve(smem, nkb);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nabuf = nabuf_of(nkb);
+
+    if (warp == 8 && lane == 0) {
+        sm100::tma_prefetch_desc(&tmap_q);
+        sm100::tma_prefetch_desc(&tmap_t);
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
+        for (int i = 0; i < NB; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_THREADS / 32); }
+        sm100::fence_barrier_init();
+    }
+    if (warp == 9) sm100::tmem_alloc<256>(sm.tmem_ptr);
+    sm100::tc_fence_before();
+    __syncthreads();
+    sm100::tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr;
+
+    if (warp == 8) {
+        // ===================== TMA producer (one thread) =====================
+        if (lane == 0) {
+            uint32_t a_cnt = 0, b_cnt = 0;
+            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+                Item it = decode_item(item, pairs, tiles_max, S, backward);
+                if (!it.valid) continue;
+                const uint32_t ab = a_cnt % nabuf;
+                sm100::mbar_wait_suspend(&sm.a_empty[ab], ((a_cnt / nabuf) & 1) ^ 1);
+                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
+                for (int kb = 0; kb < nkb; ++kb)
+                    sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                       kb * (KB_BYTES / 4), it.q_off + it.r0);
+                ++a_cnt;
+                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        const uint32_t s = b_cnt % NB;
+                        sm100::mbar_wait_suspend(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[s], (uint32_t)B_KB_BYTES);
+                        sm100::tma_load_2d(sm.b + (size_t)s * B_KB_BYTES, &tmap_t, &sm.b_full[s], kb * (KB_BYTES / 4),
+                                           it.t_off + c0);
+                        ++b_cnt;
+                    }
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer (one thread) =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
+            uint32_t a_cnt = 0, b_cnt = 0, acc_cnt = 0;
+            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+                Item it = decode_item(item, pairs, tiles_max, S, backward);
+                if (!it.valid) continue;
+                const uint32_t ab = a_cnt % nabuf;
+                sm100::mbar_wait_suspend(&sm.a_full[ab], (a_cnt / nabuf) & 1);
+                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                    const uint32_t as = acc_cnt & 1;
+                    sm100::mbar_wait_suspend(&sm.acc_empty[as], ((acc_cnt >> 1) & 1) ^ 1);
+                    sm100::tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + as * TN;
+                    for (int kb = 0; kb < nkb; ++kb) {
+                        const uint32_t s = b_cnt % NB;
+                        sm100::mbar_wait_suspend(&sm.b_full[s], (b_cnt / NB) & 1);
+                        sm100::tc_fence_after();
+                        const uint64_t adesc = sm100::make_smem_desc_sw128(
+                            sm100::smem_u32(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES));
+                        const uint64_t bdesc = sm100::make_smem_desc_sw128(sm100::smem_u32(sm.b + (size_t)s * B_KB_BYTES));
+#pragma unroll
+                        for (int k = 0; k < KB_BYTES / 32; ++k)      // UMMA K = 8 tf32 = 32 bytes; +2 = 32 B >> 4
+                            sm100::mma_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                        sm100::mma_commit(&sm.b_empty[s]);
+                        ++b_cnt;
+                    }
+                    sm100::mma_commit(&sm.acc_full[as]);
+                    ++acc_cnt;
+                }
+                sm100::mma_commit(&sm.a_empty[ab]);
+                ++a_cnt;
+            }
+        }
+    } else {
+        // ===================== epilogue: 8 warps, TMEM lane quarter = warp % 4, column half = warp / 4 =====================
+        const int e = threadIdx.x;                 // 0..255
+        const int quarter = warp & 3, half = warp >> 2;
+        const int row_in_tile = quarter * 32 + lane;
+        constexpr int HC = TN / 2;                 // columns per half
+        uint32_t acc_cnt = 0;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            CandList L;
+            L.init();
+            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                const uint32_t as = acc_cnt & 1;
+                if (e < TN) {
+                    int col = c0 + e;
+                    sm.cb[as * TN + e] = col < it.c_end ? __ldg(t_norm + it.t_off + col) : CUDART_INF_F;
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
+                sm100::tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * TN + half * HC;
+                const float* cbv = sm.cb + as * TN + half * HC;
+                uint32_t acc[2][32];
+                sm100::tmem_ld32(taddr, acc[0]);
+                sm100::tmem_ld32(taddr + 32, acc[1]);
+                sm100::tmem_ld_wait();
+                sm100::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);    // whole half-tile is in registers
+#pragma unroll
+                for (int ch = 0; ch < 2; ++ch) {
+                    float ev[32];
+                    float cm = CUDART_INF_F;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        ev[i] = fmaf(-2.0f, __uint_as_float(acc[ch][i]), cbv[ch * 32 + i]);
+                        cm = fminf(cm, ev[i]);
+                    }
+                    if (cm < L.v[KC - 1]) {
+                        const int colb = c0 + half * HC + ch * 32;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (ev[i] < L.v[KC - 1]) L.insert(ev[i], colb + i);
+                    }
+                }
+                ++acc_cnt;
+            }
+            // merge the two column halves of each row (warp w and w+4), then publish KC candidates
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (half == 1) {
+#pragma unroll
+                for (int k = 0; k < KC; ++k) sm.exch[row_in_tile * KC + k] = make_float2(L.v[k], __int_as_float(L.c[k]));
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (half == 0) {
+                int row = it.r0 + row_in_tile;
+                if (row < it.n) {
+#pragma unroll
+                    for (int k = 0; k < KC; ++k) {
+                        float2 o = sm.exch[row_in_tile * KC + k];
+                        // ties between estimates need no care here: the re-rank orders by (exact d^2, column)
+                        if (o.x < L.v[KC - 1]) L.insert(o.x, __float_as_int(o.y));
+                    }
+                    float2* dst = cand + ((long long)it.split * total_rows + it.row_base + row) * KC;
+#pragma unroll
+                    for (int k = 0; k < KC; k += 2) {
+                        float4 w = make_float4(L.v[k], __int_as_float(L.c[k]), L.v[k + 1], __int_as_float(L.c[k + 1]));
+                        *reinterpret_cast<float4*>(dst + k) = w;
+                    }
+                }
+            }
+        }
+    }
+
+    sm100::tc_fence_before();
+    __syncthreads();
+    if (warp == 9) sm100::tmem_dealloc<256>(tmem_base);
+}
+
+// max ||b|| over the train rows of each pair (for the TF32 error window)
+__global__ void __launch_bounds__(256)
+pair_max_norm_kernel(const DevPair* __restrict__ pairs, const float* __restrict__ t_norm, int backward,
+                     float* __restrict__ pmax) {
+    __shared__ float red[8];
+    DevPair pr = pairs[blockIdx.x];
+    const int t_off = backward ? pr.q_off : pr.t_off, m = backward ? pr.n : pr.m;
+    float mx = 0.0f;
+    for (int j = threadIdx.x; j < m; j += blockDim.x) mx = fmaxf(mx, __ldg(t_norm + t_off + j));
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) mx = fmaxf(mx, red[w]);
+        pmax[blockIdx.x] = sqrtf(mx);
+    }
+}
+
+__device__ unsigned long long g_f32_stats[2];   // [0] rows re-scanned exhaustively (list not provably sufficient), [1] their evaluations
+
+// One warp per query row: exact fp32 re-rank of the TF32 candidates (see the file header).
+__global__ void __launch_bounds__(256)
+refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, int blocks_per_pair,
+                  const float2* __restrict__ cand, long long total_rows, int S, const float* __restrict__ q_desc,
+                  const float* __restrict__ q_norm, const float* __restrict__ t_desc, int D,
+                  const float* __restrict__ pmax, Top2* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int p = blockIdx.x / blocks_per_pair;
+    const int i = (blockIdx.x - p * blocks_per_pair) * 8 + (threadIdx.x >> 5);
+    DevPair pr = pairs[p];
+    int q_off = pr.q_off, n = pr.n, t_off = pr.t_off, m = pr.m;
+    long long row_base = pr.fwd_off;
+    if (backward) { q_off = pr.t_off; n = pr.m; t_off = pr.q_off; m = pr.n; row_base = pr.bwd_off; }
+    if (i >= n) return;
+    const long long row = row_base + i;
+    const int nf4 = D >> 2;                                  // D is a multiple of 32 floats, <= 256
+    const float4* a4 = reinterpret_cast<const float4*>(q_desc + (long long)(q_off + i) * D);
+    float4 ar[2];
+    ar[0] = lane < nf4 ? __ldg(a4 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    ar[1] = lane + 32 < nf4 ? __ldg(a4 + lane + 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+    auto exact = [&](int col) -> float {                     // direct sum (a-b)^2 in fp32, as cv2 does
+        const float4* b4 = reinterpret_cast<const float4*>(t_desc + (long long)(t_off + col) * D);
+        float s = 0.0f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (lane + 32 * h < nf4) {
+                float4 b = __ldg(b4 + lane + 32 * h);
+                float dx = ar[h].x - b.x, dy = ar[h].y - b.y, dz = ar[h].z - b.z, dw = ar[h].w - b.w;
+                s = fmaf(dx, dx, s); s = fmaf(dy, dy, s); s = fmaf(dz, dz, s); s = fmaf(dw, dw, s);
+            }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        return s;
+    };
+    // gather the S * KC candidates (<= 64): two per lane
+    const int nent = S * KC;
+    float e[2]; int c[2];
+    float wmin = CUDART_INF_F;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        int idx = lane + 32 * h;
+        e[h] = CUDART_INF_F; c[h] = -1;
+        if (idx < nent) {
+            int s = idx / KC, k = idx - s * KC;
+            float2 v = cand[((long long)s * total_rows + row) * KC + k];
+            e[h] = v.x; c[h] = __float_as_int(v.y);
+            if (c[h] < 0) e[h] = CUDART_INF_F;
+            if (k == KC - 1) wmin = e[h];
+        }
+    }
+    float m1 = fminf(e[0], e[1]), m2 = fmaxf(e[0], e[1]);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        float o1 = __shfl_xor_sync(0xffffffffu, m1, off), o2 = __shfl_xor_sync(0xffffffffu, m2, off);
+        float hi = fmaxf(m1, o1);
+        m1 = fminf(m1, o1);
+        m2 = fminf(fminf(m2, o2), hi);
+        wmin = fminf(wmin, __shfl_xor_sync(0xffffffffu, wmin, off));
+    }
+    u64 k1 = B200M_SENTINEL, k2 = B200M_SENTINEL;
+    unsigned evals = 0;
+    bool fallback = false;
+    if (m1 < CUDART_INF_F) {
+        const float win = 2.0f * C_EPS * sqrtf(__ldg(q_norm + q_off + i)) * __ldg(pmax + p);
+        const float bound = (need2 ? m2 : m1) + win;
+        fallback = !(wmin > bound) && wmin < CUDART_INF_F;   // some list may have dropped a relevant column
+        if (!fallback) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                unsigned mask = __ballot_sync(0xffffffffu, c[h] >= 0 && e[h] <= bound);
+                while (mask) {
+                    int src = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    int col = __shfl_sync(0xffffffffu, c[h], src);
+                    float d2 = exact(col);
+                    top2_insert(k1, k2, ((u64)__float_as_uint(d2) << 32) | (u64)(u32)col);
+                    ++evals;
+                }
+            }
+        } else {
+            for (int col = 0; col < m; ++col) {
+                float d2 = exact(col);
+                top2_insert(k1, k2, ((u64)__float_as_uint(d2) << 32) | (u64)(u32)col);
+            }
+            evals = (unsigned)m;
+        }
+    }
+    if (lane == 0) {
+        Top2 t; t.k1 = k1; t.k2 = k2;
+        out[row] = t;
+        Top2 none; none.k1 = B200M_SENTINEL; none.k2 = B200M_SENTINEL;
+        for (int s = 1; s < S; ++s) out[(long long)s * total_rows + row] = none;
+        if (fallback) { atomicAdd(&g_f32_stats[0], 1ull); atomicAdd(&g_f32_stats[1], (unsigned long long)evals); }
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host side
+int b200m_f32_stats_read(unsigned long long out[2], bool reset) {
+    B200M_CUDA_CHECK(cudaMemcpyFromSymbol(out, g_f32_stats, sizeof(unsigned long long) * 2), "f32 stats read");
+    if (reset) {
+        unsigned long long z[2] = {0, 0};
+        B200M_CUDA_CHECK(cudaMemcpyToSymbol(g_f32_stats, z, sizeof(z)), "f32 stats reset");
+    }
+    return B200M_OK;
+}
+
+int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows, const float* t_desc,
+                       const float* t_norm, int64_t t_rows, int D, const DevPair* pairs, int num_pairs, int max_n,
+                       int max_m, int S, bool backward, bool need2, void* cand_ws, float* pmax, Top2* out,
+                       long long total_rows, cudaStream_t st) {
+    if (D % (KB_BYTES / 4) != 0) return B200M_EINVAL;
+    const int nkb = D / (KB_BYTES / 4);
+    if (nkb > MAX_NKB) return B200M_EUNSUPPORTED;       // query tile must stay resident in shared memory
+    if (!cand_ws || !pmax) return B200M_EINVAL;
+    if (backward) {
+        const float* d = q_desc; q_desc = t_desc; t_desc = d;
+        const float* nn = q_norm; q_norm = t_norm; t_norm = nn;
+        int64_t r = q_rows; q_rows = t_rows; t_rows = r;
+        int mx = max_n; max_n = max_m; max_m = mx;
+    }
+    CUtensorMap tq, tt;
+    int rc = b200m_make_tmap_2d(&tq, q_desc, (uint64_t)q_rows, (uint64_t)D * 4, TM, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
+    if (rc != B200M_OK) return rc;
+    rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D * 4, TN, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
+    if (rc != B200M_OK) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
+        attr_set = true;
+    }
+    int tiles_max = (max_n + TM - 1) / TM;
+    long long total_items = (long long)num_pairs * S * tiles_max;
+    if (total_items <= 0) return B200M_OK;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
+    float2* cand = (float2*)cand_ws;
+    l2_f32_cand_kernel<<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S,
+                                                              backward ? 1 : 0, nkb, cand, total_rows);
+    B200M_CUDA_CHECK(cudaGetLastError(), "l2_f32_cand_kernel launch");
+    pair_max_norm_kernel<<<num_pairs, 256, 0, st>>>(pairs, t_norm, backward ? 1 : 0, pmax);
+    B200M_CUDA_CHECK(cudaGetLastError(), "pair_max_norm_kernel launch");
+    int bpp = (max_n + 7) / 8;
+    long long rgrid = (long long)num_pairs * bpp;
+    if (rgrid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    refine_f32_kernel<<<(unsigned)rgrid, 256, 0, st>>>(backward ? 1 : 0, need2 ? 1 : 0, pairs, bpp, cand, total_rows, S,
+                                                       q_desc, q_norm, t_desc, D, pmax, out);
+    B200M_CUDA_CHECK(cudaGetLastError(), "refine_f32_kernel launch");
+    b200m_count_launch(3);
+    return B200M_OK;
 }

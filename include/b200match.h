@@ -99,7 +99,7 @@ B200M_API int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t t
  *   q_desc/t_desc  descriptor stores (may be the same pointer for all-pairs over one store):
  *                    HAMMING: uint8 [rows, D]      (D = bytes per descriptor, any D >= 1)
  *                    L2_I8  : int8  [rows, D]      (D multiple of 128, from b200m_prep_l2_i8)
- *                    L2_F32 : float [rows, D]      (D multiple of 32 floats)
+ *                    L2_F32 : float [rows, D]      (D multiple of 32 floats, D <= 256)
  *   q_norm/t_norm  L2_I8: int32 [rows]; L2_F32: float [rows]; HAMMING: NULL
  *   q_rows/t_rows  number of rows in each store (bounds for TMA maps)
  *   pairs_host     HOST array of num_pairs descriptors (copied to the device workspace)
@@ -139,6 +139,11 @@ B200M_API int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm,
  * device time (ms) and the number of knn launches since the last collect/enable. */
 B200M_API int b200m_timing_enable(int on);
 B200M_API int b200m_timing_collect(double* knn_ms, int* knn_launches);
+
+/* L2_F32 kind: number of query rows whose TF32 candidate list was not provably sufficient and were
+ * re-scanned exhaustively in fp32 (and the distance evaluations that cost) since the last reset.
+ * Synchronises the device. */
+B200M_API int b200m_f32_stats(int64_t* fallback_rows, int64_t* fallback_evals, int reset);
 
 /* Counters for bench.py's `gpu_launches`: kernels launched by this library since the last reset. */
 B200M_API int64_t b200m_launch_count(void);

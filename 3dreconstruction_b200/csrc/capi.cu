@@ -20,13 +20,15 @@ int b200m_set_cuda_error(cudaError_t e, const char* where) {
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int pow2ceil(int n) { int p = 1; while (p < n) p <<= 1; return p; }
 
-static int choose_splits(int num_pairs, int max_n, int max_m, int mode, int sm_count) {
+static int choose_splits(int kind, int num_pairs, int max_n, int max_m, int mode, int sm_count) {
     // Enough CTAs for ~2 per SM; a single image pair has only ceil(n/128) row tiles.
     long long tiles = (long long)num_pairs * ((max_n + 127) / 128);
     if (mode == B200M_MODE_CROSS) tiles += (long long)num_pairs * ((max_m + 127) / 128);
     long long want = 2LL * sm_count;
     int S = (int)((want + tiles - 1) / (tiles > 0 ? tiles : 1));
-    int max_split = (((max_n < max_m ? max_n : max_m) + 255) / 256);   // keep >= 256 columns per split
+    // keep >= 256 columns per split (>= 512 for L2_I8: four 128-column tiles, one per epilogue group)
+    const int min_cols = kind == B200M_KIND_L2_I8 ? 512 : 256;
+    int max_split = (((max_n < max_m ? max_n : max_m) + min_cols - 1) / min_cols);
     if (S > max_split) S = max_split;
     if (S > 8) S = 8;
     if (S < 1) S = 1;
@@ -55,9 +57,11 @@ static void make_plan(MatchPlan& pl, char* base, int kind, int mode, int num_pai
                       long long total_m, long long total_pad, int S, bool need_bwd) {
     size_t off = 0;
     pl.S = S; pl.total_n = total_n; pl.total_m = total_m; pl.total_pad = total_pad;
+    pl.slices = kind == B200M_KIND_L2_I8 ? S * B200M_I8_GROUPS : S;
+    const size_t SL = (size_t)pl.slices;
     pl.pairs = (DevPair*)(base + off); off = align_up(off + sizeof(DevPair) * (size_t)num_pairs, 256);
-    pl.fwd = (Top2*)(base + off);      off = align_up(off + sizeof(Top2) * (size_t)S * total_n, 256);
-    pl.bwd = (Top2*)(base + off);      off = align_up(off + (need_bwd ? sizeof(Top2) * (size_t)S * total_m : 0), 256);
+    pl.fwd = (Top2*)(base + off);      off = align_up(off + sizeof(Top2) * SL * total_n, 256);
+    pl.bwd = (Top2*)(base + off);      off = align_up(off + (need_bwd ? sizeof(Top2) * SL * total_m : 0), 256);
     pl.sortbuf = (u64*)(base + off);   off = align_up(off + sizeof(u64) * (size_t)total_pad, 256);
     pl.tbest = (int32_t*)(base + off); off = align_up(off + sizeof(int32_t) * (size_t)total_n, 256);
     pl.cand = nullptr; pl.pmax = nullptr;
@@ -142,7 +146,7 @@ int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t total_n, in
     // assumed), sum pow2ceil(n) <= 2 * total_n + P.
     MatchPlan pl;
     make_plan(pl, nullptr, kind, mode, num_pairs, total_n, total_m, 2 * total_n + num_pairs,
-              choose_splits(num_pairs, max_n, max_m, mode, 256), mode == B200M_MODE_CROSS);
+              choose_splits(kind, num_pairs, max_n, max_m, mode, 256), mode == B200M_MODE_CROSS);
     *bytes = pl.bytes;
     return B200M_OK;
 }
@@ -179,7 +183,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         if (d.npad > max_npad) max_npad = d.npad;
     }
     const bool need_bwd = mode == B200M_MODE_CROSS;
-    int S = choose_splits(num_pairs, max_n, max_m, mode, sm);
+    int S = choose_splits(kind, num_pairs, max_n, max_m, mode, sm);
     make_plan(pl, (char*)workspace, kind, mode, num_pairs, total_n, total_m, total_pad, S, need_bwd);
     if (pl.bytes > workspace_bytes) return B200M_EWORKSPACE;
     if (num_pairs == 0 || total_n == 0) return B200M_OK;
@@ -243,13 +247,12 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         if (out_ptr) B200M_CUDA_CHECK(cudaMemsetAsync(out_ptr, 0, sizeof(int64_t) * ((size_t)num_pairs + 1), st), "ptr memset");
         return B200M_OK;
     }
-    if (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) {
-        rc = launch_refine_i8(false, ratio, pl, num_pairs, max_n, (const int8_t*)q_desc, (const int32_t*)q_norm,
-                              (const int8_t*)t_desc, (const int32_t*)t_norm, D, st);
-        if (rc != B200M_OK) return rc;
-    }
+    // L2_I8: the exact runner-up refinement (inside the winner's 64-column chunk) is fused into finalize.
+    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0};
+    if (kind == B200M_KIND_L2_I8)
+        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D};
     // CSR mode counts survivors in finalize (into out_count), scans them into tight offsets, then emits.
-    rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, out_ptr ? out_count : nullptr, st);
+    rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, out_ptr ? out_count : nullptr, rf, st);
     if (rc != B200M_OK) return rc;
     if (out_ptr) {
         rc = launch_scan_offsets(pl, out_count, num_pairs, (long long*)out_ptr, st);
@@ -289,12 +292,10 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
                            B200M_MODE_NN, true, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
     if (num_pairs == 0 || pl.total_n == 0) return B200M_OK;
-    if (kind == B200M_KIND_L2_I8) {
-        rc = launch_refine_i8(true, 0.0, pl, num_pairs, max_n, (const int8_t*)q_desc, (const int32_t*)q_norm,
-                              (const int8_t*)t_desc, (const int32_t*)t_norm, D, st);
-        if (rc != B200M_OK) return rc;
-    }
-    return launch_knn2_emit(kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, st);
+    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0};
+    if (kind == B200M_KIND_L2_I8)
+        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D};
+    return launch_knn2_emit(kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
 }
 
 }  // extern "C"

@@ -13,6 +13,8 @@ typedef unsigned int u32;
 //        L2_F32  -> IEEE bits of the (non-negative) fp32 squared distance.
 struct Top2 { u64 k1, k2; };
 #define B200M_SENTINEL 0xFFFFFFFFFFFFFFFFull
+#define B200M_I8_GROUPS 4    // independent epilogue groups of the L2_I8 kernel = Top2 slices per column split
+#define B200M_I8_CHUNK 64    // columns per key chunk of the L2_I8 kernel (runner-up refined inside the winner's chunk)
 #define B200M_F32_CAND 8     // TF32 candidates kept per query row and column split (l2_f32.cu)
 
 // Device-side pair record (host b200m_pair + offsets into the per-row workspaces).
@@ -28,13 +30,14 @@ struct DevPair {
 
 struct MatchPlan {       // host-side carve-up of the caller's workspace
     DevPair* pairs;      // [P]
-    Top2* fwd;           // [S][total_n]
-    Top2* bwd;           // [S][total_m]   (MODE_CROSS)
+    Top2* fwd;           // [slices][total_n]
+    Top2* bwd;           // [slices][total_m]   (MODE_CROSS)
     u64* sortbuf;        // [sum npad]
     int32_t* tbest;      // [total_n]
     void* cand;          // L2_F32: [S][max(total_n, total_m)][B200M_F32_CAND] (estimate, column)
     float* pmax;         // L2_F32: [P] max train-row norm of the direction being processed
     int S;               // column splits per direction
+    int slices;          // Top2 slices per row the knn kernel writes (S, or S * B200M_I8_GROUPS for L2_I8)
     long long total_n, total_m, total_pad;
     size_t bytes;
 };
@@ -71,13 +74,15 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
                        const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
                        bool need2, void* cand_ws, float* pmax, Top2* out, long long total_rows, cudaStream_t st);
 int b200m_f32_stats_read(unsigned long long out[2], bool reset);
-int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_pairs, int max_n, const int8_t* q_desc,
-                     const int32_t* q_norm, const int8_t* t_desc, const int32_t* t_norm, int D, cudaStream_t st);
+// L2_I8 descriptors for the fused exact runner-up refinement (null for the other kinds)
+struct RefineI8 {
+    const int8_t* q_desc; const int32_t* q_norm; const int8_t* t_desc; const int32_t* t_norm; int D;
+};
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
-                    int32_t* counts, cudaStream_t st);
+                    int32_t* counts, const RefineI8& rf, cudaStream_t st);
 int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
                         cudaStream_t st);
 int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
                      int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st);
 int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
-                     float* d1, float* d2, cudaStream_t st);
+                     float* d1, float* d2, const RefineI8& rf, cudaStream_t st);

@@ -29,58 +29,45 @@ __device__ __forceinline__ Top2 merge_splits(const Top2* __restrict__ arr, long 
 }
 
 
-// Exact runner-up for the tensor-core L2_I8 kernel (see l2_i8.cu header): k2 so far is the best
-// among all chunks other than the winner's 32-column chunk; recompute the winner's chunk exactly
-// (int8 dp4a, one warp per query row, one lane per column) and fold it in.  In MODE_RATIO a row is
-// refined only if it passes the ratio test with the candidate (the true runner-up is never larger,
-// so a row that fails with the candidate fails anyway).  The merged result is written to split 0.
-__global__ void __launch_bounds__(256)
-refine_i8_kernel(int always, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
-                 Top2* __restrict__ fwd, long long total_n, int S, const int8_t* __restrict__ q_desc,
-                 const int32_t* __restrict__ q_norm, const int8_t* __restrict__ t_desc,
-                 const int32_t* __restrict__ t_norm, int D) {
+// Exact runner-up for the tensor-core L2_I8 kernel (see l2_i8.cu header): k2 so far is the best among
+// all chunks other than the winner's 64-column chunk; recompute the winner's chunk exactly (int8 dp4a,
+// the whole warp works on one query row at a time, one lane per column) and fold it in.  `need` is this
+// lane's row predicate: in MODE_RATIO a row is refined only if it passes the ratio test with the
+// candidate (the true runner-up is never larger, so a row that fails with the candidate fails anyway).
+// Must be called by all 32 lanes of a warp whose rows belong to the same pair.
+__device__ __forceinline__ void refine_i8_warp(bool need, int i, Top2& t, const DevPair& pr, const RefineI8& rf) {
     const int lane = threadIdx.x & 31;
-    int p = blockIdx.x / blocks_per_pair;
-    int i = (blockIdx.x - p * blocks_per_pair) * 8 + (threadIdx.x >> 5);
-    DevPair pr = pairs[p];
-    if (i >= pr.n) return;
-    const long long row = pr.fwd_off + i;
-    Top2 t = merge_splits(fwd, total_n, S, row);
-    if (t.k1 != B200M_SENTINEL) {
-        bool need = always || ratio <= 0.0 || t.k2 == B200M_SENTINEL;
-        if (!need) {
-            float d1 = value_to_distance(B200M_KIND_L2_I8, (u32)(t.k1 >> 32));
-            float d2 = value_to_distance(B200M_KIND_L2_I8, (u32)(t.k2 >> 32));
-            need = (double)d1 < ratio * (double)d2;
-        }
-        if (need) {
-            const int j1 = (int)(u32)t.k1;
-            const int col = (j1 & ~31) + lane;
-            u64 key = B200M_SENTINEL;
+    unsigned mask = __ballot_sync(0xffffffffu, need);
+    while (mask) {
+        const int src = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int ri = __shfl_sync(0xffffffffu, i, src);
+        const int j1 = __shfl_sync(0xffffffffu, (int)(u32)t.k1, src);
+        const int4* a = reinterpret_cast<const int4*>(rf.q_desc + (long long)(pr.q_off + ri) * rf.D);
+        const int nq = __ldg(rf.q_norm + pr.q_off + ri);
+        u64 key = B200M_SENTINEL;
+#pragma unroll
+        for (int h = 0; h < B200M_I8_CHUNK / 32; ++h) {
+            const int col = (j1 & ~(B200M_I8_CHUNK - 1)) + h * 32 + lane;
             if (col < pr.m && col != j1) {
-                const int4* a = reinterpret_cast<const int4*>(q_desc + (long long)(pr.q_off + i) * D);
-                const int4* b = reinterpret_cast<const int4*>(t_desc + (long long)(pr.t_off + col) * D);
+                const int4* b = reinterpret_cast<const int4*>(rf.t_desc + (long long)(pr.t_off + col) * rf.D);
                 int dot = 0;
-                for (int k = 0; k < D / 16; ++k) {
+                for (int k = 0; k < rf.D / 16; ++k) {
                     int4 x = __ldg(a + k), y = __ldg(b + k);
                     dot = __dp4a(x.x, y.x, dot); dot = __dp4a(x.y, y.y, dot);
                     dot = __dp4a(x.z, y.z, dot); dot = __dp4a(x.w, y.w, dot);
                 }
-                int d2i = __ldg(q_norm + pr.q_off + i) + __ldg(t_norm + pr.t_off + col) - 2 * dot;
-                key = ((u64)(u32)d2i << 32) | (u64)(u32)col;
+                int d2i = nq + __ldg(rf.t_norm + pr.t_off + col) - 2 * dot;
+                u64 k = ((u64)(u32)d2i << 32) | (u64)(u32)col;
+                key = k < key ? k : key;
             }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                u64 o = __shfl_xor_sync(0xffffffffu, key, off);
-                key = o < key ? o : key;
-            }
-            if (key < t.k2) t.k2 = key;
         }
-    }
-    if (lane == 0) {
-        fwd[row] = t;
-        Top2 none; none.k1 = B200M_SENTINEL; none.k2 = B200M_SENTINEL;
-        for (int s = 1; s < S; ++s) fwd[(long long)s * total_n + row] = none;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            u64 o = __shfl_xor_sync(0xffffffffu, key, off);
+            key = o < key ? o : key;
+        }
+        if (lane == src && key < t.k2) t.k2 = key;
     }
 }
 
@@ -88,13 +75,25 @@ __global__ void __launch_bounds__(256)
 finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
                 const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
                 long long total_m, int S, u64* __restrict__ sortbuf, int32_t* __restrict__ tbest,
-                int32_t* __restrict__ counts) {
+                int32_t* __restrict__ counts, RefineI8 rf) {
     int p = blockIdx.x / blocks_per_pair;
     int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
     DevPair pr = pairs[p];
     const bool active = i < pr.n;
     Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
     if (active) t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
+    if (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) {      // block-uniform branch
+        bool need = false;
+        if (t.k1 != B200M_SENTINEL) {
+            need = ratio <= 0.0 || t.k2 == B200M_SENTINEL;
+            if (!need) {
+                float c1 = value_to_distance(B200M_KIND_L2_I8, (u32)(t.k1 >> 32));
+                float c2 = value_to_distance(B200M_KIND_L2_I8, (u32)(t.k2 >> 32));
+                need = (double)c1 < ratio * (double)c2;
+            }
+        }
+        refine_i8_warp(need, i, t, pr, rf);
+    }
     u64 key = B200M_SENTINEL;
     int32_t tb = -1;
     if (t.k1 != B200M_SENTINEL) {
@@ -189,16 +188,35 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
     u64* g = sortbuf + pr.sort_off;
     const int n = pr.n, npad = pr.npad;
     if (threadIdx.x == 0) s_count = 0;
-    u64* a = npad <= smem_keys ? skeys : g;
-    int local = 0;
-    for (int t = threadIdx.x; t < npad; t += blockDim.x) {
-        u64 k = t < n ? g[t] : B200M_SENTINEL;
-        local += (k != B200M_SENTINEL);
-        if (a != g || t >= n) a[t] = k;
-    }
     __syncthreads();
-    if (local) atomicAdd(&s_count, local);
-    if (npad > 1) bitonic(a, npad);
+    u64* a;
+    int sort_n;
+    if (npad <= smem_keys) {
+        // compact the survivors into shared memory first (order is irrelevant before the sort): the bitonic
+        // network then runs over pow2ceil(#survivors) keys instead of pow2ceil(n)
+        a = skeys;
+        for (int t = threadIdx.x; t < n; t += blockDim.x) {
+            u64 k = g[t];
+            if (k != B200M_SENTINEL) a[atomicAdd(&s_count, 1)] = k;
+        }
+        __syncthreads();
+        sort_n = 1;
+        while (sort_n < s_count) sort_n <<= 1;
+        for (int t = s_count + threadIdx.x; t < sort_n; t += blockDim.x) a[t] = B200M_SENTINEL;
+        __syncthreads();
+    } else {                                            // oversized pair: sort in place in global memory
+        a = g;
+        sort_n = npad;
+        int local = 0;
+        for (int t = threadIdx.x; t < npad; t += blockDim.x) {
+            u64 k = t < n ? g[t] : B200M_SENTINEL;
+            local += (k != B200M_SENTINEL);
+            if (t >= n) a[t] = k;
+        }
+        if (local) atomicAdd(&s_count, local);
+        __syncthreads();
+    }
+    if (sort_n > 1) bitonic(a, sort_n);
     __syncthreads();
     const int cnt = s_count;
     for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
@@ -214,12 +232,15 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
 __global__ void __launch_bounds__(256)
 knn2_emit_kernel(int kind, const DevPair* __restrict__ pairs, int blocks_per_pair,
                  const Top2* __restrict__ fwd, long long total_n, int S, int32_t* __restrict__ idx1,
-                 int32_t* __restrict__ idx2, float* __restrict__ d1, float* __restrict__ d2) {
+                 int32_t* __restrict__ idx2, float* __restrict__ d1, float* __restrict__ d2, RefineI8 rf) {
     int p = blockIdx.x / blocks_per_pair;
     int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
     DevPair pr = pairs[p];
-    if (i >= pr.n) return;
-    Top2 t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
+    const bool active = i < pr.n;
+    Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
+    if (active) t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
+    if (kind == B200M_KIND_L2_I8) refine_i8_warp(t.k1 != B200M_SENTINEL, i, t, pr, rf);
+    if (!active) return;
     long long o = pr.out_off + i;
     bool h1 = t.k1 != B200M_SENTINEL, h2 = t.k2 != B200M_SENTINEL;
     idx1[o] = h1 ? (int32_t)(u32)t.k1 : -1;
@@ -231,19 +252,6 @@ knn2_emit_kernel(int kind, const DevPair* __restrict__ pairs, int blocks_per_pai
 }  // namespace
 
 
-int launch_refine_i8(bool always, double ratio, const MatchPlan& plan, int num_pairs, int max_n, const int8_t* q_desc,
-                     const int32_t* q_norm, const int8_t* t_desc, const int32_t* t_norm, int D, cudaStream_t st) {
-    int bpp = (max_n + 7) / 8;
-    long long grid = (long long)num_pairs * bpp;
-    if (grid <= 0) return B200M_OK;
-    if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    refine_i8_kernel<<<(unsigned)grid, 256, 0, st>>>(always ? 1 : 0, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
-                                                     plan.S, q_desc, q_norm, t_desc, t_norm, D);
-    b200m_count_launch();
-    B200M_CUDA_CHECK(cudaGetLastError(), "refine_i8_kernel launch");
-    return B200M_OK;
-}
-
 int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
                         cudaStream_t st) {
     scan_offsets_kernel<<<1, 1024, 0, st>>>(plan.pairs, counts, num_pairs, out_ptr);
@@ -253,13 +261,13 @@ int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pa
 }
 
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
-                    int32_t* counts, cudaStream_t st) {
+                    int32_t* counts, const RefineI8& rf, cudaStream_t st) {
     int bpp = (max_n + 255) / 256;
     long long grid = (long long)num_pairs * bpp;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
     finalize_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
-                                                    plan.bwd, plan.total_m, plan.S, plan.sortbuf, plan.tbest, counts);
+                                                    plan.bwd, plan.total_m, plan.slices, plan.sortbuf, plan.tbest, counts, rf);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "finalize_kernel launch");
     return B200M_OK;
@@ -286,13 +294,13 @@ int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npa
 }
 
 int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
-                     float* d1, float* d2, cudaStream_t st) {
+                     float* d1, float* d2, const RefineI8& rf, cudaStream_t st) {
     int bpp = (max_n + 255) / 256;
     long long grid = (long long)num_pairs * bpp;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    knn2_emit_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, plan.pairs, bpp, plan.fwd, plan.total_n, plan.S,
-                                                     idx1, idx2, d1, d2);
+    knn2_emit_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, plan.pairs, bpp, plan.fwd, plan.total_n, plan.slices,
+                                                     idx1, idx2, d1, d2, rf);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "knn2_emit_kernel launch");
     return B200M_OK;

@@ -107,6 +107,13 @@ class Engine:
                     "b200m_prep_l2_f32")
             return DeviceDescriptors(L.KIND_L2_F32, t, nrm, rows, Dpad)
 
+    def f32_stats(self, reset: bool = True):
+        """(rows re-scanned exhaustively, their distance evaluations) of the L2_F32 path since the last reset."""
+        rows, evals = ctypes.c_int64(0), ctypes.c_int64(0)
+        with torch.cuda.device(self.device):
+            L.check(self.lib.b200m_f32_stats(ctypes.byref(rows), ctypes.byref(evals), int(reset)), "b200m_f32_stats")
+        return rows.value, evals.value
+
     # ------------------------------------------------------------------ pair tables
     @staticmethod
     def make_pairs(spec: Sequence[Sequence[int]]):

@@ -73,6 +73,53 @@ void run(const char* name, uint32_t idesc, int k_elems_per_mma, int sms) {
     cudaFree(dcyc);
 }
 
+
+// Variant: tile = 4 MMAs (one 128-byte K block) into stage (it % nstage), then `commits` tcgen05.commit on scratch barriers.
+__global__ void __launch_bounds__(128, 1) tile_kernel(int iters, uint32_t idesc, int ncols, int nstage, int commits, long long* cycles) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar, scratch[2];
+    __shared__ uint32_t tptr;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
+    if (threadIdx.x == 0) { sm100::mbar_init(&bar, 1); sm100::mbar_init(&scratch[0], 1); sm100::mbar_init(&scratch[1], 1); sm100::fence_barrier_init(); }
+    if (warp == 0) sm100::tmem_alloc<512>(&tptr);
+    sm100::fence_proxy_async();
+    sm100::tc_fence_before(); __syncthreads(); sm100::tc_fence_after();
+    uint32_t tbase = tptr;
+    if (threadIdx.x == 32) {
+        uint64_t ad = sm100::make_smem_desc_sw128(sm100::smem_u32(smem));
+        uint64_t bd = sm100::make_smem_desc_sw128(sm100::smem_u32(smem + 16384));
+        long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+            uint32_t d = tbase + (it % nstage) * ncols;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_k_i8(d, ad + 2 * k, bd + 2 * k, idesc, k ? 1 : 0);
+            for (int c = 0; c < commits; ++c) sm100::mma_commit(&scratch[c]);
+        }
+        sm100::mma_commit(&bar);
+        sm100::mbar_wait(&bar, 0);
+        long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    }
+    sm100::tc_fence_before(); __syncthreads();
+    if (warp == 0) sm100::tmem_dealloc<512>(tbase);
+}
+
+void run_tile(int N, int nstage, int commits, int sms) {
+    long long* dcyc; cudaMalloc(&dcyc, 8);
+    cudaFuncSetAttribute(tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const int iters = 20000;
+    uint32_t idesc = sm100::make_idesc(2, 1, 1, 128, N);
+    tile_kernel<<<sms, 128, 64 * 1024>>>(200, idesc, N, nstage, commits, dcyc);
+    tile_kernel<<<sms, 128, 64 * 1024>>>(iters, idesc, N, nstage, commits, dcyc);
+    cudaError_t err = cudaDeviceSynchronize();
+    long long cyc = 0; cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+    printf("i8 tile M128 N%-3d stages %d commits/tile %d: %s, %.1f cycles per tile (floor %d)\n", N, nstage, commits,
+           cudaGetErrorString(err), (double)cyc / iters, N * 2);
+    cudaFree(dcyc);
+}
+
 int main() {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     printf("SMs: %d\n", sms);
@@ -81,5 +128,7 @@ int main() {
     run<1>("bf16", sm100::make_idesc(1, 1, 1, 128, 256), 16, sms);
     run<2>("tf32", sm100::make_idesc(1, 2, 2, 128, 256), 8, sms);
     run<3>("e4m3", sm100::make_idesc(1, 0, 0, 128, 256), 32, sms);
+    run_tile(256, 2, 0, sms); run_tile(256, 2, 2, sms); run_tile(128, 4, 0, sms); run_tile(128, 4, 1, sms); run_tile(128, 4, 2, sms);
+    run_tile(64, 8, 2, sms); run_tile(128, 1, 2, sms);
     return 0;
 }

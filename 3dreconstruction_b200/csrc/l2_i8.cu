@@ -5,46 +5,48 @@
 //   d^2(i,j) = ||a'_i||^2 + ||b'_j||^2 - 2 a'_i . b'_j   with a' = a-128, b' = b-128 (int8),
 // the dot product from tcgen05.mma kind::i8 (int32 accumulators in TMEM), all terms exact integers.
 //
-// Persistent, warp-specialised CTA (one per SM), 576 threads:
-//   warps 0-15  epilogue : four independent GROUPS of four warps (group = warp / 4, TMEM lane quarter =
-//                          warp % 4, so every SM sub-partition hosts one warp of each group).  Group g owns
-//                          TMEM stage g (128 columns) and drains every fourth 128 x 128 accumulator tile:
-//                          tcgen05.ld 32 columns at a time, key = (||b'||^2*64 + c) - 128*acc (one IMAD),
-//                          3-input-min tree per 64-column chunk, running top-2 of chunk minima.  Groups never
-//                          synchronise with each other; while one waits for its accumulator the other three
-//                          keep the issue slots busy.
+// Persistent, warp-specialised CTA (one per SM), 608 threads:
+//   warps 0-15  epilogue : TMEM lane quarter = warp % 4, 64-column slice of the 256-column tile = warp / 4
+//                          (every SM sub-partition hosts four epilogue warps).  Per tile and warp: two
+//                          tcgen05.ld of 32 columns, key = (||b'||^2*64 + c) - 128*acc (one IMAD per element),
+//                          3-input-min tree over the 64-column chunk, running top-2 of chunk minima.  The only
+//                          synchronisation is mbarrier waits (accumulator full, column constants staged).
 //   warp  16    producer : TMA (cp.async.bulk.tensor, SWIZZLE_128B) query tile (kept for the whole work
 //                          item, double buffered across items) and a ring of train tiles
-//   warp  17    MMA      : one thread issues tcgen05.mma M=128 N=128 K=32 x 4 per 128-byte K block, tiles
-//                          round-robin over the four TMEM stages (4 x 128 columns = all 512)
-// No N x M matrix reaches HBM: per query row and group only {best, runner-up candidate} leave the SM
-// (NGROUP slices of Top2 per column split; finalize merges them like column splits).
+//   warp  17    MMA      : one thread issues tcgen05.mma M=128 N=256 K=32 x 4 per 128-byte K block into a
+//                          double-buffered TMEM accumulator (2 x 256 columns = all 512).  N=256 because
+//                          N=128 issues at 2/3 rate and every tcgen05.commit drains the pipe (tools/mma_peak).
+//   warp  18    stager   : column constants ||b'||^2*64 + (column & 63) (or a mask for out-of-range columns)
+//                          of upcoming tiles into an 8-deep shared-memory ring, so the epilogue warps carry
+//                          no global loads, no stores and no CTA barrier.
+// No N x M matrix reaches HBM: per query row and column slice only {best, runner-up candidate} leave the
+// SM (B200M_I8_GROUPS slices of Top2 per column split; finalize merges them like column splits).
 //
 // Exactness of the runner-up: the running top-2 is over CHUNK MINIMA (64 consecutive train columns,
 // aligned to 64), so k1 is the exact best (ties -> lowest column: the column sits in the low key bits,
 // a group visits its chunks in ascending order with a strict compare, and slices merge by u64 min)
 // and k2 is the best among all OTHER chunks.  The true runner-up is min(k2, runner-up inside the
 // winner's chunk); tail.cu recomputes those <= 63 distances exactly where the result depends on it.
-#include <cstdlib>
 #include "common.cuh"
 #include "sm100.cuh"
 
 namespace {
 
 constexpr int TM = 128;            // query rows per tile  (UMMA M)
-constexpr int TN = 128;            // train columns per tile (UMMA N) = one TMEM stage
+constexpr int TN = 256;            // train columns per tile (UMMA N) = one TMEM stage
 constexpr int KB_BYTES = 128;      // one swizzle-128B K block
 constexpr int A_KB_BYTES = TM * KB_BYTES;   // 16 KiB
-constexpr int B_KB_BYTES = TN * KB_BYTES;   // 16 KiB
+constexpr int B_KB_BYTES = TN * KB_BYTES;   // 32 KiB
 constexpr int NABUF = 2;
-constexpr int NB = 8;              // train K-block ring (128 KiB)
-constexpr int NGROUP = B200M_I8_GROUPS;
-constexpr int GROUP_THREADS = 128;
-constexpr int EPI_THREADS = NGROUP * GROUP_THREADS;
-constexpr int THREADS = EPI_THREADS + 64;
-constexpr int CHUNK = B200M_I8_CHUNK;       // columns per key chunk (6 index bits)
+constexpr int NSLICE = B200M_I8_GROUPS;     // 64-column slices of a tile = Top2 slices per split
+constexpr int EPI_WARPS = 4 * NSLICE;
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+constexpr int THREADS = EPI_THREADS + 96;   // + producer, MMA, stager warps
+constexpr int CHUNK = B200M_I8_CHUNK;       // columns per key chunk (6 index bits) = slice width
+constexpr int CBR = 8;                      // column-constant ring depth (tiles)
 constexpr int MASK_CB = 0x60000000;         // column-constant of a masked column: key stays in [2^30, 2^31)
 constexpr int INVALID_VAL = 1 << 24;        // (masked key >> 6) >= 2^24 > any valid value
+static_assert(TN == NSLICE * CHUNK, "one chunk per slice per tile");
 
 struct Item {
     int q_off, n, t_off, m, r0, c_begin, c_end, split, ntiles;
@@ -74,58 +76,63 @@ __device__ __forceinline__ int min3(int a, int b, int c) { return min(min(a, b),
 
 struct SmemLayout {
     uint8_t* a;        // [NABUF][nkb][16 KiB]
-    uint8_t* b;        // [NB][16 KiB]
-    int* cb;           // [NGROUP][2][TN]
+    uint8_t* b;        // [NB][32 KiB]
+    int* cb;           // [CBR][TN]
     uint64_t* a_full;  // [NABUF]
     uint64_t* a_empty; // [NABUF]
-    uint64_t* b_full;  // [NB]
+    uint64_t* b_full;  // [NB]  (NB <= 8)
     uint64_t* b_empty; // [NB]
-    uint64_t* acc_full;   // [NGROUP]
-    uint64_t* acc_empty;  // [NGROUP]
+    uint64_t* acc_full;   // [2]
+    uint64_t* acc_empty;  // [2]
+    uint64_t* cb_full;    // [CBR]
+    uint64_t* cb_empty;   // [CBR]
     uint32_t* tmem_ptr;
 };
+
+__host__ __device__ constexpr int nb_of(int nkb) { return nkb == 1 ? 5 : 4; }
 
 __device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
     SmemLayout s;
     s.a = base;
     s.b = s.a + NABUF * nkb * A_KB_BYTES;
-    uint8_t* p = s.b + NB * B_KB_BYTES;
-    s.cb = (int*)p; p += NGROUP * 2 * TN * sizeof(int);
+    uint8_t* p = s.b + nb_of(nkb) * B_KB_BYTES;
+    s.cb = (int*)p; p += CBR * TN * sizeof(int);
     s.a_full = (uint64_t*)p; p += NABUF * 8;
     s.a_empty = (uint64_t*)p; p += NABUF * 8;
-    s.b_full = (uint64_t*)p; p += NB * 8;
-    s.b_empty = (uint64_t*)p; p += NB * 8;
-    s.acc_full = (uint64_t*)p; p += NGROUP * 8;
-    s.acc_empty = (uint64_t*)p; p += NGROUP * 8;
+    s.b_full = (uint64_t*)p; p += 8 * 8;
+    s.b_empty = (uint64_t*)p; p += 8 * 8;
+    s.acc_full = (uint64_t*)p; p += 2 * 8;
+    s.acc_empty = (uint64_t*)p; p += 2 * 8;
+    s.cb_full = (uint64_t*)p; p += CBR * 8;
+    s.cb_empty = (uint64_t*)p; p += CBR * 8;
     s.tmem_ptr = (uint32_t*)p;
     return s;
 }
 
 __host__ __device__ constexpr size_t smem_bytes(int nkb) {
-    return 1024 /*alignment slack*/ + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)NB * B_KB_BYTES +
-           NGROUP * 2 * TN * sizeof(int) + (2 * NABUF + 2 * NB + 2 * NGROUP) * 8 + 16;
+    return 1024 /*alignment slack*/ + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)nb_of(nkb) * B_KB_BYTES +
+           CBR * TN * sizeof(int) + (2 * NABUF + 16 + 4 + 2 * CBR) * 8 + 16;
 }
 
 __global__ void __launch_bounds__(THREADS, 1)
 l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const int32_t* __restrict__ q_norm, const int32_t* __restrict__ t_norm,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
-                  int nkb, Top2* __restrict__ out, long long total_rows, int dbg) {
+                  int nkb, Top2* __restrict__ out, long long total_rows) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1 KiB alignment
     const SmemLayout sm = carve(smem, nkb);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    constexpr int W_PROD = EPI_THREADS / 32, W_MMA = W_PROD + 1;
+    const int NB = nb_of(nkb);
+    constexpr int W_PROD = EPI_WARPS, W_MMA = EPI_WARPS + 1, W_STAGE = EPI_WARPS + 2;
 
     if (warp == W_PROD && lane == 0) {
         sm100::tma_prefetch_desc(&tmap_q);
         sm100::tma_prefetch_desc(&tmap_t);
         for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
         for (int i = 0; i < NB; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
-        for (int i = 0; i < NGROUP; ++i) {
-            sm100::mbar_init(&sm.acc_full[i], 1);
-            sm100::mbar_init(&sm.acc_empty[i], GROUP_THREADS / 32);
-        }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS); }
+        for (int i = 0; i < CBR; ++i) { sm100::mbar_init(&sm.cb_full[i], 1); sm100::mbar_init(&sm.cb_empty[i], EPI_WARPS); }
         sm100::fence_barrier_init();
     }
     if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
@@ -151,7 +158,6 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                     for (int kb = 0; kb < nkb; ++kb) {
                         const uint32_t s = b_cnt % NB;
-                        if (dbg & 1) { ++b_cnt; continue; }
                         sm100::mbar_wait(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
                         sm100::mbar_arrive_expect_tx(&sm.b_full[s], (uint32_t)B_KB_BYTES);
                         sm100::tma_load_2d(sm.b + (size_t)s * B_KB_BYTES, &tmap_t, &sm.b_full[s], kb * KB_BYTES,
@@ -172,13 +178,13 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 const uint32_t ab = a_cnt & 1;
                 sm100::mbar_wait(&sm.a_full[ab], (a_cnt >> 1) & 1);
                 for (int j = 0; j < it.ntiles; ++j) {
-                    const uint32_t st = tc % NGROUP, use = tc / NGROUP;
-                    if (!(dbg & 4)) sm100::mbar_wait(&sm.acc_empty[st], (use & 1) ^ 1);
+                    const uint32_t as = tc & 1;
+                    sm100::mbar_wait(&sm.acc_empty[as], ((tc >> 1) & 1) ^ 1);
                     sm100::tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + st * TN;
+                    const uint32_t d_tmem = tmem_base + as * TN;
                     for (int kb = 0; kb < nkb; ++kb) {
                         const uint32_t s = b_cnt % NB;
-                        if (!(dbg & 1)) sm100::mbar_wait(&sm.b_full[s], (b_cnt / NB) & 1);
+                        sm100::mbar_wait(&sm.b_full[s], (b_cnt / NB) & 1);
                         sm100::tc_fence_after();
                         const uint64_t adesc = sm100::make_smem_desc_sw128(
                             sm100::smem_u32(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES));
@@ -189,55 +195,68 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                         sm100::mma_commit(&sm.b_empty[s]);           // smem stage free once these MMAs retire
                         ++b_cnt;
                     }
-                    sm100::mma_commit(&sm.acc_full[st]);
+                    sm100::mma_commit(&sm.acc_full[as]);
                     ++tc;
                 }
                 sm100::mma_commit(&sm.a_empty[ab]);
                 ++a_cnt;
             }
         }
+    } else if (warp == W_STAGE) {
+        // ===================== column-constant stager (whole warp) =====================
+        uint32_t tc = 0;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            for (int j = 0; j < it.ntiles; ++j, ++tc) {
+                const int c0 = it.c_begin + j * TN;
+                int nt[TN / 32];
+#pragma unroll
+                for (int k = 0; k < TN / 32; ++k) {
+                    int col = c0 + k * 32 + lane;
+                    nt[k] = col < it.c_end ? __ldg(t_norm + it.t_off + col) : -1;
+                }
+                const uint32_t r = tc % CBR;
+                sm100::mbar_wait(&sm.cb_empty[r], ((tc / CBR) & 1) ^ 1);
+                int* dst = sm.cb + r * TN;
+#pragma unroll
+                for (int k = 0; k < TN / 32; ++k)
+                    dst[k * 32 + lane] = nt[k] >= 0 ? nt[k] * CHUNK + ((k * 32 + lane) & (CHUNK - 1)) : MASK_CB;
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.cb_full[r]);   // release: the stores above are visible to waiters
+            }
+        }
     } else {
-        // ===================== epilogue: group g = warp / 4 owns TMEM stage g, lane quarter = warp % 4 =====================
-        const int g = warp >> 2, quarter = warp & 3;
-        const int tg = threadIdx.x & (GROUP_THREADS - 1);   // column of the tile whose norm this thread stages
-        const uint32_t cb_s = sm100::smem_u32(sm.cb + g * 2 * TN);
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN;
-        uint32_t gcnt = 0, tc_base = 0;
+        // ===================== epilogue: lane quarter = warp % 4, 64-column slice = warp / 4 =====================
+        const int quarter = warp & 3, slice = warp >> 2;
+        const uint32_t cb_s = sm100::smem_u32(sm.cb) + slice * CHUNK * 4;
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + slice * CHUNK;
+        uint32_t tc = 0;
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
             int v1 = 0x7fffffff, v2 = 0x7fffffff, i1 = -1, i2 = -1;
-            const int j0 = (int)((g - tc_base) & (NGROUP - 1));
-            // raw norm of this thread's column of the group's NEXT tile: loaded early, consumed one tile later
-            auto load_nt = [&](int j) -> int {
-                int col = it.c_begin + j * TN + tg;
-                return col < it.c_end ? __ldg(t_norm + it.t_off + col) : -1;
-            };
-            int nt_next = j0 < it.ntiles ? load_nt(j0) : -1;
-            for (int j = j0; j < it.ntiles; j += NGROUP) {
-                const int c0 = it.c_begin + j * TN;
-                const uint32_t buf = gcnt & 1;
-                sm100::sts32(cb_s + (buf * TN + tg) * 4, nt_next >= 0 ? nt_next * CHUNK + (tg & (CHUNK - 1)) : MASK_CB);
-                if (j + NGROUP < it.ntiles) nt_next = load_nt(j + NGROUP);
-                asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
-                sm100::mbar_wait(&sm.acc_full[g], gcnt & 1);
+            for (int j = 0; j < it.ntiles; ++j, ++tc) {
+                const uint32_t as = tc & 1, r = tc % CBR;
+                const uint32_t taddr = taddr0 + as * TN;
+                const uint32_t cbv = cb_s + r * TN * 4;
+                sm100::mbar_wait(&sm.acc_full[as], (tc >> 1) & 1);
                 sm100::tc_fence_after();
-                const uint32_t cbv = cb_s + buf * TN * 4;
                 uint32_t acc[2][32];
                 sm100::tmem_ld32(taddr, acc[0]);
+                sm100::mbar_wait(&sm.cb_full[r], (tc / CBR) & 1);
                 int pm = 0;
 #pragma unroll
-                for (int ch = 0; ch < TN / 32; ++ch) {
+                for (int ch = 0; ch < 2; ++ch) {
                     sm100::tmem_ld_wait();                                   // sub-chunk ch is in registers
-                    if (ch + 1 < TN / 32) {
-                        sm100::tmem_ld32(taddr + (ch + 1) * 32, acc[(ch + 1) & 1]);   // overlaps the math below
+                    if (ch == 0) {
+                        sm100::tmem_ld32(taddr + 32, acc[1]);                // overlaps the math below
                     } else {
-                        sm100::tc_fence_before();                            // whole tile read: free the TMEM stage early
+                        sm100::tc_fence_before();                            // slice read: free the TMEM stage early
                         __syncwarp();
-                        if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
+                        if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
                     }
-                    const uint32_t(&a32)[32] = acc[ch & 1];
-                    if (dbg & 2) { v1 = min(v1, (int)(a32[0] ^ a32[31])); continue; }
+                    const uint32_t(&a32)[32] = acc[ch];
                     int key[32];
 #pragma unroll
                     for (int q4 = 0; q4 < 8; ++q4) {
@@ -253,25 +272,20 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     a[10] = min(key[30], key[31]);
                     int cm = min(min3(min3(a[0], a[1], a[2]), min3(a[3], a[4], a[5]), min3(a[6], a[7], a[8])),
                                  min(a[9], a[10]));
-                    if ((ch & 1) == 0) {
-                        pm = cm;
-                    } else {
-                        // insert the 64-column chunk minimum; later chunks have larger columns, so strict '<' keeps the lowest
-                        cm = min(cm, pm);
-                        const int base = c0 + (ch >> 1) * CHUNK;
-                        // compare VALUES only (key >> 6): the low bits are the column inside the chunk and must
-                        // not let a later chunk win a tie
-                        bool lt1 = cm < (v1 & ~(CHUNK - 1)), lt2 = cm < (v2 & ~(CHUNK - 1));
-                        v2 = lt1 ? v1 : (lt2 ? cm : v2);
-                        i2 = lt1 ? i1 : (lt2 ? base : i2);
-                        v1 = lt1 ? cm : v1;
-                        i1 = lt1 ? base : i1;
-                    }
+                    if (ch == 0) pm = cm; else pm = min(pm, cm);
                 }
-                ++gcnt;
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.cb_empty[r]);          // constants consumed
+                // insert the 64-column chunk minimum.  Compare VALUES only (key >> 6): the low bits are the column
+                // inside the chunk and must not let a later chunk win a tie; later chunks have larger columns.
+                const int base = it.c_begin + j * TN + slice * CHUNK;
+                bool lt1 = pm < (v1 & ~(CHUNK - 1)), lt2 = pm < (v2 & ~(CHUNK - 1));
+                v2 = lt1 ? v1 : (lt2 ? pm : v2);
+                i2 = lt1 ? i1 : (lt2 ? base : i2);
+                v1 = lt1 ? pm : v1;
+                i1 = lt1 ? base : i1;
             }
-            tc_base += (uint32_t)it.ntiles;
-            // publish this group's partial top-2 (slice = split * NGROUP + g); finalize merges the slices
+            // publish this slice's partial top-2 (Top2 slice = split * NSLICE + slice); finalize merges the slices
             const int row = it.r0 + quarter * 32 + lane;
             if (row < it.n) {
                 const int nq = __ldg(q_norm + it.q_off + row);
@@ -281,8 +295,7 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                                                          : (((u64)(u32)(val + nq)) << 32) | (u64)(u32)(i + (v & (CHUNK - 1)));
                 };
                 Top2 t; t.k1 = mk(v1, i1); t.k2 = mk(v2, i2);
-                if (dbg && v1 != 0x12345678) { t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL; }   // timing experiments only
-                out[(long long)(it.split * NGROUP + g) * total_rows + it.row_base + row] = t;
+                out[(long long)(it.split * NSLICE + slice) * total_rows + it.row_base + row] = t;
             }
         }
     }
@@ -354,9 +367,8 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
-    static int dbg = getenv("B200M_DBG") ? atoi(getenv("B200M_DBG")) : 0;
     l2_i8_top2_kernel<<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
-                                                   backward ? 1 : 0, nkb, out, total_rows, dbg);
+                                                   backward ? 1 : 0, nkb, out, total_rows);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_top2_kernel launch");
     return B200M_OK;

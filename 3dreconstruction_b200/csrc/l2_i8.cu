@@ -41,9 +41,10 @@ constexpr int NABUF = 2;
 constexpr int NSLICE = B200M_I8_GROUPS;     // 64-column slices of a tile = Top2 slices per split
 constexpr int EPI_WARPS = 4 * NSLICE;
 constexpr int EPI_THREADS = EPI_WARPS * 32;
-constexpr int THREADS = EPI_THREADS + 96;   // + producer, MMA, stager warps
+constexpr int CTRL_WARPS = 4;                // MMA, producer, stager (+1 idle) take the lowest warp ids
+constexpr int THREADS = EPI_THREADS + CTRL_WARPS * 32;
 constexpr int CHUNK = B200M_I8_CHUNK;       // columns per key chunk (6 index bits) = slice width
-constexpr int CBR = 8;                      // column-constant ring depth (tiles)
+constexpr int CBR = 4;                      // column-constant ring depth (tiles)
 constexpr int MASK_CB = 0x60000000;         // column-constant of a masked column: key stays in [2^30, 2^31)
 constexpr int INVALID_VAL = 1 << 24;        // (masked key >> 6) >= 2^24 > any valid value
 static_assert(TN == NSLICE * CHUNK, "one chunk per slice per tile");
@@ -89,7 +90,7 @@ struct SmemLayout {
     uint32_t* tmem_ptr;
 };
 
-__host__ __device__ constexpr int nb_of(int nkb) { return nkb == 1 ? 5 : 4; }
+__host__ __device__ constexpr int nb_of(int nkb) { return nkb == 1 ? 5 : 4; }   // train K-block ring depth
 
 __device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
     SmemLayout s;
@@ -114,17 +115,19 @@ __host__ __device__ constexpr size_t smem_bytes(int nkb) {
            CBR * TN * sizeof(int) + (2 * NABUF + 16 + 4 + 2 * CBR) * 8 + 16;
 }
 
+template <int NKB>
 __global__ void __launch_bounds__(THREADS, 1)
 l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const int32_t* __restrict__ q_norm, const int32_t* __restrict__ t_norm,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
-                  int nkb, Top2* __restrict__ out, long long total_rows) {
+                  Top2* __restrict__ out, long long total_rows) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1 KiB alignment
-    const SmemLayout sm = carve(smem, nkb);
+    const SmemLayout sm = carve(smem, NKB);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int NB = nb_of(nkb);
-    constexpr int W_PROD = EPI_WARPS, W_MMA = EPI_WARPS + 1, W_STAGE = EPI_WARPS + 2;
+    constexpr int NB = nb_of(NKB);
+    // Control roles take the lowest warp ids (the scheduler favours the oldest ready warp).
+    constexpr int W_MMA = 0, W_PROD = 1, W_STAGE = 2;
 
     if (warp == W_PROD && lane == 0) {
         sm100::tma_prefetch_desc(&tmap_q);
@@ -142,120 +145,155 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const uint32_t tmem_base = *sm.tmem_ptr;
 
     if (warp == W_PROD) {
-        // ===================== TMA producer (one thread) =====================
-        if (lane == 0) {
-            uint32_t a_cnt = 0, b_cnt = 0;
-            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-                Item it = decode_item(item, pairs, tiles_max, S, backward);
-                if (!it.valid) continue;
-                const uint32_t ab = a_cnt & 1;
-                sm100::mbar_wait(&sm.a_empty[ab], ((a_cnt >> 1) & 1) ^ 1);
-                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
-                for (int kb = 0; kb < nkb; ++kb)
-                    sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+        // ===================== TMA producer: the warp runs in lockstep, one elected lane issues =====================
+        uint32_t ab = 0, a_par = 1;            // a_par: parity to wait for on a_empty[ab] (fresh barrier passes parity 1)
+        uint32_t bs = 0, b_par = 1;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_empty[ab], a_par);
+            if (sm100::elect_one()) {
+                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb)
+                    sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
                                        kb * KB_BYTES, it.q_off + it.r0);
-                ++a_cnt;
-                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
-                    for (int kb = 0; kb < nkb; ++kb) {
-                        const uint32_t s = b_cnt % NB;
-                        sm100::mbar_wait(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
-                        sm100::mbar_arrive_expect_tx(&sm.b_full[s], (uint32_t)B_KB_BYTES);
-                        sm100::tma_load_2d(sm.b + (size_t)s * B_KB_BYTES, &tmap_t, &sm.b_full[s], kb * KB_BYTES,
-                                           it.t_off + c0);
-                        ++b_cnt;
+            }
+            __syncwarp();
+            if (++ab == NABUF) { ab = 0; a_par ^= 1; }
+            const int row0 = it.t_off + it.c_begin;
+            for (int j = 0; j < it.ntiles; ++j) {
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb) {
+                    sm100::mbar_wait(&sm.b_empty[bs], b_par);
+                    if (sm100::elect_one()) {
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
+                        sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * KB_BYTES,
+                                           row0 + j * TN);
                     }
+                    __syncwarp();
+                    if (++bs == NB) { bs = 0; b_par ^= 1; }
                 }
             }
         }
     } else if (warp == W_MMA) {
-        // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
-            uint32_t a_cnt = 0, b_cnt = 0, tc = 0;
-            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-                Item it = decode_item(item, pairs, tiles_max, S, backward);
-                if (!it.valid) continue;
-                const uint32_t ab = a_cnt & 1;
-                sm100::mbar_wait(&sm.a_full[ab], (a_cnt >> 1) & 1);
-                for (int j = 0; j < it.ntiles; ++j) {
-                    const uint32_t as = tc & 1;
-                    sm100::mbar_wait(&sm.acc_empty[as], ((tc >> 1) & 1) ^ 1);
-                    sm100::tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + as * TN;
-                    for (int kb = 0; kb < nkb; ++kb) {
-                        const uint32_t s = b_cnt % NB;
-                        sm100::mbar_wait(&sm.b_full[s], (b_cnt / NB) & 1);
-                        sm100::tc_fence_after();
-                        const uint64_t adesc = sm100::make_smem_desc_sw128(
-                            sm100::smem_u32(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES));
-                        const uint64_t bdesc = sm100::make_smem_desc_sw128(sm100::smem_u32(sm.b + (size_t)s * B_KB_BYTES));
-#pragma unroll
-                        for (int k = 0; k < KB_BYTES / 32; ++k)      // UMMA K = 32 bytes of int8; +2 = 32 B >> 4
-                            sm100::mma_i8(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
-                        sm100::mma_commit(&sm.b_empty[s]);           // smem stage free once these MMAs retire
-                        ++b_cnt;
-                    }
-                    sm100::mma_commit(&sm.acc_full[as]);
-                    ++tc;
-                }
-                sm100::mma_commit(&sm.a_empty[ab]);
-                ++a_cnt;
-            }
-        }
-    } else if (warp == W_STAGE) {
-        // ===================== column-constant stager (whole warp) =====================
-        uint32_t tc = 0;
+        // ===================== MMA issuer: lockstep warp, one elected lane issues =====================
+        // Everything per tile is a handful of 32-bit adds: descriptors are kept as (constant hi, running lo).
+        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
+        const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
+        const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
+        uint32_t ab = 0, a_par = 0;            // parity to wait for on a_full[ab]
+        uint32_t bs = 0, b_par = 0;
+        uint32_t as = 0, acc_par = 3;          // bit s: parity to wait for on acc_empty[s]
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
-            for (int j = 0; j < it.ntiles; ++j, ++tc) {
-                const int c0 = it.c_begin + j * TN;
-                int nt[TN / 32];
+            sm100::mbar_wait(&sm.a_full[ab], a_par);
+            const uint32_t a_lo = a_lo0 + ab * (NKB * A_KB_BYTES >> 4);
+            for (int j = 0; j < it.ntiles; ++j) {
+                sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
+                acc_par ^= 1u << as;
+                sm100::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * TN;
 #pragma unroll
-                for (int k = 0; k < TN / 32; ++k) {
-                    int col = c0 + k * 32 + lane;
-                    nt[k] = col < it.c_end ? __ldg(t_norm + it.t_off + col) : -1;
+                for (int kb = 0; kb < NKB; ++kb) {
+                    sm100::mbar_wait(&sm.b_full[bs], b_par);
+                    sm100::tc_fence_after();
+                    if (sm100::elect_one()) {
+                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
+#pragma unroll
+                        for (int k = 0; k < KB_BYTES / 32; ++k)      // UMMA K = 32 bytes of int8; +2 = 32 B >> 4
+                            sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                          idesc, (kb | k) ? 1u : 0u);
+                        sm100::mma_commit(&sm.b_empty[bs]);          // smem stage free once these MMAs retire
+                        if (kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
+                    }
+                    __syncwarp();
+                    if (++bs == NB) { bs = 0; b_par ^= 1; }
                 }
-                const uint32_t r = tc % CBR;
-                sm100::mbar_wait(&sm.cb_empty[r], ((tc / CBR) & 1) ^ 1);
-                int* dst = sm.cb + r * TN;
-#pragma unroll
-                for (int k = 0; k < TN / 32; ++k)
-                    dst[k * 32 + lane] = nt[k] >= 0 ? nt[k] * CHUNK + ((k * 32 + lane) & (CHUNK - 1)) : MASK_CB;
-                __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.cb_full[r]);   // release: the stores above are visible to waiters
+                as ^= 1;
             }
+            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            __syncwarp();
+            if (++ab == NABUF) { ab = 0; a_par ^= 1; }
         }
-    } else {
-        // ===================== epilogue: lane quarter = warp % 4, 64-column slice = warp / 4 =====================
-        const int quarter = warp & 3, slice = warp >> 2;
+    } else if (warp == W_STAGE) {
+        // ===================== column-constant stager (whole warp) =====================
+        // Software pipelined: the norms of the next two tiles are in flight while one tile is written to the ring.
+        struct TileIter { long long item; Item it; int j; bool ok; };
+        auto advance = [&](TileIter& ti, bool first) {
+            if (!first && ++ti.j < ti.it.ntiles) return;
+            for (;;) {
+                ti.item = first ? (long long)blockIdx.x : ti.item + gridDim.x;
+                first = false;
+                if (ti.item >= total_items) { ti.ok = false; return; }
+                ti.it = decode_item(ti.item, pairs, tiles_max, S, backward);
+                if (ti.it.valid && ti.it.ntiles > 0) { ti.j = 0; ti.ok = true; return; }
+            }
+        };
+        auto load = [&](const TileIter& ti, int (&nt)[TN / 32]) {
+            const int c0 = ti.it.c_begin + ti.j * TN;
+#pragma unroll
+            for (int k = 0; k < TN / 32; ++k) {
+                int col = c0 + k * 32 + lane;
+                nt[k] = (ti.ok && col < ti.it.c_end) ? __ldg(t_norm + ti.it.t_off + col) : -1;
+            }
+        };
+        TileIter L; L.item = 0; L.j = 0; L.ok = false;
+        advance(L, true);
+        int q0[TN / 32], q1[TN / 32];
+        bool v0 = L.ok;
+        load(L, q0);
+        if (L.ok) advance(L, false);
+        bool v1 = L.ok;
+        load(L, q1);
+        if (L.ok) advance(L, false);
+        uint32_t r = 0, par = 1;               // parity to wait for on cb_empty[r]
+        while (v0) {
+            sm100::mbar_wait(&sm.cb_empty[r], par);
+            int* dst = sm.cb + r * TN;
+#pragma unroll
+            for (int k = 0; k < TN / 32; ++k)
+                dst[k * 32 + lane] = q0[k] >= 0 ? q0[k] * CHUNK + ((k * 32 + lane) & (CHUNK - 1)) : MASK_CB;
+            __syncwarp();
+            if (lane == 0) sm100::mbar_arrive(&sm.cb_full[r]);   // release: the stores above are visible to waiters
+            if (++r == CBR) { r = 0; par ^= 1; }
+#pragma unroll
+            for (int k = 0; k < TN / 32; ++k) q0[k] = q1[k];
+            v0 = v1;
+            v1 = L.ok;
+            if (L.ok) { load(L, q1); advance(L, false); }
+        }
+    } else if (warp >= CTRL_WARPS) {
+        // ===================== epilogue: lane quarter = warp % 4, 64-column slice = (warp - 4) / 4 =====================
+        const int quarter = warp & 3, slice = (warp - CTRL_WARPS) >> 2;
         const uint32_t cb_s = sm100::smem_u32(sm.cb) + slice * CHUNK * 4;
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + slice * CHUNK;
-        uint32_t tc = 0;
+        uint32_t as = 0, full_par = 0;         // bit s: parity to wait for on acc_full[s]
+        uint32_t r = 0, cb_par = 0;            // parity to wait for on cb_full[r]
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
             int v1 = 0x7fffffff, v2 = 0x7fffffff, i1 = -1, i2 = -1;
-            for (int j = 0; j < it.ntiles; ++j, ++tc) {
-                const uint32_t as = tc & 1, r = tc % CBR;
+            int base = it.c_begin + slice * CHUNK;
+            for (int j = 0; j < it.ntiles; ++j, base += TN) {
                 const uint32_t taddr = taddr0 + as * TN;
                 const uint32_t cbv = cb_s + r * TN * 4;
-                sm100::mbar_wait(&sm.acc_full[as], (tc >> 1) & 1);
+                sm100::mbar_wait(&sm.acc_full[as], (full_par >> as) & 1);
+                full_par ^= 1u << as;
                 sm100::tc_fence_after();
                 uint32_t acc[2][32];
                 sm100::tmem_ld32(taddr, acc[0]);
-                sm100::mbar_wait(&sm.cb_full[r], (tc / CBR) & 1);
+                sm100::tmem_ld32(taddr + 32, acc[1]);
+                sm100::tmem_ld_wait();                                       // the whole slice is in registers:
+                sm100::tc_fence_before();                                    // free the TMEM stage before the math
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
+                as ^= 1;
+                sm100::mbar_wait(&sm.cb_full[r], cb_par);
                 int pm = 0;
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch) {
-                    sm100::tmem_ld_wait();                                   // sub-chunk ch is in registers
-                    if (ch == 0) {
-                        sm100::tmem_ld32(taddr + 32, acc[1]);                // overlaps the math below
-                    } else {
-                        sm100::tc_fence_before();                            // slice read: free the TMEM stage early
-                        __syncwarp();
-                        if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
-                    }
                     const uint32_t(&a32)[32] = acc[ch];
                     int key[32];
 #pragma unroll
@@ -276,9 +314,9 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 }
                 __syncwarp();
                 if (lane == 0) sm100::mbar_arrive(&sm.cb_empty[r]);          // constants consumed
+                if (++r == CBR) { r = 0; cb_par ^= 1; }
                 // insert the 64-column chunk minimum.  Compare VALUES only (key >> 6): the low bits are the column
                 // inside the chunk and must not let a later chunk win a tie; later chunks have larger columns.
-                const int base = it.c_begin + j * TN + slice * CHUNK;
                 bool lt1 = pm < (v1 & ~(CHUNK - 1)), lt2 = pm < (v2 & ~(CHUNK - 1));
                 v2 = lt1 ? v1 : (lt2 ? pm : v2);
                 i2 = lt1 ? i1 : (lt2 ? base : i2);
@@ -355,9 +393,10 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     const size_t smem = smem_bytes(nkb);
     static bool attr_set = false;
     if (!attr_set) {
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem_bytes(2)),
-                         "l2_i8 smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(1)), "l2_i8 smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(2)), "l2_i8 smem attr");
         attr_set = true;
     }
     int tiles_max = (max_n + TM - 1) / TM;
@@ -367,8 +406,12 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
-    l2_i8_top2_kernel<<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
-                                                   backward ? 1 : 0, nkb, out, total_rows);
+    if (nkb == 1)
+        l2_i8_top2_kernel<1><<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
+                                                          backward ? 1 : 0, out, total_rows);
+    else
+        l2_i8_top2_kernel<2><<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
+                                                          backward ? 1 : 0, out, total_rows);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_top2_kernel launch");
     return B200M_OK;

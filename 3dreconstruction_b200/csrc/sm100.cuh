@@ -62,6 +62,18 @@ __device__ __forceinline__ void sts32(uint32_t saddr, int v) {
     asm volatile("st.shared.s32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
 }
 
+// One lane of a converged warp (the warp runs the role in lockstep; only the issue is predicated, so
+// operands stay warp-uniform and the compiler needs no per-lane broadcast loops).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)m) : "memory");
@@ -139,6 +151,15 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr) {
     d |= (uint64_t)1 << 46;                           // descriptor version (Blackwell)
     d |= (uint64_t)2 << 61;                           // layout type SWIZZLE_128B
     return d;
+}
+// Same descriptor split in halves: the high word is constant, the low word is
+// ((addr >> 4) & 0x3FFF) | LBO, so stepping K by 32 bytes or a stage by its size is one 32-bit add.
+constexpr uint32_t SMEM_DESC_HI_SW128 = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+__device__ __forceinline__ uint32_t smem_desc_lo_sw128(uint32_t smem_addr) {
+    return ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
+}
+__device__ __forceinline__ uint64_t smem_desc_join(uint32_t lo) {
+    return ((uint64_t)SMEM_DESC_HI_SW128 << 32) | (uint64_t)lo;
 }
 // Instruction descriptor (cute::UMMA::InstrDescriptor bit layout).
 //   c_format [4,6): 1 = F32, 2 = S32; a_format [7,10), b_format [10,13): i8 kind 0 = u8, 1 = s8;

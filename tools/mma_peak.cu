@@ -120,6 +120,84 @@ void run_tile(int N, int nstage, int commits, int sms) {
     cudaFree(dcyc);
 }
 
+// Contention probe: the MMA thread issues N=256 tiles (4 MMAs + 2 commits) while 16 other warps hammer
+// TMEM (tcgen05.ld of the OTHER stage) and/or shared memory (broadcast LDS.128), like the epilogue does.
+__global__ void __launch_bounds__(576, 1) contend_kernel(int iters, uint32_t idesc, int act, long long* cycles, int* sink) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar, scratch[2];
+    __shared__ uint32_t tptr;
+    __shared__ volatile int done;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < (56 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
+    if (threadIdx.x == 0) { done = 0; sm100::mbar_init(&bar, 1); sm100::mbar_init(&scratch[0], 1); sm100::mbar_init(&scratch[1], 1); sm100::fence_barrier_init(); }
+    if (warp == 16) sm100::tmem_alloc<512>(&tptr);
+    sm100::fence_proxy_async();
+    sm100::tc_fence_before(); __syncthreads(); sm100::tc_fence_after();
+    uint32_t tbase = tptr;
+    if (warp == 17) {
+        if (lane == 0) {
+            uint64_t ad = sm100::make_smem_desc_sw128(sm100::smem_u32(smem));
+            uint64_t bd = sm100::make_smem_desc_sw128(sm100::smem_u32(smem + 16384));
+            long long t0 = clock64();
+            for (int it = 0; it < iters; ++it) {
+                uint32_t d = tbase + (it & 1) * 256;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) mma_k_i8(d, ad + 2 * k, bd + 2 * k, idesc, k ? 1 : 0);
+                sm100::mma_commit(&scratch[0]);
+                sm100::mma_commit(&scratch[1]);
+            }
+            sm100::mma_commit(&bar);
+            sm100::mbar_wait(&bar, 0);
+            long long t1 = clock64();
+            if (blockIdx.x == 0) *cycles = t1 - t0;
+            done = 1;
+        }
+    } else if (warp < 16) {
+        const uint32_t taddr = tbase + ((uint32_t)((warp & 3) * 32) << 16) + (warp >> 2) * 64;
+        const uint32_t cb = sm100::smem_u32(smem + 49152);
+        int acc_x = 0;
+        long long n = 0;
+        while (!done) {
+            for (int rep = 0; rep < 16; ++rep) {
+                if (act & 1) {
+                    uint32_t v[32];
+                    sm100::tmem_ld32(taddr + ((rep & 1) ? 256 : 0), v);
+                    sm100::tmem_ld32(taddr + ((rep & 1) ? 256 : 0) + 32, v);
+                    sm100::tmem_ld_wait();
+                    acc_x ^= v[lane & 31];
+                }
+                if (act & 2) {
+#pragma unroll
+                    for (int q = 0; q < 16; ++q) { int4 c = sm100::lds128(cb + q * 16); acc_x += c.x ^ c.y ^ c.z ^ c.w; }
+                }
+                if (act & 4) {
+#pragma unroll
+                    for (int q = 0; q < 64; ++q) acc_x = acc_x * -128 + q;
+                }
+                ++n;
+            }
+        }
+        if (acc_x == 0x7654321) sink[0] = acc_x;
+        if (blockIdx.x == 0 && threadIdx.x == 0) cycles[1] = n;
+    }
+    sm100::tc_fence_before(); __syncthreads();
+    if (warp == 16) sm100::tmem_dealloc<512>(tbase);
+}
+
+void run_contend(int act, int sms) {
+    long long* dcyc; cudaMalloc(&dcyc, 16); int* sink; cudaMalloc(&sink, 4);
+    cudaFuncSetAttribute(contend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const int iters = 20000;
+    uint32_t idesc = sm100::make_idesc(2, 1, 1, 128, 256);
+    contend_kernel<<<sms, 576, 64 * 1024>>>(iters, idesc, act, dcyc, sink);
+    cudaError_t err = cudaDeviceSynchronize();
+    long long cyc[2] = {0, 0}; cudaMemcpy(cyc, dcyc, 16, cudaMemcpyDeviceToHost);
+    printf("contend act=%d (1=LDTM 2=LDS.128 bcast 4=IMAD): %s, %.1f cycles per N256 tile (floor 512, alone 590); side-warp iterations per tile %.2f\n",
+           act, cudaGetErrorString(err), (double)cyc[0] / iters, (double)cyc[1] / iters);
+    cudaFree(dcyc); cudaFree(sink);
+}
+
 int main() {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     printf("SMs: %d\n", sms);
@@ -130,5 +208,6 @@ int main() {
     run<3>("e4m3", sm100::make_idesc(1, 0, 0, 128, 256), 32, sms);
     run_tile(256, 2, 0, sms); run_tile(256, 2, 2, sms); run_tile(128, 4, 0, sms); run_tile(128, 4, 1, sms); run_tile(128, 4, 2, sms);
     run_tile(64, 8, 2, sms); run_tile(128, 1, 2, sms);
+    for (int act = 0; act < 8; ++act) run_contend(act, sms);
     return 0;
 }

@@ -67,7 +67,7 @@ static void make_plan(MatchPlan& pl, char* base, int kind, int mode, int num_pai
     pl.cand = nullptr; pl.pmax = nullptr;
     if (kind == B200M_KIND_L2_F32) {
         long long rows = need_bwd && total_m > total_n ? total_m : total_n;
-        pl.cand = (void*)(base + off);  off = align_up(off + 8ull * B200M_F32_CAND * (size_t)S * rows, 256);
+        pl.cand = (void*)(base + off);  off = align_up(off + (8ull * B200M_F32_CAND + 4ull) * 2 * (size_t)S * rows + 8ull * rows + 64, 256);
         pl.pmax = (float*)(base + off); off = align_up(off + sizeof(float) * (size_t)num_pairs, 256);
     }
     pl.bytes = off;

@@ -15,7 +15,7 @@ struct Top2 { u64 k1, k2; };
 #define B200M_SENTINEL 0xFFFFFFFFFFFFFFFFull
 #define B200M_I8_GROUPS 4    // independent epilogue groups of the L2_I8 kernel = Top2 slices per column split
 #define B200M_I8_CHUNK 64    // columns per key chunk of the L2_I8 kernel (runner-up refined inside the winner's chunk)
-#define B200M_F32_CAND 8     // TF32 candidates kept per query row and column split (l2_f32.cu)
+#define B200M_F32_CAND 32    // TF32 candidate list capacity per (query row, column half, column split) (l2_f32.cu)
 
 // Device-side pair record (host b200m_pair + offsets into the per-row workspaces).
 struct DevPair {
@@ -34,7 +34,7 @@ struct MatchPlan {       // host-side carve-up of the caller's workspace
     Top2* bwd;           // [slices][total_m]   (MODE_CROSS)
     u64* sortbuf;        // [sum npad]
     int32_t* tbest;      // [total_n]
-    void* cand;          // L2_F32: [S][max(total_n, total_m)][B200M_F32_CAND] (estimate, column)
+    void* cand;          // L2_F32: [2S][rows][B200M_F32_CAND] (estimate, column) + [2S][rows] counts, rows = max(total_n, total_m)
     float* pmax;         // L2_F32: [P] max train-row norm of the direction being processed
     int S;               // column splits per direction
     int slices;          // Top2 slices per row the knn kernel writes (S, or S * B200M_I8_GROUPS for L2_I8)

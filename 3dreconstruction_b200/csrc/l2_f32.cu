@@ -5,16 +5,18 @@
 // Two stages:
 //   1. l2_f32_cand_kernel — TF32 CANDIDATES on the tensor cores.  Same persistent, warp-specialised
 //      pipeline as l2_i8.cu (TMA SWIZZLE_128B -> tcgen05.mma kind::tf32 M128 x N128 x K8, fp32
-//      accumulators double-buffered in TMEM) with an epilogue that keeps, per query row, the
-//      KC = 8 smallest estimates e_j = ||b_j||^2 - 2 a.b_j  (+ column) in registers.
+//      accumulators double-buffered in TMEM).  The epilogue forms the estimates
+//      e_j = ||b_j||^2 - 2 a.b_j, keeps a branch-free running top-2 (v1, v2) of 16-column minima per
+//      query row, and APPENDS every column with e_j <= v2 + window to a small per-row list.
 //   2. refine_f32_kernel — exact fp32 RE-RANK.  The TF32 estimate of d^2 is off by at most
 //      eps = C_EPS * ||a|| * max_j ||b_j||  (operands truncated to 10 mantissa bits: relative 2^-10
 //      each, |sum a_k b_k| <= ||a|| ||b||, d^2 carries 2x the dot error; C_EPS = 0.0042 > 2^-8 covers
-//      the fp32 accumulation and norm rounding as well).  The true top-2 therefore lie among the
-//      columns with e <= e_min2 + 2 eps; the kept list provably contains all of them when its
-//      worst entry is above that bound (every dropped column has a larger estimate).  Those few
-//      candidates get the direct fp32 sum (a-b)^2 — what cv2 computes — and rows whose list is not
-//      provably sufficient are re-scanned exhaustively in fp32 (rare; counted).
+//      the fp32 accumulation and norm rounding as well), window = 2 eps.  The true top-2 lie among
+//      the columns with e <= e_s + window, e_s the second smallest estimate of the row.  At any time
+//      v2 (second smallest of minima of disjoint column groups seen so far) is >= e_s, so every such
+//      column passes the append test when it is visited: the list is complete by construction
+//      unless it overflows (counted -> the row is re-scanned exhaustively in fp32).  The few
+//      survivors of the final bound get the direct fp32 sum (a-b)^2 — what cv2 computes.
 // Result: Top2 keys (IEEE bits of the exact fp32 d^2 << 32 | column), ties -> lowest column.
 #include <math_constants.h>
 #include "common.cuh"
@@ -28,14 +30,15 @@ constexpr int KB_BYTES = 128;      // one swizzle-128B K block = 32 floats
 constexpr int A_KB_BYTES = TM * KB_BYTES;   // 16 KiB
 constexpr int B_KB_BYTES = TN * KB_BYTES;   // 16 KiB
 constexpr int MAX_NKB = 8;         // D <= 256 floats: the whole query tile stays resident (128 KiB)
-constexpr int NB = 5;              // train K-block ring
+constexpr int NB = 6;              // train K-block ring (as deep as 227 KB of shared memory allow)
 constexpr int EPI_THREADS = 256;
 constexpr int THREADS = EPI_THREADS + 64;
-constexpr int KC = B200M_F32_CAND; // candidates kept per row
+constexpr int KC = B200M_F32_CAND; // list capacity per (row, column half, column split)
 constexpr float C_EPS = 0.0042f;
+constexpr float BIG_F = 3.0e38f;   // ||b||^2 of a masked column: never appended, never a minimum that matters
 
 struct Item {
-    int q_off, n, t_off, m, r0, c_begin, c_end, split;
+    int q_off, n, t_off, m, r0, c_begin, c_end, split, pair;
     long long row_base;
     bool valid;
 };
@@ -46,6 +49,7 @@ __device__ __forceinline__ Item decode_item(long long item, const DevPair* __res
     int tile = (int)(item % tiles_max); item /= tiles_max;
     it.split = (int)(item % S);
     int p = (int)(item / S);
+    it.pair = p;
     DevPair pr = pairs[p];
     if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
     else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
@@ -61,7 +65,6 @@ struct SmemLayout {
     uint8_t* a;        // [nabuf][nkb][16 KiB]
     uint8_t* b;        // [NB][16 KiB]
     float* cb;         // [2][TN]   ||b||^2 of the tile's columns (+inf when masked)
-    float2* exch;      // [TM][KC]  column-half exchange
     uint64_t* a_full; uint64_t* a_empty;   // [2]
     uint64_t* b_full; uint64_t* b_empty;   // [NB]
     uint64_t* acc_full; uint64_t* acc_empty;   // [2]
@@ -76,7 +79,6 @@ __device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
     s.b = s.a + nabuf_of(nkb) * nkb * A_KB_BYTES;
     uint8_t* p = s.b + NB * B_KB_BYTES;
     s.cb = (float*)p; p += 2 * TN * sizeof(float);
-    s.exch = (float2*)p; p += TM * KC * sizeof(float2);
     s.a_full = (uint64_t*)p; p += 2 * 8;
     s.a_empty = (uint64_t*)p; p += 2 * 8;
     s.b_full = (uint64_t*)p; p += NB * 8;
@@ -89,33 +91,15 @@ __device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
 
 __host__ __device__ constexpr size_t smem_bytes(int nkb) {
     return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NB * B_KB_BYTES + 2 * TN * sizeof(float) +
-           TM * KC * sizeof(float2) + (8 + 2 * NB) * 8 + 16;
+           (8 + 2 * NB) * 8 + 16;
 }
-
-// Sorted (ascending) list of the KC smallest (estimate, column); strict '<' keeps the earlier column on ties.
-struct CandList {
-    float v[KC];
-    int c[KC];
-    __device__ __forceinline__ void init() {
-#pragma unroll
-        for (int k = 0; k < KC; ++k) { v[k] = CUDART_INF_F; c[k] = -1; }
-    }
-    __device__ __forceinline__ void insert(float x, int col) {   // caller checked x < v[KC-1]
-        v[KC - 1] = x; c[KC - 1] = col;
-#pragma unroll
-        for (int k = KC - 1; k > 0; --k) {
-            bool sw = v[k] < v[k - 1];
-            float tv = v[k - 1]; int tc = c[k - 1];
-            v[k - 1] = sw ? v[k] : tv; c[k - 1] = sw ? c[k] : tc;
-            v[k] = sw ? tv : v[k];     c[k] = sw ? tc : c[k];
-        }
-    }
-};
 
 __global__ void __launch_bounds__(THREADS, 1)
 l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                    const float* __restrict__ t_norm, const DevPair* __restrict__ pairs, long long total_items,
-                   int tiles_max, int S, int backward, int nkb, float2* __restrict__ cand, long long total_rows) {
+                   int tiles_max, int S, int backward, int nkb, const float* __restrict__ q_norm,
+                   const float* __restrict__ pmax, float2* __restrict__ cand, int* __restrict__ cand_cnt,
+                   long long total_rows) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const SmemLayout sm = carve(smem, nkb);
@@ -137,65 +121,71 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     const uint32_t tmem_base = *sm.tmem_ptr;
 
     if (warp == 8) {
-        // ===================== TMA producer (one thread) =====================
-        if (lane == 0) {
-            uint32_t a_cnt = 0, b_cnt = 0;
-            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-                Item it = decode_item(item, pairs, tiles_max, S, backward);
-                if (!it.valid) continue;
-                const uint32_t ab = a_cnt % nabuf;
-                sm100::mbar_wait_suspend(&sm.a_empty[ab], ((a_cnt / nabuf) & 1) ^ 1);
+        // ===================== TMA producer: lockstep warp, one elected lane issues =====================
+        uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;     // parities to wait for on a_empty / b_empty
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_empty[ab], a_par);
+            if (sm100::elect_one()) {
                 sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
                 for (int kb = 0; kb < nkb; ++kb)
                     sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
                                        kb * (KB_BYTES / 4), it.q_off + it.r0);
-                ++a_cnt;
-                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
-                    for (int kb = 0; kb < nkb; ++kb) {
-                        const uint32_t s = b_cnt % NB;
-                        sm100::mbar_wait_suspend(&sm.b_empty[s], ((b_cnt / NB) & 1) ^ 1);
-                        sm100::mbar_arrive_expect_tx(&sm.b_full[s], (uint32_t)B_KB_BYTES);
-                        sm100::tma_load_2d(sm.b + (size_t)s * B_KB_BYTES, &tmap_t, &sm.b_full[s], kb * (KB_BYTES / 4),
+            }
+            __syncwarp();
+            if (++ab == (uint32_t)nabuf) { ab = 0; a_par ^= 1; }
+            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                for (int kb = 0; kb < nkb; ++kb) {
+                    sm100::mbar_wait(&sm.b_empty[bs], b_par);
+                    if (sm100::elect_one()) {
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
+                        sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * (KB_BYTES / 4),
                                            it.t_off + c0);
-                        ++b_cnt;
                     }
+                    __syncwarp();
+                    if (++bs == NB) { bs = 0; b_par ^= 1; }
                 }
             }
         }
     } else if (warp == 9) {
-        // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
-            uint32_t a_cnt = 0, b_cnt = 0, acc_cnt = 0;
-            for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-                Item it = decode_item(item, pairs, tiles_max, S, backward);
-                if (!it.valid) continue;
-                const uint32_t ab = a_cnt % nabuf;
-                sm100::mbar_wait_suspend(&sm.a_full[ab], (a_cnt / nabuf) & 1);
-                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
-                    const uint32_t as = acc_cnt & 1;
-                    sm100::mbar_wait_suspend(&sm.acc_empty[as], ((acc_cnt >> 1) & 1) ^ 1);
+        // ===================== MMA issuer: lockstep warp, one elected lane issues =====================
+        // (a single thread with per-tile modulo arithmetic and 64-bit descriptor maths was the bottleneck of
+        // the int8 kernel; descriptors here are a constant high word and a running 32-bit low word)
+        constexpr uint32_t idesc = sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
+        const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
+        const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
+        uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_full[ab], a_par);
+            const uint32_t a_lo = a_lo0 + ab * (uint32_t)(nkb * (A_KB_BYTES >> 4));
+            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
+                acc_par ^= 1u << as;
+                sm100::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * TN;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    sm100::mbar_wait(&sm.b_full[bs], b_par);
                     sm100::tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + as * TN;
-                    for (int kb = 0; kb < nkb; ++kb) {
-                        const uint32_t s = b_cnt % NB;
-                        sm100::mbar_wait_suspend(&sm.b_full[s], (b_cnt / NB) & 1);
-                        sm100::tc_fence_after();
-                        const uint64_t adesc = sm100::make_smem_desc_sw128(
-                            sm100::smem_u32(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES));
-                        const uint64_t bdesc = sm100::make_smem_desc_sw128(sm100::smem_u32(sm.b + (size_t)s * B_KB_BYTES));
+                    if (sm100::elect_one()) {
+                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
 #pragma unroll
                         for (int k = 0; k < KB_BYTES / 32; ++k)      // UMMA K = 8 tf32 = 32 bytes; +2 = 32 B >> 4
-                            sm100::mma_tf32(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
-                        sm100::mma_commit(&sm.b_empty[s]);
-                        ++b_cnt;
+                            sm100::mma_tf32(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                            idesc, (kb | k) ? 1u : 0u);
+                        sm100::mma_commit(&sm.b_empty[bs]);
+                        if (kb == nkb - 1) sm100::mma_commit(&sm.acc_full[as]);
                     }
-                    sm100::mma_commit(&sm.acc_full[as]);
-                    ++acc_cnt;
+                    __syncwarp();
+                    if (++bs == NB) { bs = 0; b_par ^= 1; }
                 }
-                sm100::mma_commit(&sm.a_empty[ab]);
-                ++a_cnt;
+                as ^= 1;
             }
+            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            __syncwarp();
+            if (++ab == (uint32_t)nabuf) { ab = 0; a_par ^= 1; }
         }
     } else {
         // ===================== epilogue: 8 warps, TMEM lane quarter = warp % 4, column half = warp / 4 =====================
@@ -207,13 +197,20 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
-            CandList L;
-            L.init();
+            // per-row state: running top-2 of 16-column minima, append window, list cursor
+            const int row = it.r0 + row_in_tile;
+            const bool row_ok = row < it.n;
+            float v1 = CUDART_INF_F, v2 = CUDART_INF_F;
+            const float win = row_ok ? 2.0f * C_EPS * sqrtf(__ldg(q_norm + it.q_off + (row_ok ? row : 0))) * __ldg(pmax + it.pair)
+                                     : -CUDART_INF_F;
+            const long long lrow = (long long)(it.split * 2 + half) * total_rows + it.row_base + (row_ok ? row : 0);
+            float2* list = cand + lrow * KC;
+            int cnt = 0;
             for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                 const uint32_t as = acc_cnt & 1;
                 if (e < TN) {
                     int col = c0 + e;
-                    sm.cb[as * TN + e] = col < it.c_end ? __ldg(t_norm + it.t_off + col) : CUDART_INF_F;
+                    sm.cb[as * TN + e] = col < it.c_end ? __ldg(t_norm + it.t_off + col) : BIG_F;
                 }
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
@@ -230,45 +227,29 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch) {
                     float ev[32];
-                    float cm = CUDART_INF_F;
+                    float h0 = CUDART_INF_F, h1 = CUDART_INF_F;
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
                         ev[i] = fmaf(-2.0f, __uint_as_float(acc[ch][i]), cbv[ch * 32 + i]);
-                        cm = fminf(cm, ev[i]);
+                        if (i < 16) h0 = fminf(h0, ev[i]); else h1 = fminf(h1, ev[i]);
                     }
-                    if (cm < L.v[KC - 1]) {
+                    // top-2 of group minima first (the tighter, still valid bound), then the append test
+                    v2 = fminf(v2, fmaxf(v1, h0)); v1 = fminf(v1, h0);
+                    v2 = fminf(v2, fmaxf(v1, h1)); v1 = fminf(v1, h1);
+                    const float tau = v2 + win;
+                    if (fminf(h0, h1) <= tau) {
                         const int colb = c0 + half * HC + ch * 32;
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
-                            if (ev[i] < L.v[KC - 1]) L.insert(ev[i], colb + i);
+                            if (ev[i] <= tau && ev[i] < BIG_F * 0.5f) {
+                                if (cnt < KC) list[cnt] = make_float2(ev[i], __int_as_float(colb + i));
+                                ++cnt;
+                            }
                     }
                 }
                 ++acc_cnt;
             }
-            // merge the two column halves of each row (warp w and w+4), then publish KC candidates
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            if (half == 1) {
-#pragma unroll
-                for (int k = 0; k < KC; ++k) sm.exch[row_in_tile * KC + k] = make_float2(L.v[k], __int_as_float(L.c[k]));
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            if (half == 0) {
-                int row = it.r0 + row_in_tile;
-                if (row < it.n) {
-#pragma unroll
-                    for (int k = 0; k < KC; ++k) {
-                        float2 o = sm.exch[row_in_tile * KC + k];
-                        // ties between estimates need no care here: the re-rank orders by (exact d^2, column)
-                        if (o.x < L.v[KC - 1]) L.insert(o.x, __float_as_int(o.y));
-                    }
-                    float2* dst = cand + ((long long)it.split * total_rows + it.row_base + row) * KC;
-#pragma unroll
-                    for (int k = 0; k < KC; k += 2) {
-                        float4 w = make_float4(L.v[k], __int_as_float(L.c[k]), L.v[k + 1], __int_as_float(L.c[k + 1]));
-                        *reinterpret_cast<float4*>(dst + k) = w;
-                    }
-                }
-            }
+            if (row_ok) cand_cnt[lrow] = cnt;
         }
     }
 
@@ -301,9 +282,10 @@ __device__ unsigned long long g_f32_stats[2];   // [0] rows re-scanned exhaustiv
 // One warp per query row: exact fp32 re-rank of the TF32 candidates (see the file header).
 __global__ void __launch_bounds__(256)
 refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, int blocks_per_pair,
-                  const float2* __restrict__ cand, long long total_rows, int S, const float* __restrict__ q_desc,
+                  const float2* __restrict__ cand, const int* __restrict__ cand_cnt, long long total_rows, int S,
+                  const float* __restrict__ q_desc,
                   const float* __restrict__ q_norm, const float* __restrict__ t_desc, int D,
-                  const float* __restrict__ pmax, Top2* __restrict__ out) {
+                  const float* __restrict__ pmax, Top2* __restrict__ out, u64* __restrict__ fbq, int* __restrict__ fb_count) {
     const int lane = threadIdx.x & 31;
     const int p = blockIdx.x / blocks_per_pair;
     const int i = (blockIdx.x - p * blocks_per_pair) * 8 + (threadIdx.x >> 5);
@@ -333,69 +315,125 @@ refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, in
         for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
         return s;
     };
-    // gather the S * KC candidates (<= 64): two per lane
-    const int nent = S * KC;
-    float e[2]; int c[2];
-    float wmin = CUDART_INF_F;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        int idx = lane + 32 * h;
-        e[h] = CUDART_INF_F; c[h] = -1;
-        if (idx < nent) {
-            int s = idx / KC, k = idx - s * KC;
-            float2 v = cand[((long long)s * total_rows + row) * KC + k];
-            e[h] = v.x; c[h] = __float_as_int(v.y);
-            if (c[h] < 0) e[h] = CUDART_INF_F;
-            if (k == KC - 1) wmin = e[h];
-        }
+    // Walk the 2 * S lists of this row (<= KC entries each): second smallest estimate, then the survivors.
+    const int nlist = 2 * S;
+    float m1 = CUDART_INF_F, m2 = CUDART_INF_F;
+    bool overflow = false;
+    for (int l = 0; l < nlist; ++l) {
+        const long long lrow = (long long)l * total_rows + row;
+        const int c = __ldg(cand_cnt + lrow);
+        overflow |= c > KC;
+        float e = lane < min(c, KC) ? cand[lrow * KC + lane].x : CUDART_INF_F;
+        float hi = fmaxf(m1, e);
+        m1 = fminf(m1, e);
+        m2 = fminf(m2, hi);
     }
-    float m1 = fminf(e[0], e[1]), m2 = fmaxf(e[0], e[1]);
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
         float o1 = __shfl_xor_sync(0xffffffffu, m1, off), o2 = __shfl_xor_sync(0xffffffffu, m2, off);
         float hi = fmaxf(m1, o1);
         m1 = fminf(m1, o1);
         m2 = fminf(fminf(m2, o2), hi);
-        wmin = fminf(wmin, __shfl_xor_sync(0xffffffffu, wmin, off));
     }
     u64 k1 = B200M_SENTINEL, k2 = B200M_SENTINEL;
-    unsigned evals = 0;
-    bool fallback = false;
-    if (m1 < CUDART_INF_F) {
+    const bool fallback = overflow;
+    if (m > 0 && !fallback) {
         const float win = 2.0f * C_EPS * sqrtf(__ldg(q_norm + q_off + i)) * __ldg(pmax + p);
-        const float bound = (need2 ? m2 : m1) + win;
-        fallback = !(wmin > bound) && wmin < CUDART_INF_F;   // some list may have dropped a relevant column
-        if (!fallback) {
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                unsigned mask = __ballot_sync(0xffffffffu, c[h] >= 0 && e[h] <= bound);
-                while (mask) {
-                    int src = __ffs(mask) - 1;
-                    mask &= mask - 1;
-                    int col = __shfl_sync(0xffffffffu, c[h], src);
-                    float d2 = exact(col);
-                    top2_insert(k1, k2, ((u64)__float_as_uint(d2) << 32) | (u64)(u32)col);
-                    ++evals;
-                }
-            }
-        } else {
-            for (int col = 0; col < m; ++col) {
+        const float bound = (need2 ? m2 : m1) + win;       // m2 == +inf with a single column: everything passes
+        for (int l = 0; l < nlist; ++l) {
+            const long long lrow = (long long)l * total_rows + row;
+            const int c = min(__ldg(cand_cnt + lrow), KC);
+            float2 v = lane < c ? cand[lrow * KC + lane] : make_float2(CUDART_INF_F, 0.0f);
+            unsigned mask = __ballot_sync(0xffffffffu, lane < c && v.x <= bound);
+            while (mask) {
+                int src = __ffs(mask) - 1;
+                mask &= mask - 1;
+                int col = __shfl_sync(0xffffffffu, __float_as_int(v.y), src);
                 float d2 = exact(col);
                 top2_insert(k1, k2, ((u64)__float_as_uint(d2) << 32) | (u64)(u32)col);
             }
-            evals = (unsigned)m;
         }
+    } else if (m > 0 && lane == 0) {
+        // list overflow: the row goes to the exhaustive fp32 re-scan (fallback_f32_kernel, one CTA per row)
+        fbq[atomicAdd(fb_count, 1)] = ((u64)(u32)p << 32) | (u64)(u32)i;
     }
     if (lane == 0) {
         Top2 t; t.k1 = k1; t.k2 = k2;
         out[row] = t;
         Top2 none; none.k1 = B200M_SENTINEL; none.k2 = B200M_SENTINEL;
         for (int s = 1; s < S; ++s) out[(long long)s * total_rows + row] = none;
-        if (fallback) { atomicAdd(&g_f32_stats[0], 1ull); atomicAdd(&g_f32_stats[1], (unsigned long long)evals); }
+    }
+}
+
+// Exhaustive fp32 re-scan of the queued rows (candidate list overflowed): one CTA per row, each warp takes
+// an eighth of the columns, 8 columns per step so that 16 independent 512-byte loads are in flight per warp.
+__global__ void __launch_bounds__(256)
+fallback_f32_kernel(int backward, const DevPair* __restrict__ pairs, const u64* __restrict__ fbq,
+                    const int* __restrict__ fb_count, const float* __restrict__ q_desc,
+                    const float* __restrict__ t_desc, int D, Top2* __restrict__ out) {
+    __shared__ u64 red[8][2];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int count = *fb_count;
+    const int nf4 = D >> 2;
+    for (int q = blockIdx.x; q < count; q += gridDim.x) {
+        const u64 ent = fbq[q];
+        const int p = (int)(ent >> 32), i = (int)(u32)ent;
+        DevPair pr = pairs[p];
+        int q_off = pr.q_off, t_off = pr.t_off, m = pr.m;
+        long long row_base = pr.fwd_off;
+        if (backward) { q_off = pr.t_off; t_off = pr.q_off; m = pr.n; row_base = pr.bwd_off; }
+        const float4* a4 = reinterpret_cast<const float4*>(q_desc + (long long)(q_off + i) * D);
+        float4 ar[2];
+        ar[0] = lane < nf4 ? __ldg(a4 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+        ar[1] = lane + 32 < nf4 ? __ldg(a4 + lane + 32) : make_float4(0.f, 0.f, 0.f, 0.f);
+        u64 k1 = B200M_SENTINEL, k2 = B200M_SENTINEL;
+        for (int c0 = w * 8; c0 < m; c0 += 64) {
+            float s[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int col = min(c0 + u, m - 1);
+                const float4* b4 = reinterpret_cast<const float4*>(t_desc + (long long)(t_off + col) * D);
+                float acc = 0.0f;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    if (lane + 32 * h < nf4) {
+                        float4 b = __ldg(b4 + lane + 32 * h);
+                        float dx = ar[h].x - b.x, dy = ar[h].y - b.y, dz = ar[h].z - b.z, dw = ar[h].w - b.w;
+                        acc = fmaf(dx, dx, acc); acc = fmaf(dy, dy, acc); acc = fmaf(dz, dz, acc); acc = fmaf(dw, dw, acc);
+                    }
+                }
+                s[u] = acc;
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s[u] += __shfl_xor_sync(0xffffffffu, s[u], off);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (c0 + u < m) top2_insert(k1, k2, ((u64)__float_as_uint(s[u]) << 32) | (u64)(u32)(c0 + u));
+        }
+        if (lane == 0) { red[w][0] = k1; red[w][1] = k2; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int ww = 1; ww < 8; ++ww) { top2_insert(k1, k2, red[ww][0]); top2_insert(k1, k2, red[ww][1]); }
+            Top2 t; t.k1 = k1; t.k2 = k2;
+            out[row_base + i] = t;
+        }
+        __syncthreads();
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && count > 0) {
+        atomicAdd(&g_f32_stats[0], (unsigned long long)count);
+        unsigned long long ev = 0;
+        for (int q = 0; q < count; ++q) {
+            DevPair pr = pairs[(int)(fbq[q] >> 32)];
+            ev += (unsigned long long)(backward ? pr.n : pr.m);
+        }
+        atomicAdd(&g_f32_stats[1], ev);
     }
 }
 
 }  // namespace
+
 
 // ---------------------------------------------------------------- host side
 int b200m_f32_stats_read(unsigned long long out[2], bool reset) {
@@ -440,17 +478,23 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
     float2* cand = (float2*)cand_ws;
-    l2_f32_cand_kernel<<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S,
-                                                              backward ? 1 : 0, nkb, cand, total_rows);
-    B200M_CUDA_CHECK(cudaGetLastError(), "l2_f32_cand_kernel launch");
+    int* cand_cnt = (int*)((char*)cand_ws + 8ull * KC * 2 * (size_t)S * (size_t)total_rows);
+    u64* fbq = (u64*)(cand_cnt + 2 * (size_t)S * (size_t)total_rows + (((2 * (size_t)S * (size_t)total_rows) & 1) ? 1 : 0));
+    int* fb_count = (int*)(fbq + total_rows);
+    B200M_CUDA_CHECK(cudaMemsetAsync(fb_count, 0, sizeof(int), st), "fallback counter");
     pair_max_norm_kernel<<<num_pairs, 256, 0, st>>>(pairs, t_norm, backward ? 1 : 0, pmax);
     B200M_CUDA_CHECK(cudaGetLastError(), "pair_max_norm_kernel launch");
+    l2_f32_cand_kernel<<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S,
+                                                              backward ? 1 : 0, nkb, q_norm, pmax, cand, cand_cnt, total_rows);
+    B200M_CUDA_CHECK(cudaGetLastError(), "l2_f32_cand_kernel launch");
     int bpp = (max_n + 7) / 8;
     long long rgrid = (long long)num_pairs * bpp;
     if (rgrid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    refine_f32_kernel<<<(unsigned)rgrid, 256, 0, st>>>(backward ? 1 : 0, need2 ? 1 : 0, pairs, bpp, cand, total_rows, S,
-                                                       q_desc, q_norm, t_desc, D, pmax, out);
+    refine_f32_kernel<<<(unsigned)rgrid, 256, 0, st>>>(backward ? 1 : 0, need2 ? 1 : 0, pairs, bpp, cand, cand_cnt, total_rows, S,
+                                                       q_desc, q_norm, t_desc, D, pmax, out, fbq, fb_count);
     B200M_CUDA_CHECK(cudaGetLastError(), "refine_f32_kernel launch");
-    b200m_count_launch(3);
+    fallback_f32_kernel<<<4 * sms, 256, 0, st>>>(backward ? 1 : 0, pairs, fbq, fb_count, q_desc, t_desc, D, out);
+    B200M_CUDA_CHECK(cudaGetLastError(), "fallback_f32_kernel launch");
+    b200m_count_launch(4);
     return B200M_OK;
 }

@@ -221,6 +221,99 @@ def single_pair_extras(torch, b, eng, pk):
     out["orb_pair_10000x10000_crosscheck"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": gd,
                                               "gdist_both_directions_per_s": 2 * gd,
                                               "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": 2 * gd / popc_peak}
+    out.update(allpairs_extras(torch, b, eng, pk))
+    return out
+
+
+def superpoint_set_gpu(torch, device, images, n, d=256, seed=2, pool=8192, shared=0.5, sigma=0.05):
+    """Same recipe as 3dreconstruction_b200.synth.superpoint_set, generated on the GPU."""
+    g = torch.Generator(device=device); g.manual_seed(seed)
+    unit = lambda x: x / (x.norm(dim=1, keepdim=True) + 1e-12)   # noqa: E731
+    scene = unit(torch.randn((pool, d), device=device, generator=g))
+    k = int(n * shared)
+    out = torch.empty((images, n, d), dtype=torch.float32, device=device)
+    for i in range(images):
+        pick = torch.randperm(pool, device=device, generator=g)[:k]
+        out[i, :k] = unit(scene[pick] + sigma * torch.randn((k, d), device=device, generator=g))
+        out[i, k:] = unit(torch.randn((n - k, d), device=device, generator=g))
+        out[i] = out[i][torch.randperm(n, device=device, generator=g)]
+    return out
+
+
+def binary_set_gpu(torch, device, images, n, nbytes, seed=4, shared=0.5, flip=0.08):
+    """Same recipe as synth.binary_set (planted correspondences through a shared pool), on the GPU."""
+    g = torch.Generator(device=device); g.manual_seed(seed)
+    pool = 2 * n
+    scene = torch.randint(0, 256, (pool, nbytes), device=device, generator=g, dtype=torch.uint8)
+    k = int(n * shared)
+    out = torch.empty((images, n, nbytes), dtype=torch.uint8, device=device)
+    weights = (2 ** torch.arange(8, device=device, dtype=torch.int32)).view(1, 1, 8)
+    for i in range(images):
+        pick = torch.randperm(pool, device=device, generator=g)[:k]
+        bits = (torch.rand((k, nbytes, 8), device=device, generator=g) < flip).to(torch.int32)
+        mask = (bits * weights).sum(dim=2).to(torch.uint8)
+        out[i, :k] = scene[pick] ^ mask
+        out[i, k:] = torch.randint(0, 256, (n - k, nbytes), device=device, generator=g, dtype=torch.uint8)
+        out[i] = out[i][torch.randperm(n, device=device, generator=g)]
+    return out
+
+
+def allpairs_extras(torch, b, eng, pk):
+    """configs[2] (SuperPoint 256-d mutual NN, 100 images x 4096, 4950 pairs: the full config) and a
+    bounded sample of configs[4] (AKAZE 61-byte rows padded to 64, 16384 keypoints, mutual check)."""
+    ap = importlib.import_module("3dreconstruction_b200.allpairs")
+    out = {}
+    lib = eng.lib
+
+    def timed_pass(store, pairs, reps):
+        m = ap.AllPairsMatcher(eng, chunk_pairs=1024)
+        r = m.match(store, pairs, cross_check=True)           # warm-up (also sizes the buffers)
+        torch.cuda.synchronize()
+        lib.b200m_timing_enable(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            r = m.match(store, pairs, cross_check=True)
+        e1.record(); torch.cuda.synchronize()
+        import ctypes
+        knn_ms, knn_l = ctypes.c_double(0), ctypes.c_int(0)
+        lib.b200m_timing_collect(ctypes.byref(knn_ms), ctypes.byref(knn_l))
+        lib.b200m_timing_enable(0)
+        return e0.elapsed_time(e1) / reps, knn_ms.value / reps, int(r.query_idx.numel())
+
+    # ---- configs[2]
+    I, n, D = 100, 4096, 256
+    desc = superpoint_set_gpu(torch, eng.device, I, n, D)
+    store = ap.build_store(eng, desc.view(I * n, D), b.NORM_L2, counts=[n] * I)
+    del desc
+    pairs = ap.all_pairs(I)
+    eng.f32_stats(reset=True)
+    ms, knn_ms, matches = timed_pass(store, pairs, 2)
+    fb_rows, _ = eng.f32_stats()
+    flops = 2.0 * n * n * D * len(pairs) * 2                  # both directions are computed for the mutual check
+    peak = 0.5 * pk["bf16_tflops_sustained"]
+    out["superpoint_allpairs_100x4096x256_mutual"] = {
+        "pairs": len(pairs), "ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3),
+        "gdist_per_s_one_direction": len(pairs) * n * n / 1e9 / (ms / 1e3), "matches": matches,
+        "knn_stage_ms": knn_ms, "tf32_tflops_achieved_knn_stage": flops / (knn_ms / 1e3) / 1e12,
+        "tf32_peak_tflops": peak, "frac_of_tf32_roofline": flops / (knn_ms / 1e3) / 1e12 / peak,
+        "peak_source": "0.5 x bf16_tflops_sustained (SURVEY 8d); tools/mma_peak measures 1117 TFLOP/s burst tf32",
+        "exhaustive_fallback_rows": fb_rows, "rows_total": 2 * n * len(pairs)}
+    del store
+    # ---- configs[4], bounded: 48 of the 1000 images (1128 of 499500 pairs), AKAZE 61 bytes padded to 64
+    I, n, nb = 48, 16384, 61
+    desc = binary_set_gpu(torch, eng.device, I, n, nb)
+    desc = torch.nn.functional.pad(desc.view(I * n, nb), (0, 3))
+    store = ap.build_store(eng, desc, b.NORM_HAMMING, counts=[n] * I)
+    pairs = ap.all_pairs(I)
+    ms, knn_ms, matches = timed_pass(store, pairs, 1)
+    gd = len(pairs) * n * n / 1e9 / (ms / 1e3)
+    popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 16 / 1e9      # Gdist/s, 512-bit rows, at max clock
+    out["akaze_allpairs_sample_48x16384x61B_mutual"] = {
+        "pairs": len(pairs), "of_pairs": 499500, "ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3),
+        "gdist_per_s_one_direction": gd, "gdist_both_directions_per_s": 2 * gd, "matches": matches,
+        "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": 2 * gd / popc_peak,
+        "full_config_estimate_s_1gpu": 499500 / (len(pairs) / (ms / 1e3))}
     return out
 
 

@@ -198,6 +198,58 @@ void run_contend(int act, int sms) {
     cudaFree(dcyc); cudaFree(sink);
 }
 
+// cycles per MMA instruction as a function of N (no commits inside the loop), i8 and tf32
+template <int KIND>
+__global__ void __launch_bounds__(128, 1) nsweep_kernel(int iters, uint32_t idesc, long long* cycles) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tptr;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
+    if (threadIdx.x == 0) { sm100::mbar_init(&bar, 1); sm100::fence_barrier_init(); }
+    if (warp == 0) sm100::tmem_alloc<512>(&tptr);
+    sm100::fence_proxy_async();
+    sm100::tc_fence_before(); __syncthreads(); sm100::tc_fence_after();
+    uint32_t tbase = tptr;
+    if (threadIdx.x == 32) {
+        uint64_t ad = sm100::make_smem_desc_sw128(sm100::smem_u32(smem));
+        uint64_t bd = sm100::make_smem_desc_sw128(sm100::smem_u32(smem + 16384));
+        long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+            uint32_t d = tbase + ((it & 1) ? 256 : 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (KIND == 0) mma_k_i8(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+                else mma_k_tf32(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+            }
+        }
+        sm100::mma_commit(&bar);
+        sm100::mbar_wait(&bar, 0);
+        long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    }
+    sm100::tc_fence_before(); __syncthreads();
+    if (warp == 0) sm100::tmem_dealloc<512>(tbase);
+}
+void run_nsweep(int sms) {
+    long long* dcyc; cudaMalloc(&dcyc, 8);
+    cudaFuncSetAttribute(nsweep_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaFuncSetAttribute(nsweep_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const int iters = 10000;
+    for (int kind = 0; kind < 2; ++kind)
+        for (int N = 32; N <= 256; N += 32) {
+            uint32_t idesc = kind == 0 ? sm100::make_idesc(2, 1, 1, 128, N) : sm100::make_idesc(1, 2, 2, 128, N);
+            if (kind == 0) nsweep_kernel<0><<<sms, 128, 64 * 1024>>>(iters, idesc, dcyc);
+            else nsweep_kernel<1><<<sms, 128, 64 * 1024>>>(iters, idesc, dcyc);
+            cudaError_t err = cudaDeviceSynchronize();
+            long long cyc = 0; cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+            printf("%s M128 N%-3d K=32B: %s, %.1f cycles per MMA (ideal N/2 = %d)\n", kind ? "tf32" : "i8  ", N,
+                   cudaGetErrorString(err), (double)cyc / (iters * 4.0), N / 2);
+        }
+    cudaFree(dcyc);
+}
+
 int main() {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     printf("SMs: %d\n", sms);
@@ -208,6 +260,7 @@ int main() {
     run<3>("e4m3", sm100::make_idesc(1, 0, 0, 128, 256), 32, sms);
     run_tile(256, 2, 0, sms); run_tile(256, 2, 2, sms); run_tile(128, 4, 0, sms); run_tile(128, 4, 1, sms); run_tile(128, 4, 2, sms);
     run_tile(64, 8, 2, sms); run_tile(128, 1, 2, sms);
-    for (int act = 0; act < 8; ++act) run_contend(act, sms);
+    for (int act = 0; act < 4; ++act) run_contend(act, sms);
+    run_nsweep(sms);
     return 0;
 }

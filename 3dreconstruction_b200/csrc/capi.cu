@@ -183,6 +183,8 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         if (d.npad > max_npad) max_npad = d.npad;
     }
     const bool need_bwd = mode == B200M_MODE_CROSS;
+    // Hamming cross-check: one pass yields both the row top-2 and the column minima (atomicMin on packed keys)
+    const bool fused_cross = need_bwd && kind == B200M_KIND_HAMMING && max_n <= (1 << B200M_HAMMING_IDX_BITS);
     int S = choose_splits(kind, num_pairs, max_n, max_m, mode, sm);
     make_plan(pl, (char*)workspace, kind, mode, num_pairs, total_n, total_m, total_pad, S, need_bwd);
     if (pl.bytes > workspace_bytes) return B200M_EWORKSPACE;
@@ -190,7 +192,10 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
     B200M_CUDA_CHECK(cudaMemcpyAsync(pl.pairs, dp.data(), sizeof(DevPair) * (size_t)num_pairs,
                                      cudaMemcpyHostToDevice, st), "pair table upload");
     // pageable source: the copy is staged before the call returns, so `dp` may go out of scope.
-    for (int dir = 0; dir < (need_bwd ? 2 : 1); ++dir) {
+    pl.colmin = fused_cross ? (u32*)pl.bwd : nullptr;
+    if (fused_cross)
+        B200M_CUDA_CHECK(cudaMemsetAsync(pl.colmin, 0xFF, sizeof(u32) * (size_t)total_m, st), "colmin memset");
+    for (int dir = 0; dir < (need_bwd && !fused_cross ? 2 : 1); ++dir) {
         bool back = dir == 1;
         Top2* out = back ? pl.bwd : pl.fwd;
         long long rows = back ? total_m : total_n;
@@ -209,7 +214,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         }
         if (kind == B200M_KIND_HAMMING)
             rc = launch_hamming_top2((const uint8_t*)q_desc, (const uint8_t*)t_desc, D, pl.pairs, num_pairs,
-                                     max_n, max_m, S, back, out, rows, st);
+                                     max_n, max_m, S, back, out, rows, pl.colmin, st);
         else if (kind == B200M_KIND_L2_I8)
             rc = launch_l2_i8_top2((const int8_t*)q_desc, (const int32_t*)q_norm, q_rows, (const int8_t*)t_desc,
                                    (const int32_t*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,

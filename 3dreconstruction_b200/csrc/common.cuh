@@ -32,6 +32,7 @@ struct MatchPlan {       // host-side carve-up of the caller's workspace
     DevPair* pairs;      // [P]
     Top2* fwd;           // [slices][total_n]
     Top2* bwd;           // [slices][total_m]   (MODE_CROSS)
+    u32* colmin;         // HAMMING MODE_CROSS, fused single pass: [total_m] best (dist << 19 | query row) per train row; aliases bwd
     u64* sortbuf;        // [sum npad]
     int32_t* tbest;      // [total_n]
     void* cand;          // L2_F32: [2S][rows][B200M_F32_CAND] (estimate, column) + [2S][rows] counts, rows = max(total_n, total_m)
@@ -64,7 +65,8 @@ int b200m_set_cuda_error(cudaError_t e, const char* where);
 // kernel launchers (one per .cu)
 int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, const DevPair* pairs,
                         int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
-                        long long total_rows, cudaStream_t st);
+                        long long total_rows, u32* colmin, cudaStream_t st);
+#define B200M_HAMMING_IDX_BITS 19   // key32 = dist << 19 | index (hamming.cu); fused column minima need n <= 2^19
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows,
                       const int8_t* t_desc, const int32_t* t_norm, int64_t t_rows, int D,
                       const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,

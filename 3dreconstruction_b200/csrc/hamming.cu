@@ -42,12 +42,18 @@ __device__ __forceinline__ void load_tile(uint4* __restrict__ smem, const uint8_
     }
 }
 
+// COLMIN: also reduce every train COLUMN's best query row (key = dist << 19 | query row, ties -> lowest row)
+// into colmin[] with atomicMin, so that the mutual cross-check (feature_matchers.py:225-238 with
+// crossCheck=True) needs ONE pass over the N x M distances instead of a second, role-swapped pass.
+template <bool COLMIN>
 __global__ void __launch_bounds__(256)
 hamming_top2_kernel(const uint8_t* __restrict__ q_desc, const uint8_t* __restrict__ t_desc, int D,
                     const DevPair* __restrict__ pairs, int tiles_max, int S, int backward,
-                    Top2* __restrict__ out, long long total_rows) {
+                    Top2* __restrict__ out, long long total_rows, u32* __restrict__ colmin) {
     __shared__ uint4 sq[KB * TM];
     __shared__ uint4 st[KB * TN];
+    __shared__ u32 scol[TN];
+    if (COLMIN && threadIdx.x < TN) scol[threadIdx.x] = 0xFFFFFFFFu;
 
     // work item = (pair, split, row tile)
     int item = blockIdx.x;
@@ -108,6 +114,28 @@ hamming_top2_kernel(const uint8_t* __restrict__ q_desc, const uint8_t* __restric
                 }
             }
         }
+        if (COLMIN) {
+            // column minima of this 128 x 128 tile: 8 rows in registers, the partner half-warp by shuffle, the 8
+            // warps through shared-memory atomics, then one global atomicMin per column
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                u32 best = 0xFFFFFFFFu;
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    int row = r0 + ty * 8 + r;
+                    u32 key = row < n ? (((u32)acc[r][c] << IDX_BITS) | (u32)row) : 0xFFFFFFFFu;
+                    best = min(best, key);
+                }
+                best = min(best, __shfl_xor_sync(0xffffffffu, best, 16));
+                if ((threadIdx.x & 16) == 0) atomicMin(&scol[tx + 16 * c], best);
+            }
+            __syncthreads();
+            if (threadIdx.x < TN) {
+                int col = c0 + threadIdx.x;
+                if (col < c_end) atomicMin(&colmin[pr.bwd_off + col], scol[threadIdx.x]);
+                scol[threadIdx.x] = 0xFFFFFFFFu;
+            }
+        }
         // fused top-2 (ties -> lowest column, because the column index sits in the low key bits)
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
@@ -149,7 +177,7 @@ hamming_top2_kernel(const uint8_t* __restrict__ q_desc, const uint8_t* __restric
 
 int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, const DevPair* pairs,
                         int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
-                        long long total_rows, cudaStream_t stream) {
+                        long long total_rows, u32* colmin, cudaStream_t stream) {
     if (D * 8 >= (1 << (32 - IDX_BITS))) return B200M_EUNSUPPORTED;       // distance must fit 13 bits
     int max_rows = backward ? max_m : max_n;
     int max_cols = backward ? max_n : max_m;
@@ -158,8 +186,14 @@ int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, con
     long long grid = (long long)num_pairs * S * tiles_max;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    hamming_top2_kernel<<<(unsigned)grid, 256, 0, stream>>>(q_desc, t_desc, D, pairs, tiles_max, S,
-                                                            backward ? 1 : 0, out, total_rows);
+    if (colmin) {
+        if (backward || max_n > (1 << IDX_BITS)) return B200M_EINVAL;    // query row must fit the key's index bits
+        hamming_top2_kernel<true><<<(unsigned)grid, 256, 0, stream>>>(q_desc, t_desc, D, pairs, tiles_max, S, 0, out,
+                                                                      total_rows, colmin);
+    } else {
+        hamming_top2_kernel<false><<<(unsigned)grid, 256, 0, stream>>>(q_desc, t_desc, D, pairs, tiles_max, S,
+                                                                       backward ? 1 : 0, out, total_rows, nullptr);
+    }
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "hamming_top2_kernel launch");
     return B200M_OK;

@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(256)
 finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
                 const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
                 long long total_m, int S, u64* __restrict__ sortbuf, int32_t* __restrict__ tbest,
-                int32_t* __restrict__ counts, RefineI8 rf) {
+                int32_t* __restrict__ counts, RefineI8 rf, const u32* __restrict__ colmin) {
     int p = blockIdx.x / blocks_per_pair;
     int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
     DevPair pr = pairs[p];
@@ -107,8 +107,12 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
                 keep = (double)d1 < ratio * (double)d2;
             }
         } else if (mode == B200M_MODE_CROSS) {
-            Top2 b = merge_splits(bwd, total_m, S, pr.bwd_off + j1);
-            keep = (u32)b.k1 == (u32)i;
+            if (colmin) {          // fused Hamming pass: packed (dist << 19 | best query row) per train row
+                keep = (colmin[pr.bwd_off + j1] & ((1u << B200M_HAMMING_IDX_BITS) - 1u)) == (u32)i;
+            } else {
+                Top2 b = merge_splits(bwd, total_m, S, pr.bwd_off + j1);
+                keep = (u32)b.k1 == (u32)i;
+            }
         } else {
             keep = true;
         }
@@ -267,7 +271,7 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
     finalize_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
-                                                    plan.bwd, plan.total_m, plan.slices, plan.sortbuf, plan.tbest, counts, rf);
+                                                    plan.bwd, plan.total_m, plan.slices, plan.sortbuf, plan.tbest, counts, rf, plan.colmin);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "finalize_kernel launch");
     return B200M_OK;

@@ -30,6 +30,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 RATIO = 0.75
+HW_INT8_TOPS = 4590.0      # measured issue-rate peak of tcgen05.mma kind::i8 (tools/mma_peak.cu)
 
 
 def parse_args():
@@ -219,8 +220,9 @@ def single_pair_extras(torch, b, eng, pk):
     gd = 1e8 / 1e9 / (ms / 1e3)
     popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 8 / 1e9       # Gdist/s, 256-bit, at max clock
     out["orb_pair_10000x10000_crosscheck"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": gd,
-                                              "gdist_both_directions_per_s": 2 * gd,
-                                              "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": 2 * gd / popc_peak}
+                                              "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": gd / popc_peak,
+                                              "note": "single fused pass: row top-2 and column minima from the same distances; "
+                                                      "one pair = 79 row tiles, cannot fill 148 SMs evenly"}
     out.update(allpairs_extras(torch, b, eng, pk))
     return out
 
@@ -311,8 +313,11 @@ def allpairs_extras(torch, b, eng, pk):
     popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 16 / 1e9      # Gdist/s, 512-bit rows, at max clock
     out["akaze_allpairs_sample_48x16384x61B_mutual"] = {
         "pairs": len(pairs), "of_pairs": 499500, "ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3),
-        "gdist_per_s_one_direction": gd, "gdist_both_directions_per_s": 2 * gd, "matches": matches,
-        "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": 2 * gd / popc_peak,
+        "gdist_per_s": gd, "matches": matches, "knn_stage_ms": knn_ms,
+        "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": gd / popc_peak,
+        "frac_of_popc_roofline_knn_stage": len(pairs) * n * n / 1e9 / (knn_ms / 1e3) / popc_peak,
+        "note": "each distance is computed once (fused row top-2 + column minima); POPC roofline at 1965 MHz",
+        "matches_d2h_bytes_compact": matches * 6,
         "full_config_estimate_s_1gpu": 499500 / (len(pairs) / (ms / 1e3))}
     return out
 
@@ -429,6 +434,11 @@ def run_b200(args):
                 "roofline": {"bound": "tensor", "kernel": "l2_i8_top2_kernel (tcgen05 kind::i8)", "achieved": achieved,
                              "peak": peak, "unit": "TOP/s int8 (TFLOP/s-equivalent)", "frac": achieved / peak if achieved else None,
                              "peak_source": f"2 x bf16_tflops_sustained of {pk_src} MEASURED_PEAKS.json (int8 peak not measured by the driver)",
+                             "peak_hw_int8_microbench": HW_INT8_TOPS,
+                             "frac_of_hw_int8_microbench": achieved / HW_INT8_TOPS if achieved else None,
+                             "peak_hw_source": "tools/mma_peak.cu on this pool's B200: back-to-back tcgen05.mma kind::i8 M128 N256, "
+                                               "8192 MAC/clk/SM at 1965 MHz (profiles/r01_mma_peak_microbench.txt); "
+                                               "ncu's sm__ops_path_tensor_op_utcimma pct uses the same hardware rate",
                              "kernel_ms_per_step": knn_ms.value / args.steps, "kernel_launches": knn_launches.value,
                              "kernel_share_of_step": knn_ms.value / ms_total if world == 1 else None,
                              "algorithmic_ops_per_pair": 2.0 * n * n * D, "algorithmic_hbm_bytes_per_pair": 2 * n * D + 12 * n,

@@ -134,8 +134,8 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         sm100::tma_prefetch_desc(&tmap_t);
         for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
         for (int i = 0; i < NB; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS); }
-        for (int i = 0; i < CBR; ++i) { sm100::mbar_init(&sm.cb_full[i], 1); sm100::mbar_init(&sm.cb_empty[i], EPI_WARPS); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
+        for (int i = 0; i < CBR; ++i) { sm100::mbar_init(&sm.cb_full[i], 1); sm100::mbar_init(&sm.cb_empty[i], EPI_WARPS / 2); }
         sm100::fence_barrier_init();
     }
     if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
@@ -265,65 +265,76 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             if (L.ok) { load(L, q1); advance(L, false); }
         }
     } else if (warp >= CTRL_WARPS) {
-        // ===================== epilogue: lane quarter = warp % 4, 64-column slice = (warp - 4) / 4 =====================
-        const int quarter = warp & 3, slice = (warp - CTRL_WARPS) >> 2;
-        const uint32_t cb_s = sm100::smem_u32(sm.cb) + slice * CHUNK * 4;
-        const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + slice * CHUNK;
-        uint32_t as = 0, full_par = 0;         // bit s: parity to wait for on acc_full[s]
-        uint32_t r = 0, cb_par = 0;            // parity to wait for on cb_full[r]
+        // ===================== epilogue: two GROUPS of 8 warps on alternate tiles =====================
+        // group g = (warp - 4) / 8 owns TMEM stage g and drains the tiles with (global tile counter & 1) == g;
+        // inside a group: TMEM lane quarter = warp % 4, 128-column half of the tile = ((warp - 4) / 4) & 1.
+        // While one group waits for its accumulator and its tcgen05.ld, the other group's math keeps the issue
+        // slots busy (with all 16 warps on the same tile those latencies were exposed once per tile for everybody).
+        const int e = warp - CTRL_WARPS;
+        const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
+        const int slice = g * 2 + half;                                    // Top2 slice of this warp's partial result
+        const uint32_t cb_s = sm100::smem_u32(sm.cb) + half * 2 * CHUNK * 4;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * 2 * CHUNK;
+        uint32_t k = 0;                        // tiles this group has drained: acc_full[g] parity = k & 1,
+                                               // constant ring slot = g + 2 * (k & 1), its parity = (k >> 1) & 1
+        uint32_t tc_base = 0;                  // global tile counter at the start of the item
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
             int v1 = 0x7fffffff, v2 = 0x7fffffff, i1 = -1, i2 = -1;
-            int base = it.c_begin + slice * CHUNK;
-            for (int j = 0; j < it.ntiles; ++j, base += TN) {
-                const uint32_t taddr = taddr0 + as * TN;
-                const uint32_t cbv = cb_s + r * TN * 4;
-                sm100::mbar_wait(&sm.acc_full[as], (full_par >> as) & 1);
-                full_par ^= 1u << as;
-                sm100::tc_fence_after();
-                uint32_t acc[2][32];
-                sm100::tmem_ld32(taddr, acc[0]);
-                sm100::tmem_ld32(taddr + 32, acc[1]);
-                sm100::tmem_ld_wait();                                       // the whole slice is in registers:
-                sm100::tc_fence_before();                                    // free the TMEM stage before the math
-                __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
-                as ^= 1;
-                sm100::mbar_wait(&sm.cb_full[r], cb_par);
-                int pm = 0;
-#pragma unroll
-                for (int ch = 0; ch < 2; ++ch) {
-                    const uint32_t(&a32)[32] = acc[ch];
-                    int key[32];
-#pragma unroll
-                    for (int q4 = 0; q4 < 8; ++q4) {
-                        int4 c4 = sm100::lds128(cbv + (ch * 32 + q4 * 4) * 4);   // warp-uniform address: broadcast
-                        key[4 * q4 + 0] = c4.x - 2 * CHUNK * (int)a32[4 * q4 + 0];
-                        key[4 * q4 + 1] = c4.y - 2 * CHUNK * (int)a32[4 * q4 + 1];
-                        key[4 * q4 + 2] = c4.z - 2 * CHUNK * (int)a32[4 * q4 + 2];
-                        key[4 * q4 + 3] = c4.w - 2 * CHUNK * (int)a32[4 * q4 + 3];
-                    }
-                    int a[11];
-#pragma unroll
-                    for (int k = 0; k < 10; ++k) a[k] = min3(key[3 * k], key[3 * k + 1], key[3 * k + 2]);
-                    a[10] = min(key[30], key[31]);
-                    int cm = min(min3(min3(a[0], a[1], a[2]), min3(a[3], a[4], a[5]), min3(a[6], a[7], a[8])),
-                                 min(a[9], a[10]));
-                    if (ch == 0) pm = cm; else pm = min(pm, cm);
-                }
-                __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.cb_empty[r]);          // constants consumed
-                if (++r == CBR) { r = 0; cb_par ^= 1; }
-                // insert the 64-column chunk minimum.  Compare VALUES only (key >> 6): the low bits are the column
-                // inside the chunk and must not let a later chunk win a tie; later chunks have larger columns.
+            auto insert = [&](int pm, int base) {
+                // insert a 64-column chunk minimum.  Compare VALUES only (key >> 6): the low bits are the column inside
+                // the chunk and must not let a later chunk win a tie; later chunks have larger columns.
                 bool lt1 = pm < (v1 & ~(CHUNK - 1)), lt2 = pm < (v2 & ~(CHUNK - 1));
                 v2 = lt1 ? v1 : (lt2 ? pm : v2);
                 i2 = lt1 ? i1 : (lt2 ? base : i2);
                 v1 = lt1 ? pm : v1;
                 i1 = lt1 ? base : i1;
+            };
+            auto sub_min = [&](const uint32_t(&a32)[32], uint32_t cbv) -> int {      // min key of 32 columns
+                int key[32];
+#pragma unroll
+                for (int q4 = 0; q4 < 8; ++q4) {
+                    int4 c4 = sm100::lds128(cbv + q4 * 16);                  // warp-uniform address: broadcast
+                    key[4 * q4 + 0] = c4.x - 2 * CHUNK * (int)a32[4 * q4 + 0];
+                    key[4 * q4 + 1] = c4.y - 2 * CHUNK * (int)a32[4 * q4 + 1];
+                    key[4 * q4 + 2] = c4.z - 2 * CHUNK * (int)a32[4 * q4 + 2];
+                    key[4 * q4 + 3] = c4.w - 2 * CHUNK * (int)a32[4 * q4 + 3];
+                }
+                int a[11];
+#pragma unroll
+                for (int t = 0; t < 10; ++t) a[t] = min3(key[3 * t], key[3 * t + 1], key[3 * t + 2]);
+                a[10] = min(key[30], key[31]);
+                return min(min3(min3(a[0], a[1], a[2]), min3(a[3], a[4], a[5]), min3(a[6], a[7], a[8])), min(a[9], a[10]));
+            };
+            for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
+                const uint32_t slot = g + 2 * (k & 1);
+                const uint32_t cbv = cb_s + slot * TN * 4;
+                const int base = it.c_begin + j * TN + half * 2 * CHUNK;
+                sm100::mbar_wait(&sm.acc_full[g], k & 1);
+                sm100::tc_fence_after();
+                uint32_t acc[2][32];
+                sm100::tmem_ld32(taddr, acc[0]);
+                sm100::tmem_ld32(taddr + 32, acc[1]);
+                sm100::mbar_wait(&sm.cb_full[slot], (k >> 1) & 1);
+                sm100::tmem_ld_wait();
+                int m0 = sub_min(acc[0], cbv);
+                sm100::tmem_ld32(taddr + 64, acc[0]);                        // overlaps the math below
+                int m1 = sub_min(acc[1], cbv + 32 * 4);
+                sm100::tmem_ld32(taddr + 96, acc[1]);
+                insert(min(m0, m1), base);
+                sm100::tmem_ld_wait();                                       // whole half-tile read:
+                sm100::tc_fence_before();                                    // free the TMEM stage before the rest of the math
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
+                m0 = sub_min(acc[0], cbv + 64 * 4);
+                m1 = sub_min(acc[1], cbv + 96 * 4);
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.cb_empty[slot]);       // constants consumed
+                insert(min(m0, m1), base + CHUNK);
             }
-            // publish this slice's partial top-2 (Top2 slice = split * NSLICE + slice); finalize merges the slices
+            tc_base += (uint32_t)it.ntiles;
+            // publish this warp's partial top-2 (Top2 slice = split * NSLICE + slice); finalize merges the slices
             const int row = it.r0 + quarter * 32 + lane;
             if (row < it.n) {
                 const int nq = __ldg(q_norm + it.q_off + row);

@@ -160,7 +160,7 @@ def broadcast_store(store: Optional[Store], norm_type: int, device: torch.device
     meta = [None]
     if rank == src:
         dd = store.dd
-        meta = [(dd.kind, tuple(dd.desc.shape), str(dd.desc.dtype), None if dd.norm is None else str(dd.norm.dtype),
+        meta = [(dd.kind, tuple(dd.desc.shape), str(dd.desc.dtype), None if dd.norm is None else (str(dd.norm.dtype), int(dd.norm.numel())),
                  dd.rows, dd.width, store.offsets.tolist())]
     dist.broadcast_object_list(meta, src=src)
     kind, shape, dt, ndt, rows, width, offsets = meta[0]
@@ -169,7 +169,7 @@ def broadcast_store(store: Optional[Store], norm_type: int, device: torch.device
     dist.broadcast(desc, src=src)
     norm = None
     if ndt is not None:
-        norm = store.dd.norm if rank == src else torch.empty((rows,), dtype=getattr(torch, ndt.split(".")[-1]), device=device)
+        norm = store.dd.norm if rank == src else torch.empty((ndt[1],), dtype=getattr(torch, ndt[0].split(".")[-1]), device=device)
         dist.broadcast(norm, src=src)
     return Store(DeviceDescriptors(kind, desc, norm, rows, width), np.asarray(offsets, np.int64), norm_type)
 

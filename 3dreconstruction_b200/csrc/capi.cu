@@ -218,7 +218,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         else if (kind == B200M_KIND_L2_I8)
             rc = launch_l2_i8_top2((const int8_t*)q_desc, (const int32_t*)q_norm, q_rows, (const int8_t*)t_desc,
                                    (const int32_t*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
-                                   back, out, rows, st);
+                                   back, mode == B200M_MODE_RATIO, out, rows, st);
         else
             rc = launch_l2_f32_top2((const float*)q_desc, (const float*)q_norm, q_rows, (const float*)t_desc,
                                     (const float*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
@@ -253,9 +253,10 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         return B200M_OK;
     }
     // L2_I8: the exact runner-up refinement (inside the winner's 64-column chunk) is fused into finalize.
-    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0};
+    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr};
     if (kind == B200M_KIND_L2_I8)
-        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D};
+        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D,
+                      mode == B200M_MODE_RATIO ? (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows)) : nullptr};
     // CSR mode counts survivors in finalize (into out_count), scans them into tight offsets, then emits.
     rc = launch_finalize(kind, mode, ratio, pl, num_pairs, max_n, out_ptr ? out_count : nullptr, rf, st);
     if (rc != B200M_OK) return rc;
@@ -297,9 +298,9 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
                            B200M_MODE_NN, true, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
     if (num_pairs == 0 || pl.total_n == 0) return B200M_OK;
-    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0};
+    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr};
     if (kind == B200M_KIND_L2_I8)
-        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D};
+        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D, nullptr};
     return launch_knn2_emit(kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
 }
 

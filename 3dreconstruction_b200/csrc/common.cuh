@@ -15,6 +15,23 @@ struct Top2 { u64 k1, k2; };
 #define B200M_SENTINEL 0xFFFFFFFFFFFFFFFFull
 #define B200M_I8_GROUPS 4    // independent epilogue groups of the L2_I8 kernel = Top2 slices per column split
 #define B200M_I8_CHUNK 64    // columns per key chunk of the L2_I8 kernel (runner-up refined inside the winner's chunk)
+// L2_I8 "folded norm" block (l2_i8.cu, fold kernel): 32 extra int8 K-dims per descriptor row.  The query side
+// of the block is the constant vector c = {-128 x15, -1} x2, the train side holds digits t with
+// sum c.t = -(h - bias), h = ||b'||^2 >> 1, so the int32 accumulator is E = a'.b' - h + bias and
+// d^2 = ||a'||^2 + (||b'||^2 & 1) + 2 (bias - E): the epilogue needs no per-column constant at all.
+// 30 coarse digits (weight 128) and one fine digit (weight 1) cover h - bias in [XMIN, XMIN + SPREAD].
+#define B200M_FOLD_K 32
+#define B200M_FOLD_XMIN (-491520)     // -128 * 30 * 128
+#define B200M_FOLD_SPREAD 979327      // 127 * 30 * 128 + 127 - XMIN
+#define B200M_FOLD_VBIAS (1 << 24)    // Top2 value of a fold-kernel result = VBIAS - E  (|E| < 2^23)
+// Auxiliary block b200m_prep_l2_i8 writes into the caller's `norms` buffer (b200m_l2_i8_aux_bytes(rows) bytes):
+//   int32 norms[rows] | int8 fold[rows][32] at fold_off | int32 info[8] at info_off  (both 256-byte aligned)
+//   info: [0] min h, [1] max h over the store, [2] bias, [3] 1 if every row's h - bias fits the digits
+__host__ __device__ inline size_t b200m_aux_fold_off(long long rows) { return ((size_t)rows * 4 + 255) / 256 * 256; }
+__host__ __device__ inline size_t b200m_aux_info_off(long long rows) {
+    return b200m_aux_fold_off(rows) + ((size_t)rows * B200M_FOLD_K + 255) / 256 * 256;
+}
+__host__ __device__ inline size_t b200m_aux_bytes(long long rows) { return b200m_aux_info_off(rows) + 256; }
 #define B200M_F32_CAND 32    // TF32 candidate list capacity per (query row, column half, column split) (l2_f32.cu)
 
 // Device-side pair record (host b200m_pair + offsets into the per-row workspaces).
@@ -70,7 +87,7 @@ int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, con
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows,
                       const int8_t* t_desc, const int32_t* t_norm, int64_t t_rows, int D,
                       const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
-                      Top2* out, long long total_rows, cudaStream_t st);
+                      bool allow_fold, Top2* out, long long total_rows, cudaStream_t st);
 int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
                        const float* t_desc, const float* t_norm, int64_t t_rows, int D,
                        const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
@@ -79,6 +96,7 @@ int b200m_f32_stats_read(unsigned long long out[2], bool reset);
 // L2_I8 descriptors for the fused exact runner-up refinement (null for the other kinds)
 struct RefineI8 {
     const int8_t* q_desc; const int32_t* q_norm; const int8_t* t_desc; const int32_t* t_norm; int D;
+    const int32_t* t_info;      // info words of the train store's aux block (fold kernel results iff t_info[3])
 };
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
                     int32_t* counts, const RefineI8& rf, cudaStream_t st);

@@ -120,7 +120,8 @@ __global__ void __launch_bounds__(THREADS, 1)
 l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const int32_t* __restrict__ q_norm, const int32_t* __restrict__ t_norm,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
-                  Top2* __restrict__ out, long long total_rows) {
+                  Top2* __restrict__ out, long long total_rows, const int32_t* __restrict__ fold_info) {
+    if (fold_info && __ldg(fold_info + 3)) return;      // MODE_RATIO with usable fold digits: l2_i8_fold_kernel runs instead
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1 KiB alignment
     const SmemLayout sm = carve(smem, NKB);
@@ -354,6 +355,229 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     if (warp == W_MMA) sm100::tmem_dealloc<512>(tmem_base);
 }
 
+// =====================================================================================================
+// Folded-norm variant (MODE_RATIO): a fifth K step of 32 int8 dims carries -(||b'||^2 >> 1) + bias into the
+// accumulator (common.cuh, prep.cu), so the epilogue is a bare 3-input MAX tree over the TMEM values: no
+// column constants, no IMAD, no shared-memory loads.  Per 64-column chunk only the maximum E = a'.b' - h + bias
+// survives; the running top-2 of chunk maxima (value, chunk base) leaves the SM.  tail.cu recomputes the
+// winner's chunk exactly (dp4a) for the rows whose ratio test is not already decided by the bounds
+//   d1 >= na + 2 (bias - E1),   d2 <= na + 1 + 2 (bias - E2).
+constexpr int X_BYTES = TN * B200M_FOLD_K;       // 8 KiB: fold digits of one train tile (SWIZZLE_32B rows)
+constexpr int AX_BYTES = TM * B200M_FOLD_K;      // 4 KiB: the constant query-side block
+constexpr int NBF = 4;                           // train K-block ring depth of the fold kernel
+
+struct SmemFold {
+    uint8_t *a, *b, *x, *ax;
+    uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
+    uint32_t* tmem_ptr;
+};
+__device__ __forceinline__ SmemFold carve_fold(uint8_t* base, int nkb) {
+    SmemFold s;
+    s.a = base;
+    s.b = s.a + NABUF * nkb * A_KB_BYTES;
+    s.x = s.b + NBF * B_KB_BYTES;
+    s.ax = s.x + (NBF / nkb) * X_BYTES;
+    uint8_t* p = s.ax + AX_BYTES;
+    s.a_full = (uint64_t*)p; p += NABUF * 8;
+    s.a_empty = (uint64_t*)p; p += NABUF * 8;
+    s.b_full = (uint64_t*)p; p += NBF * 8;
+    s.b_empty = (uint64_t*)p; p += NBF * 8;
+    s.acc_full = (uint64_t*)p; p += 2 * 8;
+    s.acc_empty = (uint64_t*)p; p += 2 * 8;
+    s.tmem_ptr = (uint32_t*)p;
+    return s;
+}
+__host__ __device__ constexpr size_t smem_bytes_fold(int nkb) {
+    return 1024 + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)NBF * B_KB_BYTES + (size_t)(NBF / nkb) * X_BYTES + AX_BYTES +
+           (2 * NABUF + 2 * NBF + 4) * 8 + 16;
+}
+
+__device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
+__device__ __forceinline__ int max32(const uint32_t (&v)[32]) {
+    int a[11];
+#pragma unroll
+    for (int t = 0; t < 10; ++t) a[t] = max3((int)v[3 * t], (int)v[3 * t + 1], (int)v[3 * t + 2]);
+    a[10] = max((int)v[30], (int)v[31]);
+    return max(max3(max3(a[0], a[1], a[2]), max3(a[3], a[4], a[5]), max3(a[6], a[7], a[8])), max(a[9], a[10]));
+}
+__device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // columns >= lim do not exist
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : 0x80000000u;
+}
+
+template <int NKB>
+__global__ void __launch_bounds__(THREADS, 1)
+l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
+                  const __grid_constant__ CUtensorMap tmap_x, const int32_t* __restrict__ t_info,
+                  const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S,
+                  Top2* __restrict__ out, long long total_rows) {
+    if (__ldg(t_info + 3) == 0) return;            // digits do not cover this store: the keyed kernel runs instead
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const SmemFold sm = carve_fold(smem, NKB);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int W_MMA = 0, W_PROD = 1, W_CONST = 2;
+    constexpr int backward = 0;
+
+    if (warp == W_PROD && lane == 0) {
+        sm100::tma_prefetch_desc(&tmap_q);
+        sm100::tma_prefetch_desc(&tmap_t);
+        sm100::tma_prefetch_desc(&tmap_x);
+        for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
+        for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
+        sm100::fence_barrier_init();
+    }
+    if (warp == W_CONST) {
+        // query side of the fold block: every row is c = {-128 x15, -1} x2.  Both 16-byte halves of a row are equal,
+        // so the tile is invariant under the 16-byte chunk permutation of SWIZZLE_32B (and so is sum c.t).
+        const uint32_t ax = sm100::smem_u32(sm.ax);
+        for (int w = lane; w < AX_BYTES / 4; w += 32) sm100::sts32(ax + 4 * w, (w & 3) == 3 ? (int)0xFF808080 : (int)0x80808080);
+        sm100::fence_proxy_async();                // generic-proxy stores -> visible to tcgen05.mma (async proxy)
+    }
+    if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    sm100::tc_fence_before();
+    __syncthreads();
+    sm100::tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr;
+
+    if (warp == W_PROD) {
+        uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_empty[ab], a_par);
+            if (sm100::elect_one()) {
+                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb)
+                    sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                       kb * KB_BYTES, it.q_off + it.r0);
+            }
+            __syncwarp();
+            if (++ab == NABUF) { ab = 0; a_par ^= 1; }
+            const int row0 = it.t_off + it.c_begin;
+            for (int j = 0; j < it.ntiles; ++j) {
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb) {
+                    sm100::mbar_wait(&sm.b_empty[bs], b_par);
+                    if (sm100::elect_one()) {
+                        const bool last = kb == NKB - 1;       // the fold digits travel with the tile's last K block
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (last ? X_BYTES : 0)));
+                        sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * KB_BYTES,
+                                           row0 + j * TN);
+                        if (last)
+                            sm100::tma_load_2d(sm.x + (size_t)(bs / NKB) * X_BYTES, &tmap_x, &sm.b_full[bs], 0, row0 + j * TN);
+                    }
+                    __syncwarp();
+                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                }
+            }
+        }
+    } else if (warp == W_MMA) {
+        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
+        const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
+        const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
+        const uint32_t x_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.x));      // same low-word format
+        const uint64_t ax_desc = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32,
+                                                          sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.ax)));
+        uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_full[ab], a_par);
+            const uint32_t a_lo = a_lo0 + ab * (NKB * A_KB_BYTES >> 4);
+            for (int j = 0; j < it.ntiles; ++j) {
+                sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
+                acc_par ^= 1u << as;
+                sm100::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * TN;
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb) {
+                    sm100::mbar_wait(&sm.b_full[bs], b_par);
+                    sm100::tc_fence_after();
+                    if (sm100::elect_one()) {
+                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
+#pragma unroll
+                        for (int k = 0; k < KB_BYTES / 32; ++k)
+                            sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                          idesc, (kb | k) ? 1u : 0u);
+                        if (kb == NKB - 1)                      // + c . t = -(h - bias)
+                            sm100::mma_i8(d_tmem, ax_desc,
+                                          sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + (bs / NKB) * (X_BYTES >> 4)),
+                                          idesc, 1u);
+                        sm100::mma_commit(&sm.b_empty[bs]);
+                        if (kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
+                    }
+                    __syncwarp();
+                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                }
+                as ^= 1;
+            }
+            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            __syncwarp();
+            if (++ab == NABUF) { ab = 0; a_par ^= 1; }
+        }
+    } else if (warp >= CTRL_WARPS) {
+        // epilogue: two groups of 8 warps on alternate tiles (as in the keyed kernel), 128 columns per warp
+        const int e = warp - CTRL_WARPS;
+        const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
+        const int slice = g * 2 + half;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * 2 * CHUNK;
+        uint32_t k = 0, tc_base = 0;
+        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            if (!it.valid) continue;
+            int v1 = (int)0x80000000, v2 = (int)0x80000000, i1 = -1, i2 = -1;
+            auto insert = [&](int pm, int base) {           // top-2 of chunk maxima; ties keep the earlier chunk
+                bool gt1 = pm > v1, gt2 = pm > v2;
+                v2 = gt1 ? v1 : (gt2 ? pm : v2);
+                i2 = gt1 ? i1 : (gt2 ? base : i2);
+                v1 = gt1 ? pm : v1;
+                i1 = gt1 ? base : i1;
+            };
+            for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
+                const int base = it.c_begin + j * TN + half * 2 * CHUNK;
+                const int lim = it.c_end - base;              // existing columns in this warp's 128 (tail tile: < 128)
+                sm100::mbar_wait(&sm.acc_full[g], k & 1);
+                sm100::tc_fence_after();
+                uint32_t acc[2][32];
+                sm100::tmem_ld32(taddr, acc[0]);
+                sm100::tmem_ld32(taddr + 32, acc[1]);
+                sm100::tmem_ld_wait();
+                if (lim < 2 * CHUNK) { mask32(acc[0], lim); mask32(acc[1], lim - 32); }
+                int m0 = max32(acc[0]);
+                sm100::tmem_ld32(taddr + 64, acc[0]);
+                int m1 = max32(acc[1]);
+                sm100::tmem_ld32(taddr + 96, acc[1]);
+                insert(max(m0, m1), base);
+                sm100::tmem_ld_wait();
+                sm100::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
+                if (lim < 2 * CHUNK) { mask32(acc[0], lim - 64); mask32(acc[1], lim - 96); }
+                m0 = max32(acc[0]);
+                m1 = max32(acc[1]);
+                insert(max(m0, m1), base + CHUNK);
+            }
+            tc_base += (uint32_t)it.ntiles;
+            const int row = it.r0 + quarter * 32 + lane;
+            if (row < it.n) {
+                auto mk = [&](int v, int i) -> u64 {
+                    return (i < 0 || v == (int)0x80000000) ? B200M_SENTINEL
+                                                           : (((u64)(u32)(B200M_FOLD_VBIAS - v)) << 32) | (u64)(u32)i;
+                };
+                Top2 t; t.k1 = mk(v1, i1); t.k2 = mk(v2, i2);
+                out[(long long)(it.split * NSLICE + slice) * total_rows + it.row_base + row] = t;
+            }
+        }
+    }
+
+    sm100::tc_fence_before();
+    __syncthreads();
+    if (warp == W_MMA) sm100::tmem_dealloc<512>(tmem_base);
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- host side
@@ -371,22 +595,27 @@ static b200m_encode_tiled_fn get_encode_fn() {
 
 int b200m_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_bytes, uint32_t box_rows,
                        CUtensorMapDataType dtype, uint32_t elem_bytes) {
+    return b200m_make_tmap_2d_ex(out, base, rows, row_bytes, box_rows, dtype, elem_bytes, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int b200m_make_tmap_2d_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_bytes, uint32_t box_rows,
+                          CUtensorMapDataType dtype, uint32_t elem_bytes, uint32_t inner_bytes, CUtensorMapSwizzle swz) {
     b200m_encode_tiled_fn enc = get_encode_fn();
     if (!enc) return b200m_set_cuda_error(cudaErrorNotSupported, "cuTensorMapEncodeTiled entry point");
     if (((uintptr_t)base & 15) || (row_bytes & 15) || rows == 0) return B200M_EINVAL;
     cuuint64_t gdim[2] = {row_bytes / elem_bytes, rows};
     cuuint64_t gstride[1] = {row_bytes};
-    cuuint32_t box[2] = {128u / elem_bytes, box_rows};        // inner box = one 128-byte swizzle span
+    cuuint32_t box[2] = {inner_bytes / elem_bytes, box_rows};  // inner box = one swizzle span
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(out, dtype, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                     swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return b200m_set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
     return B200M_OK;
 }
 
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows, const int8_t* t_desc,
                       const int32_t* t_norm, int64_t t_rows, int D, const DevPair* pairs, int num_pairs, int max_n,
-                      int max_m, int S, bool backward, Top2* out, long long total_rows, cudaStream_t st) {
+                      int max_m, int S, bool backward, bool allow_fold, Top2* out, long long total_rows, cudaStream_t st) {
     if (D % KB_BYTES != 0) return B200M_EINVAL;
     const int nkb = D / KB_BYTES;
     if (nkb > 2) return B200M_EUNSUPPORTED;      // d^2 must stay < 2^24 (exact in fp32, as in cv2) and keys in int32
@@ -395,12 +624,20 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
         const int32_t* nn = q_norm; q_norm = t_norm; t_norm = nn;
         int64_t r = q_rows; q_rows = t_rows; t_rows = r;
         int mx = max_n; max_n = max_m; max_m = mx;
+        allow_fold = false;
     }
-    CUtensorMap tq, tt;
+    CUtensorMap tq, tt, tx;
     int rc = b200m_make_tmap_2d(&tq, q_desc, (uint64_t)q_rows, (uint64_t)D, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
     rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D, TN, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
+    // the train store's aux block (b200m_prep_l2_i8): fold digits + info words behind the norms
+    const int32_t* t_info = (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows));
+    if (allow_fold) {
+        rc = b200m_make_tmap_2d_ex(&tx, (const char*)t_norm + b200m_aux_fold_off(t_rows), (uint64_t)t_rows, B200M_FOLD_K, TN,
+                                   CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B200M_FOLD_K, CU_TENSOR_MAP_SWIZZLE_32B);
+        if (rc != B200M_OK) return rc;
+    }
     const size_t smem = smem_bytes(nkb);
     static bool attr_set = false;
     if (!attr_set) {
@@ -408,6 +645,10 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
                                               (int)smem_bytes(1)), "l2_i8 smem attr");
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(2)), "l2_i8 smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes_fold(1)), "l2_i8 fold smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes_fold(2)), "l2_i8 fold smem attr");
         attr_set = true;
     }
     int tiles_max = (max_n + TM - 1) / TM;
@@ -417,13 +658,26 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
+    // Device-side dispatch (no host sync): with allow_fold both kernels are enqueued and exactly one of them
+    // finds its precondition in t_info[3]; the other returns at once.
+    const int32_t* fold_info = allow_fold ? t_info : nullptr;
     if (nkb == 1)
         l2_i8_top2_kernel<1><<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
-                                                          backward ? 1 : 0, out, total_rows);
+                                                          backward ? 1 : 0, out, total_rows, fold_info);
     else
         l2_i8_top2_kernel<2><<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
-                                                          backward ? 1 : 0, out, total_rows);
+                                                          backward ? 1 : 0, out, total_rows, fold_info);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_top2_kernel launch");
+    if (allow_fold) {
+        if (nkb == 1)
+            l2_i8_fold_kernel<1><<<grid, THREADS, smem_bytes_fold(1), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
+                                                                            S, out, total_rows);
+        else
+            l2_i8_fold_kernel<2><<<grid, THREADS, smem_bytes_fold(2), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
+                                                                            S, out, total_rows);
+        b200m_count_launch();
+        B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_fold_kernel launch");
+    }
     return B200M_OK;
 }

@@ -182,6 +182,12 @@ __device__ __forceinline__ uint32_t smem_desc_lo_sw128(uint32_t smem_addr) {
 __device__ __forceinline__ uint64_t smem_desc_join(uint32_t lo) {
     return ((uint64_t)SMEM_DESC_HI_SW128 << 32) | (uint64_t)lo;
 }
+// K-major operand tile of 32-byte rows stored with SWIZZLE_32B: dense 32-byte row pitch, 8-row groups 256 bytes
+// apart (SBO), 16-byte chunks permuted inside a row.
+constexpr uint32_t SMEM_DESC_HI_SW32 = (uint32_t)(256 >> 4) | (1u << 14) | (6u << 29);
+__device__ __forceinline__ uint64_t smem_desc_join_hi(uint32_t hi, uint32_t lo) {
+    return ((uint64_t)hi << 32) | (uint64_t)lo;
+}
 // Instruction descriptor (cute::UMMA::InstrDescriptor bit layout).
 //   c_format [4,6): 1 = F32, 2 = S32; a_format [7,10), b_format [10,13): i8 kind 0 = u8, 1 = s8;
 //   f16 kind 2 = TF32; a_major bit 15, b_major bit 16 (0 = K-major); n_dim [17,23) = N>>3; m_dim [24,29) = M>>4.
@@ -200,3 +206,6 @@ typedef CUresult (*b200m_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuu
 // 2-D row-major [rows, row_bytes] byte matrix, box = [box_rows, 128 bytes], SWIZZLE_128B.  Implemented in l2_i8.cu.
 int b200m_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_bytes, uint32_t box_rows,
                        CUtensorMapDataType dtype, uint32_t elem_bytes);
+// Same with an explicit inner box width (bytes) and swizzle mode (inner_bytes must equal the swizzle span).
+int b200m_make_tmap_2d_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_bytes, uint32_t box_rows,
+                          CUtensorMapDataType dtype, uint32_t elem_bytes, uint32_t inner_bytes, CUtensorMapSwizzle swz);

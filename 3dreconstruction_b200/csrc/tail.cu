@@ -71,6 +71,115 @@ __device__ __forceinline__ void refine_i8_warp(bool need, int i, Top2& t, const 
     }
 }
 
+
+// ---- exact int8 distances for the folded-norm kernel's results (l2_i8.cu): whole-warp helpers -------------
+__device__ __forceinline__ u64 exact_key_i8(const int4* __restrict__ a, int nq, int col, const DevPair& pr,
+                                            const RefineI8& rf) {
+    const int4* b = reinterpret_cast<const int4*>(rf.t_desc + (long long)(pr.t_off + col) * rf.D);
+    int dot = 0;
+    for (int k = 0; k < rf.D / 16; ++k) {
+        int4 x = __ldg(a + k), y = __ldg(b + k);
+        dot = __dp4a(x.x, y.x, dot); dot = __dp4a(x.y, y.y, dot);
+        dot = __dp4a(x.z, y.z, dot); dot = __dp4a(x.w, y.w, dot);
+    }
+    const int d2i = nq + __ldg(rf.t_norm + pr.t_off + col) - 2 * dot;
+    return ((u64)(u32)d2i << 32) | (u64)(u32)col;
+}
+__device__ __forceinline__ void warp_merge_top2(u64& k1, u64& k2) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        u64 o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
+        top2_insert(k1, k2, o1);
+        top2_insert(k1, k2, o2);
+    }
+}
+// exact top-2 of query row ri over train columns [c0, c1) of its pair (every lane returns the same pair of keys)
+__device__ __forceinline__ void warp_exact_top2_i8(int ri, int c0, int c1, const DevPair& pr, const RefineI8& rf,
+                                                   u64& k1, u64& k2) {
+    const int lane = threadIdx.x & 31;
+    const int4* a = reinterpret_cast<const int4*>(rf.q_desc + (long long)(pr.q_off + ri) * rf.D);
+    const int nq = __ldg(rf.q_norm + pr.q_off + ri);
+    k1 = B200M_SENTINEL; k2 = B200M_SENTINEL;
+    for (int col = c0 + lane; col < c1; col += 32) top2_insert(k1, k2, exact_key_i8(a, nq, col, pr, rf));
+    warp_merge_top2(k1, k2);
+}
+
+__device__ __forceinline__ bool ratio_pass_i8(double ratio, int v1, int v2) {      // the test of finalize, on exact d^2
+    float c1 = __fsqrt_rn((float)v1), c2 = __fsqrt_rn((float)v2);
+    return (double)c1 < ratio * (double)c2;
+}
+
+// MODE_RATIO on fold-kernel results.  t holds the top-2 CHUNKS by E = a'.b' - h + bias (value = VBIAS - E, index =
+// first column of the 64-column chunk).  With p = ||b'||^2 & 1 of the column, d^2 = nq + p + 2 (bias - E), so a chunk
+// value brackets its best column's distance within {lb, lb + 1}.  Rows are decided, in this order, by
+//   (1) bounds only: d1 >= lb(E1), d2 <= lb(E2) + 1 and the test is monotone -> most rows fail here, untouched;
+//   (2) exact recomputation of the winner's chunk (E1 > E2: the best column is in it): d1 exact, and d2 is either
+//       the chunk's exact runner-up (if <= lb(E2)) or one of {lb(E2), lb(E2) + 1} -- enough unless the test
+//       flips between those two;
+//   (3) an exhaustive exact scan of the row (chunk-level tie E1 == E2, or the flip in (2)): rare.
+// Returns keep; t.k1 becomes the exact (d^2 << 32 | column) key of the best neighbour when keep is true.
+// Must be called by all 32 lanes of a warp whose rows belong to the same pair.
+__device__ __forceinline__ bool fold_ratio_warp(bool has, int i, Top2& t, double ratio, const DevPair& pr,
+                                                const RefineI8& rf) {
+    const int lane = threadIdx.x & 31;
+    const int bias = __ldg(rf.t_info + 2);
+    int nq = 0, lb1 = 0, lb2 = 0;
+    bool need = false;
+    const bool other = t.k2 != B200M_SENTINEL;
+    if (has) {
+        nq = __ldg(rf.q_norm + pr.q_off + i);
+        lb1 = nq + 2 * (bias - (B200M_FOLD_VBIAS - (int)(u32)(t.k1 >> 32)));
+        if (other) {
+            lb2 = nq + 2 * (bias - (B200M_FOLD_VBIAS - (int)(u32)(t.k2 >> 32)));
+            need = ratio_pass_i8(ratio, max(lb1, 0), lb2 + 1);
+        } else {
+            need = true;
+        }
+    }
+    u64 a1 = B200M_SENTINEL, a2 = B200M_SENTINEL;
+    unsigned mask = __ballot_sync(0xffffffffu, need);
+    while (mask) {
+        const int src = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int ri = __shfl_sync(0xffffffffu, i, src);
+        const int c0 = __shfl_sync(0xffffffffu, (int)(u32)t.k1, src);
+        u64 x1, x2;
+        warp_exact_top2_i8(ri, c0, min(c0 + B200M_I8_CHUNK, pr.m), pr, rf, x1, x2);
+        if (lane == src) { a1 = x1; a2 = x2; }
+    }
+    bool keep = false, full = false;
+    if (need) {
+        const int d1 = (int)(u32)(a1 >> 32);
+        const bool has2 = a2 != B200M_SENTINEL;
+        const int r2 = (int)(u32)(a2 >> 32);
+        if (!other) {
+            keep = has2 && ratio_pass_i8(ratio, d1, r2);       // a single chunk: everything is exact already
+        } else if (lb1 == lb2) {
+            full = true;                                        // two chunks tie on E: the winner may be in either (or a third)
+        } else if (has2 && r2 <= lb2) {
+            keep = ratio_pass_i8(ratio, d1, r2);
+        } else if (ratio_pass_i8(ratio, d1, max(lb2, 0))) {
+            keep = true;                                        // passes with the smallest possible runner-up
+        } else if (ratio_pass_i8(ratio, d1, lb2 + 1)) {
+            full = true;                                        // outcome depends on the parity of the other chunk's best column
+        }
+    }
+    mask = __ballot_sync(0xffffffffu, full);
+    while (mask) {
+        const int src = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int ri = __shfl_sync(0xffffffffu, i, src);
+        u64 x1, x2;
+        warp_exact_top2_i8(ri, 0, pr.m, pr, rf, x1, x2);
+        if (lane == src) {
+            a1 = x1;
+            keep = x2 != B200M_SENTINEL && ratio_pass_i8(ratio, (int)(u32)(x1 >> 32), (int)(u32)(x2 >> 32));
+        }
+    }
+    if (keep) t.k1 = a1;
+    return keep;
+}
+
 __global__ void __launch_bounds__(256)
 finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
                 const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
@@ -82,7 +191,11 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
     const bool active = i < pr.n;
     Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
     if (active) t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
-    if (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) {      // block-uniform branch
+    const bool fold = kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO && rf.t_info && __ldg(rf.t_info + 3);
+    bool keep_fold = false;
+    if (fold) {                                                      // grid-uniform branch
+        keep_fold = fold_ratio_warp(t.k1 != B200M_SENTINEL, i, t, ratio, pr, rf);
+    } else if (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) {      // block-uniform branch
         bool need = false;
         if (t.k1 != B200M_SENTINEL) {
             need = ratio <= 0.0 || t.k2 == B200M_SENTINEL;
@@ -100,7 +213,9 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
         u32 j1 = (u32)t.k1;
         float d1 = value_to_distance(kind, (u32)(t.k1 >> 32));
         bool keep;
-        if (mode == B200M_MODE_RATIO) {
+        if (fold) {
+            keep = keep_fold;
+        } else if (mode == B200M_MODE_RATIO) {
             keep = false;
             if (t.k2 != B200M_SENTINEL) {            // cv2 returns a single neighbour when m == 1
                 float d2 = value_to_distance(kind, (u32)(t.k2 >> 32));

@@ -32,7 +32,7 @@ class DeviceDescriptors(NamedTuple):
     """One descriptor store resident in HBM, already in the layout its kernel wants."""
     kind: int
     desc: torch.Tensor                 # uint8 [rows, D] | int8 [rows, Dpad] | float32 [rows, Dpad]
-    norm: Optional[torch.Tensor]       # int32 [rows] | float32 [rows] | None
+    norm: Optional[torch.Tensor]       # L2_I8: int32 aux block (norms[rows], fold digits, info) | float32 [rows] | None
     rows: int
     width: int                         # D as passed to the C-ABI
 
@@ -93,7 +93,9 @@ class Engine:
             if force_kind != L.KIND_L2_F32:
                 Dpad = (D + 127) // 128 * 128
                 d8 = torch.empty((rows, Dpad), dtype=torch.int8, device=self.device)
-                nrm = torch.empty((rows,), dtype=torch.int32, device=self.device)
+                nb = ctypes.c_size_t(0)
+                L.check(self.lib.b200m_l2_i8_aux_bytes(rows, ctypes.byref(nb)), "b200m_l2_i8_aux_bytes")
+                nrm = torch.empty((nb.value // 4,), dtype=torch.int32, device=self.device)   # norms[rows] + fold digits + info
                 flag = torch.zeros((1,), dtype=torch.int32, device=self.device)
                 L.check(self.lib.b200m_prep_l2_i8(t.data_ptr(), rows, D, d8.data_ptr(), Dpad, nrm.data_ptr(),
                                                   flag.data_ptr(), self._stream()), "b200m_prep_l2_i8")

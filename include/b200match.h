@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 100
+#define B200M_VERSION 110
 
 #if defined(__GNUC__)
 #define B200M_API __attribute__((visibility("default")))
@@ -73,12 +73,17 @@ B200M_API int         b200m_device_info(int* sm_count, int* cc_major, int* cc_mi
  * this is the exact re-encoding SURVEY §7.1 step 4 calls the pre-pass).
  *   src   float32 [rows, D] row-major
  *   dst   int8    [rows, Dpad]  (Dpad = D rounded up to 128, zero padded), value = src - 128
- *   norms int32   [rows]        sum over D of (src-128)^2
+ *   aux   b200m_l2_i8_aux_bytes(rows) bytes, 256-byte aligned.  Starts with int32 norms[rows]
+ *         = sum over D of (src-128)^2; behind them the "folded norm" digits (32 int8 per row) that
+ *         let MODE_RATIO carry the train norm through the tensor cores, and 8 info words.  This
+ *         block is what b200m_match_pairs* / b200m_knn2_pairs take as q_norm / t_norm for L2_I8,
+ *         together with the same `rows` as q_rows / t_rows.
  *   not_integer  int32[1]       set to 1 if any element is not an integer in 0..255
  *                               (caller must then use the F32 kind); caller zeroes it first.
  */
+B200M_API int b200m_l2_i8_aux_bytes(int64_t rows, size_t* bytes);
 B200M_API int b200m_prep_l2_i8(const float* src, int64_t rows, int D, int8_t* dst, int Dpad,
-                     int32_t* norms, int32_t* not_integer, void* stream);
+                     void* aux, int32_t* not_integer, void* stream);
 
 /* Row squared norms for the F32 kind: norms[r] = sum_k src[r,k]^2 (fp32). */
 B200M_API int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream);
@@ -100,7 +105,8 @@ B200M_API int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t t
  *                    HAMMING: uint8 [rows, D]      (D = bytes per descriptor, any D >= 1)
  *                    L2_I8  : int8  [rows, D]      (D multiple of 128, from b200m_prep_l2_i8)
  *                    L2_F32 : float [rows, D]      (D multiple of 32 floats, D <= 256)
- *   q_norm/t_norm  L2_I8: int32 [rows]; L2_F32: float [rows]; HAMMING: NULL
+ *   q_norm/t_norm  L2_I8: the aux block of b200m_prep_l2_i8 (int32 norms first); L2_F32: float [rows];
+ *                  HAMMING: NULL
  *   q_rows/t_rows  number of rows in each store (bounds for TMA maps)
  *   pairs_host     HOST array of num_pairs descriptors (copied to the device workspace)
  *   mode, ratio    B200M_MODE_*; ratio used by MODE_RATIO only (fp64, as Python does at :216)

@@ -153,6 +153,71 @@ def test_l2_i8_extremes_and_ties(eng):
         assert_exact(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"ties {mode}")
 
 
+def _fold_flag(dd):
+    """info[3] of the aux block b200m_prep_l2_i8 wrote: 1 = MODE_RATIO runs the folded-norm kernel."""
+    rows = dd.rows
+    fold_off = (rows * 4 + 255) // 256 * 256
+    info_off = fold_off + (rows * 32 + 255) // 256 * 256
+    assert dd.norm.numel() * 4 == info_off + 256
+    return int(dd.norm[info_off // 4 + 3].item())
+
+
+def test_l2_i8_fold_digits_encode_the_norm(eng):
+    """sum_k c_k t_k == -(norm >> 1 - bias) for every row, c = {-128 x15, -1} x2 (prep.cu / common.cuh)."""
+    a, _ = synth.sift_pair(seed=77, n=3000)
+    dd = eng.prepare(a, b.NORM_L2)
+    assert dd.kind == b._lib.KIND_L2_I8 and _fold_flag(dd) == 1
+    rows = dd.rows
+    fold_off = (rows * 4 + 255) // 256 * 256
+    info_off = fold_off + (rows * 32 + 255) // 256 * 256
+    raw = dd.norm.cpu().numpy()
+    norms = raw[:rows].astype(np.int64)
+    want = ((a.astype(np.int64) - 128) ** 2).sum(1)
+    assert np.array_equal(norms, want)
+    digits = raw.view(np.int8)[fold_off:fold_off + rows * 32].reshape(rows, 32).astype(np.int64)
+    info = raw[info_off // 4: info_off // 4 + 4]
+    c = np.array(([-128] * 15 + [-1]) * 2, np.int64)
+    assert info[0] == (norms >> 1).min() and info[1] == (norms >> 1).max()
+    assert np.array_equal(digits @ c, -((norms >> 1) - int(info[2])))
+
+
+@pytest.mark.parametrize("ratio", [0.5, 0.9, 0.99, 1.0, 1.5])
+def test_l2_i8_fold_ratio_sweep_with_ties(eng, ratio):
+    """Folded-norm kernel + bounds/refine/exhaustive decision ladder of finalize: exact for any ratio, with exact
+    duplicates (d = 0), chunk-level ties and odd/even norms mixed."""
+    rng = np.random.default_rng(int(ratio * 100))
+    a = rng.integers(0, 4, size=(700, 128)).astype(np.float32)
+    c = np.concatenate([a[:150], a[100:250], rng.integers(0, 4, size=(1500, 128)).astype(np.float32)])
+    assert _fold_flag(eng.prepare(c, b.NORM_L2)) == 1
+    assert_exact(eng.match_arrays(a, c, b.NORM_L2, False, ratio), O.reference_match(a, c, O.NORM_L2, False, ratio),
+                 f"fold ties ratio={ratio}")
+    a, c = synth.sift_pair(seed=31, n=1500, m=1300)
+    assert_exact(eng.match_arrays(a, c, b.NORM_L2, False, ratio), O.reference_match(a, c, O.NORM_L2, False, ratio),
+                 f"fold sift ratio={ratio}")
+
+
+def test_l2_i8_fold_disabled_when_norm_spread_too_large(eng):
+    """Rows of all 0 (norm 2^21) next to rows of all 128 (norm 0): h spread > digit range -> keyed kernel, same answers."""
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, size=(400, 128)).astype(np.float32)
+    c = rng.integers(0, 256, size=(600, 128)).astype(np.float32)
+    c[:20] = 0.0
+    c[20:40] = 128.0
+    assert _fold_flag(eng.prepare(c, b.NORM_L2)) == 0
+    for mode in MODES:
+        assert_exact(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"no-fold {mode}")
+
+
+def test_l2_i8_fold_small_and_ragged(eng):
+    for seed, (n, m) in enumerate([(1, 1), (1, 2), (3, 64), (5, 65), (129, 257), (40, 1000), (700, 255), (256, 512)]):
+        a, c = synth.sift_pair(seed=400 + seed, n=max(n, m))
+        a, c = a[:n], np.ascontiguousarray(c[:m])
+        for ratio in (0.75, 0.95):
+            assert_exact(eng.match_arrays(a, c, b.NORM_L2, False, ratio), O.reference_match(a, c, O.NORM_L2, False, ratio),
+                         f"fold n={n} m={m} ratio={ratio}")
+
+
+
 def test_l2_i8_knn2_raw(eng):
     a, c = synth.sift_pair(seed=6, n=900, m=800)
     got = eng.knn2_arrays(a, c, b.NORM_L2)

@@ -10,7 +10,7 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libb200match.so")
+SO_PATH = os.environ.get("B200MATCH_SO") or os.path.join(HERE, "libb200match.so")   # override: experiment builds only
 
 OK, EINVAL, EWORKSPACE, ECUDA, ENODEVICE, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
 MODE_RATIO, MODE_CROSS, MODE_NN = 0, 1, 2

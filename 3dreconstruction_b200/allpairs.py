@@ -95,6 +95,7 @@ class AllPairsMatcher:
         self.engine = engine
         self.chunk_pairs = int(chunk_pairs)
         self._bufs = {}
+        self._streams = None
 
     def _buf(self, name: str, numel: int, dtype) -> torch.Tensor:
         t = self._bufs.get(name)
@@ -103,51 +104,86 @@ class AllPairsMatcher:
             self._bufs[name] = t
         return t
 
+    def _enqueue_chunk(self, store: Store, chunk: np.ndarray, mode: int, ratio: float, slot: int, stream_handle: int):
+        """Plan + enqueue one chunk of pairs on `stream_handle` into the buffers of `slot`; returns (C, optr, oq, ot, od)."""
+        eng, lib, dd = self.engine, self.engine.lib, store.dd
+        n_of = np.diff(store.offsets)
+        C = len(chunk)
+        rec = np.zeros(C, dtype=_PAIR_DTYPE)
+        rec["q_off"] = store.offsets[chunk[:, 0]]; rec["n"] = n_of[chunk[:, 0]]
+        rec["t_off"] = store.offsets[chunk[:, 1]]; rec["m"] = n_of[chunk[:, 1]]
+        arr = rec.ctypes.data_as(ctypes.POINTER(L.Pair))
+        tn, tm = int(rec["n"].sum(dtype=np.int64)), int(rec["m"].sum(dtype=np.int64))
+        mn, mm = int(rec["n"].max()), int(rec["m"].max())
+        nbytes = ctypes.c_size_t(0)
+        L.check(lib.b200m_workspace_bytes(dd.kind, mode, C, tn, tm, mn, mm, dd.width, ctypes.byref(nbytes)),
+                "b200m_workspace_bytes")
+        ws = self._buf(f"ws{slot}", max(nbytes.value, 1 << 20), torch.uint8)
+        oq = self._buf(f"q{slot}", tn, torch.int32); ot = self._buf(f"t{slot}", tn, torch.int32)
+        od = self._buf(f"d{slot}", tn, torch.float32); oc = self._buf(f"c{slot}", C, torch.int32)
+        optr = self._buf(f"p{slot}", C + 1, torch.int64)
+        with torch.cuda.device(eng.device):
+            rc = lib.b200m_match_pairs_csr(dd.kind, dd.desc.data_ptr(), 0 if dd.norm is None else dd.norm.data_ptr(),
+                                           dd.rows, dd.desc.data_ptr(), 0 if dd.norm is None else dd.norm.data_ptr(),
+                                           dd.rows, dd.width, arr, C, mode, ratio, oq.data_ptr(), ot.data_ptr(),
+                                           od.data_ptr(), oc.data_ptr(), optr.data_ptr(), ws.data_ptr(), ws.numel(),
+                                           stream_handle)
+        L.check(rc, "b200m_match_pairs_csr")      # the pair table was staged inside the call: `rec` may go away
+        return C, optr, oq, ot, od
+
     def match(self, store: Store, pairs: np.ndarray, cross_check: bool = False,
               ratio_threshold: Optional[float] = None) -> PairCSR:
-        """Returns a device-resident CSR over `pairs` (order preserved)."""
-        eng, lib, dd = self.engine, self.engine.lib, store.dd
+        """Returns a device-resident CSR over `pairs` (order preserved).
+
+        More than one chunk: chunks alternate between two side streams with their own workspaces, so that the
+        tail of chunk k (finalize, scan, sort, result copy, the host's size read-back) runs while the knn kernel
+        of chunk k+1 already occupies the SMs; the caller's stream waits for both at the end."""
+        eng = self.engine
         mode = mode_of(cross_check, ratio_threshold)
         ratio = float(ratio_threshold or 0.0)
-        n_of = np.diff(store.offsets)
         P = len(pairs)
-        outs_q, outs_t, outs_d, ptrs = [], [], [], []
-        base = 0
         dev = eng.device
-        for c0 in range(0, P, self.chunk_pairs):
-            chunk = pairs[c0:c0 + self.chunk_pairs]
-            C = len(chunk)
-            rec = np.zeros(C, dtype=_PAIR_DTYPE)
-            rec["q_off"] = store.offsets[chunk[:, 0]]; rec["n"] = n_of[chunk[:, 0]]
-            rec["t_off"] = store.offsets[chunk[:, 1]]; rec["m"] = n_of[chunk[:, 1]]
-            arr = rec.ctypes.data_as(ctypes.POINTER(L.Pair))
-            tn, tm = int(rec["n"].sum(dtype=np.int64)), int(rec["m"].sum(dtype=np.int64))
-            mn, mm = int(rec["n"].max()), int(rec["m"].max())
-            nbytes = ctypes.c_size_t(0)
-            L.check(lib.b200m_workspace_bytes(dd.kind, mode, C, tn, tm, mn, mm, dd.width, ctypes.byref(nbytes)),
-                    "b200m_workspace_bytes")
-            ws = eng._workspace(nbytes.value)
-            oq = self._buf("q", tn, torch.int32); ot = self._buf("t", tn, torch.int32)
-            od = self._buf("d", tn, torch.float32); oc = self._buf("c", C, torch.int32)
-            optr = self._buf("p", C + 1, torch.int64)
-            with torch.cuda.device(dev):
-                rc = lib.b200m_match_pairs_csr(dd.kind, dd.desc.data_ptr(), 0 if dd.norm is None else dd.norm.data_ptr(),
-                                               dd.rows, dd.desc.data_ptr(), 0 if dd.norm is None else dd.norm.data_ptr(),
-                                               dd.rows, dd.width, arr, C, mode, ratio, oq.data_ptr(), ot.data_ptr(),
-                                               od.data_ptr(), oc.data_ptr(), optr.data_ptr(), ws.data_ptr(), ws.numel(),
-                                               eng._stream())
-            L.check(rc, "b200m_match_pairs_csr")
-            if P <= self.chunk_pairs:          # single chunk: hand the buffers out without a copy
-                total = int(optr[C].item())
-                return PairCSR(pairs, optr[:C + 1].clone(), oq[:total].clone(), ot[:total].clone(), od[:total].clone())
-            total = int(optr[C].item())        # sync: the tight size of this chunk
-            outs_q.append(oq[:total].clone()); outs_t.append(ot[:total].clone()); outs_d.append(od[:total].clone())
-            ptrs.append(optr[:C] + base)
-            base += total
         if P == 0:
             z = torch.zeros(1, dtype=torch.int64, device=dev)
             e = torch.empty(0, dtype=torch.int32, device=dev)
             return PairCSR(pairs, z, e, e.clone(), torch.empty(0, dtype=torch.float32, device=dev))
+        if P <= self.chunk_pairs:              # single chunk on the caller's stream
+            C, optr, oq, ot, od = self._enqueue_chunk(store, pairs, mode, ratio, 0, eng._stream())
+            total = int(optr[C].item())
+            return PairCSR(pairs, optr[:C + 1].clone(), oq[:total].clone(), ot[:total].clone(), od[:total].clone())
+        cur = torch.cuda.current_stream(dev)
+        if self._streams is None:
+            self._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
+        for st in self._streams:
+            st.wait_stream(cur)
+        outs_q, outs_t, outs_d, ptrs = [], [], [], []
+        base = 0
+
+        def finish(slot, C, optr, oq, ot, od):
+            nonlocal base
+            with torch.cuda.stream(self._streams[slot]):
+                total = int(optr[C].item())    # waits for this chunk only; the next one is already enqueued
+                for lst, src in ((outs_q, oq), (outs_t, ot), (outs_d, od)):
+                    t = src[:total].clone()
+                    t.record_stream(cur)
+                    lst.append(t)
+                p = optr[:C] + base
+                p.record_stream(cur)
+                ptrs.append(p)
+            base += total
+
+        pending = None
+        for ci, c0 in enumerate(range(0, P, self.chunk_pairs)):
+            slot = ci & 1
+            with torch.cuda.stream(self._streams[slot]):
+                job = self._enqueue_chunk(store, pairs[c0:c0 + self.chunk_pairs], mode, ratio, slot,
+                                          self._streams[slot].cuda_stream)
+            if pending is not None:
+                finish(*pending)
+            pending = (slot, *job)
+        finish(*pending)
+        for st in self._streams:
+            cur.wait_stream(st)
         ptrs.append(torch.tensor([base], dtype=torch.int64, device=dev))
         return PairCSR(pairs, torch.cat(ptrs), torch.cat(outs_q), torch.cat(outs_t), torch.cat(outs_d))
 

@@ -33,15 +33,16 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, defs=(), so: str = SO, tag: str = "") -> str:
+    """defs/so/tag: experiment builds (extra -D flags into another .so); the product build uses none."""
+    if not force and not defs and not needs_build():
         return SO
     objs = []
     procs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for src in SOURCES:
-        obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
-        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(HERE, "build", src.replace(".cu", tag + ".o"))
+        cmd = [_nvcc(), *NVCC_FLAGS, *defs, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -55,11 +56,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if failed:
         raise RuntimeError("nvcc failed")
     # -cudart shared would need libcudart on the box; static cudart keeps the .so self-contained.
-    link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", SO, *objs,
+    link = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", so, *objs,
             "-Xcompiler", "-fPIC", "-cudart", "static"]
     subprocess.run(link, check=True)
-    return SO
+    return so
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    _defs = [a for a in sys.argv[1:] if a.startswith("-D")]
+    _tag = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--tag=")), "")
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, defs=_defs,
+                so=SO.replace(".so", _tag + ".so") if _tag else SO, tag=_tag))

@@ -264,7 +264,7 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         rc = launch_scan_offsets(pl, out_count, num_pairs, (long long*)out_ptr, st);
         if (rc != B200M_OK) return rc;
     }
-    return launch_sort_emit(kind, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, st);
+    return launch_sort_emit(mode, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, st);
 }
 
 int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,

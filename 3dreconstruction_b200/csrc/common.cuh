@@ -21,6 +21,11 @@ struct Top2 { u64 k1, k2; };
 // d^2 = ||a'||^2 + (||b'||^2 & 1) + 2 (bias - E): the epilogue needs no per-column constant at all.
 // 30 coarse digits (weight 128) and one fine digit (weight 1) cover h - bias in [XMIN, XMIN + SPREAD].
 #define B200M_FOLD_K 32
+#define B200M_FOLD_SLICES 4          // Top2 slices per column split the fold kernel writes (the keyed kernel: B200M_I8_GROUPS)
+#ifndef B200M_FOLD_CHUNK
+#define B200M_FOLD_CHUNK 16
+#endif
+//          // columns per chunk of the fold kernel (finalize recomputes one chunk per undecided row)
 #define B200M_FOLD_XMIN (-491520)     // -128 * 30 * 128
 #define B200M_FOLD_SPREAD 979327      // 127 * 30 * 128 + 127 - XMIN
 #define B200M_FOLD_VBIAS (1 << 24)    // Top2 value of a fold-kernel result = VBIAS - E  (|E| < 2^23)
@@ -102,7 +107,7 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
                     int32_t* counts, const RefineI8& rf, cudaStream_t st);
 int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
                         cudaStream_t st);
-int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
+int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
                      int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st);
 int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
                      float* d1, float* d2, const RefineI8& rf, cudaStream_t st);

@@ -358,13 +358,17 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 // =====================================================================================================
 // Folded-norm variant (MODE_RATIO): a fifth K step of 32 int8 dims carries -(||b'||^2 >> 1) + bias into the
 // accumulator (common.cuh, prep.cu), so the epilogue is a bare 3-input MAX tree over the TMEM values: no
-// column constants, no IMAD, no shared-memory loads.  Per 64-column chunk only the maximum E = a'.b' - h + bias
-// survives; the running top-2 of chunk maxima (value, chunk base) leaves the SM.  tail.cu recomputes the
+// column constants, no IMAD, no shared-memory loads.  Per 16-column chunk only the maximum E = a'.b' - h + bias
+// survives (fold chunks are B200M_FOLD_CHUNK = 16 columns); the running top-2 of chunk maxima (value, chunk base) leaves the SM.  tail.cu recomputes the
 // winner's chunk exactly (dp4a) for the rows whose ratio test is not already decided by the bounds
 //   d1 >= na + 2 (bias - E1),   d2 <= na + 1 + 2 (bias - E2).
 constexpr int X_BYTES = TN * B200M_FOLD_K;       // 8 KiB: fold digits of one train tile (SWIZZLE_32B rows)
 constexpr int AX_BYTES = TM * B200M_FOLD_K;      // 4 KiB: the constant query-side block
-constexpr int NBF = 4;                           // train K-block ring depth of the fold kernel
+static_assert(B200M_FOLD_CHUNK == 16, "the epilogue reduces 16-column chunks");
+constexpr int NBF = 4;
+constexpr int FOLD_SLICES = B200M_FOLD_SLICES;   // Top2 slices per column split = epilogue groups
+constexpr int FOLD_EPI_WARPS = 4 * FOLD_SLICES;
+constexpr int FOLD_THREADS = (CTRL_WARPS + FOLD_EPI_WARPS) * 32;                           // train K-block ring depth of the fold kernel
 
 struct SmemFold {
     uint8_t *a, *b, *x, *ax;
@@ -393,12 +397,13 @@ __host__ __device__ constexpr size_t smem_bytes_fold(int nkb) {
 }
 
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
-__device__ __forceinline__ int max32(const uint32_t (&v)[32]) {
-    int a[11];
-#pragma unroll
-    for (int t = 0; t < 10; ++t) a[t] = max3((int)v[3 * t], (int)v[3 * t + 1], (int)v[3 * t + 2]);
-    a[10] = max((int)v[30], (int)v[31]);
-    return max(max3(max3(a[0], a[1], a[2]), max3(a[3], a[4], a[5]), max3(a[6], a[7], a[8])), max(a[9], a[10]));
+// maximum of 16 consecutive accumulator columns v[O .. O+15] = one fold chunk: 8 three-input max instructions
+template <int O>
+__device__ __forceinline__ int max16(const uint32_t (&v)[32]) {
+    int a0 = max3((int)v[O + 0], (int)v[O + 1], (int)v[O + 2]), a1 = max3((int)v[O + 3], (int)v[O + 4], (int)v[O + 5]);
+    int a2 = max3((int)v[O + 6], (int)v[O + 7], (int)v[O + 8]), a3 = max3((int)v[O + 9], (int)v[O + 10], (int)v[O + 11]);
+    int a4 = max3((int)v[O + 12], (int)v[O + 13], (int)v[O + 14]);
+    return max(max3(a0, a1, a2), max3(a3, a4, (int)v[O + 15]));
 }
 __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // columns >= lim do not exist
 #pragma unroll
@@ -406,7 +411,7 @@ __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // colu
 }
 
 template <int NKB>
-__global__ void __launch_bounds__(THREADS, 1)
+__global__ void __launch_bounds__(FOLD_THREADS, 1)
 l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const __grid_constant__ CUtensorMap tmap_x, const int32_t* __restrict__ t_info,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S,
@@ -425,7 +430,7 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         sm100::tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
         for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], FOLD_EPI_WARPS / 2); }
         sm100::fence_barrier_init();
     }
     if (warp == W_CONST) {
@@ -519,11 +524,11 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             if (++ab == NABUF) { ab = 0; a_par ^= 1; }
         }
     } else if (warp >= CTRL_WARPS) {
-        // epilogue: two groups of 8 warps on alternate tiles (as in the keyed kernel), 128 columns per warp
+        // epilogue: two groups of 8 warps on alternate tiles (group g owns TMEM stage g); inside a group a warp drains
+        // 128 columns (half) of its 32 TMEM lanes: 32-column tcgen05.ld, two in flight while it reduces the previous two.
         const int e = warp - CTRL_WARPS;
         const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
-        const int slice = g * 2 + half;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * 2 * CHUNK;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * (TN / 2);
         uint32_t k = 0, tc_base = 0;
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
@@ -537,7 +542,7 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 i1 = gt1 ? base : i1;
             };
             for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
-                const int base = it.c_begin + j * TN + half * 2 * CHUNK;
+                const int base = it.c_begin + j * TN + half * (TN / 2);
                 const int lim = it.c_end - base;              // existing columns in this warp's 128 (tail tile: < 128)
                 sm100::mbar_wait(&sm.acc_full[g], k & 1);
                 sm100::tc_fence_after();
@@ -545,20 +550,20 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 sm100::tmem_ld32(taddr, acc[0]);
                 sm100::tmem_ld32(taddr + 32, acc[1]);
                 sm100::tmem_ld_wait();
-                if (lim < 2 * CHUNK) { mask32(acc[0], lim); mask32(acc[1], lim - 32); }
-                int m0 = max32(acc[0]);
+                if (lim < TN / 2) { mask32(acc[0], lim); mask32(acc[1], lim - 32); }
+                int m0 = max16<0>(acc[0]), m1 = max16<16>(acc[0]);
                 sm100::tmem_ld32(taddr + 64, acc[0]);
-                int m1 = max32(acc[1]);
+                int m2 = max16<0>(acc[1]), m3 = max16<16>(acc[1]);
                 sm100::tmem_ld32(taddr + 96, acc[1]);
-                insert(max(m0, m1), base);
-                sm100::tmem_ld_wait();
+                insert(m0, base); insert(m1, base + 16); insert(m2, base + 32); insert(m3, base + 48);
+                sm100::tmem_ld_wait();                        // everything is in registers: hand the TMEM stage back first
                 sm100::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
-                if (lim < 2 * CHUNK) { mask32(acc[0], lim - 64); mask32(acc[1], lim - 96); }
-                m0 = max32(acc[0]);
-                m1 = max32(acc[1]);
-                insert(max(m0, m1), base + CHUNK);
+                if (lim < TN / 2) { mask32(acc[0], lim - 64); mask32(acc[1], lim - 96); }
+                m0 = max16<0>(acc[0]); m1 = max16<16>(acc[0]);
+                m2 = max16<0>(acc[1]); m3 = max16<16>(acc[1]);
+                insert(m0, base + 64); insert(m1, base + 80); insert(m2, base + 96); insert(m3, base + 112);
             }
             tc_base += (uint32_t)it.ntiles;
             const int row = it.r0 + quarter * 32 + lane;
@@ -568,7 +573,7 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                                                            : (((u64)(u32)(B200M_FOLD_VBIAS - v)) << 32) | (u64)(u32)i;
                 };
                 Top2 t; t.k1 = mk(v1, i1); t.k2 = mk(v2, i2);
-                out[(long long)(it.split * NSLICE + slice) * total_rows + it.row_base + row] = t;
+                out[(long long)(it.split * FOLD_SLICES + g * 2 + half) * total_rows + it.row_base + row] = t;
             }
         }
     }
@@ -671,10 +676,10 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_top2_kernel launch");
     if (allow_fold) {
         if (nkb == 1)
-            l2_i8_fold_kernel<1><<<grid, THREADS, smem_bytes_fold(1), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
+            l2_i8_fold_kernel<1><<<grid, FOLD_THREADS, smem_bytes_fold(1), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
                                                                             S, out, total_rows);
         else
-            l2_i8_fold_kernel<2><<<grid, THREADS, smem_bytes_fold(2), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
+            l2_i8_fold_kernel<2><<<grid, FOLD_THREADS, smem_bytes_fold(2), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
                                                                             S, out, total_rows);
         b200m_count_launch();
         B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_fold_kernel launch");

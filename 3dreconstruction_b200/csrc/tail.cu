@@ -73,18 +73,6 @@ __device__ __forceinline__ void refine_i8_warp(bool need, int i, Top2& t, const 
 
 
 // ---- exact int8 distances for the folded-norm kernel's results (l2_i8.cu): whole-warp helpers -------------
-__device__ __forceinline__ u64 exact_key_i8(const int4* __restrict__ a, int nq, int col, const DevPair& pr,
-                                            const RefineI8& rf) {
-    const int4* b = reinterpret_cast<const int4*>(rf.t_desc + (long long)(pr.t_off + col) * rf.D);
-    int dot = 0;
-    for (int k = 0; k < rf.D / 16; ++k) {
-        int4 x = __ldg(a + k), y = __ldg(b + k);
-        dot = __dp4a(x.x, y.x, dot); dot = __dp4a(x.y, y.y, dot);
-        dot = __dp4a(x.z, y.z, dot); dot = __dp4a(x.w, y.w, dot);
-    }
-    const int d2i = nq + __ldg(rf.t_norm + pr.t_off + col) - 2 * dot;
-    return ((u64)(u32)d2i << 32) | (u64)(u32)col;
-}
 __device__ __forceinline__ void warp_merge_top2(u64& k1, u64& k2) {
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
@@ -93,14 +81,75 @@ __device__ __forceinline__ void warp_merge_top2(u64& k1, u64& k2) {
         top2_insert(k1, k2, o2);
     }
 }
-// exact top-2 of query row ri over train columns [c0, c1) of its pair (every lane returns the same pair of keys)
+// exact top-2 of query row ri over train columns [c0, c1) of its pair (every lane returns the same pair of keys).
+// Eight lanes share a column (16 bytes of the 128-byte row each: a load instruction reads four whole rows,
+// fully coalesced), partial dot products meet by three butterfly shuffles.  D == 128 * nkb, nkb <= 2.
 __device__ __forceinline__ void warp_exact_top2_i8(int ri, int c0, int c1, const DevPair& pr, const RefineI8& rf,
                                                    u64& k1, u64& k2) {
-    const int lane = threadIdx.x & 31;
-    const int4* a = reinterpret_cast<const int4*>(rf.q_desc + (long long)(pr.q_off + ri) * rf.D);
+    const int lane = threadIdx.x & 31, part = lane & 7, sub = lane >> 3;
+    const int8_t* qrow = rf.q_desc + (long long)(pr.q_off + ri) * rf.D;
+    const int nq = __ldg(rf.q_norm + pr.q_off + ri);
+    const int nkb = rf.D >> 7;
+    int4 a0 = __ldg(reinterpret_cast<const int4*>(qrow) + part), a1 = make_int4(0, 0, 0, 0);
+    if (nkb > 1) a1 = __ldg(reinterpret_cast<const int4*>(qrow + 128) + part);
+    k1 = B200M_SENTINEL; k2 = B200M_SENTINEL;
+    for (int cb = c0; cb < c1; cb += 4) {
+        const int col = cb + sub;
+        const bool ok = col < c1;
+        const int8_t* trow = rf.t_desc + (long long)(pr.t_off + (ok ? col : c0)) * rf.D;
+        int4 y = __ldg(reinterpret_cast<const int4*>(trow) + part);
+        int dot = __dp4a(a0.x, y.x, 0);
+        dot = __dp4a(a0.y, y.y, dot); dot = __dp4a(a0.z, y.z, dot); dot = __dp4a(a0.w, y.w, dot);
+        if (nkb > 1) {
+            y = __ldg(reinterpret_cast<const int4*>(trow + 128) + part);
+            dot = __dp4a(a1.x, y.x, dot); dot = __dp4a(a1.y, y.y, dot);
+            dot = __dp4a(a1.z, y.z, dot); dot = __dp4a(a1.w, y.w, dot);
+        }
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        if (ok && part == 0) {
+            const int d2i = nq + __ldg(rf.t_norm + pr.t_off + col) - 2 * dot;
+            top2_insert(k1, k2, ((u64)(u32)d2i << 32) | (u64)(u32)col);
+        }
+    }
+    warp_merge_top2(k1, k2);
+}
+
+// The same for one fold chunk [c0, c0 + B200M_FOLD_CHUNK) clipped to the pair: the chunk's B200M_FOLD_CHUNK / 4 row
+// loads are issued back to back (rows past the end re-read row c0 and are dropped), so a row costs one memory round trip.
+__device__ __forceinline__ void warp_exact_top2_chunk_i8(int ri, int c0, const DevPair& pr, const RefineI8& rf,
+                                                         u64& k1, u64& k2) {
+    constexpr int IT = B200M_FOLD_CHUNK / 4;
+    const int lane = threadIdx.x & 31, part = lane & 7, sub = lane >> 3;
+    const int8_t* qrow = rf.q_desc + (long long)(pr.q_off + ri) * rf.D;
+    const int nkb = rf.D >> 7;
+    int4 a0 = __ldg(reinterpret_cast<const int4*>(qrow) + part), a1 = make_int4(0, 0, 0, 0);
+    if (nkb > 1) a1 = __ldg(reinterpret_cast<const int4*>(qrow + 128) + part);
+    int4 y0[IT], y1[IT];
+    int nt[IT];
+#pragma unroll
+    for (int t = 0; t < IT; ++t) {
+        const int col = c0 + 4 * t + sub;
+        const int8_t* trow = rf.t_desc + (long long)(pr.t_off + (col < pr.m ? col : c0)) * rf.D;
+        y0[t] = __ldg(reinterpret_cast<const int4*>(trow) + part);
+        y1[t] = nkb > 1 ? __ldg(reinterpret_cast<const int4*>(trow + 128) + part) : make_int4(0, 0, 0, 0);
+        nt[t] = __ldg(rf.t_norm + pr.t_off + (col < pr.m ? col : c0));
+    }
     const int nq = __ldg(rf.q_norm + pr.q_off + ri);
     k1 = B200M_SENTINEL; k2 = B200M_SENTINEL;
-    for (int col = c0 + lane; col < c1; col += 32) top2_insert(k1, k2, exact_key_i8(a, nq, col, pr, rf));
+#pragma unroll
+    for (int t = 0; t < IT; ++t) {
+        int dot = __dp4a(a0.x, y0[t].x, 0);
+        dot = __dp4a(a0.y, y0[t].y, dot); dot = __dp4a(a0.z, y0[t].z, dot); dot = __dp4a(a0.w, y0[t].w, dot);
+        dot = __dp4a(a1.x, y1[t].x, dot); dot = __dp4a(a1.y, y1[t].y, dot);
+        dot = __dp4a(a1.z, y1[t].z, dot); dot = __dp4a(a1.w, y1[t].w, dot);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        const int col = c0 + 4 * t + sub;
+        if (col < pr.m && part == 0) top2_insert(k1, k2, ((u64)(u32)(nq + nt[t] - 2 * dot) << 32) | (u64)(u32)col);
+    }
     warp_merge_top2(k1, k2);
 }
 
@@ -110,7 +159,7 @@ __device__ __forceinline__ bool ratio_pass_i8(double ratio, int v1, int v2) {   
 }
 
 // MODE_RATIO on fold-kernel results.  t holds the top-2 CHUNKS by E = a'.b' - h + bias (value = VBIAS - E, index =
-// first column of the 64-column chunk).  With p = ||b'||^2 & 1 of the column, d^2 = nq + p + 2 (bias - E), so a chunk
+// first column of the 16-column chunk).  With p = ||b'||^2 & 1 of the column, d^2 = nq + p + 2 (bias - E), so a chunk
 // value brackets its best column's distance within {lb, lb + 1}.  Rows are decided, in this order, by
 //   (1) bounds only: d1 >= lb(E1), d2 <= lb(E2) + 1 and the test is monotone -> most rows fail here, untouched;
 //   (2) exact recomputation of the winner's chunk (E1 > E2: the best column is in it): d1 exact, and d2 is either
@@ -144,7 +193,7 @@ __device__ __forceinline__ bool fold_ratio_warp(bool has, int i, Top2& t, double
         const int ri = __shfl_sync(0xffffffffu, i, src);
         const int c0 = __shfl_sync(0xffffffffu, (int)(u32)t.k1, src);
         u64 x1, x2;
-        warp_exact_top2_i8(ri, c0, min(c0 + B200M_I8_CHUNK, pr.m), pr, rf, x1, x2);
+        warp_exact_top2_chunk_i8(ri, c0, pr, rf, x1, x2);
         if (lane == src) { a1 = x1; a2 = x2; }
     }
     bool keep = false, full = false;
@@ -190,8 +239,9 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
     DevPair pr = pairs[p];
     const bool active = i < pr.n;
     Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
-    if (active) t = merge_splits(fwd, total_n, S, pr.fwd_off + i);
     const bool fold = kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO && rf.t_info && __ldg(rf.t_info + 3);
+    // S counts Top2 slices: splits x B200M_I8_GROUPS for the keyed L2_I8 kernel, splits x B200M_FOLD_SLICES when the fold kernel ran
+    if (active) t = merge_splits(fwd, total_n, fold ? S / B200M_I8_GROUPS * B200M_FOLD_SLICES : S, pr.fwd_off + i);
     bool keep_fold = false;
     if (fold) {                                                      // grid-uniform branch
         keep_fold = fold_ratio_warp(t.k1 != B200M_SENTINEL, i, t, ratio, pr, rf);
@@ -238,9 +288,9 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
         sortbuf[pr.sort_off + i] = key;
         tbest[pr.fwd_off + i] = tb;
     }
-    if (counts) {                                   // CSR mode: survivors per pair (block = one pair)
-        int c = __syncthreads_count(key != B200M_SENTINEL);
-        if (threadIdx.x == 0 && c) atomicAdd(&counts[p], c);
+    if (counts) {                                   // CSR mode: survivors per pair (a block never spans pairs);
+        int c = __popc(__ballot_sync(0xffffffffu, key != B200M_SENTINEL));   // per warp: no block barrier, warps retire alone
+        if ((threadIdx.x & 31) == 0 && c) atomicAdd(&counts[p], c);
     }
 }
 
@@ -252,8 +302,8 @@ scan_offsets_kernel(DevPair* __restrict__ pairs, const int32_t* __restrict__ cou
     __shared__ long long carry;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (int base = 0; base < num_pairs; base += 1024) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int base = 0; base < num_pairs; base += blockDim.x) {
         int p = base + threadIdx.x;
         long long v = p < num_pairs ? counts[p] : 0, x = v;
 #pragma unroll
@@ -264,7 +314,7 @@ scan_offsets_kernel(DevPair* __restrict__ pairs, const int32_t* __restrict__ cou
         if (lane == 31) warp_sums[w] = x;
         __syncthreads();
         if (w == 0) {
-            long long y = warp_sums[lane];
+            long long y = lane < nw ? warp_sums[lane] : 0;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
                 long long o = __shfl_up_sync(0xffffffffu, y, off);
@@ -276,7 +326,7 @@ scan_offsets_kernel(DevPair* __restrict__ pairs, const int32_t* __restrict__ cou
         long long excl = carry + (w ? warp_sums[w - 1] : 0) + x - v;
         if (p < num_pairs) { pairs[p].out_off = excl; out_ptr[p] = excl; }
         __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
+        if (threadIdx.x == blockDim.x - 1) carry = excl + v;
         __syncthreads();
     }
     if (threadIdx.x == 0) out_ptr[num_pairs] = carry;
@@ -310,29 +360,26 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
     __syncthreads();
     u64* a;
     int sort_n;
-    if (npad <= smem_keys) {
-        // compact the survivors into shared memory first (order is irrelevant before the sort): the bitonic
-        // network then runs over pow2ceil(#survivors) keys instead of pow2ceil(n)
-        a = skeys;
-        for (int t = threadIdx.x; t < n; t += blockDim.x) {
-            u64 k = g[t];
-            if (k != B200M_SENTINEL) a[atomicAdd(&s_count, 1)] = k;
+    // compact the survivors into shared memory (order is irrelevant before the sort): the bitonic network then runs
+    // over pow2ceil(#survivors) keys instead of pow2ceil(n), and the block needs only a small shared-memory slice
+    for (int t = threadIdx.x; t < n; t += blockDim.x) {
+        u64 k = g[t];
+        if (k != B200M_SENTINEL) {
+            int slot = atomicAdd(&s_count, 1);
+            if (slot < smem_keys) skeys[slot] = k;
         }
-        __syncthreads();
+    }
+    __syncthreads();
+    if (s_count <= smem_keys) {
+        a = skeys;
         sort_n = 1;
         while (sort_n < s_count) sort_n <<= 1;
         for (int t = s_count + threadIdx.x; t < sort_n; t += blockDim.x) a[t] = B200M_SENTINEL;
         __syncthreads();
-    } else {                                            // oversized pair: sort in place in global memory
+    } else {                                            // more survivors than the slice holds: sort in place in global memory
         a = g;
         sort_n = npad;
-        int local = 0;
-        for (int t = threadIdx.x; t < npad; t += blockDim.x) {
-            u64 k = t < n ? g[t] : B200M_SENTINEL;
-            local += (k != B200M_SENTINEL);
-            if (t >= n) a[t] = k;
-        }
-        if (local) atomicAdd(&s_count, local);
+        for (int t = n + threadIdx.x; t < npad; t += blockDim.x) a[t] = B200M_SENTINEL;
         __syncthreads();
     }
     if (sort_n > 1) bitonic(a, sort_n);
@@ -373,7 +420,7 @@ knn2_emit_kernel(int kind, const DevPair* __restrict__ pairs, int blocks_per_pai
 
 int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
                         cudaStream_t st) {
-    scan_offsets_kernel<<<1, 1024, 0, st>>>(plan.pairs, counts, num_pairs, out_ptr);
+    scan_offsets_kernel<<<1, 256, 0, st>>>(plan.pairs, counts, num_pairs, out_ptr);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "scan_offsets_kernel launch");
     return B200M_OK;
@@ -381,20 +428,21 @@ int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pa
 
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
                     int32_t* counts, const RefineI8& rf, cudaStream_t st) {
-    int bpp = (max_n + 255) / 256;
+    // 128-thread blocks: small enough to share an SM with the persistent knn kernel of the next chunk
+    const int threads = 128;
+    int bpp = (max_n + threads - 1) / threads;
     long long grid = (long long)num_pairs * bpp;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    finalize_kernel<<<(unsigned)grid, 256, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
+    finalize_kernel<<<(unsigned)grid, threads, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
                                                     plan.bwd, plan.total_m, plan.slices, plan.sortbuf, plan.tbest, counts, rf, plan.colmin);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "finalize_kernel launch");
     return B200M_OK;
 }
 
-int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
+int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
                      int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st) {
-    (void)kind;
     if (num_pairs <= 0) return B200M_OK;
     static bool attr_set = false;
     const int kMaxSmemKeys = 16384;                       // 128 KiB of 64-bit keys
@@ -403,8 +451,12 @@ int launch_sort_emit(int kind, const MatchPlan& plan, int num_pairs, int max_npa
                                               kMaxSmemKeys * (int)sizeof(u64)), "sort_emit smem attr");
         attr_set = true;
     }
-    int smem_keys = max_npad <= kMaxSmemKeys ? max_npad : kMaxSmemKeys;
-    int threads = max_npad >= 2048 ? 1024 : (max_npad >= 512 ? 256 : 64);
+    // MODE_RATIO keeps a few percent of the rows: a 16 KiB slice (2048 keys) and 256 threads are enough, and such a
+    // block fits beside a resident knn CTA of the next chunk.  The other modes keep most rows: big slice, 1024 threads.
+    const bool few = mode == B200M_MODE_RATIO;
+    const int cap = few ? 2048 : kMaxSmemKeys;
+    int smem_keys = max_npad <= cap ? max_npad : cap;
+    int threads = max_npad >= 2048 && !few ? 1024 : (max_npad >= 512 ? 256 : 64);
     sort_emit_kernel<<<num_pairs, threads, (size_t)smem_keys * sizeof(u64), st>>>(
         plan.pairs, plan.sortbuf, plan.tbest, smem_keys, out_q, out_t, out_d, out_count);
     b200m_count_launch();

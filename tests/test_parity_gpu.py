@@ -209,7 +209,7 @@ def test_l2_i8_fold_disabled_when_norm_spread_too_large(eng):
 
 
 def test_l2_i8_fold_small_and_ragged(eng):
-    for seed, (n, m) in enumerate([(1, 1), (1, 2), (3, 64), (5, 65), (129, 257), (40, 1000), (700, 255), (256, 512)]):
+    for seed, (n, m) in enumerate([(1, 1), (1, 2), (2, 16), (2, 17), (4, 33), (3, 64), (5, 65), (129, 257), (40, 1000), (700, 255), (256, 512)]):
         a, c = synth.sift_pair(seed=400 + seed, n=max(n, m))
         a, c = a[:n], np.ascontiguousarray(c[:m])
         for ratio in (0.75, 0.95):

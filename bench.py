@@ -30,7 +30,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 RATIO = 0.75
-HW_INT8_TOPS = 4590.0      # measured issue-rate peak of tcgen05.mma kind::i8 (tools/mma_peak.cu)
+HW_INT8_TOPS = 4590.0
+NCU_DRAM_BYTES_PER_PAIR = (468.655872e6 + 539.030272e6) / 1128.0     # profiles/r01_l2i8_v8_fold_ncu_full.md      # measured issue-rate peak of tcgen05.mma kind::i8 (tools/mma_peak.cu)
 
 
 def parse_args():
@@ -433,7 +434,8 @@ def run_b200(args):
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "int8", "data": "synthetic", "config": workload_config(args),
                 "matches_per_step": matches_total if world == 1 else None,
-                "roofline": {"bound": "tensor", "kernel": "l2_i8_top2_kernel (tcgen05 kind::i8)", "achieved": achieved,
+                "roofline": {"bound": "tensor", "kernel": "l2_i8_fold_kernel (tcgen05 kind::i8 M128 N256; 4 descriptor K-steps + 1 folded-norm K-step, "
+                                                        "achieved counts the 4 algorithmic ones)", "achieved": achieved,
                              "peak": peak, "unit": "TOP/s int8 (TFLOP/s-equivalent)", "frac": achieved / peak if achieved else None,
                              "peak_source": f"2 x bf16_tflops_sustained of {pk_src} MEASURED_PEAKS.json (int8 peak not measured by the driver)",
                              "peak_hw_int8_microbench": HW_INT8_TOPS,
@@ -443,8 +445,12 @@ def run_b200(args):
                                                "ncu's sm__ops_path_tensor_op_utcimma pct uses the same hardware rate",
                              "kernel_ms_per_step": knn_ms.value / args.steps, "kernel_launches": knn_launches.value,
                              "kernel_share_of_step": knn_ms.value / ms_total if world == 1 else None,
-                             "algorithmic_ops_per_pair": 2.0 * n * n * D, "algorithmic_hbm_bytes_per_pair": 2 * n * D + 12 * n,
-                             "traffic": None},
+                             "algorithmic_ops_per_pair": 2.0 * n * n * D,
+                             "algorithmic_hbm_bytes_per_pair": 2 * n * (D + 36) + 64 * n,
+                             "traffic": NCU_DRAM_BYTES_PER_PAIR * my_pairs * args.steps / max(knn_launches.value, 1),
+                             "traffic_source": "ncu --set full of l2_i8_fold_kernel, 1128-pair launch: dram read 468.7 MB + write 539.0 MB "
+                                               "(profiles/r01_l2i8_v8_fold_ncu_full.md) = 0.893 MB/pair, scaled to this run's pairs per launch; "
+                                               "the write side is the 4 x 16 B Top2 slices per query row (0.52 MB/pair)"},
                 "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel() * 4),
                         "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                         "path": "pinned host float32 descriptors -> H2D -> b200m_prep_l2_i8 -> b200m_match_pairs_csr -> D2H CSR"},

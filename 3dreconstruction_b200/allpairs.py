@@ -188,6 +188,134 @@ class AllPairsMatcher:
         return PairCSR(pairs, torch.cat(ptrs), torch.cat(outs_q), torch.cat(outs_t), torch.cat(outs_d))
 
 
+class StreamingAllPairs:
+    """All pairs of ONE host-resident set of integer-valued float32 descriptors (SIFT), with the upload hidden
+    behind the matching: images go up in groups on a copy stream (pinned host -> HBM -> b200m_prep_l2_i8_rows),
+    and as soon as group g is resident the pairs (i < j, j in group g) are matched, chunk by chunk, on two
+    compute streams; each chunk's CSR goes back to pinned host memory as it completes.
+
+    The result is a host PairCSR whose `pairs` are in PROCESSING order (by group of j, then j, then i) — the same
+    set as itertools.combinations, permuted (look a pair up through `pairs`).  Its arrays are views of a pinned
+    arena owned by this object: valid until the next match_host() call.
+    Single GPU only; anything that is not integer-valued 0..255 falls back to build_store + AllPairsMatcher."""
+
+    def __init__(self, engine: Engine, chunk_pairs: int = 2048, group_images: int = 25):
+        self.engine = engine
+        self.matcher = AllPairsMatcher(engine, chunk_pairs)
+        self.group_images = int(group_images)
+        self._copy_stream = None
+        self._pinned = {}
+        self._dev = {}
+
+    def _host_buf(self, name: str, numel: int, dtype) -> torch.Tensor:
+        t = self._pinned.get(name)
+        if t is None or t.numel() < numel:
+            new = torch.empty(max(numel, 1 << 22, 0 if t is None else 2 * t.numel()), dtype=dtype, pin_memory=True)
+            if t is not None:
+                torch.cuda.synchronize(self.engine.device)     # copies into the old arena must have landed
+                new[:t.numel()].copy_(t)           # growth keeps what is already there
+            self._pinned[name] = t = new
+        return t
+
+    @staticmethod
+    def group_major_pairs(num_images: int, group_images: int):
+        """[(j_end, pairs[K,2])]: for every group of images [j0, j_end), the pairs (i, j), i < j, j in the group."""
+        out = []
+        for j0 in range(0, num_images, group_images):
+            j1 = min(num_images, j0 + group_images)
+            js = np.arange(max(j0, 1), j1)
+            if len(js) == 0:
+                continue
+            i = np.concatenate([np.arange(0, j) for j in js])
+            j = np.repeat(js, js)
+            out.append((j1, np.stack([i, j], axis=1).astype(np.int32)))
+        return out
+
+    def match_host(self, host: torch.Tensor, counts: Sequence[int], ratio_threshold: Optional[float] = None,
+                   cross_check: bool = False) -> PairCSR:
+        eng, mt = self.engine, self.matcher
+        dev = eng.device
+        counts = [int(c) for c in counts]
+        I = len(counts)
+        offsets = np.zeros(I + 1, np.int64)
+        np.cumsum(counts, out=offsets[1:])
+        rows, D = int(offsets[-1]), int(host.shape[1])
+        assert host.dtype == torch.float32 and host.shape[0] == rows
+        mode = mode_of(cross_check, ratio_threshold)
+        ratio = float(ratio_threshold or 0.0)
+        cur = torch.cuda.current_stream(dev)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        if mt._streams is None:
+            mt._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
+        cs = self._copy_stream
+        key = (rows, D)
+        if self._dev.get("key") != key:                 # device staging + store, reused across calls of the same shape
+            self._dev = {"key": key, "f32": torch.empty((rows, D), dtype=torch.float32, device=dev)}
+        cs.wait_stream(cur)
+        with torch.cuda.stream(cs):
+            dd, flag = eng.alloc_l2_i8_store(rows, D)
+        store = Store(dd, offsets, NORM_L2)
+        for st in mt._streams:
+            st.wait_stream(cur)
+
+        plan = self.group_major_pairs(I, self.group_images)
+        P = sum(len(p) for _, p in plan)
+        ptr_host = np.zeros(P + 1, np.int64)
+        pairs_out = np.concatenate([p for _, p in plan]) if plan else np.zeros((0, 2), np.int32)
+        state = {"base": 0, "pbase": 0}
+        f32 = self._dev["f32"]
+
+        def finish(slot, C, optr, oq, ot, od):
+            st = mt._streams[slot]
+            with torch.cuda.stream(st):
+                cnts = optr[:C + 1].cpu().numpy()      # waits for this chunk only
+                total = int(cnts[C])
+                b0 = state["base"]
+                for name, src, dt in (("q", oq, torch.int32), ("t", ot, torch.int32), ("d", od, torch.float32)):
+                    self._host_buf(name, b0 + total, dt)[b0:b0 + total].copy_(src[:total], non_blocking=True)
+            ptr_host[state["pbase"]:state["pbase"] + C] = cnts[:C] + b0
+            state["base"] = b0 + total
+            state["pbase"] += C
+
+        pending = None
+        ci = 0
+        uploaded = 0                                     # images whose upload + prep is enqueued
+        for j_end, gp in plan:
+            with torch.cuda.stream(cs):                  # upload + re-encode images [uploaded, j_end)
+                r0, r1 = int(offsets[uploaded]), int(offsets[j_end])
+                f32[r0:r1].copy_(host[r0:r1], non_blocking=True)
+                eng.prepare_l2_i8_rows(dd, flag, f32[r0:r1], r0)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+            uploaded = j_end
+            for st in mt._streams:
+                st.wait_event(ev)
+            for c0 in range(0, len(gp), mt.chunk_pairs):
+                slot = ci & 1
+                ci += 1
+                with torch.cuda.stream(mt._streams[slot]):
+                    job = mt._enqueue_chunk(store, gp[c0:c0 + mt.chunk_pairs], mode, ratio, slot,
+                                            mt._streams[slot].cuda_stream)
+                if pending is not None:
+                    finish(*pending)
+                pending = (slot, *job)
+        if pending is not None:
+            finish(*pending)
+        for st in mt._streams + [cs]:
+            cur.wait_stream(st)
+        cur.synchronize()                                # results are host arrays: the D2H copies must have landed
+        if int(flag.item()) != 0:                        # not integer-valued: the int8 encoding is not exact -> generic path
+            st2 = build_store(eng, host.to(dev), NORM_L2, counts=counts)
+            return self.matcher.match(st2, pairs_out, cross_check, ratio_threshold).to_host()
+        total = state["base"]
+        ptr_host[P] = total
+        q = self._host_buf("q", total, torch.int32)[:total].numpy()
+        t = self._host_buf("t", total, torch.int32)[:total].numpy()
+        d = self._host_buf("d", total, torch.float32)[:total].numpy()
+        return PairCSR(pairs_out, ptr_host, q, t, d)
+
+
 # ---------------------------------------------------------------------------------- multi-GPU
 def broadcast_store(store: Optional[Store], norm_type: int, device: torch.device, src: int = 0) -> Store:
     """Broadcast the packed store (descriptors, norms, offsets) from `src` to every rank."""

@@ -12,15 +12,23 @@
 
 namespace {
 
+// One warp per row.  `row0` = first row of this call inside the store (incremental uploads prepare row ranges);
+// src holds only the call's rows.  Besides the int8 row and its norm the warp writes the row's folded-norm digits
+// (common.cuh): t with sum_k c_k t_k = -(h - bias), c = {-128 x15, -1} x2, h = norm >> 1.  bias is a constant of
+// the descriptor width (info[2], set by fold_init_kernel): the digit range is anchored at the largest possible h,
+// so it covers every row whose norm is above ~13 % of the maximum (SIFT-like rows always are); a row below that
+// clears info[3] and the matcher then uses the keyed kernel for this store.
 __global__ void __launch_bounds__(256)
-prep_l2_i8_kernel(const float* __restrict__ src, long long rows, int D, int8_t* __restrict__ dst, int Dpad,
-                  int32_t* __restrict__ norms, int32_t* __restrict__ not_integer, int32_t* __restrict__ info) {
+prep_l2_i8_kernel(const float* __restrict__ src, long long row0, long long rows, int D, int8_t* __restrict__ dst, int Dpad,
+                  int32_t* __restrict__ norms, int8_t* __restrict__ fold, int32_t* __restrict__ not_integer,
+                  int32_t* __restrict__ info) {
     __shared__ int s_min[8], s_max[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    long long row = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
-    const bool valid = row < rows;
-    if (!valid) row = rows - 1;                       // recompute the last row: keeps the block barrier simple
-    const float* s = src + row * D;
+    long long r = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
+    const bool valid = r < rows;
+    if (!valid) r = rows - 1;                         // recompute the last row: keeps the block barrier simple
+    const float* s = src + r * D;
+    const long long row = row0 + r;
     int8_t* d = dst + row * Dpad;
     int acc = 0, bad = 0;
     // Dpad is a multiple of 128: each lane converts 4 consecutive elements per step.
@@ -31,9 +39,9 @@ prep_l2_i8_kernel(const float* __restrict__ src, long long rows, int D, int8_t* 
             int kk = k + e;
             if (kk < D) {
                 float f = __ldg(s + kk);
-                float r = rintf(f);
-                bad |= !(f == r && r >= 0.0f && r <= 255.0f);
-                int iv = (int)fminf(fmaxf(r, 0.0f), 255.0f) - 128;
+                float rr = rintf(f);
+                bad |= !(f == rr && rr >= 0.0f && rr <= 255.0f);
+                int iv = (int)fminf(fmaxf(rr, 0.0f), 255.0f) - 128;
                 v[e] = iv;
                 acc += iv * iv;
             } else {
@@ -49,13 +57,35 @@ prep_l2_i8_kernel(const float* __restrict__ src, long long rows, int D, int8_t* 
         acc += __shfl_xor_sync(0xffffffffu, acc, off);
         bad |= __shfl_xor_sync(0xffffffffu, bad, off);
     }
+    // fold digits: lanes 0..7 each build one 32-bit word (4 digits) of the row's 32-byte block
+    const int h = acc >> 1;
+    int x = h - __ldg(info + 2);
+    const bool fits = x >= B200M_FOLD_XMIN && x <= B200M_FOLD_XMIN + B200M_FOLD_SPREAD;
+    x = min(max(x, B200M_FOLD_XMIN), B200M_FOLD_XMIN + B200M_FOLD_SPREAD);     // clamped digits are never used (flag)
+    const int S = x >> 7, F = x & 127;                 // x = 128 S + F, S in [-3840, 3810]
+    int a = S / 30, b = S - a * 30;
+    if (b < 0) { b += 30; a -= 1; }                    // floor division: S = 30 a + b, 0 <= b < 30
+    if (lane < 8) {
+        u32 word = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const int k = 4 * lane + e;                // K position; coarse digit index skips positions 15 and 31
+            int v;
+            if (k == 15) v = F;
+            else if (k == 31) v = 0;
+            else { const int ci = k < 15 ? k : k - 1; v = a + (ci < b ? 1 : 0); }
+            word |= (u32)(v & 0xff) << (8 * e);
+        }
+        reinterpret_cast<u32*>(fold + row * B200M_FOLD_K)[lane] = word;
+    }
     if (lane == 0) {
         if (valid) norms[row] = acc;
         if (bad) atomicOr(not_integer, 1);
-        s_min[warp] = s_max[warp] = acc >> 1;
+        if (!fits) atomicAnd(info + 3, 0);
+        s_min[warp] = s_max[warp] = h;
     }
     __syncthreads();
-    if (threadIdx.x == 0) {                           // range of h = norm >> 1 over the store, for the fold digits
+    if (threadIdx.x == 0) {                           // range of h over the store (diagnostics, tests)
         int lo = s_min[0], hi = s_max[0];
         for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { lo = min(lo, s_min[w]); hi = max(hi, s_max[w]); }
         atomicMin(info + 0, lo);
@@ -63,45 +93,11 @@ prep_l2_i8_kernel(const float* __restrict__ src, long long rows, int D, int8_t* 
     }
 }
 
-__global__ void fold_init_kernel(int32_t* __restrict__ info) {
-    info[0] = 0x7fffffff; info[1] = (int)0x80000000; info[2] = 0; info[3] = 0;
-}
-
-// Digits of the folded-norm K block (common.cuh): row r gets t with  sum_k c_k t_k = -(h_r - bias),
-// c = {-128 x15, -1} x2.  bias = min h - XMIN so that the smallest h sits at the bottom of the digit range;
-// info[3] says whether the largest h still fits (else the matcher uses the keyed kernel for this store).
-__global__ void __launch_bounds__(256)
-fold_encode_kernel(const int32_t* __restrict__ norms, long long rows, int8_t* __restrict__ fold,
-                   int32_t* __restrict__ info) {
-    const int hmin = info[0], hmax = info[1];
-    const int bias = hmin - B200M_FOLD_XMIN;
-    const bool ok = (long long)hmax - hmin <= B200M_FOLD_SPREAD;
-    long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row == 0) { info[2] = bias; info[3] = ok ? 1 : 0; }
-    if (row >= rows) return;
-    int x = (norms[row] >> 1) - bias;
-    x = min(max(x, B200M_FOLD_XMIN), B200M_FOLD_XMIN + B200M_FOLD_SPREAD);     // only clamps when !ok (digits unused then)
-    const int S = x >> 7, F = x & 127;                 // x = 128 S + F, S in [-3840, 3810]
-    int a = S / 30, b = S - a * 30;
-    if (b < 0) { b += 30; a -= 1; }                    // floor division: S = 30 a + b, 0 <= b < 30
-    u32 w[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        u32 word = 0;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const int k = 4 * i + e;                   // K position; coarse digit index skips positions 15 and 31
-            int v;
-            if (k == 15) v = F;
-            else if (k == 31) v = 0;
-            else { const int ci = k < 15 ? k : k - 1; v = a + (ci < b ? 1 : 0); }
-            word |= (u32)(v & 0xff) << (8 * e);
-        }
-        w[i] = word;
-    }
-    uint4* dst = reinterpret_cast<uint4*>(fold + row * B200M_FOLD_K);
-    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+// info words of a fresh aux block: [0] min h, [1] max h, [2] bias, [3] digits usable.  D == 0: an empty store (unusable).
+__global__ void fold_init_kernel(int32_t* __restrict__ info, int D) {
+    info[0] = 0x7fffffff; info[1] = (int)0x80000000;
+    info[2] = D * 8192 - (B200M_FOLD_XMIN + B200M_FOLD_SPREAD);     // largest possible h = D * 128^2 / 2 maps to the top digit value
+    info[3] = D > 0 ? 1 : 0;
 }
 
 __global__ void __launch_bounds__(256)
@@ -127,26 +123,41 @@ int b200m_l2_i8_aux_bytes(int64_t rows, size_t* bytes) {
     return B200M_OK;
 }
 
+int b200m_l2_i8_aux_init(void* aux, int64_t total_rows, int D, void* stream) {
+    if (!aux || total_rows < 0 || D <= 0 || ((uintptr_t)aux & 255)) return B200M_EINVAL;
+    fold_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((int32_t*)((char*)aux + b200m_aux_info_off(total_rows)),
+                                                        total_rows > 0 ? D : 0);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "fold_init_kernel launch");
+    return B200M_OK;
+}
+
+int b200m_prep_l2_i8_rows(const float* src, int64_t row_begin, int64_t row_count, int64_t total_rows, int D,
+                          int8_t* dst, int Dpad, void* aux, int32_t* not_integer, void* stream) {
+    if (row_begin < 0 || row_count < 0 || row_begin + row_count > total_rows || D <= 0 || Dpad < D || Dpad % 128 != 0 ||
+        ((uintptr_t)aux & 255))
+        return B200M_EINVAL;
+    if (row_count == 0) return B200M_OK;
+    if (!src || !dst || !aux || !not_integer) return B200M_EINVAL;
+    long long blocks = (row_count + 7) / 8;
+    if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    prep_l2_i8_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        src, row_begin, row_count, D, dst, Dpad, (int32_t*)aux, (int8_t*)aux + b200m_aux_fold_off(total_rows), not_integer,
+        (int32_t*)((char*)aux + b200m_aux_info_off(total_rows)));
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_i8_kernel launch");
+    return B200M_OK;
+}
+
 int b200m_prep_l2_i8(const float* src, int64_t rows, int D, int8_t* dst, int Dpad, void* aux,
                      int32_t* not_integer, void* stream) {
     if (rows < 0 || D <= 0 || Dpad < D || Dpad % 128 != 0 || ((uintptr_t)aux & 255)) return B200M_EINVAL;
-    if (rows == 0) {                                 // empty store: only the info words exist (fold disabled)
-        if (aux) { fold_init_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((int32_t*)((char*)aux + b200m_aux_info_off(0))); b200m_count_launch(); }
-        return B200M_OK;
+    if (rows > 0 && (!src || !dst || !aux || !not_integer)) return B200M_EINVAL;
+    if (aux) {
+        int rc = b200m_l2_i8_aux_init(aux, rows, D, stream);
+        if (rc != B200M_OK) return rc;
     }
-    if (!src || !dst || !aux || !not_integer) return B200M_EINVAL;
-    long long blocks = (rows + 7) / 8;
-    if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    cudaStream_t st = (cudaStream_t)stream;
-    int32_t* norms = (int32_t*)aux;
-    int8_t* fold = (int8_t*)aux + b200m_aux_fold_off(rows);
-    int32_t* info = (int32_t*)((char*)aux + b200m_aux_info_off(rows));
-    fold_init_kernel<<<1, 1, 0, st>>>(info);
-    prep_l2_i8_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, rows, D, dst, Dpad, norms, not_integer, info);
-    fold_encode_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(norms, rows, fold, info);
-    b200m_count_launch(3);
-    B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_i8 kernels launch");
-    return B200M_OK;
+    return b200m_prep_l2_i8_rows(src, 0, rows, rows, D, dst, Dpad, aux, not_integer, stream);
 }
 
 int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream) {

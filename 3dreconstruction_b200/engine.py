@@ -109,6 +109,28 @@ class Engine:
                     "b200m_prep_l2_f32")
             return DeviceDescriptors(L.KIND_L2_F32, t, nrm, rows, Dpad)
 
+    # ------------------------------------------------------------------ incremental L2_I8 store (upload in pieces)
+    def alloc_l2_i8_store(self, rows: int, D: int):
+        """Empty int8 store for `rows` integer-valued float descriptors of width D, to be filled by
+        prepare_l2_i8_rows().  Returns (DeviceDescriptors, not_integer flag tensor)."""
+        Dpad = (D + 127) // 128 * 128
+        with torch.cuda.device(self.device):
+            d8 = torch.empty((rows, Dpad), dtype=torch.int8, device=self.device)
+            nb = ctypes.c_size_t(0)
+            L.check(self.lib.b200m_l2_i8_aux_bytes(rows, ctypes.byref(nb)), "b200m_l2_i8_aux_bytes")
+            aux = torch.empty((nb.value // 4,), dtype=torch.int32, device=self.device)
+            flag = torch.zeros((1,), dtype=torch.int32, device=self.device)
+            L.check(self.lib.b200m_l2_i8_aux_init(aux.data_ptr(), rows, D, self._stream()), "b200m_l2_i8_aux_init")
+        return DeviceDescriptors(L.KIND_L2_I8, d8, aux, rows, Dpad), flag
+
+    def prepare_l2_i8_rows(self, dd: DeviceDescriptors, flag: torch.Tensor, src: torch.Tensor, row_begin: int) -> None:
+        """Re-encode float32 rows `src` [cnt, D] (device) into rows [row_begin, row_begin + cnt) of `dd` on the current stream."""
+        cnt, D = int(src.shape[0]), int(src.shape[1])
+        with torch.cuda.device(self.device):
+            L.check(self.lib.b200m_prep_l2_i8_rows(src.data_ptr(), row_begin, cnt, dd.rows, D, dd.desc.data_ptr(), dd.width,
+                                                   dd.norm.data_ptr(), flag.data_ptr(), self._stream()),
+                    "b200m_prep_l2_i8_rows")
+
     def f32_stats(self, reset: bool = True):
         """(rows re-scanned exhaustively, their distance evaluations) of the L2_F32 path since the last reset."""
         rows, evals = ctypes.c_int64(0), ctypes.c_int64(0)

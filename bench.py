@@ -397,7 +397,14 @@ def run_b200(args):
     value = P * args.steps / (ms_total / 1e3)
 
     # ---- end to end: HOST float32 descriptors -> H2D -> prep -> (broadcast) -> match -> (gather) -> D2H CSR
+    streaming = ap.StreamingAllPairs(eng, chunk_pairs=args.chunk_pairs) if world == 1 else None
+
     def e2e_step():
+        if streaming is not None:         # 1 GPU: upload in image groups, hidden behind the matching of resident groups
+            h = streaming.match_host(host_pinned, [n] * I, ratio_threshold=RATIO)
+            if int(h.ptr[-1]) != matches_total:
+                raise RuntimeError(f"e2e path found {int(h.ptr[-1])} matches, device-resident path {matches_total}")
+            return h.ptr.nbytes + h.query_idx.nbytes + h.train_idx.nbytes + h.distance.nbytes
         st = None
         if rank == 0:
             dev_desc = host_pinned.to(device, non_blocking=True)
@@ -453,7 +460,10 @@ def run_b200(args):
                                                "the write side is the 4 x 16 B Top2 slices per query row (0.52 MB/pair)"},
                 "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel() * 4),
                         "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                        "path": "pinned host float32 descriptors -> H2D -> b200m_prep_l2_i8 -> b200m_match_pairs_csr -> D2H CSR"},
+                        "path": ("pinned host float32 descriptors -> H2D in image groups on a copy stream -> b200m_prep_l2_i8_rows -> "
+                                 "b200m_match_pairs_csr on the resident groups (two compute streams) -> per-chunk D2H of the CSR into pinned memory"
+                                 if world == 1 else
+                                 "pinned host float32 descriptors -> H2D -> b200m_prep_l2_i8 -> broadcast -> b200m_match_pairs_csr -> gather -> D2H CSR")},
                 "gpu_launches": int(launches.item()), "clocks": clocks}
         if world == 1:
             imgs = host_sample_images(args, 4)

@@ -84,6 +84,13 @@ B200M_API int         b200m_device_info(int* sm_count, int* cc_major, int* cc_mi
 B200M_API int b200m_l2_i8_aux_bytes(int64_t rows, size_t* bytes);
 B200M_API int b200m_prep_l2_i8(const float* src, int64_t rows, int D, int8_t* dst, int Dpad,
                      void* aux, int32_t* not_integer, void* stream);
+/* Incremental form, for a store that is uploaded in pieces while matching already runs on the rows that
+ * are resident: b200m_l2_i8_aux_init() once for a store of total_rows rows of width D, then
+ * b200m_prep_l2_i8_rows() per piece: src = float32 [row_count, D] (the piece only), written to rows
+ * [row_begin, row_begin + row_count) of dst / aux.  b200m_prep_l2_i8 == init + one piece of all rows. */
+B200M_API int b200m_l2_i8_aux_init(void* aux, int64_t total_rows, int D, void* stream);
+B200M_API int b200m_prep_l2_i8_rows(const float* src, int64_t row_begin, int64_t row_count, int64_t total_rows,
+                     int D, int8_t* dst, int Dpad, void* aux, int32_t* not_integer, void* stream);
 
 /* Row squared norms for the F32 kind: norms[r] = sum_k src[r,k]^2 (fp32). */
 B200M_API int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream);

@@ -367,3 +367,36 @@ def test_all_pairs_csr_equals_per_pair_oracle(eng, kind, mode):
                 assert_close_float(O.Matches(q, t, d), want, f"{kind} pair {i},{j} chunk={chunk} mode={mode}", 0.02)
             else:
                 assert_exact(O.Matches(q, t, d), want, f"{kind} pair {i},{j} chunk={chunk} mode={mode}")
+
+
+@pytest.mark.parametrize("group", [1, 2, 4, 100])
+def test_streaming_all_pairs_equals_per_pair_oracle(eng, group):
+    """Upload-overlapped all-pairs path (StreamingAllPairs): same pair set as itertools.combinations, every pair exact;
+    ragged image sizes, groups smaller/larger than the set, chunks that straddle groups; twice (arena reuse)."""
+    import itertools
+    ap = pkg("allpairs")
+    sizes = [300, 129, 1, 640, 77, 256, 18]
+    imgs = [synth.sift_pair(seed=160 + i, n=max(s, 2))[0][:s] for i, s in enumerate(sizes)]
+    imgs[3][:200] = np.clip(imgs[0][:200] + np.random.default_rng(1).integers(-4, 5, size=(200, 128)), 0, 255)
+    imgs[5][:60] = imgs[1][:60]
+    host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+    sm = ap.StreamingAllPairs(eng, chunk_pairs=5, group_images=group)
+    for rep in range(2):
+        res = sm.match_host(host, sizes, ratio_threshold=0.8)
+        assert sorted(map(tuple, res.pairs)) == list(itertools.combinations(range(len(sizes)), 2))
+        assert res.ptr[0] == 0 and res.ptr[-1] == len(res.query_idx)
+        for p, (i, j) in enumerate(res.pairs):
+            want = O.reference_match(imgs[i], imgs[j], O.NORM_L2, False, 0.8)
+            assert_exact(O.Matches(*res.pair(p)), want, f"streaming pair {i},{j} group={group} rep={rep}")
+
+
+def test_streaming_all_pairs_non_integer_falls_back_to_generic_path(eng):
+    ap = pkg("allpairs")
+    rng = np.random.default_rng(11)
+    sizes = [90, 40, 64]
+    imgs = [rng.normal(size=(s, 128)).astype(np.float32) for s in sizes]
+    host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+    res = ap.StreamingAllPairs(eng, chunk_pairs=2, group_images=2).match_host(host, sizes, ratio_threshold=0.9)
+    for p, (i, j) in enumerate(res.pairs):
+        want = O.reference_match(imgs[i], imgs[j], O.NORM_L2, False, 0.9)
+        assert_close_float(O.Matches(*res.pair(p)), want, f"streaming fallback pair {i},{j}", 0.05)

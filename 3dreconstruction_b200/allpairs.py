@@ -231,16 +231,25 @@ class StreamingAllPairs:
             out.append((j1, np.stack([i, j], axis=1).astype(np.int32)))
         return out
 
-    def match_host(self, host: torch.Tensor, counts: Sequence[int], ratio_threshold: Optional[float] = None,
-                   cross_check: bool = False) -> PairCSR:
+    def match_host(self, host: Optional[torch.Tensor], counts: Sequence[int], ratio_threshold: Optional[float] = None,
+                   cross_check: bool = False, D: Optional[int] = None) -> Optional[PairCSR]:
+        """host: pinned float32 [sum(counts), D] (rank 0; other ranks pass None and D).  Under torch.distributed
+        (world > 1) rank 0 uploads and re-encodes each image group and broadcasts the encoded rows (NCCL) while every
+        rank matches its 1/world slice of the pairs of the groups already resident; the per-rank CSRs are gathered to
+        rank 0, which returns the host CSR (other ranks return None)."""
+        import torch.distributed as dist
         eng, mt = self.engine, self.matcher
         dev = eng.device
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        rank = dist.get_rank() if world > 1 else 0
         counts = [int(c) for c in counts]
         I = len(counts)
         offsets = np.zeros(I + 1, np.int64)
         np.cumsum(counts, out=offsets[1:])
-        rows, D = int(offsets[-1]), int(host.shape[1])
-        assert host.dtype == torch.float32 and host.shape[0] == rows
+        rows = int(offsets[-1])
+        D = int(host.shape[1]) if host is not None else int(D)
+        if rank == 0:
+            assert host.dtype == torch.float32 and host.shape[0] == rows
         mode = mode_of(cross_check, ratio_threshold)
         ratio = float(ratio_threshold or 0.0)
         cur = torch.cuda.current_stream(dev)
@@ -250,7 +259,7 @@ class StreamingAllPairs:
             mt._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
         cs = self._copy_stream
         key = (rows, D)
-        if self._dev.get("key") != key:                 # device staging + store, reused across calls of the same shape
+        if rank == 0 and self._dev.get("key") != key:   # device staging buffer, reused across calls of the same shape
             self._dev = {"key": key, "f32": torch.empty((rows, D), dtype=torch.float32, device=dev)}
         cs.wait_stream(cur)
         with torch.cuda.stream(cs):
@@ -258,13 +267,17 @@ class StreamingAllPairs:
         store = Store(dd, offsets, NORM_L2)
         for st in mt._streams:
             st.wait_stream(cur)
+        fold_off = (rows * 4 + 255) // 256 * 256 // 4   # aux block layout (csrc/common.cuh), in int32 words
+        info_off = fold_off + (rows * 32 + 255) // 256 * 256 // 4
 
         plan = self.group_major_pairs(I, self.group_images)
+        if world > 1:                                    # every rank takes a contiguous 1/world slice of each group's pairs
+            plan = [(j_end, np.array_split(gp, world)[rank]) for j_end, gp in plan]
         P = sum(len(p) for _, p in plan)
         ptr_host = np.zeros(P + 1, np.int64)
         pairs_out = np.concatenate([p for _, p in plan]) if plan else np.zeros((0, 2), np.int32)
         state = {"base": 0, "pbase": 0}
-        f32 = self._dev["f32"]
+        dev_out = {"q": [], "t": [], "d": [], "p": []}  # world > 1: per-chunk device results, gathered at the end
 
         def finish(slot, C, optr, oq, ot, od):
             st = mt._streams[slot]
@@ -272,20 +285,33 @@ class StreamingAllPairs:
                 cnts = optr[:C + 1].cpu().numpy()      # waits for this chunk only
                 total = int(cnts[C])
                 b0 = state["base"]
-                for name, src, dt in (("q", oq, torch.int32), ("t", ot, torch.int32), ("d", od, torch.float32)):
-                    self._host_buf(name, b0 + total, dt)[b0:b0 + total].copy_(src[:total], non_blocking=True)
+                if world == 1:
+                    for name, src, dt in (("q", oq, torch.int32), ("t", ot, torch.int32), ("d", od, torch.float32)):
+                        self._host_buf(name, b0 + total, dt)[b0:b0 + total].copy_(src[:total], non_blocking=True)
+                else:
+                    for name, src in (("q", oq), ("t", ot), ("d", od)):
+                        t = src[:total].clone()
+                        t.record_stream(cur)
+                        dev_out[name].append(t)
             ptr_host[state["pbase"]:state["pbase"] + C] = cnts[:C] + b0
             state["base"] = b0 + total
             state["pbase"] += C
 
         pending = None
         ci = 0
-        uploaded = 0                                     # images whose upload + prep is enqueued
+        uploaded = 0                                     # images whose upload + prep (+ broadcast) is enqueued
         for j_end, gp in plan:
-            with torch.cuda.stream(cs):                  # upload + re-encode images [uploaded, j_end)
+            with torch.cuda.stream(cs):                  # upload + re-encode (+ broadcast) images [uploaded, j_end)
                 r0, r1 = int(offsets[uploaded]), int(offsets[j_end])
-                f32[r0:r1].copy_(host[r0:r1], non_blocking=True)
-                eng.prepare_l2_i8_rows(dd, flag, f32[r0:r1], r0)
+                if rank == 0:
+                    f32 = self._dev["f32"]
+                    f32[r0:r1].copy_(host[r0:r1], non_blocking=True)
+                    eng.prepare_l2_i8_rows(dd, flag, f32[r0:r1], r0)
+                if world > 1:                            # encoded rows, their norms, fold digits and the info words
+                    aux = dd.norm
+                    for piece in (dd.desc[r0:r1], aux[r0:r1], aux[fold_off + r0 * 8:fold_off + r1 * 8],
+                                  aux[info_off:info_off + 8]):
+                        dist.broadcast(piece, src=0)     # enqueued after the prep on this stream; ordered on it
                 ev = torch.cuda.Event()
                 ev.record(cs)
             uploaded = j_end
@@ -304,16 +330,42 @@ class StreamingAllPairs:
             finish(*pending)
         for st in mt._streams + [cs]:
             cur.wait_stream(st)
+        bad = flag.clone()
+        if world > 1:
+            dist.broadcast(bad, src=0)
         cur.synchronize()                                # results are host arrays: the D2H copies must have landed
-        if int(flag.item()) != 0:                        # not integer-valued: the int8 encoding is not exact -> generic path
-            st2 = build_store(eng, host.to(dev), NORM_L2, counts=counts)
-            return self.matcher.match(st2, pairs_out, cross_check, ratio_threshold).to_host()
+        if int(bad.item()) != 0:                         # not integer-valued: the int8 encoding is not exact -> generic path
+            st2 = None
+            if rank == 0:
+                st2 = build_store(eng, host.to(dev), NORM_L2, counts=counts)
+            if world > 1:
+                st2 = broadcast_store(st2, NORM_L2, dev)
+            r = self.matcher.match(st2, pairs_out, cross_check, ratio_threshold)
+            if world > 1:
+                r = gather_csr(r, dev)
+            return r.to_host() if r is not None else None
         total = state["base"]
         ptr_host[P] = total
-        q = self._host_buf("q", total, torch.int32)[:total].numpy()
-        t = self._host_buf("t", total, torch.int32)[:total].numpy()
-        d = self._host_buf("d", total, torch.float32)[:total].numpy()
-        return PairCSR(pairs_out, ptr_host, q, t, d)
+        if world == 1:
+            q = self._host_buf("q", total, torch.int32)[:total].numpy()
+            t = self._host_buf("t", total, torch.int32)[:total].numpy()
+            d = self._host_buf("d", total, torch.float32)[:total].numpy()
+            return PairCSR(pairs_out, ptr_host, q, t, d)
+        cat = lambda xs, dt: torch.cat(xs) if xs else torch.empty(0, dtype=dt, device=dev)   # noqa: E731
+        local = PairCSR(pairs_out, torch.from_numpy(ptr_host).to(dev), cat(dev_out["q"], torch.int32),
+                        cat(dev_out["t"], torch.int32), cat(dev_out["d"], torch.float32))
+        full = gather_csr(local, dev)
+        if full is None:
+            return None
+        K = int(full.query_idx.numel())                  # rank 0: D2H into the pinned arena (pageable copies are ~3x slower)
+        outs = []
+        for name, src, dt in (("q", full.query_idx, torch.int32), ("t", full.train_idx, torch.int32),
+                              ("d", full.distance, torch.float32)):
+            hb = self._host_buf(name, K, dt)[:K]
+            hb.copy_(src, non_blocking=True)
+            outs.append(hb)
+        ptr = full.ptr.cpu().numpy()                     # synchronises the stream: the copies above have landed
+        return PairCSR(full.pairs, ptr, outs[0].numpy(), outs[1].numpy(), outs[2].numpy())
 
 
 # ---------------------------------------------------------------------------------- multi-GPU

@@ -397,13 +397,19 @@ def run_b200(args):
     value = P * args.steps / (ms_total / 1e3)
 
     # ---- end to end: HOST float32 descriptors -> H2D -> prep -> (broadcast) -> match -> (gather) -> D2H CSR
-    streaming = ap.StreamingAllPairs(eng, chunk_pairs=args.chunk_pairs) if world == 1 else None
+    streaming = ap.StreamingAllPairs(eng, chunk_pairs=args.chunk_pairs)
+    matches_all = torch.tensor([matches_total], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(matches_all, op=dist.ReduceOp.SUM)
+    matches_all = int(matches_all.item())
 
     def e2e_step():
-        if streaming is not None:         # 1 GPU: upload in image groups, hidden behind the matching of resident groups
-            h = streaming.match_host(host_pinned, [n] * I, ratio_threshold=RATIO)
-            if int(h.ptr[-1]) != matches_total:
-                raise RuntimeError(f"e2e path found {int(h.ptr[-1])} matches, device-resident path {matches_total}")
+        if streaming is not None:         # upload in image groups (rank 0), hidden behind the matching of resident groups
+            h = streaming.match_host(host_pinned, [n] * I, ratio_threshold=RATIO, D=D)
+            if rank != 0:
+                return 0
+            if int(h.ptr[-1]) != matches_all or len(h.pairs) != P:
+                raise RuntimeError(f"e2e path found {int(h.ptr[-1])} matches, device-resident path {matches_all}")
             return h.ptr.nbytes + h.query_idx.nbytes + h.train_idx.nbytes + h.distance.nbytes
         st = None
         if rank == 0:
@@ -440,7 +446,7 @@ def run_b200(args):
                 "gdist_per_s": value * n * n / 1e9, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "int8", "data": "synthetic", "config": workload_config(args),
-                "matches_per_step": matches_total if world == 1 else None,
+                "matches_per_step": matches_all,
                 "roofline": {"bound": "tensor", "kernel": "l2_i8_fold_kernel (tcgen05 kind::i8 M128 N256; 4 descriptor K-steps + 1 folded-norm K-step, "
                                                         "achieved counts the 4 algorithmic ones)", "achieved": achieved,
                              "peak": peak, "unit": "TOP/s int8 (TFLOP/s-equivalent)", "frac": achieved / peak if achieved else None,
@@ -463,7 +469,9 @@ def run_b200(args):
                         "path": ("pinned host float32 descriptors -> H2D in image groups on a copy stream -> b200m_prep_l2_i8_rows -> "
                                  "b200m_match_pairs_csr on the resident groups (two compute streams) -> per-chunk D2H of the CSR into pinned memory"
                                  if world == 1 else
-                                 "pinned host float32 descriptors -> H2D -> b200m_prep_l2_i8 -> broadcast -> b200m_match_pairs_csr -> gather -> D2H CSR")},
+                                 "rank 0: pinned host float32 descriptors -> H2D in image groups -> b200m_prep_l2_i8_rows -> NCCL broadcast of the "
+                                 "encoded group; every rank: b200m_match_pairs_csr on its slice of the resident groups' pairs; gather of the CSRs to "
+                                 "rank 0 -> D2H")},
                 "gpu_launches": int(launches.item()), "clocks": clocks}
         if world == 1:
             imgs = host_sample_images(args, 4)

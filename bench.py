@@ -57,13 +57,55 @@ def peaks():
 
 # --------------------------------------------------------------------------- clocks
 class ClockSampler:
+    """SM clock + throttle reasons DURING the timed region: an NVML thread sampling every 5 ms (short multi-GPU steps
+    end before an nvidia-smi loop prints its first line); nvidia-smi -lms as the fallback when pynvml is missing."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NVML_REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                    0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, index: int):
         self.index, self.proc, self.lines = index, None, []
+        self.nvml, self.samples, self.stop_flag = None, [], False
+
+    def _nvml_loop(self):
+        nv, h = self.nvml
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                self.samples.append((nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), int(get_reasons(h))))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def _start_nvml(self) -> bool:
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.nvml = (nv, h)
+            self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thread.start()
+            return True
+        except Exception:
+            self.nvml = None
+            return False
+
+    def _stop_nvml(self):
+        self.stop_flag = True
+        self.thread.join(timeout=1)
+        sm = [float(c) for c, _ in self.samples]
+        bits = 0
+        for _, r in self.samples:
+            bits |= r
+        busy = [x for x in sm if x > 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": self.max_mhz, "samples": len(sm),
+                "reasons": sorted(name for bit, name in self.NVML_REASONS.items() if bits & bit), "source": "nvml, 5 ms"}
 
     def start(self):
+        if self._start_nvml():
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -78,6 +120,8 @@ class ClockSampler:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml:
+            return self._stop_nvml()
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()

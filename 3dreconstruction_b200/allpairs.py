@@ -91,9 +91,10 @@ def partition_pairs(pairs: np.ndarray, offsets: np.ndarray, world: int) -> List[
 class AllPairsMatcher:
     """Chunked CSR matching of an arbitrary pair list over one Store (single GPU)."""
 
-    def __init__(self, engine: Engine, chunk_pairs: int = 2048):
+    def __init__(self, engine: Engine, chunk_pairs: int = 2048, pipeline: bool = True):
         self.engine = engine
         self.chunk_pairs = int(chunk_pairs)
+        self.pipeline = bool(pipeline)     # False: every chunk on the caller's stream, one after the other (kernel timing)
         self._bufs = {}
         self._streams = None
 
@@ -152,16 +153,20 @@ class AllPairsMatcher:
             total = int(optr[C].item())
             return PairCSR(pairs, optr[:C + 1].clone(), oq[:total].clone(), ot[:total].clone(), od[:total].clone())
         cur = torch.cuda.current_stream(dev)
-        if self._streams is None:
-            self._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
-        for st in self._streams:
-            st.wait_stream(cur)
+        if not self.pipeline:
+            streams = [cur, cur]
+        else:
+            if self._streams is None:
+                self._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
+            streams = self._streams
+            for st in streams:
+                st.wait_stream(cur)
         outs_q, outs_t, outs_d, ptrs = [], [], [], []
         base = 0
 
         def finish(slot, C, optr, oq, ot, od):
             nonlocal base
-            with torch.cuda.stream(self._streams[slot]):
+            with torch.cuda.stream(streams[slot]):
                 total = int(optr[C].item())    # waits for this chunk only; the next one is already enqueued
                 for lst, src in ((outs_q, oq), (outs_t, ot), (outs_d, od)):
                     t = src[:total].clone()
@@ -175,15 +180,16 @@ class AllPairsMatcher:
         pending = None
         for ci, c0 in enumerate(range(0, P, self.chunk_pairs)):
             slot = ci & 1
-            with torch.cuda.stream(self._streams[slot]):
+            with torch.cuda.stream(streams[slot]):
                 job = self._enqueue_chunk(store, pairs[c0:c0 + self.chunk_pairs], mode, ratio, slot,
-                                          self._streams[slot].cuda_stream)
+                                          streams[slot].cuda_stream)
             if pending is not None:
                 finish(*pending)
             pending = (slot, *job)
         finish(*pending)
-        for st in self._streams:
-            cur.wait_stream(st)
+        if self.pipeline:
+            for st in streams:
+                cur.wait_stream(st)
         ptrs.append(torch.tensor([base], dtype=torch.int64, device=dev))
         return PairCSR(pairs, torch.cat(ptrs), torch.cat(outs_q), torch.cat(outs_t), torch.cat(outs_d))
 

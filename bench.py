@@ -313,16 +313,24 @@ def allpairs_extras(torch, b, eng, pk):
     lib = eng.lib
 
     def timed_pass(store, pairs, reps):
+        """(ms per pass with the two-stream chunk pipeline, knn-kernel ms per pass from a second, un-pipelined pass
+        whose per-kernel CUDA events bracket nothing but the kernel, matches)."""
+        import ctypes
         m = ap.AllPairsMatcher(eng, chunk_pairs=1024)
         r = m.match(store, pairs, cross_check=True)           # warm-up (also sizes the buffers)
         torch.cuda.synchronize()
-        lib.b200m_timing_enable(1)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(reps):
             r = m.match(store, pairs, cross_check=True)
         e1.record(); torch.cuda.synchronize()
-        import ctypes
+        m2 = ap.AllPairsMatcher(eng, chunk_pairs=1024, pipeline=False)
+        m2.match(store, pairs, cross_check=True)
+        torch.cuda.synchronize()
+        lib.b200m_timing_enable(1)
+        for _ in range(reps):
+            m2.match(store, pairs, cross_check=True)
+        torch.cuda.synchronize()
         knn_ms, knn_l = ctypes.c_double(0), ctypes.c_int(0)
         lib.b200m_timing_collect(ctypes.byref(knn_ms), ctypes.byref(knn_l))
         lib.b200m_timing_enable(0)
@@ -419,7 +427,6 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     lib.b200m_reset_launch_count()
-    lib.b200m_timing_enable(1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
@@ -432,11 +439,24 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(launches, op=dist.ReduceOp.SUM)
+    clocks = sampler.stop() if rank == 0 else None
+    # ---- the dominant kernel alone: the same K steps once more with the two-stream chunk pipeline OFF, so that the
+    # CUDA events the library records around each knn launch (on the launching stream) bracket that kernel only
     import ctypes
+    seq = ap.AllPairsMatcher(eng, chunk_pairs=args.chunk_pairs, pipeline=False)
+    seq.match(store, mine, cross_check=False, ratio_threshold=RATIO)
+    barrier()
+    lib.b200m_timing_enable(1)
+    ek0, ek1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ek0.record()
+    for _ in range(args.steps):
+        seq.match(store, mine, cross_check=False, ratio_threshold=RATIO)
+    ek1.record()
+    barrier()
     knn_ms, knn_launches = ctypes.c_double(0), ctypes.c_int(0)
     lib.b200m_timing_collect(ctypes.byref(knn_ms), ctypes.byref(knn_launches))
     lib.b200m_timing_enable(0)
-    clocks = sampler.stop() if rank == 0 else None
+    seq_ms_total = ek0.elapsed_time(ek1)
     ms_total = float(ms.item())
     value = P * args.steps / (ms_total / 1e3)
 
@@ -501,7 +521,10 @@ def run_b200(args):
                                                "8192 MAC/clk/SM at 1965 MHz (profiles/r01_mma_peak_microbench.txt); "
                                                "ncu's sm__ops_path_tensor_op_utcimma pct uses the same hardware rate",
                              "kernel_ms_per_step": knn_ms.value / args.steps, "kernel_launches": knn_launches.value,
-                             "kernel_share_of_step": knn_ms.value / ms_total if world == 1 else None,
+                             "kernel_share_of_step": knn_ms.value / seq_ms_total,
+                             "kernel_timing": "per-launch CUDA events on the launching stream over a second pass of the same K steps with the "
+                                              "two-stream chunk pipeline off (sequential step %.1f ms); with the pipeline on, the events of one "
+                                              "stream would include waiting for the other stream's kernel" % (seq_ms_total / args.steps),
                              "algorithmic_ops_per_pair": 2.0 * n * n * D,
                              "algorithmic_hbm_bytes_per_pair": 2 * n * (D + 36) + 64 * n,
                              "traffic": NCU_DRAM_BYTES_PER_PAIR * my_pairs * args.steps / max(knn_launches.value, 1),

@@ -27,6 +27,8 @@
 // a group visits its chunks in ascending order with a strict compare, and slices merge by u64 min)
 // and k2 is the best among all OTHER chunks.  The true runner-up is min(k2, runner-up inside the
 // winner's chunk); tail.cu recomputes those <= 63 distances exactly where the result depends on it.
+#include <cstdio>
+#include <cstdlib>
 #include "common.cuh"
 #include "sm100.cuh"
 
@@ -55,12 +57,17 @@ struct Item {
     bool valid;
 };
 
+__device__ __forceinline__ Item decode_tile(int p, int split, int tile, const DevPair* __restrict__ pairs, int S, int backward);
+
 __device__ __forceinline__ Item decode_item(long long item, const DevPair* __restrict__ pairs, int tiles_max, int S,
                                             int backward) {
-    Item it;
     int tile = (int)(item % tiles_max); item /= tiles_max;
-    it.split = (int)(item % S);
-    int p = (int)(item / S);
+    return decode_tile((int)(item / S), (int)(item % S), tile, pairs, S, backward);
+}
+
+__device__ __forceinline__ Item decode_tile(int p, int split, int tile, const DevPair* __restrict__ pairs, int S, int backward) {
+    Item it;
+    it.split = split;
     DevPair pr = pairs[p];
     if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
     else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
@@ -410,7 +417,13 @@ __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // colu
     for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : 0x80000000u;
 }
 
-template <int NKB>
+// CS = CTAs per cluster (1 or 2).  With CS == 2 the two CTAs of a cluster work on two adjacent query row tiles of
+// the same pair, so they stream the SAME train tiles: each CTA fetches half of every train tile (128 of the 256 rows,
+// and half of the fold digits) and TMA multicasts it into both CTAs' shared memory -- L2 -> SM read traffic per CTA
+// halves.  A ring stage may be refilled only when BOTH CTAs' MMAs have consumed it: the stage's empty barrier counts
+// CS arrivals and every MMA issuer commits to the barrier of both CTAs (tcgen05.commit ... multicast::cluster).
+// Work items are (pair, split, tile pair) over clusters; the MMAs themselves stay single-CTA (cta_group::1).
+template <int NKB, int CS>
 __global__ void __launch_bounds__(FOLD_THREADS, 1)
 l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const __grid_constant__ CUtensorMap tmap_x, const int32_t* __restrict__ t_info,
@@ -423,14 +436,26 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int W_MMA = 0, W_PROD = 1, W_CONST = 2;
     constexpr int backward = 0;
+    constexpr uint16_t MC_MASK = (1u << CS) - 1;
+    const uint32_t crank = CS > 1 ? sm100::cluster_ctarank() : 0;
+    // work items: total_items counts (pair, split, tile group of CS row tiles); this CTA takes row tile CS * group + crank
+    const long long first_item = CS > 1 ? (long long)sm100::cluster_id_x() : (long long)blockIdx.x;
+    const long long item_stride = CS > 1 ? (long long)sm100::cluster_count_x() : (long long)gridDim.x;
+    auto decode = [&](long long item) -> Item {
+        int tg = (int)(item % tiles_max); item /= tiles_max;     // tiles_max = tile groups per (pair, split)
+        Item it = decode_tile((int)(item / S), (int)(item % S), tg * CS + (int)crank, pairs, S, backward);
+        // a CTA whose own row tile lies past the pair still streams its half of the train tiles for its peer
+        it.valid = tg * CS * TM < it.n;
+        return it;
+    };
 
     if (warp == W_PROD && lane == 0) {
         sm100::tma_prefetch_desc(&tmap_q);
         sm100::tma_prefetch_desc(&tmap_t);
         sm100::tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
-        for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], FOLD_EPI_WARPS / 2); }
+        for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], CS); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
         sm100::fence_barrier_init();
     }
     if (warp == W_CONST) {
@@ -443,13 +468,15 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
     sm100::tc_fence_before();
     __syncthreads();
+    if constexpr (CS > 1) sm100::cluster_sync_all();      // the peer's barriers exist before anything is multicast to them
     sm100::tc_fence_after();
     const uint32_t tmem_base = *sm.tmem_ptr;
+    constexpr int HALF_ROWS = TN / CS;                     // train rows this CTA fetches per tile
 
     if (warp == W_PROD) {
         uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;
-        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward);
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode(item);
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_empty[ab], a_par);
             if (sm100::elect_one()) {
@@ -461,18 +488,23 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
             __syncwarp();
             if (++ab == NABUF) { ab = 0; a_par ^= 1; }
-            const int row0 = it.t_off + it.c_begin;
+            const int row0 = it.t_off + it.c_begin + (int)crank * HALF_ROWS;
             for (int j = 0; j < it.ntiles; ++j) {
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb) {
-                    sm100::mbar_wait(&sm.b_empty[bs], b_par);
+                    sm100::mbar_wait(&sm.b_empty[bs], b_par);          // CS arrivals: every CTA of the cluster is done with it
                     if (sm100::elect_one()) {
                         const bool last = kb == NKB - 1;       // the fold digits travel with the tile's last K block
                         sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (last ? X_BYTES : 0)));
-                        sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * KB_BYTES,
-                                           row0 + j * TN);
-                        if (last)
-                            sm100::tma_load_2d(sm.x + (size_t)(bs / NKB) * X_BYTES, &tmap_x, &sm.b_full[bs], 0, row0 + j * TN);
+                        uint8_t* bdst = sm.b + (size_t)bs * B_KB_BYTES + (size_t)crank * (B_KB_BYTES / CS);
+                        uint8_t* xdst = sm.x + (size_t)(bs / NKB) * X_BYTES + (size_t)crank * (X_BYTES / CS);
+                        if constexpr (CS > 1) {
+                            sm100::tma_load_2d_mc(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN, MC_MASK);
+                            if (last) sm100::tma_load_2d_mc(xdst, &tmap_x, &sm.b_full[bs], 0, row0 + j * TN, MC_MASK);
+                        } else {
+                            sm100::tma_load_2d(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN);
+                            if (last) sm100::tma_load_2d(xdst, &tmap_x, &sm.b_full[bs], 0, row0 + j * TN);
+                        }
                     }
                     __syncwarp();
                     if (++bs == NBF) { bs = 0; b_par ^= 1; }
@@ -487,8 +519,8 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         const uint64_t ax_desc = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32,
                                                           sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.ax)));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
-        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward);
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode(item);
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_full[ab], a_par);
             const uint32_t a_lo = a_lo0 + ab * (NKB * A_KB_BYTES >> 4);
@@ -511,7 +543,8 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                             sm100::mma_i8(d_tmem, ax_desc,
                                           sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + (bs / NKB) * (X_BYTES >> 4)),
                                           idesc, 1u);
-                        sm100::mma_commit(&sm.b_empty[bs]);
+                        if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);   // free the stage in both CTAs
+                        else sm100::mma_commit(&sm.b_empty[bs]);
                         if (kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
                     }
                     __syncwarp();
@@ -530,8 +563,8 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * (TN / 2);
         uint32_t k = 0, tc_base = 0;
-        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward);
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode(item);
             if (!it.valid) continue;
             int v1 = (int)0x80000000, v2 = (int)0x80000000, i1 = -1, i2 = -1;
             auto insert = [&](int pm, int base) {           // top-2 of chunk maxima; ties keep the earlier chunk
@@ -580,6 +613,7 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 
     sm100::tc_fence_before();
     __syncthreads();
+    if constexpr (CS > 1) sm100::cluster_sync_all();      // the peer may still commit to this CTA's barriers until it is done too
     if (warp == W_MMA) sm100::tmem_dealloc<512>(tmem_base);
 }
 
@@ -631,37 +665,54 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
         int mx = max_n; max_n = max_m; max_m = mx;
         allow_fold = false;
     }
-    CUtensorMap tq, tt, tx;
+    CUtensorMap tq, tt;
     int rc = b200m_make_tmap_2d(&tq, q_desc, (uint64_t)q_rows, (uint64_t)D, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
     rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D, TN, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
     // the train store's aux block (b200m_prep_l2_i8): fold digits + info words behind the norms
     const int32_t* t_info = (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows));
-    if (allow_fold) {
-        rc = b200m_make_tmap_2d_ex(&tx, (const char*)t_norm + b200m_aux_fold_off(t_rows), (uint64_t)t_rows, B200M_FOLD_K, TN,
-                                   CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B200M_FOLD_K, CU_TENSOR_MAP_SWIZZLE_32B);
-        if (rc != B200M_OK) return rc;
-    }
     const size_t smem = smem_bytes(nkb);
     static bool attr_set = false;
+    static int fold_cs = 1;                          // CTAs per cluster of the fold kernel (2 when the device co-schedules pairs)
+    static int fold_clusters = 0;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (!attr_set) {
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(1)), "l2_i8 smem attr");
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(2)), "l2_i8 smem attr");
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes_fold(1)), "l2_i8 fold smem attr");
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes_fold(2)), "l2_i8 fold smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes_fold(1)), "l2_i8 fold smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes_fold(2)), "l2_i8 fold smem attr");
+        // How many 2-CTA clusters of the fold kernel can be resident at once?  Use them only if they cover every SM.
+        cudaLaunchConfig_t qc = {};
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+        qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(FOLD_THREADS); qc.dynamicSmemBytes = smem_bytes_fold(1);
+        qc.attrs = qa; qc.numAttrs = 1;
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, l2_i8_fold_kernel<1, 2>, &qc) == cudaSuccess && nc * 2 >= sms &&
+            !getenv("B200M_NO_CLUSTER")) {
+            fold_cs = 2;
+            fold_clusters = nc;
+        } else {
+            cudaGetLastError();
+        }
+        if (getenv("B200M_VERBOSE")) fprintf(stderr, "b200match: fold kernel clusters of %d (max active 2-CTA clusters %d, SMs %d)\n", fold_cs, nc, sms);
         attr_set = true;
     }
     int tiles_max = (max_n + TM - 1) / TM;
     long long total_items = (long long)num_pairs * S * tiles_max;
     if (total_items <= 0) return B200M_OK;
-    int dev = 0, sms = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
     // Device-side dispatch (no host sync): with allow_fold both kernels are enqueued and exactly one of them
     // finds its precondition in t_info[3]; the other returns at once.
@@ -675,14 +726,34 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_top2_kernel launch");
     if (allow_fold) {
-        if (nkb == 1)
-            l2_i8_fold_kernel<1><<<grid, FOLD_THREADS, smem_bytes_fold(1), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
-                                                                            S, out, total_rows);
+        const int cs = fold_cs;
+        CUtensorMap tth, tx;                          // per-CTA share of a train tile: TN / cs rows
+        rc = b200m_make_tmap_2d(&tth, t_desc, (uint64_t)t_rows, (uint64_t)D, TN / cs, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+        if (rc != B200M_OK) return rc;
+        rc = b200m_make_tmap_2d_ex(&tx, (const char*)t_norm + b200m_aux_fold_off(t_rows), (uint64_t)t_rows, B200M_FOLD_K, TN / cs,
+                                   CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, B200M_FOLD_K, CU_TENSOR_MAP_SWIZZLE_32B);
+        if (rc != B200M_OK) return rc;
+        const int groups = (tiles_max + cs - 1) / cs;               // tile groups of cs row tiles per (pair, split)
+        const long long fitems = (long long)num_pairs * S * groups;
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        const long long max_units = cs == 2 ? fold_clusters : sms;
+        cfg.gridDim = dim3((unsigned)((fitems < max_units ? fitems : max_units) * cs));
+        cfg.blockDim = dim3(FOLD_THREADS);
+        cfg.dynamicSmemBytes = smem_bytes_fold(nkb);
+        cfg.stream = st;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaError_t e;
+        if (cs == 2)
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 2>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 2>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows);
         else
-            l2_i8_fold_kernel<2><<<grid, FOLD_THREADS, smem_bytes_fold(2), st>>>(tq, tt, tx, t_info, pairs, total_items, tiles_max,
-                                                                            S, out, total_rows);
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 1>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 1>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows);
         b200m_count_launch();
-        B200M_CUDA_CHECK(cudaGetLastError(), "l2_i8_fold_kernel launch");
+        B200M_CUDA_CHECK(e, "l2_i8_fold_kernel launch");
     }
     return B200M_OK;
 }

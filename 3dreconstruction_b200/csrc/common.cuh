@@ -21,7 +21,8 @@ struct Top2 { u64 k1, k2; };
 // d^2 = ||a'||^2 + (||b'||^2 & 1) + 2 (bias - E): the epilogue needs no per-column constant at all.
 // 30 coarse digits (weight 128) and one fine digit (weight 1) cover h - bias in [XMIN, XMIN + SPREAD].
 #define B200M_FOLD_K 32
-#define B200M_FOLD_SLICES 4          // Top2 slices per column split the fold kernel writes (the keyed kernel: B200M_I8_GROUPS)
+#define B200M_FOLD_SLICES 1          // Top2 slices per column split the fold kernel writes: its epilogue warps merge in shared memory
+                                     // (the keyed kernel writes B200M_I8_GROUPS)
 #ifndef B200M_FOLD_CHUNK
 #define B200M_FOLD_CHUNK 16
 #endif

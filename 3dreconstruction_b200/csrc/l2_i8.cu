@@ -373,12 +373,12 @@ constexpr int X_BYTES = TN * B200M_FOLD_K;       // 8 KiB: fold digits of one tr
 constexpr int AX_BYTES = TM * B200M_FOLD_K;      // 4 KiB: the constant query-side block
 static_assert(B200M_FOLD_CHUNK == 16, "the epilogue reduces 16-column chunks");
 constexpr int NBF = 4;
-constexpr int FOLD_SLICES = B200M_FOLD_SLICES;   // Top2 slices per column split = epilogue groups
-constexpr int FOLD_EPI_WARPS = 4 * FOLD_SLICES;
+constexpr int FOLD_EPI_WARPS = EPI_WARPS;
 constexpr int FOLD_THREADS = (CTRL_WARPS + FOLD_EPI_WARPS) * 32;                           // train K-block ring depth of the fold kernel
 
 struct SmemFold {
     uint8_t *a, *b, *x, *ax;
+    int4* xch;            // [2][EPI_WARPS - 4][32] partial top-2s of the non-merging epilogue warps, double buffered by item parity
     uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
     uint32_t* tmem_ptr;
 };
@@ -388,7 +388,8 @@ __device__ __forceinline__ SmemFold carve_fold(uint8_t* base, int nkb) {
     s.b = s.a + NABUF * nkb * A_KB_BYTES;
     s.x = s.b + NBF * B_KB_BYTES;
     s.ax = s.x + (NBF / nkb) * X_BYTES;
-    uint8_t* p = s.ax + AX_BYTES;
+    s.xch = (int4*)(s.ax + AX_BYTES);
+    uint8_t* p = (uint8_t*)(s.xch + 2 * (EPI_WARPS - 4) * 32);
     s.a_full = (uint64_t*)p; p += NABUF * 8;
     s.a_empty = (uint64_t*)p; p += NABUF * 8;
     s.b_full = (uint64_t*)p; p += NBF * 8;
@@ -400,8 +401,10 @@ __device__ __forceinline__ SmemFold carve_fold(uint8_t* base, int nkb) {
 }
 __host__ __device__ constexpr size_t smem_bytes_fold(int nkb) {
     return 1024 + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)NBF * B_KB_BYTES + (size_t)(NBF / nkb) * X_BYTES + AX_BYTES +
-           (2 * NABUF + 2 * NBF + 4) * 8 + 16;
+           2 * (EPI_WARPS - 4) * 32 * sizeof(int4) + (2 * NABUF + 2 * NBF + 4) * 8 + 16;
 }
+
+static_assert(smem_bytes_fold(1) <= 232448 && smem_bytes_fold(2) <= 232448, "fold kernel shared memory");
 
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
 // maximum of 16 consecutive accumulator columns v[O .. O+15] = one fold chunk: 8 three-input max instructions
@@ -543,9 +546,11 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                             sm100::mma_i8(d_tmem, ax_desc,
                                           sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + (bs / NKB) * (X_BYTES >> 4)),
                                           idesc, 1u);
-                        if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);   // free the stage in both CTAs
+                        // ONE commit per K block: it frees the ring stage (in both CTAs of a cluster) and, for the tile's last
+                        // K block, is also what the epilogue waits on -- every tcgen05.commit drains the MMA pipe for ~40 cycles
+                        // (tools/mma_peak), so a separate "accumulator full" commit per tile would cost ~5 % of the tensor time.
+                        if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
                         else sm100::mma_commit(&sm.b_empty[bs]);
-                        if (kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
                     }
                     __syncwarp();
                     if (++bs == NBF) { bs = 0; b_par ^= 1; }
@@ -562,7 +567,7 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         const int e = warp - CTRL_WARPS;
         const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * (TN / 2);
-        uint32_t k = 0, tc_base = 0;
+        uint32_t k = 0, tc_base = 0, nitem = 0;
         for (long long item = first_item; item < total_items; item += item_stride) {
             Item it = decode(item);
             if (!it.valid) continue;
@@ -577,7 +582,11 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
                 const int base = it.c_begin + j * TN + half * (TN / 2);
                 const int lim = it.c_end - base;              // existing columns in this warp's 128 (tail tile: < 128)
-                sm100::mbar_wait(&sm.acc_full[g], k & 1);
+                {   // accumulator ready == the ring stage of this tile's last K block has been released (see the MMA warp)
+                    const uint32_t tc = 2 * k + g;                    // this CTA's tile counter
+                    const uint32_t use = (tc * NKB + NKB - 1) / NBF, stage = (tc * NKB + NKB - 1) % NBF;
+                    sm100::mbar_wait(&sm.b_empty[stage], use & 1);
+                }
                 sm100::tc_fence_after();
                 uint32_t acc[2][32];
                 sm100::tmem_ld32(taddr, acc[0]);
@@ -599,14 +608,29 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 insert(m0, base + 64); insert(m1, base + 80); insert(m2, base + 96); insert(m3, base + 112);
             }
             tc_base += (uint32_t)it.ntiles;
-            const int row = it.r0 + quarter * 32 + lane;
-            if (row < it.n) {
-                auto mk = [&](int v, int i) -> u64 {
-                    return (i < 0 || v == (int)0x80000000) ? B200M_SENTINEL
-                                                           : (((u64)(u32)(B200M_FOLD_VBIAS - v)) << 32) | (u64)(u32)i;
-                };
-                Top2 t; t.k1 = mk(v1, i1); t.k2 = mk(v2, i2);
-                out[(long long)(it.split * FOLD_SLICES + g * 2 + half) * total_rows + it.row_base + row] = t;
+            // The four warps of a TMEM lane quarter hold partial top-2s of the same 32 query rows (2 groups x 2 column
+            // halves): merge them through shared memory so that ONE Top2 per row and split leaves the SM.
+            int4* xbuf = sm.xch + (size_t)(nitem & 1) * (EPI_WARPS - 4) * 32;
+            ++nitem;
+            const bool merger = e < 4;                      // g == 0, half == 0
+            if (!merger) xbuf[(e - 4) * 32 + lane] = make_int4(v1, i1, v2, i2);
+            asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");     // epilogue warps only
+            if (merger) {
+#pragma unroll
+                for (int w = 1; w < 4; ++w) {
+                    const int4 o = xbuf[((w - 1) * 4 + quarter) * 32 + lane];
+                    if (o.y >= 0) insert(o.x, o.y);
+                    if (o.w >= 0) insert(o.z, o.w);
+                }
+                const int row = it.r0 + quarter * 32 + lane;
+                if (row < it.n) {
+                    auto mk = [&](int v, int i) -> u64 {
+                        return (i < 0 || v == (int)0x80000000) ? B200M_SENTINEL
+                                                               : (((u64)(u32)(B200M_FOLD_VBIAS - v)) << 32) | (u64)(u32)i;
+                    };
+                    Top2 t; t.k1 = mk(v1, i1); t.k2 = mk(v2, i2);
+                    out[(long long)it.split * total_rows + it.row_base + row] = t;
+                }
             }
         }
     }

@@ -2,6 +2,8 @@
 // One CTA per SM; one thread issues back-to-back M=128 N=256 K=32-byte MMAs on (uninitialised) smem operands
 // into two TMEM accumulators.  Prints TOP/s per kind: the honest tensor-pipe roofline for each data type.
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/mma_peak tools/mma_peak.cu && tools/mma_peak
+#include <cstring>
+#include <cstdlib>
 #include <cstdio>
 #include <cuda_runtime.h>
 #include "../3dreconstruction_b200/csrc/sm100.cuh"
@@ -18,13 +20,17 @@ MMA_KIND(mma_k_tf32, "tf32")
 MMA_KIND(mma_k_f8, "f8f6f4")
 
 template <int KIND>
-__global__ void __launch_bounds__(128, 1) peak_kernel(int iters, uint32_t idesc, long long* cycles) {
+__global__ void __launch_bounds__(128, 1) peak_kernel(int iters, uint32_t idesc, long long* cycles, int random_fill = 0) {
     extern __shared__ uint8_t raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
     __shared__ uint64_t bar;
     __shared__ uint32_t tptr;
     const int warp = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x3c003c00u;  // benign values
+    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) {
+        uint32_t v = 0x3c003c00u;                                  // benign values
+        if (random_fill) { v = (uint32_t)i * 2654435761u + blockIdx.x * 40503u; v ^= v >> 15; v *= 2246822519u; v ^= v >> 13; }
+        ((uint32_t*)smem)[i] = v;                                  // random bytes: realistic operand toggling for power
+    }
     if (threadIdx.x == 0) { sm100::mbar_init(&bar, 1); sm100::fence_barrier_init(); }
     if (warp == 0) sm100::tmem_alloc<512>(&tptr);
     sm100::fence_proxy_async();
@@ -250,9 +256,35 @@ void run_nsweep(int sms) {
     cudaFree(dcyc);
 }
 
-int main() {
+// Sustained int8 issue rate under the power cap: the i8 peak kernel (operands resident in shared memory, random bytes,
+// no TMA, no epilogue) back to back for `seconds`; prints each launch's TOP/s and SM cycles/ms so the settled clock shows.
+static void run_sustained(int sms, double seconds) {
+    long long* dcyc; cudaMalloc(&dcyc, 8);
+    cudaFuncSetAttribute(peak_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const uint32_t idesc = sm100::make_idesc(2, 1, 1, 128, 256);
+    const int iters = 100000;                                       // ~26 ms per launch at 1.965 GHz
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    double elapsed = 0; int n = 0;
+    while (elapsed < seconds * 1e3) {
+        cudaEventRecord(e0);
+        peak_kernel<0><<<sms, 128, 64 * 1024>>>(iters, idesc, dcyc, 1);
+        cudaEventRecord(e1);
+        cudaDeviceSynchronize();
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        long long cyc = 0; cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+        double macs = (double)sms * iters * 4.0 * 128 * 256 * 32;
+        elapsed += ms; ++n;
+        if (n % 8 == 0)
+            printf("sustained i8 t=%.2fs: %.1f TOP/s, SM clock %.0f MHz (cycles/ms), %.1f cycles per MMA\n", elapsed / 1e3,
+                   2 * macs / (ms * 1e-3) / 1e12, (double)cyc / ms / 1e3, (double)cyc / (iters * 4.0));
+    }
+    cudaFree(dcyc);
+}
+
+int main(int argc, char** argv) {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     printf("SMs: %d\n", sms);
+    if (argc > 1 && !strcmp(argv[1], "sustained")) { run_sustained(sms, argc > 2 ? atof(argv[2]) : 4.0); return 0; }
     run<0>("i8", sm100::make_idesc(2, 1, 1, 128, 256), 32, sms);
     run<1>("f16", sm100::make_idesc(1, 0, 0, 128, 256), 16, sms);
     run<1>("bf16", sm100::make_idesc(1, 1, 1, 128, 256), 16, sms);

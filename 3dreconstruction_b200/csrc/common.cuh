@@ -38,6 +38,7 @@ __host__ __device__ inline size_t b200m_aux_info_off(long long rows) {
     return b200m_aux_fold_off(rows) + ((size_t)rows * B200M_FOLD_K + 255) / 256 * 256;
 }
 __host__ __device__ inline size_t b200m_aux_bytes(long long rows) { return b200m_aux_info_off(rows) + 256; }
+#define B200M_HTC_CHUNK 16   // columns per key chunk of the tensor-core Hamming kernel (hamming_tc.cu); resolve recomputes two chunks per row
 #define B200M_F32_CAND 32    // TF32 candidate list capacity per (query row, column half, column split) (l2_f32.cu)
 
 // Device-side pair record (host b200m_pair + offsets into the per-row workspaces).
@@ -89,6 +90,12 @@ int b200m_set_cuda_error(cudaError_t e, const char* where);
 int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, const DevPair* pairs,
                         int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
                         long long total_rows, u32* colmin, cudaStream_t st);
+// Tensor-core Hamming (hamming_tc.cu): knn over the +-1 int8 stores, then the exact per-row resolve on the packed bits
+int launch_hamming_tc_top2(const int8_t* q_pm1, int64_t q_rows, const int8_t* t_pm1, int64_t t_rows, int Dpad, int dbits,
+                           const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
+                           long long total_rows, cudaStream_t st);
+int launch_hamming_tc_resolve(const uint8_t* q_bits, const uint8_t* t_bits, int D, const DevPair* pairs, int num_pairs,
+                              int max_n, int max_m, int S, bool backward, Top2* arr, long long total_rows, cudaStream_t st);
 #define B200M_HAMMING_IDX_BITS 19   // key32 = dist << 19 | index (hamming.cu); fused column minima need n <= 2^19
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows,
                       const int8_t* t_desc, const int32_t* t_norm, int64_t t_rows, int D,
@@ -109,6 +116,6 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
 int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
                         cudaStream_t st);
 int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
-                     int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st);
+                     int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st);
 int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
                      float* d1, float* d2, const RefineI8& rf, cudaStream_t st);

@@ -1,0 +1,499 @@
+// hamming_tc.cu — NORM_HAMMING knn (k=2) on the 5th-gen tensor cores.
+// Same contract as hamming.cu (cv2.BFMatcher(NORM_HAMMING).knnMatch(k=2)/match as called at
+// /root/reference/FeatureMatchingExtraction/feature_matchers.py:210,227 for ORB/AKAZE/BRISK rows), bit-exact,
+// but the N x M distance evaluations run as an int8 GEMM instead of XOR+POPC:
+//   every descriptor bit becomes one int8 dimension, +1 for a set bit and -1 for a clear one (prep_hamming_tc_kernel);
+//   then a.b = (#agreeing bits) - (#differing bits) = Dbits - 2 h, i.e. h = (Dbits - a.b) / 2 exactly.
+// POPC issues 16 lanes/clk/SM: a 256-bit distance costs 8 POPC, so the INT pipe tops out at 582 Gdist/s (hamming.cu).
+// tcgen05.mma kind::i8 retires 8192 MAC/clk/SM: the same distance is 256 MACs = 1/32 clk/SM, 9.3 Tdist/s at the
+// same clock -- 16x the POPC bound, at the price of an 8x larger operand stream (256 B instead of 32 B per row).
+//
+// Kernel = the pipeline of l2_i8_fold_kernel (l2_i8.cu) without the norm: persistent warp-specialised CTAs in
+// clusters of two that share the train stream by TMA multicast, M128 x N256 tiles, NKB = Dbits / 128 K-blocks of
+// 128 int8, int32 accumulators double-buffered in TMEM.  All rows have the same norm, so the epilogue is a bare
+// 3-input MAX tree over the raw accumulators (larger a.b == closer).  Per 16-column chunk only the maximum
+// survives, packed with the chunk index into ONE int32 key ((a.b + 512) << 20 | ~chunk): the running top-2 of chunk
+// keys is two integer max/min instructions and orders chunks by (distance asc, first column asc) -- cv2's tie rule.
+// hamming_tc_resolve_kernel then recomputes the 2 x 16 distances of a row's two best chunks with POPC on the packed
+// bits and writes the exact (distance, column) top-2 in the format the POPC kernel produces; tail.cu is unchanged.
+//   Exactness: the best column lies in the best chunk (ties: the lowest chunk holds the lowest column).  The
+//   runner-up is either another column of that chunk or the best column of the best OTHER chunk, which is what the
+//   second key names (again lowest chunk first); both chunks are recomputed, so index and distance are exact.
+#include <cstdio>
+#include <cstdlib>
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace {
+
+constexpr int TM = 128, TN = 256, KB_BYTES = 128;
+constexpr int A_KB_BYTES = TM * KB_BYTES;      // 16 KiB
+constexpr int B_KB_BYTES = TN * KB_BYTES;      // 32 KiB
+constexpr int NBF = 4;                         // train K-block ring depth
+constexpr int CTRL_WARPS = 4, EPI_WARPS = 16;
+constexpr int THREADS = (CTRL_WARPS + EPI_WARPS) * 32;
+constexpr int CHUNK = B200M_HTC_CHUNK;         // columns per key chunk
+constexpr int KEY_SHIFT = 20;                  // key = (a.b + 512) << 20 | (0xFFFFF - chunk index)
+constexpr int KEY_LOW = (1 << KEY_SHIFT) - 1;
+constexpr int MASKED = -1024;                  // accumulator value of a column that does not exist: key < 0
+static_assert(CHUNK == 16, "the epilogue reduces 16-column chunks");
+
+__host__ __device__ constexpr int nabuf_of(int nkb) { return nkb <= 2 ? 2 : 1; }      // query tile buffers
+// "accumulator ready" can ride on the ring-stage release of the tile's last K block (saving one tcgen05.commit per tile)
+// only while an epilogue group meets every phase of the barriers it waits on in order: a parity wait that trails by two
+// phases passes early.  With NKB <= 2 a group always waits on the same stage, once per use; with NKB = 3 it alternates
+// between two stages and skips uses, with NKB = 4 the stage is reused by the very next tile -- both get their own commit
+// (one per 1536 / 2048 cycles of MMA).
+__host__ __device__ constexpr bool sep_acc_of(int nkb) { return nkb > 2; }
+
+struct Item {
+    int q_off, n, t_off, m, r0, c_begin, c_end, split, ntiles;
+    long long row_base;
+    bool valid;
+};
+
+__device__ __forceinline__ Item decode_tile(int p, int split, int tile, const DevPair* __restrict__ pairs, int S, int backward) {
+    Item it;
+    it.split = split;
+    DevPair pr = pairs[p];
+    if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
+    else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
+    it.r0 = tile * TM;
+    int cols_per = ((it.m + S - 1) / S + TN - 1) / TN * TN;
+    it.c_begin = it.split * cols_per;
+    it.c_end = min(it.m, it.c_begin + cols_per);
+    it.valid = it.r0 < it.n;
+    it.ntiles = it.c_end > it.c_begin ? (it.c_end - it.c_begin + TN - 1) / TN : 0;
+    return it;
+}
+
+struct Smem {
+    uint8_t *a, *b;
+    int2* xch;            // [2][EPI_WARPS - 4][32] partial top-2 keys of the non-merging epilogue warps
+    uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
+    uint32_t* tmem_ptr;
+};
+__device__ __forceinline__ Smem carve(uint8_t* base, int nkb) {
+    Smem s;
+    s.a = base;
+    s.b = s.a + nabuf_of(nkb) * nkb * A_KB_BYTES;
+    s.xch = (int2*)(s.b + NBF * B_KB_BYTES);
+    uint8_t* p = (uint8_t*)(s.xch + 2 * (EPI_WARPS - 4) * 32);
+    s.a_full = (uint64_t*)p; p += 2 * 8;
+    s.a_empty = (uint64_t*)p; p += 2 * 8;
+    s.b_full = (uint64_t*)p; p += NBF * 8;
+    s.b_empty = (uint64_t*)p; p += NBF * 8;
+    s.acc_full = (uint64_t*)p; p += 2 * 8;
+    s.acc_empty = (uint64_t*)p; p += 2 * 8;
+    s.tmem_ptr = (uint32_t*)p;
+    return s;
+}
+__host__ __device__ constexpr size_t smem_bytes(int nkb) {
+    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NBF * B_KB_BYTES +
+           2 * (EPI_WARPS - 4) * 32 * sizeof(int2) + (4 + 2 * NBF + 4) * 8 + 16;
+}
+static_assert(smem_bytes(1) <= 232448 && smem_bytes(2) <= 232448 && smem_bytes(3) <= 232448 && smem_bytes(4) <= 232448,
+              "shared memory");
+
+__device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
+template <int O>
+__device__ __forceinline__ int max16(const uint32_t (&v)[32]) {
+    int a0 = max3((int)v[O + 0], (int)v[O + 1], (int)v[O + 2]), a1 = max3((int)v[O + 3], (int)v[O + 4], (int)v[O + 5]);
+    int a2 = max3((int)v[O + 6], (int)v[O + 7], (int)v[O + 8]), a3 = max3((int)v[O + 9], (int)v[O + 10], (int)v[O + 11]);
+    int a4 = max3((int)v[O + 12], (int)v[O + 13], (int)v[O + 14]);
+    return max(max3(a0, a1, a2), max3(a3, a4, (int)v[O + 15]));
+}
+__device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : (uint32_t)MASKED;
+}
+
+// CS = CTAs per cluster (1 or 2): the two CTAs of a cluster take adjacent query row tiles of the same pair, each fetches
+// half of every train tile and TMA-multicasts it to both (see l2_i8_fold_kernel for the protocol).
+template <int NKB, int CS>
+__global__ void __launch_bounds__(THREADS, 1)
+hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
+                  const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
+                  int dbits, Top2* __restrict__ out, long long total_rows) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const Smem sm = carve(smem, NKB);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int W_MMA = 0, W_PROD = 1;
+    constexpr int NABUF = nabuf_of(NKB);
+    constexpr bool SEP_ACC = sep_acc_of(NKB);
+    constexpr uint16_t MC_MASK = (1u << CS) - 1;
+    const uint32_t crank = CS > 1 ? sm100::cluster_ctarank() : 0;
+    const long long first_item = CS > 1 ? (long long)sm100::cluster_id_x() : (long long)blockIdx.x;
+    const long long item_stride = CS > 1 ? (long long)sm100::cluster_count_x() : (long long)gridDim.x;
+    auto decode = [&](long long item) -> Item {
+        int tg = (int)(item % tiles_max); item /= tiles_max;     // tiles_max = tile groups per (pair, split)
+        Item it = decode_tile((int)(item / S), (int)(item % S), tg * CS + (int)crank, pairs, S, backward);
+        it.valid = tg * CS * TM < it.n;        // a CTA whose own row tile lies past the pair still streams for its peer
+        return it;
+    };
+
+    if (warp == W_PROD && lane == 0) {
+        sm100::tma_prefetch_desc(&tmap_q);
+        sm100::tma_prefetch_desc(&tmap_t);
+        for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
+        for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], CS); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
+        sm100::fence_barrier_init();
+    }
+    if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    sm100::tc_fence_before();
+    __syncthreads();
+    if constexpr (CS > 1) sm100::cluster_sync_all();
+    sm100::tc_fence_after();
+    const uint32_t tmem_base = *sm.tmem_ptr;
+    constexpr int HALF_ROWS = TN / CS;
+
+    if (warp == W_PROD) {
+        uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode(item);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_empty[ab], a_par);
+            if (sm100::elect_one()) {
+                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb)
+                    sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                       kb * KB_BYTES, it.q_off + it.r0);
+            }
+            __syncwarp();
+            if (++ab == NABUF) { ab = 0; a_par ^= 1; }
+            const int row0 = it.t_off + it.c_begin + (int)crank * HALF_ROWS;
+            for (int j = 0; j < it.ntiles; ++j) {
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb) {
+                    sm100::mbar_wait(&sm.b_empty[bs], b_par);
+                    if (sm100::elect_one()) {
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
+                        uint8_t* bdst = sm.b + (size_t)bs * B_KB_BYTES + (size_t)crank * (B_KB_BYTES / CS);
+                        if constexpr (CS > 1) sm100::tma_load_2d_mc(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN, MC_MASK);
+                        else sm100::tma_load_2d(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN);
+                    }
+                    __syncwarp();
+                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                }
+            }
+        }
+    } else if (warp == W_MMA) {
+        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
+        const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
+        const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
+        uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode(item);
+            if (!it.valid) continue;
+            sm100::mbar_wait(&sm.a_full[ab], a_par);
+            const uint32_t a_lo = a_lo0 + ab * (NKB * A_KB_BYTES >> 4);
+            for (int j = 0; j < it.ntiles; ++j) {
+                sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
+                acc_par ^= 1u << as;
+                sm100::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * TN;
+#pragma unroll
+                for (int kb = 0; kb < NKB; ++kb) {
+                    sm100::mbar_wait(&sm.b_full[bs], b_par);
+                    sm100::tc_fence_after();
+                    if (sm100::elect_one()) {
+                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
+#pragma unroll
+                        for (int k = 0; k < KB_BYTES / 32; ++k)
+                            sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                          idesc, (kb | k) ? 1u : 0u);
+                        if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
+                        else sm100::mma_commit(&sm.b_empty[bs]);
+                        if (SEP_ACC && kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
+                    }
+                    __syncwarp();
+                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                }
+                as ^= 1;
+            }
+            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            __syncwarp();
+            if (++ab == NABUF) { ab = 0; a_par ^= 1; }
+        }
+    } else if (warp >= CTRL_WARPS) {
+        // epilogue: two groups of 8 warps on alternate tiles (group g owns TMEM stage g); a warp drains 128 columns
+        // (half a tile) of its 32 TMEM lanes
+        const int e = warp - CTRL_WARPS;
+        const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * (TN / 2);
+        constexpr int KOFF = (512 << KEY_SHIFT) + KEY_LOW;
+        uint32_t k = 0, tc_base = 0, nitem = 0;
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode(item);
+            if (!it.valid) continue;
+            int v1 = (int)0x80000000, v2 = (int)0x80000000;
+            auto insert = [&](int key) {                   // running top-2 of packed chunk keys
+                v2 = max(v2, min(v1, key));
+                v1 = max(v1, key);
+            };
+            for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
+                const int base = it.c_begin + j * TN + half * (TN / 2);
+                const int lim = it.c_end - base;
+                const int kc = KOFF - (base >> 4);        // key of chunk c of this warp's 8 = (max << 20) + kc - c
+                if constexpr (SEP_ACC) {
+                    sm100::mbar_wait(&sm.acc_full[g], k & 1);
+                } else {   // accumulator ready == the ring stage of this tile's last K block has been released
+                    const uint32_t tc = 2 * k + g;
+                    const uint32_t use = (tc * NKB + NKB - 1) / NBF, stage = (tc * NKB + NKB - 1) % NBF;
+                    sm100::mbar_wait(&sm.b_empty[stage], use & 1);
+                }
+                sm100::tc_fence_after();
+                uint32_t acc[2][32];
+                sm100::tmem_ld32(taddr, acc[0]);
+                sm100::tmem_ld32(taddr + 32, acc[1]);
+                sm100::tmem_ld_wait();
+                if (lim < TN / 2) { mask32(acc[0], lim); mask32(acc[1], lim - 32); }
+                int m0 = max16<0>(acc[0]), m1 = max16<16>(acc[0]);
+                sm100::tmem_ld32(taddr + 64, acc[0]);
+                int m2 = max16<0>(acc[1]), m3 = max16<16>(acc[1]);
+                sm100::tmem_ld32(taddr + 96, acc[1]);
+                insert((m0 << KEY_SHIFT) + kc); insert((m1 << KEY_SHIFT) + kc - 1);
+                insert((m2 << KEY_SHIFT) + kc - 2); insert((m3 << KEY_SHIFT) + kc - 3);
+                sm100::tmem_ld_wait();
+                sm100::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
+                if (lim < TN / 2) { mask32(acc[0], lim - 64); mask32(acc[1], lim - 96); }
+                m0 = max16<0>(acc[0]); m1 = max16<16>(acc[0]);
+                m2 = max16<0>(acc[1]); m3 = max16<16>(acc[1]);
+                insert((m0 << KEY_SHIFT) + kc - 4); insert((m1 << KEY_SHIFT) + kc - 5);
+                insert((m2 << KEY_SHIFT) + kc - 6); insert((m3 << KEY_SHIFT) + kc - 7);
+            }
+            tc_base += (uint32_t)it.ntiles;
+            // the four warps of a TMEM lane quarter hold partial top-2s of the same 32 query rows: merge in shared memory
+            int2* xbuf = sm.xch + (size_t)(nitem & 1) * (EPI_WARPS - 4) * 32;
+            ++nitem;
+            const bool merger = e < 4;
+            if (!merger) xbuf[(e - 4) * 32 + lane] = make_int2(v1, v2);
+            asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+            if (merger) {
+#pragma unroll
+                for (int w = 1; w < 4; ++w) {
+                    const int2 o = xbuf[((w - 1) * 4 + quarter) * 32 + lane];
+                    insert(o.x); insert(o.y);
+                }
+                const int row = it.r0 + quarter * 32 + lane;
+                if (row < it.n) {
+                    auto mk = [&](int key) -> u64 {        // (Hamming distance of the chunk's best column, chunk's first column)
+                        if (key < 0) return B200M_SENTINEL;
+                        const int dot = (key >> KEY_SHIFT) - 512;
+                        const int c0 = (KEY_LOW - (key & KEY_LOW)) << 4;
+                        return ((u64)(u32)((dbits - dot) >> 1) << 32) | (u64)(u32)c0;
+                    };
+                    Top2 t; t.k1 = mk(v1); t.k2 = mk(v2);
+                    out[(long long)it.split * total_rows + it.row_base + row] = t;
+                }
+            }
+        }
+    }
+
+    sm100::tc_fence_before();
+    __syncthreads();
+    if constexpr (CS > 1) sm100::cluster_sync_all();
+    if (warp == W_MMA) sm100::tmem_dealloc<512>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Hamming distance between two D-byte rows (any D, any alignment class named by `vec`: 16, 4 or 1 bytes per load).
+__device__ __forceinline__ int popc_row(const uint8_t* __restrict__ a, const uint8_t* __restrict__ b, int D, int vec) {
+    int d = 0;
+    if (vec == 16) {
+        for (int k = 0; k < D; k += 16) {
+            uint4 x = __ldg(reinterpret_cast<const uint4*>(a + k)), y = __ldg(reinterpret_cast<const uint4*>(b + k));
+            d += __popc(x.x ^ y.x) + __popc(x.y ^ y.y) + __popc(x.z ^ y.z) + __popc(x.w ^ y.w);
+        }
+    } else if (vec == 4) {
+        for (int k = 0; k < D; k += 4)
+            d += __popc(__ldg(reinterpret_cast<const u32*>(a + k)) ^ __ldg(reinterpret_cast<const u32*>(b + k)));
+    } else {
+        for (int k = 0; k < D; ++k) d += __popc((u32)(__ldg(a + k) ^ __ldg(b + k)));
+    }
+    return d;
+}
+
+// One warp per query row: merge the column splits' chunk-level top-2, recompute both chunks (lane = chunk x column)
+// with POPC on the packed bits, write the exact (distance << 32 | column) top-2 into slice 0.
+__global__ void __launch_bounds__(256)
+hamming_tc_resolve_kernel(const uint8_t* __restrict__ q_bits, const uint8_t* __restrict__ t_bits, int D, int vec,
+                          const DevPair* __restrict__ pairs, int blocks_per_pair, Top2* __restrict__ arr,
+                          long long total_rows, int S, int backward) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int p = blockIdx.x / blocks_per_pair;
+    const int i = (blockIdx.x - p * blocks_per_pair) * 8 + warp;
+    const DevPair pr = pairs[p];
+    int q_off = pr.q_off, n = pr.n, t_off = pr.t_off, m = pr.m;
+    long long row_base = pr.fwd_off;
+    const uint8_t *qb = q_bits, *tb = t_bits;
+    if (backward) { q_off = pr.t_off; n = pr.m; t_off = pr.q_off; m = pr.n; row_base = pr.bwd_off; qb = t_bits; tb = q_bits; }
+    if (i >= n) return;
+    const long long row = row_base + i;
+    Top2 t = arr[row];
+    for (int s = 1; s < S; ++s) {
+        Top2 o = arr[(long long)s * total_rows + row];
+        top2_insert(t.k1, t.k2, o.k1);
+        top2_insert(t.k1, t.k2, o.k2);
+    }
+    const u64 ck = lane < CHUNK ? t.k1 : t.k2;
+    const int col = (int)(u32)ck + (lane & (CHUNK - 1));
+    u64 k1 = B200M_SENTINEL, k2 = B200M_SENTINEL;
+    if (ck != B200M_SENTINEL && col < m) {
+        const int d = popc_row(qb + (long long)(q_off + i) * D, tb + (long long)(t_off + col) * D, D, vec);
+        k1 = ((u64)(u32)d << 32) | (u64)(u32)col;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        u64 o1 = __shfl_xor_sync(0xffffffffu, k1, off), o2 = __shfl_xor_sync(0xffffffffu, k2, off);
+        top2_insert(k1, k2, o1);
+        top2_insert(k1, k2, o2);
+    }
+    if (lane == 0) { Top2 r; r.k1 = k1; r.k2 = k2; arr[row] = r; }
+}
+
+// bits -> +-1 int8 dimensions.  One thread per source byte: 8 output bytes (dimension 8k + b = bit b of byte k);
+// dimensions past 8 D are 0 (add nothing to any dot product).
+__global__ void __launch_bounds__(256)
+prep_hamming_tc_kernel(const uint8_t* __restrict__ src, long long rows, int D, int8_t* __restrict__ dst, int Dpad) {
+    const int per_row = Dpad >> 3;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * per_row) return;
+    const long long r = idx / per_row;
+    const int k = (int)(idx - r * per_row);
+    uint2 o = make_uint2(0u, 0u);
+    if (k < D) {
+        const u32 x = __ldg(src + r * D + k);
+        auto spread = [](u32 nib) -> u32 {             // 4 bits -> 4 bytes of 0x01 (set) / 0xFF (clear)
+            u32 w = (nib & 1u) | ((nib & 2u) << 7) | ((nib & 4u) << 14) | ((nib & 8u) << 21);
+            return w | ((w ^ 0x01010101u) * 0xFFu);
+        };
+        o.x = spread(x & 15u);
+        o.y = spread(x >> 4);
+    }
+    *reinterpret_cast<uint2*>(dst + r * Dpad + 8 * k) = o;
+}
+
+}  // namespace
+
+int launch_hamming_tc_top2(const int8_t* q_pm1, int64_t q_rows, const int8_t* t_pm1, int64_t t_rows, int Dpad, int dbits,
+                           const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
+                           long long total_rows, cudaStream_t st) {
+    if (Dpad % KB_BYTES != 0 || Dpad < dbits) return B200M_EINVAL;
+    const int nkb = Dpad / KB_BYTES;
+    if (nkb < 1 || nkb > 4) return B200M_EUNSUPPORTED;           // |a.b| <= 512 is what the packed key holds
+    if (backward) {
+        const int8_t* d = q_pm1; q_pm1 = t_pm1; t_pm1 = d;
+        int64_t r = q_rows; q_rows = t_rows; t_rows = r;
+        int mx = max_n; max_n = max_m; max_m = mx;
+    }
+    if (((long long)max_m + TN) >> 4 > KEY_LOW) return B200M_EUNSUPPORTED;
+    static bool attr_set = false;
+    static int cs_ok[5] = {0, 0, 0, 0, 0};       // max active 2-CTA clusters per K-block count (0: use single CTAs)
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    auto kern = [](int nkb_, int cs_) -> const void* {
+        switch (nkb_ * 2 + cs_ - 1) {
+            case 2: return (const void*)hamming_tc_kernel<1, 1>; case 3: return (const void*)hamming_tc_kernel<1, 2>;
+            case 4: return (const void*)hamming_tc_kernel<2, 1>; case 5: return (const void*)hamming_tc_kernel<2, 2>;
+            case 6: return (const void*)hamming_tc_kernel<3, 1>; case 7: return (const void*)hamming_tc_kernel<3, 2>;
+            case 8: return (const void*)hamming_tc_kernel<4, 1>; default: return (const void*)hamming_tc_kernel<4, 2>;
+        }
+    };
+    if (!attr_set) {
+        for (int nk = 1; nk <= 4; ++nk) {
+            for (int cs = 1; cs <= 2; ++cs)
+                B200M_CUDA_CHECK(cudaFuncSetAttribute(kern(nk, cs), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                      (int)smem_bytes(nk)), "hamming_tc smem attr");
+            cudaLaunchConfig_t qc = {};
+            cudaLaunchAttribute qa[1];
+            qa[0].id = cudaLaunchAttributeClusterDimension;
+            qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+            qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(THREADS); qc.dynamicSmemBytes = smem_bytes(nk);
+            qc.attrs = qa; qc.numAttrs = 1;
+            int nc = 0;
+            if (cudaOccupancyMaxActiveClusters(&nc, kern(nk, 2), &qc) == cudaSuccess && nc * 2 >= sms && !getenv("B200M_NO_CLUSTER"))
+                cs_ok[nk] = nc;
+            else
+                cudaGetLastError();
+        }
+        attr_set = true;
+    }
+    CUtensorMap tq, tt;
+    const int cs = cs_ok[nkb] > 0 ? 2 : 1;
+    int rc = b200m_make_tmap_2d(&tq, q_pm1, (uint64_t)q_rows, (uint64_t)Dpad, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+    if (rc != B200M_OK) return rc;
+    rc = b200m_make_tmap_2d(&tt, t_pm1, (uint64_t)t_rows, (uint64_t)Dpad, TN / cs, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+    if (rc != B200M_OK) return rc;
+    const int tiles_max = (max_n + TM - 1) / TM;
+    int groups = (tiles_max + cs - 1) / cs;
+    long long items = (long long)num_pairs * S * groups;
+    if (items <= 0) return B200M_OK;
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = (unsigned)cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    const long long max_units = cs == 2 ? cs_ok[nkb] : sms;
+    cfg.gridDim = dim3((unsigned)((items < max_units ? items : max_units) * cs));
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem_bytes(nkb);
+    cfg.stream = st;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int bw = backward ? 1 : 0;
+    void* args[] = {(void*)&tq, (void*)&tt, (void*)&pairs, (void*)&items, (void*)&groups, (void*)&S, (void*)&bw,
+                    (void*)&dbits, (void*)&out, (void*)&total_rows};
+    cudaError_t e = cudaLaunchKernelExC(&cfg, kern(nkb, cs), args);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(e, "hamming_tc_kernel launch");
+    return B200M_OK;
+}
+
+int launch_hamming_tc_resolve(const uint8_t* q_bits, const uint8_t* t_bits, int D, const DevPair* pairs, int num_pairs,
+                              int max_n, int max_m, int S, bool backward, Top2* arr, long long total_rows, cudaStream_t st) {
+    const int max_rows = backward ? max_m : max_n;
+    const int bpp = (max_rows + 7) / 8;
+    const long long grid = (long long)num_pairs * bpp;
+    if (grid <= 0) return B200M_OK;
+    if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    const uintptr_t al = (uintptr_t)q_bits | (uintptr_t)t_bits | (uintptr_t)D;
+    const int vec = (al & 15) == 0 ? 16 : ((al & 3) == 0 ? 4 : 1);
+    hamming_tc_resolve_kernel<<<(unsigned)grid, 256, 0, st>>>(q_bits, t_bits, D, vec, pairs, bpp, arr, total_rows, S,
+                                                              backward ? 1 : 0);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "hamming_tc_resolve_kernel launch");
+    return B200M_OK;
+}
+
+extern "C" {
+
+int b200m_hamming_tc_width(int D, int* Dpad) {
+    if (D <= 0 || !Dpad) return B200M_EINVAL;
+    const int w = (8 * D + KB_BYTES - 1) / KB_BYTES * KB_BYTES;
+    if (w > 4 * KB_BYTES) return B200M_EUNSUPPORTED;
+    *Dpad = w;
+    return B200M_OK;
+}
+
+int b200m_prep_hamming_tc(const uint8_t* src, int64_t rows, int D, int8_t* dst, int Dpad, void* stream) {
+    int want = 0;
+    int rc = b200m_hamming_tc_width(D, &want);
+    if (rc != B200M_OK) return rc;
+    if (rows < 0 || Dpad != want) return B200M_EINVAL;
+    if (rows == 0) return B200M_OK;
+    if (!src || !dst || ((uintptr_t)dst & 15)) return B200M_EINVAL;
+    const long long work = rows * (Dpad >> 3);
+    const long long blocks = (work + 255) / 256;
+    if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    prep_hamming_tc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, rows, D, dst, Dpad);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "prep_hamming_tc_kernel launch");
+    return B200M_OK;
+}
+
+}  // extern "C"

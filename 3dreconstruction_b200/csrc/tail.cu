@@ -350,9 +350,16 @@ __device__ __forceinline__ void bitonic(u64* a, int npad) {
 __global__ void __launch_bounds__(1024)
 sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
                  const int32_t* __restrict__ tbest, int smem_keys, int32_t* __restrict__ out_q,
-                 int32_t* __restrict__ out_t, float* __restrict__ out_d, int32_t* __restrict__ out_count) {
+                 int32_t* __restrict__ out_t, float* __restrict__ out_d, int32_t* __restrict__ out_count,
+                 const int32_t* __restrict__ counts, int lo_count, int hi_count) {
+    // This launch handles the pairs with lo_count < survivors <= hi_count (two launches with different block shapes
+    // split the pairs between them); `counts` (CSR mode: finalize's survivor counts) lets the others leave at once.
     extern __shared__ u64 skeys[];
     __shared__ int s_count;
+    if (counts) {
+        const int c = counts[blockIdx.x];
+        if (c <= lo_count || c > hi_count) return;
+    }
     DevPair pr = pairs[blockIdx.x];
     u64* g = sortbuf + pr.sort_off;
     const int n = pr.n, npad = pr.npad;
@@ -370,6 +377,7 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
         }
     }
     __syncthreads();
+    if (s_count <= lo_count || s_count > hi_count) return;
     if (s_count <= smem_keys) {
         a = skeys;
         sort_n = 1;
@@ -442,7 +450,7 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
 }
 
 int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
-                     int32_t* out_t, float* out_d, int32_t* out_count, cudaStream_t st) {
+                     int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st) {
     if (num_pairs <= 0) return B200M_OK;
     static bool attr_set = false;
     const int kMaxSmemKeys = 16384;                       // 128 KiB of 64-bit keys
@@ -451,14 +459,20 @@ int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npa
                                               kMaxSmemKeys * (int)sizeof(u64)), "sort_emit smem attr");
         attr_set = true;
     }
-    // MODE_RATIO keeps a few percent of the rows: a 16 KiB slice (2048 keys) and 256 threads are enough, and such a
-    // block fits beside a resident knn CTA of the next chunk.  The other modes keep most rows: big slice, 1024 threads.
-    const bool few = mode == B200M_MODE_RATIO;
-    const int cap = few ? 2048 : kMaxSmemKeys;
-    int smem_keys = max_npad <= cap ? max_npad : cap;
-    int threads = max_npad >= 2048 && !few ? 1024 : (max_npad >= 512 ? 256 : 64);
-    sort_emit_kernel<<<num_pairs, threads, (size_t)smem_keys * sizeof(u64), st>>>(
-        plan.pairs, plan.sortbuf, plan.tbest, smem_keys, out_q, out_t, out_d, out_count);
+    // MODE_RATIO usually keeps a few percent of the rows: a 16 KiB slice (2048 keys) and 256 threads are enough, and such
+    // a block fits beside a resident knn CTA of the next chunk.  Pairs that keep more (and the other modes, which keep
+    // most rows) take the big shape: 128 KiB slice, 1024 threads.  A handful of pairs has nothing to overlap with: big only.
+    const bool few = mode == B200M_MODE_RATIO && num_pairs >= 64 && max_npad > 2048;
+    const int big_keys = max_npad <= kMaxSmemKeys ? max_npad : kMaxSmemKeys;
+    const int big_threads = max_npad >= 2048 ? 1024 : (max_npad >= 512 ? 256 : 64);
+    if (few) {
+        sort_emit_kernel<<<num_pairs, 256, 2048 * sizeof(u64), st>>>(plan.pairs, plan.sortbuf, plan.tbest, 2048, out_q, out_t,
+                                                                     out_d, out_count, counts, -1, 2048);
+        b200m_count_launch();
+        B200M_CUDA_CHECK(cudaGetLastError(), "sort_emit_kernel launch");
+    }
+    sort_emit_kernel<<<num_pairs, big_threads, (size_t)big_keys * sizeof(u64), st>>>(
+        plan.pairs, plan.sortbuf, plan.tbest, big_keys, out_q, out_t, out_d, out_count, counts, few ? 2048 : -1, 0x7fffffff);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "sort_emit_kernel launch");
     return B200M_OK;

@@ -5,6 +5,7 @@ missing library or device raises — there is no CPU path.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import NamedTuple, Optional, Sequence
 
 import numpy as np
@@ -33,6 +34,7 @@ class DeviceDescriptors(NamedTuple):
     kind: int
     desc: torch.Tensor                 # uint8 [rows, D] | int8 [rows, Dpad] | float32 [rows, Dpad]
     norm: Optional[torch.Tensor]       # L2_I8: int32 aux block (norms[rows], fold digits, info) | float32 [rows] | None
+                                       # HAMMING_TC: int8 [rows, Dpad] +-1 expansion of `desc` (which stays the packed bits)
     rows: int
     width: int                         # D as passed to the C-ABI
 
@@ -49,8 +51,14 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
 
 
 class Engine:
-    def __init__(self, device: Optional[torch.device | str | int] = None):
+    def __init__(self, device: Optional[torch.device | str | int] = None, hamming_path: Optional[str] = None):
+        """hamming_path: "tensor" (tcgen05 kind::i8 over +-1 expanded bits, descriptors up to 64 bytes), "popc"
+        (the INT-pipe kernel) or "auto" (tensor where the width allows it); default from B200M_HAMMING_PATH, else auto.
+        Both produce identical results."""
         self.lib = L.load()
+        self.hamming_path = hamming_path or os.environ.get("B200M_HAMMING_PATH", "auto")
+        if self.hamming_path not in ("auto", "tensor", "popc"):
+            raise ValueError("hamming_path must be auto, tensor or popc")
         if not torch.cuda.is_available():
             raise L.B200MatchError(L.ENODEVICE, "Engine", "no CUDA device: the matcher has no CPU fallback")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -82,7 +90,18 @@ class Engine:
         if norm_type == NORM_HAMMING:
             if t.dtype != torch.uint8:
                 raise ValueError("NORM_HAMMING needs uint8 descriptors")      # cv2.error in the reference
-            return DeviceDescriptors(L.KIND_HAMMING, t, None, rows, D)
+            if force_kind == L.KIND_HAMMING or (force_kind is None and self.hamming_path == "popc"):
+                return DeviceDescriptors(L.KIND_HAMMING, t, None, rows, D)
+            wpad = ctypes.c_int(0)
+            rc = self.lib.b200m_hamming_tc_width(D, ctypes.byref(wpad))
+            if rc == L.EUNSUPPORTED and force_kind is None and self.hamming_path == "auto":
+                return DeviceDescriptors(L.KIND_HAMMING, t, None, rows, D)     # wider than 512 bits: INT-pipe kernel
+            L.check(rc, "b200m_hamming_tc_width")
+            with torch.cuda.device(self.device):
+                pm1 = torch.empty((rows, wpad.value), dtype=torch.int8, device=self.device)
+                L.check(self.lib.b200m_prep_hamming_tc(t.data_ptr(), rows, D, pm1.data_ptr(), wpad.value, self._stream()),
+                        "b200m_prep_hamming_tc")
+            return DeviceDescriptors(L.KIND_HAMMING_TC, t, pm1, rows, D)
         if norm_type != NORM_L2:
             raise ValueError(f"unsupported norm_type {norm_type}")
         if t.dtype == torch.uint8:

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 110
+#define B200M_VERSION 120
 
 #if defined(__GNUC__)
 #define B200M_API __attribute__((visibility("default")))
@@ -53,6 +53,11 @@ extern "C" {
 #define B200M_KIND_L2_I8   1  /* int8 rows (= integer-valued 0..255 float descriptors shifted by
                                  -128) + int32 row norms: tcgen05 kind::i8, exact              */
 #define B200M_KIND_L2_F32  2  /* float32 rows: tcgen05 kind::tf32 candidates + fp32 re-rank     */
+#define B200M_KIND_HAMMING_TC 3 /* uint8 rows, NORM_HAMMING, on the tensor cores: every bit is a +-1 int8
+                                 dimension (b200m_prep_hamming_tc), a.b = Dbits - 2 h exactly; tcgen05
+                                 kind::i8 finds each row's two best 16-column chunks, a POPC pass over the
+                                 packed bits resolves them to the exact neighbours.  Same results as
+                                 B200M_KIND_HAMMING, D <= 64 bytes                              */
 
 /* One image pair of a batch: rows [q_off, q_off+n) of the query store against rows
  * [t_off, t_off+m) of the train store; its matches are written at out_off.. (capacity n). */
@@ -92,6 +97,15 @@ B200M_API int b200m_l2_i8_aux_init(void* aux, int64_t total_rows, int D, void* s
 B200M_API int b200m_prep_l2_i8_rows(const float* src, int64_t row_begin, int64_t row_count, int64_t total_rows,
                      int D, int8_t* dst, int Dpad, void* aux, int32_t* not_integer, void* stream);
 
+/* +-1 expansion for B200M_KIND_HAMMING_TC.
+ *   src   uint8 [rows, D] packed descriptor bits (what cv2 consumes: ORB 32, BRISK 64, AKAZE 61 bytes)
+ *   dst   int8  [rows, Dpad], Dpad from b200m_hamming_tc_width(D) (8 D rounded up to 128; B200M_EUNSUPPORTED when
+ *         D > 64): dimension 8k+b = +1 if bit b of byte k is set, else -1; dimensions past 8 D are 0.  16-byte aligned.
+ * Stateless per row, so a store can be expanded in pieces (offset src/dst by whole rows).  The expanded store is
+ * what b200m_match_pairs* / b200m_knn2_pairs take as q_norm / t_norm for this kind, next to the packed bits. */
+B200M_API int b200m_hamming_tc_width(int D, int* Dpad);
+B200M_API int b200m_prep_hamming_tc(const uint8_t* src, int64_t rows, int D, int8_t* dst, int Dpad, void* stream);
+
 /* Row squared norms for the F32 kind: norms[r] = sum_k src[r,k]^2 (fp32). */
 B200M_API int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream);
 
@@ -110,10 +124,11 @@ B200M_API int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t t
  *   kind           B200M_KIND_*
  *   q_desc/t_desc  descriptor stores (may be the same pointer for all-pairs over one store):
  *                    HAMMING: uint8 [rows, D]      (D = bytes per descriptor, any D >= 1)
+ *                    HAMMING_TC: the same packed uint8 [rows, D], D <= 64
  *                    L2_I8  : int8  [rows, D]      (D multiple of 128, from b200m_prep_l2_i8)
  *                    L2_F32 : float [rows, D]      (D multiple of 32 floats, D <= 256)
  *   q_norm/t_norm  L2_I8: the aux block of b200m_prep_l2_i8 (int32 norms first); L2_F32: float [rows];
- *                  HAMMING: NULL
+ *                  HAMMING: NULL; HAMMING_TC: int8 [rows, Dpad] from b200m_prep_hamming_tc
  *   q_rows/t_rows  number of rows in each store (bounds for TMA maps)
  *   pairs_host     HOST array of num_pairs descriptors (copied to the device workspace)
  *   mode, ratio    B200M_MODE_*; ratio used by MODE_RATIO only (fp64, as Python does at :216)

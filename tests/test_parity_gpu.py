@@ -25,6 +25,15 @@ def eng():
     return b.Engine()
 
 
+@pytest.fixture(scope="module", params=["auto", "popc"])
+def heng(request):
+    """Hamming engines: "auto" = tensor-core kernel (+-1 int8 GEMM + POPC resolve) up to 64-byte descriptors, INT-pipe
+    kernel above; "popc" = INT-pipe kernel everywhere.  Both must be bit-exact against the oracle."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return b.Engine(hamming_path=request.param)
+
+
 def assert_exact(got, want, what=""):
     assert len(got.query_idx) == len(want.query_idx), f"{what}: count {len(got.query_idx)} != {len(want.query_idx)}"
     assert np.array_equal(got.query_idx, want.query_idx), what
@@ -67,64 +76,107 @@ def test_golden_vectors(eng, golden):
 # ------------------------------------------------------------------ Hamming
 @pytest.mark.parametrize("nbytes", [1, 5, 32, 61, 64, 128, 200])
 @pytest.mark.parametrize("mode", MODES)
-def test_hamming_vs_oracle(eng, nbytes, mode):
+def test_hamming_vs_oracle(heng, nbytes, mode):
     for seed, (n, m) in enumerate([(1, 1), (1, 7), (9, 1), (2, 2), (130, 127), (257, 513), (1000, 777)]):
         a, c = synth.binary_pair(seed=100 + seed, n=max(n, m), nbytes=nbytes)
         a, c = a[:n], c[:m]
-        assert_exact(eng.match_arrays(a, c, b.NORM_HAMMING, *mode), O.reference_match(a, c, O.NORM_HAMMING, *mode),
+        assert_exact(heng.match_arrays(a, c, b.NORM_HAMMING, *mode), O.reference_match(a, c, O.NORM_HAMMING, *mode),
                      f"hamming D={nbytes} n={n} m={m} mode={mode}")
 
 
-def test_hamming_heavy_ties(eng):
+def test_hamming_heavy_ties(heng):
     rng = np.random.default_rng(7)
     for nbytes, hi in [(1, 2), (1, 4), (2, 3), (32, 2)]:
         a = rng.integers(0, hi, size=(300, nbytes), dtype=np.uint8)
         c = np.concatenate([a[:100], a[:100], np.zeros((10, nbytes), np.uint8),
                             rng.integers(0, hi, size=(211, nbytes), dtype=np.uint8)])
         for mode in MODES:
-            assert_exact(eng.match_arrays(a, c, b.NORM_HAMMING, *mode),
+            assert_exact(heng.match_arrays(a, c, b.NORM_HAMMING, *mode),
                          O.reference_match(a, c, O.NORM_HAMMING, *mode), f"ties D={nbytes} hi={hi} {mode}")
 
 
-def test_hamming_knn2_raw(eng):
+def test_hamming_knn2_raw(heng):
     a, c = synth.binary_pair(seed=5, n=700, m=650, nbytes=32)
-    got = eng.knn2_arrays(a, c, b.NORM_HAMMING)
+    got = heng.knn2_arrays(a, c, b.NORM_HAMMING)
     want = O.knn2_c(a, c, O.NORM_HAMMING)
     for x, y in zip(got, want):
         assert np.array_equal(x, y)
-    got = eng.knn2_arrays(a, c[:1], b.NORM_HAMMING)          # M == 1: second neighbour absent
+    got = heng.knn2_arrays(a, c[:1], b.NORM_HAMMING)          # M == 1: second neighbour absent
     assert np.all(got.idx2 == -1) and np.all(got.d2 == -1)
 
 
-def test_hamming_config2_full_size(eng):
+def test_hamming_config2_full_size(heng):
     """BASELINE config 2: ORB 256-bit, 10k x 10k, cross-check.  Oracle finishes in seconds here."""
     a, c = synth.binary_pair(seed=1, n=10000, nbytes=32)
-    got = eng.match_arrays(a, c, b.NORM_HAMMING, True, None)
+    got = heng.match_arrays(a, c, b.NORM_HAMMING, True, None)
     assert_exact(got, O.reference_match(a, c, O.NORM_HAMMING, True, None), "config2")
     assert len(got.query_idx) > 5000
     # properties: sorted by (distance, queryIdx); mutual (swap roles -> same pair set)
     key = got.distance.astype(np.float64) * 1e6 + got.query_idx
     assert np.all(np.diff(key) > 0)
-    rev = eng.match_arrays(c, a, b.NORM_HAMMING, True, None)
+    rev = heng.match_arrays(c, a, b.NORM_HAMMING, True, None)
     assert set(zip(got.query_idx.tolist(), got.train_idx.tolist())) == set(zip(rev.train_idx.tolist(), rev.query_idx.tolist()))
 
 
-def test_hamming_batched_pairs_equal_single(eng):
+def test_hamming_batched_pairs_equal_single(heng):
     """Several pairs with ragged sizes in one C-ABI call == the same pairs one by one."""
     sets = [synth.binary_pair(seed=40 + i, n=n, nbytes=32)[0] for i, n in enumerate([300, 129, 1, 640, 77])]
     store = np.concatenate(sets)
     offs = np.cumsum([0] + [len(s) for s in sets])
-    dd = eng.prepare(store, b.NORM_HAMMING)
+    dd = heng.prepare(store, b.NORM_HAMMING)
     spec, pairs = [], [(0, 1), (0, 3), (2, 4), (3, 1), (4, 2), (1, 1)]
     for i, j in pairs:
         spec.append((offs[i], len(sets[i]), offs[j], len(sets[j])))
     for mode in MODES:
-        oq, ot, od, oc, ooff = eng.match_device(dd, dd, spec, b.mode_of(*mode), mode[1] or 0.0)
+        oq, ot, od, oc, ooff = heng.match_device(dd, dd, spec, b.mode_of(*mode), mode[1] or 0.0)
         oq, ot, od, oc = oq.cpu().numpy(), ot.cpu().numpy(), od.cpu().numpy(), oc.cpu().numpy()
         for p, (i, j) in enumerate(pairs):
             want = O.reference_match(sets[i], sets[j], O.NORM_HAMMING, *mode)
             s = slice(int(ooff[p]), int(ooff[p]) + int(oc[p]))
             assert_exact(O.Matches(oq[s], ot[s], od[s]), want, f"batched pair {p} mode {mode}")
+
+
+def test_hamming_tc_kind_is_used_and_matches_popc(heng):
+    """The tensor path must actually be the one that runs under "auto" (no silent detour through the POPC kernel)."""
+    a, c = synth.binary_pair(seed=9, n=1500, m=1300, nbytes=32)
+    dd = heng.prepare(a, b.NORM_HAMMING)
+    L = pkg("_lib")
+    assert dd.kind == (L.KIND_HAMMING_TC if heng.hamming_path == "auto" else L.KIND_HAMMING)
+    if dd.kind == L.KIND_HAMMING_TC:
+        pm1 = dd.norm.cpu().numpy()
+        bits = np.unpackbits(a, axis=1, bitorder="little").astype(np.int8) * 2 - 1
+        assert pm1.shape == (1500, 256) and np.array_equal(pm1, bits)
+        dd61 = heng.prepare(a[:, :29], b.NORM_HAMMING)          # 232 bits -> 256 dims, the last 24 are zero
+        p = dd61.norm.cpu().numpy()
+        assert p.shape == (1500, 256) and np.array_equal(p[:, :232], bits[:, :232]) and not p[:, 232:].any()
+
+
+@pytest.mark.parametrize("nbytes", [16, 32, 48, 61, 64])
+def test_hamming_tc_column_splits_tails_and_chunk_ties(heng, nbytes):
+    """Sizes that exercise one/two CTAs per cluster, ragged last tiles, several column splits; duplicated train rows
+    put equal distances into different 16-column chunks, tiles and splits (ties -> lowest train index)."""
+    rng = np.random.default_rng(nbytes)
+    for n, m in [(128, 256), (129, 257), (255, 4096), (700, 5000), (2100, 1031)]:
+        a = rng.integers(0, 256, size=(n, nbytes), dtype=np.uint8)
+        c = rng.integers(0, 256, size=(m, nbytes), dtype=np.uint8)
+        k = min(n, m) // 3
+        c[m - k:] = a[:k]                            # exact copies late in the train set ...
+        c[5:5 + k // 2] = a[:k // 2]                 # ... and earlier duplicates of half of them
+        c[m // 2] = c[m // 2 + 17] = a[n - 1]
+        for mode in MODES:
+            assert_exact(heng.match_arrays(a, c, b.NORM_HAMMING, *mode), O.reference_match(a, c, O.NORM_HAMMING, *mode),
+                         f"tc D={nbytes} n={n} m={m} mode={mode}")
+        got = heng.knn2_arrays(a, c, b.NORM_HAMMING)
+        for x, y in zip(got, O.knn2_c(a, c, O.NORM_HAMMING)):
+            assert np.array_equal(x, y), f"knn2 D={nbytes} n={n} m={m}"
+
+
+def test_hamming_akaze_full_size_pair(heng):
+    """One pair of BASELINE config 5's shape (AKAZE 16384 x 16384 x 61 bytes, mutual check) against the C oracle."""
+    a, c = synth.binary_pair(seed=4, n=16384, nbytes=61)
+    got = heng.match_arrays(a, c, b.NORM_HAMMING, True, None)
+    assert_exact(got, O.reference_match(a, c, O.NORM_HAMMING, True, None), "akaze full pair")
+
 
 
 # ------------------------------------------------------------------ integer-valued L2 (SIFT) — tcgen05 kind::i8

@@ -260,14 +260,18 @@ def single_pair_extras(torch, b, eng, pk):
     out["sift_pair_8192x8192_ratio0.75"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": gd,
                                             "note": "one pair cannot fill 148 SMs x tensor pipe; latency-bound"}
     a, c = b.synth.binary_pair(seed=1, n=10000, nbytes=32)
-    da, dc = eng.prepare(a, b.NORM_HAMMING), eng.prepare(c, b.NORM_HAMMING)
-    ms = timed(lambda: eng.match_device(da, dc, [(0, 10000, 0, 10000)], L.MODE_CROSS))
-    gd = 1e8 / 1e9 / (ms / 1e3)
     popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 8 / 1e9       # Gdist/s, 256-bit, at max clock
-    out["orb_pair_10000x10000_crosscheck"] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": gd,
-                                              "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": gd / popc_peak,
-                                              "note": "single fused pass: row top-2 and column minima from the same distances; "
-                                                      "one pair = 79 row tiles, cannot fill 148 SMs evenly"}
+    orb = {}
+    for path, e in (("tensor", eng), ("popc", b.Engine(eng.device, hamming_path="popc"))):
+        da, dc = e.prepare(a, b.NORM_HAMMING), e.prepare(c, b.NORM_HAMMING)
+        ms = timed(lambda: e.match_device(da, dc, [(0, 10000, 0, 10000)], L.MODE_CROSS))
+        orb[path] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": 1e8 / 1e9 / (ms / 1e3)}
+    orb["tensor"]["note"] = ("default path: bits as +-1 int8, tcgen05 kind::i8 in both directions + POPC resolve of the two best "
+                             "16-column chunks per row (hamming_tc.cu); one pair = 79 row tiles, launch/tail latency-bound")
+    orb["popc"].update({"popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": orb["popc"]["gdist_per_s"] / popc_peak,
+                        "note": "INT-pipe kernel (hamming.cu): single fused pass, row top-2 and column minima from the same distances"})
+    out["orb_pair_10000x10000_crosscheck"] = {**orb["tensor"], "popc_path": orb["popc"],
+                                              "speedup_over_popc_path": orb["popc"]["ms_per_pair"] / orb["tensor"]["ms_per_pair"]}
     out.update(allpairs_extras(torch, b, eng, pk))
     return out
 
@@ -311,12 +315,13 @@ def allpairs_extras(torch, b, eng, pk):
     ap = importlib.import_module("3dreconstruction_b200.allpairs")
     out = {}
     lib = eng.lib
+    timed_eng = [eng]                      # the engine timed_pass drives (the Hamming sample runs both kernel paths)
 
     def timed_pass(store, pairs, reps):
         """(ms per pass with the two-stream chunk pipeline, knn-kernel ms per pass from a second, un-pipelined pass
         whose per-kernel CUDA events bracket nothing but the kernel, matches)."""
         import ctypes
-        m = ap.AllPairsMatcher(eng, chunk_pairs=1024)
+        m = ap.AllPairsMatcher(timed_eng[0], chunk_pairs=1024)
         r = m.match(store, pairs, cross_check=True)           # warm-up (also sizes the buffers)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -324,7 +329,7 @@ def allpairs_extras(torch, b, eng, pk):
         for _ in range(reps):
             r = m.match(store, pairs, cross_check=True)
         e1.record(); torch.cuda.synchronize()
-        m2 = ap.AllPairsMatcher(eng, chunk_pairs=1024, pipeline=False)
+        m2 = ap.AllPairsMatcher(timed_eng[0], chunk_pairs=1024, pipeline=False)
         m2.match(store, pairs, cross_check=True)
         torch.cuda.synchronize()
         lib.b200m_timing_enable(1)
@@ -359,19 +364,34 @@ def allpairs_extras(torch, b, eng, pk):
     I, n, nb = 48, 16384, 61
     desc = binary_set_gpu(torch, eng.device, I, n, nb)
     desc = torch.nn.functional.pad(desc.view(I * n, nb), (0, 3))
-    store = ap.build_store(eng, desc, b.NORM_HAMMING, counts=[n] * I)
     pairs = ap.all_pairs(I)
-    ms, knn_ms, matches = timed_pass(store, pairs, 1)
-    gd = len(pairs) * n * n / 1e9 / (ms / 1e3)
     popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 16 / 1e9      # Gdist/s, 512-bit rows, at max clock
+    int8_peak = 2.0 * pk["bf16_tflops_sustained"]
+    res = {}
+    for path in ("tensor", "popc"):
+        e = eng if path == "tensor" else b.Engine(eng.device, hamming_path="popc")
+        store = ap.build_store(e, desc, b.NORM_HAMMING, counts=[n] * I)
+        timed_eng[0] = e
+        ms, knn_ms, matches = timed_pass(store, pairs, 2 if path == "tensor" else 1)
+        gd = len(pairs) * n * n / 1e9 / (ms / 1e3)
+        res[path] = {"ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3), "gdist_per_s": gd, "matches": matches,
+                     "knn_stage_ms": knn_ms, "full_config_estimate_s_1gpu": 499500 / (len(pairs) / (ms / 1e3))}
+        del store
+    timed_eng[0] = eng
+    tops = 2.0 * 2 * len(pairs) * n * n * 512 / (res["tensor"]["knn_stage_ms"] / 1e3) / 1e12     # both directions, 512 int8 dims
+    res["tensor"].update({
+        "int8_tops_achieved_knn_stage": tops, "int8_peak_tops": int8_peak, "frac_of_int8_roofline": tops / int8_peak,
+        "frac_of_hw_int8_microbench": tops / 4590.0,
+        "peak_source": "2 x bf16_tflops_sustained of MEASURED_PEAKS.json; 4590 = tools/mma_peak.cu issue peak at 1965 MHz",
+        "note": "default path (hamming_tc.cu): bits as +-1 int8, K = 512, forward and backward knn on the tensor cores, "
+                "exact POPC resolve of two 16-column chunks per row; knn stage = both directions + resolve"})
+    res["popc"].update({
+        "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": res["popc"]["gdist_per_s"] / popc_peak,
+        "note": "INT-pipe kernel (hamming.cu): each distance computed once (fused row top-2 + column minima); POPC roofline at 1965 MHz"})
     out["akaze_allpairs_sample_48x16384x61B_mutual"] = {
-        "pairs": len(pairs), "of_pairs": 499500, "ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3),
-        "gdist_per_s": gd, "matches": matches, "knn_stage_ms": knn_ms,
-        "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": gd / popc_peak,
-        "frac_of_popc_roofline_knn_stage": len(pairs) * n * n / 1e9 / (knn_ms / 1e3) / popc_peak,
-        "note": "each distance is computed once (fused row top-2 + column minima); POPC roofline at 1965 MHz",
-        "matches_d2h_bytes_compact": matches * 6,
-        "full_config_estimate_s_1gpu": 499500 / (len(pairs) / (ms / 1e3))}
+        "pairs": len(pairs), "of_pairs": 499500, **res["tensor"], "popc_path": res["popc"],
+        "speedup_over_popc_path": res["popc"]["ms_per_pass"] / res["tensor"]["ms_per_pass"],
+        "matches_d2h_bytes_compact": res["tensor"]["matches"] * 6}
     return out
 
 

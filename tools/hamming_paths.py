@@ -46,15 +46,17 @@ def main():
     pa = argparse.ArgumentParser()
     pa.add_argument("--images", type=int, default=32)
     pa.add_argument("--reps", type=int, default=3)
+    pa.add_argument("--paths", default="popc,tensor")
+    pa.add_argument("--cases", default="pair,orb,akaze")
     args = pa.parse_args()
     dev = torch.device("cuda:0")
     g = torch.Generator(device=dev); g.manual_seed(0)
-    for path in ("popc", "tensor"):
+    for path in args.paths.split(","):
         eng = b.Engine(dev, hamming_path=path)
         # one ORB pair, 10k x 10k, cross-check and ratio
         a, c = b.synth.binary_pair(seed=1, n=10000, nbytes=32)
         da, dc = eng.prepare(a, b.NORM_HAMMING), eng.prepare(c, b.NORM_HAMMING)
-        for mode, name in ((L.MODE_CROSS, "cross"), (L.MODE_RATIO, "ratio0.7")):
+        for mode, name in ((L.MODE_CROSS, "cross"), (L.MODE_RATIO, "ratio0.7")) if "pair" in args.cases else ():
             fn = lambda: eng.match_device(da, dc, [(0, 10000, 0, 10000)], mode, 0.7)   # noqa: E731
             ms = timed(fn, 20)
             k = knn_ms(eng.lib, fn, 20)
@@ -62,6 +64,8 @@ def main():
                               "gdist_per_s": 1e8 / 1e9 / (ms / 1e3)}), flush=True)
         # all pairs: ORB 8192 x 32 B and AKAZE 16384 x 64 B
         for name, n, nb, images in (("orb_allpairs", 8192, 32, 2 * args.images), ("akaze_allpairs", 16384, 64, args.images)):
+            if name.split("_")[0] not in args.cases:
+                continue
             desc = torch.randint(0, 256, (images * n, nb), device=dev, generator=g, dtype=torch.uint8)
             store = ap.build_store(eng, desc, b.NORM_HAMMING, counts=[n] * images)
             pairs = ap.all_pairs(images)

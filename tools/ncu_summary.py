@@ -46,8 +46,16 @@ def main():
     except StopIteration:
         return
     hdr = src[hi]
-    data = [r for r in src[hi + 1:] if len(r) == len(hdr)]
     ix = {h: i for i, h in enumerate(hdr)}
+    # several kernels in one report repeat the header: keep the kernel with the most samples
+    groups, cur = [], []
+    for r in src[hi + 1:]:
+        if len(r) == len(hdr) and r[ix["# Samples"]].strip().isdigit():
+            cur.append(r)
+        elif r and r[0] == "Address":
+            groups.append(cur); cur = []
+    groups.append(cur)
+    data = max(groups, key=len)        # the longest kernel = the knn kernel, not its helpers
     stalls = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
     tot = sum(int(r[ix["# Samples"]] or 0) for r in data) or 1
     agg = sorted(((sum(int(r[ix[s]] or 0) for r in data), s) for s in stalls), reverse=True)

@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libb200match.so")
-SOURCES = ["capi.cu", "hamming.cu", "hamming_tc.cu", "l2_i8.cu", "l2_f32.cu", "tail.cu", "prep.cu"]
+SOURCES = ["capi.cu", "hamming.cu", "hamming_tc.cu", "l2_i8.cu", "l2_f32.cu", "tail.cu", "prep.cu", "adapter.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

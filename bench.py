@@ -273,7 +273,64 @@ def single_pair_extras(torch, b, eng, pk):
     out["orb_pair_10000x10000_crosscheck"] = {**orb["tensor"], "popc_path": orb["popc"],
                                               "speedup_over_popc_path": orb["popc"]["ms_per_pair"] / orb["tensor"]["ms_per_pair"]}
     out.update(allpairs_extras(torch, b, eng, pk))
+    out.update(sfm_extras(torch, b, eng, pk))
     return out
+
+
+def sfm_extras(torch, b, eng, pk):
+    """features of every image cached in HBM once, all pairs matched, N x 4 correspondences gathered on
+    the device (csrc/adapter.cu) and copied out; beside it the reference's per-match Python assembly
+    (result_converters.py:763-766) timed on a sample of the same matches."""
+    import time
+    import numpy as np
+    sfm = importlib.import_module("3dreconstruction_b200.sfm")
+    ap = importlib.import_module("3dreconstruction_b200.allpairs")
+    I, n = 32, 8192
+    desc = sift_set_gpu(torch, eng.device, I, n).view(I * n, 128)
+    store = ap.build_store(eng, desc, b.NORM_L2, counts=[n] * I)
+    g = torch.Generator(device=eng.device); g.manual_seed(5)
+    kp = torch.rand((I * n, 2), device=eng.device, generator=g) * 2000.0
+    fs = sfm.FeatureSet([f"img_{i:03d}" for i in range(I)], [(2000, 2000)] * I, store, kp, "SIFT")
+    m = ap.AllPairsMatcher(eng, chunk_pairs=2048)
+    sfm.match_feature_set(eng, fs, None, False, RATIO, matcher=m)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    r = sfm.match_feature_set(eng, fs, None, False, RATIO, matcher=m)
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3
+    # the gather alone, device-resident CSR
+    csr = m.match(store, r.pairs, False, RATIO)
+    K = int(csr.query_idx.numel())
+    q_off = torch.from_numpy(store.offsets[r.pairs[:, 0]].astype(np.int32)).to(eng.device)
+    t_off = torch.from_numpy(store.offsets[r.pairs[:, 1]].astype(np.int32)).to(eng.device)
+    corr = torch.empty((max(K, 1), 4), dtype=torch.float32, device=eng.device)
+    call = lambda: eng.lib.b200m_gather_correspondences(kp.data_ptr(), I * n, q_off.data_ptr(), t_off.data_ptr(),   # noqa: E731
+                                                        csr.ptr.data_ptr(), len(r.pairs), csr.query_idx.data_ptr(),
+                                                        csr.train_idx.data_ptr(), corr.data_ptr(), eng._stream())
+    call(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        call()
+    e1.record(); torch.cuda.synchronize()
+    gms = e0.elapsed_time(e1) / 20
+    # reference way on the host for the first pairs: one list comprehension per side over Python match objects
+    kp_host = kp.cpu().numpy()
+    pts = [tuple(map(float, xy)) for xy in kp_host[:2 * n]]
+    s = r.pair_slice(0)
+    q, t = r.query_idx[s].tolist(), r.train_idx[s].tolist()
+    reps = max(1, 20000 // max(len(q), 1))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        np.hstack([np.array([pts[i] for i in q]), np.array([pts[n + j] for j in t])])
+    cpu_us_per_match = (time.perf_counter() - t0) / (reps * max(len(q), 1)) * 1e6
+    return {"sfm_handoff_sift_32x8192": {
+        "pairs": len(r.pairs), "matches": K, "ms_match_gather_d2h": ms, "pairs_per_s": len(r.pairs) / (ms / 1e3),
+        "gather_kernel_ms": gms, "gather_bytes": K * 40, "gather_gbs": K * 40 / (gms / 1e3) / 1e9, "hbm_peak_gbs": pk["hbm_gbs"],
+        "reference_python_assembly_us_per_match": cpu_us_per_match,
+        "reference_python_assembly_ms_for_these_matches": cpu_us_per_match * K / 1e3,
+        "note": "feature cache + all-pairs + device gather of keypoint coordinates into N x 4 correspondences; "
+                "the gather is latency-bound at this size (40 algorithmic bytes per match)"}}
 
 
 def superpoint_set_gpu(torch, device, images, n, d=256, seed=2, pool=8192, shared=0.5, sigma=0.05):

@@ -162,6 +162,19 @@ B200M_API int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm,
                      int32_t* idx1, int32_t* idx2, float* d1, float* d2,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Matches -> N x 4 correspondences (x1, y1, x2, y2) for the structure-from-motion stage: the rows the reference
+ * builds one Python object at a time at result_converters.py:763-766 and CameraPoseEstimation reads as
+ * matches_data[(img_i, img_j)]['correspondences'] (pair_selector.py:54-67, correspondence_manager.py:78-119).
+ *   kp_xy       float32 [rows, 2]: cv2.KeyPoint.pt of every row of the descriptor store (same row order)
+ *   pair_q_off / pair_t_off   int32 [num_pairs] (device): first store row of each pair's query / train image
+ *   ptr, q_idx, t_idx         the CSR b200m_match_pairs_csr produced (device)
+ *   out_xyxy    float32 [ptr[num_pairs], 4], 16-byte aligned: row k = (kp[q_off + q_idx[k]], kp[t_off + t_idx[k]])
+ */
+B200M_API int b200m_gather_correspondences(const float* kp_xy, int64_t rows, const int32_t* pair_q_off,
+                     const int32_t* pair_t_off, const int64_t* ptr, int num_pairs, const int32_t* q_idx,
+                     const int32_t* t_idx, float* out_xyxy, void* stream);
+
 /* Measurement hooks for bench.py's roofline: when enabled, CUDA events are recorded on the
  * launching stream around every knn-stage kernel; collect() synchronises them and returns the summed
  * device time (ms) and the number of knn launches since the last collect/enable. */

@@ -33,5 +33,23 @@ def golden():
     return out
 
 
+def sfm_golden_sets():
+    """tests/golden/sfm_golden.npz (oracle/make_golden_sfm.py): the reference's matcher + converter on small image sets."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "sfm_golden.npz"))
+    out = {}
+    for name in z["_sets"]:
+        name = str(name)
+        norm, cc, ratio = z[f"{name}/params"]
+        count = z[f"{name}/count"]
+        pairs = {}
+        for i in range(len(count)):
+            for j in range(i + 1, len(count)):
+                k = f"{name}/{i}_{j}"
+                pairs[(i, j)] = dict(q=z[k + "/q"], t=z[k + "/t"], s=z[k + "/s"], c=z[k + "/c"])
+        out[name] = dict(norm=int(norm), cross_check=bool(cc), ratio=None if ratio < 0 else float(ratio), count=count,
+                         desc=z[f"{name}/desc"], xy=z[f"{name}/xy"], pairs=pairs)
+    return out
+
+
 def is_integer_valued(a) -> bool:
     return a.dtype == np.uint8 or bool(np.all(a == np.rint(a)))

@@ -452,3 +452,26 @@ def test_streaming_all_pairs_non_integer_falls_back_to_generic_path(eng):
     for p, (i, j) in enumerate(res.pairs):
         want = O.reference_match(imgs[i], imgs[j], O.NORM_L2, False, 0.9)
         assert_close_float(O.Matches(*res.pair(p)), want, f"streaming fallback pair {i},{j}", 0.05)
+
+
+# ------------------------------------------------------------------ SfM hand-off (feature cache -> all pairs -> correspondences)
+@pytest.mark.parametrize("name", ["orb_cross", "orb_ratio07", "sift_ratio075"])
+def test_sfm_handoff_equals_reference_converter(eng, name):
+    """build_feature_set + match_feature_set (device gather of keypoint coordinates) against what the reference's
+    EnhancedBFMatcher + ResultConverter._convert_method produced for every pair (tests/golden/sfm_golden.npz)."""
+    from conftest import sfm_golden_sets
+    sfm = pkg("sfm")
+    g = sfm_golden_sets()[name]
+    offs = np.concatenate([[0], np.cumsum(g["count"])])
+    F = b.contracts.FeatureData
+    feats = {f"img_{i}": F(keypoints=g["xy"][offs[i]:offs[i + 1]], descriptors=g["desc"][offs[i]:offs[i + 1]], method=name)
+             for i in range(len(g["count"]))}
+    fs = sfm.build_feature_set(eng, feats, g["norm"], {k: (1600, 1200) for k in feats})
+    r = sfm.match_feature_set(eng, fs, None, g["cross_check"], g["ratio"])
+    assert len(r) == len(g["pairs"])
+    for p, (i, j) in enumerate(r.pairs):
+        want, got = g["pairs"][(int(i), int(j))], r.pair_dict(p)
+        assert np.array_equal(got["query_indices"], want["q"]) and np.array_equal(got["train_indices"], want["t"]), (i, j)
+        assert np.array_equal(got["match_scores"], want["s"]) and np.array_equal(got["correspondences"], want["c"]), (i, j)
+    blob = r.to_matches_pickle()
+    assert all(v["num_matches"] == len(v["correspondences"]) for v in blob["matches_data"].values())

@@ -390,18 +390,20 @@ def broadcast_store(store: Optional[Store], norm_type: int, device: torch.device
     desc = store.dd.desc if rank == src else torch.empty(shape, dtype=tdt, device=device)
     dist.broadcast(desc, src=src)
     norm = None
-    if kind == L.KIND_HAMMING_TC:
-        # the +-1 expansion is 8x the packed bits: ship the bits only, every rank expands its own copy
+    if kind in (L.KIND_HAMMING_TC, L.KIND_HAMMING_FP4):
+        # the +-1 expansion is 8x / 4x the packed bits: ship the bits only, every rank expands its own copy
         if rank == src:
             norm = store.dd.norm
         else:
             lib = L.load()
+            fp4 = kind == L.KIND_HAMMING_FP4
             wpad = ctypes.c_int(0)
-            L.check(lib.b200m_hamming_tc_width(width, ctypes.byref(wpad)), "b200m_hamming_tc_width")
-            norm = torch.empty((rows, wpad.value), dtype=torch.int8, device=device)
+            L.check((lib.b200m_hamming_fp4_width if fp4 else lib.b200m_hamming_tc_width)(width, ctypes.byref(wpad)), "b200m_hamming_*_width")
+            norm = torch.empty((rows, wpad.value), dtype=torch.uint8 if fp4 else torch.int8, device=device)
             with torch.cuda.device(device):
-                L.check(lib.b200m_prep_hamming_tc(desc.data_ptr(), rows, width, norm.data_ptr(), wpad.value,
-                                                  torch.cuda.current_stream(device).cuda_stream), "b200m_prep_hamming_tc")
+                L.check((lib.b200m_prep_hamming_fp4 if fp4 else lib.b200m_prep_hamming_tc)(
+                    desc.data_ptr(), rows, width, norm.data_ptr(), wpad.value, torch.cuda.current_stream(device).cuda_stream),
+                    "b200m_prep_hamming_*")
     elif ndt is not None:
         norm = store.dd.norm if rank == src else torch.empty((ndt[1],), dtype=getattr(torch, ndt[0].split(".")[-1]), device=device)
         dist.broadcast(norm, src=src)

@@ -27,7 +27,7 @@ static int choose_splits(int kind, int num_pairs, int max_n, int max_m, int mode
     long long want = 2LL * sm_count;
     int S = (int)((want + tiles - 1) / (tiles > 0 ? tiles : 1));
     // keep >= 256 columns per split (>= 512 for L2_I8: four 128-column tiles, one per epilogue group)
-    const int min_cols = kind == B200M_KIND_L2_I8 || kind == B200M_KIND_HAMMING_TC ? 512 : 256;
+    const int min_cols = kind == B200M_KIND_L2_I8 || kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? 512 : 256;
     int max_split = (((max_n < max_m ? max_n : max_m) + min_cols - 1) / min_cols);
     if (S > max_split) S = max_split;
     if (S > 8) S = 8;
@@ -160,12 +160,14 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
                          cudaStream_t st, MatchPlan& pl, int& max_n, int& max_npad) {
     if (num_pairs < 0 || D <= 0 || (num_pairs > 0 && (!pairs_host || !q_desc || !t_desc || !workspace)))
         return B200M_EINVAL;
-    if (kind != B200M_KIND_HAMMING && kind != B200M_KIND_L2_I8 && kind != B200M_KIND_L2_F32 && kind != B200M_KIND_HAMMING_TC)
+    if (kind != B200M_KIND_HAMMING && kind != B200M_KIND_L2_I8 && kind != B200M_KIND_L2_F32 && kind != B200M_KIND_HAMMING_TC &&
+        kind != B200M_KIND_HAMMING_FP4)
         return B200M_EINVAL;
     if (kind != B200M_KIND_HAMMING && (!q_norm || !t_norm) && num_pairs > 0) return B200M_EINVAL;
     int htc_pad = 0;                                  // HAMMING_TC: width of the +-1 stores
-    if (kind == B200M_KIND_HAMMING_TC) {
-        int rc = b200m_hamming_tc_width(D, &htc_pad);
+    const bool htc = kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4;
+    if (htc) {
+        int rc = kind == B200M_KIND_HAMMING_FP4 ? b200m_hamming_fp4_width(D, &htc_pad) : b200m_hamming_tc_width(D, &htc_pad);
         if (rc != B200M_OK) return rc;
     }
     int sm = device_sm_count();
@@ -221,8 +223,8 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         if (kind == B200M_KIND_HAMMING)
             rc = launch_hamming_top2((const uint8_t*)q_desc, (const uint8_t*)t_desc, D, pl.pairs, num_pairs,
                                      max_n, max_m, S, back, out, rows, pl.colmin, st);
-        else if (kind == B200M_KIND_HAMMING_TC) {
-            rc = launch_hamming_tc_top2((const int8_t*)q_norm, q_rows, (const int8_t*)t_norm, t_rows, htc_pad, 8 * D,
+        else if (htc) {
+            rc = launch_hamming_tc_top2(q_norm, q_rows, t_norm, t_rows, htc_pad, 8 * D, kind == B200M_KIND_HAMMING_FP4,
                                         pl.pairs, num_pairs, max_n, max_m, S, back, out, rows, st);
             if (rc == B200M_OK)      // chunk-level top-2 -> exact (distance, column) top-2 in slice 0, the POPC kernel's format
                 rc = launch_hamming_tc_resolve((const uint8_t*)q_desc, (const uint8_t*)t_desc, D, pl.pairs, num_pairs,
@@ -238,7 +240,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         if (e1) cudaEventRecord(e1, st);
         if (rc != B200M_OK) return rc;
     }
-    if (kind == B200M_KIND_HAMMING_TC) pl.slices = 1;     // resolved into slice 0
+    if (htc) pl.slices = 1;     // resolved into slice 0
     return B200M_OK;
 }
 
@@ -271,7 +273,7 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D,
                       mode == B200M_MODE_RATIO ? (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows)) : nullptr};
     // CSR mode counts survivors in finalize (into out_count), scans them into tight offsets, then emits.
-    const int tail_kind = kind == B200M_KIND_HAMMING_TC ? B200M_KIND_HAMMING : kind;   // integer bit counts either way
+    const int tail_kind = kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING : kind;   // integer bit counts either way
     rc = launch_finalize(tail_kind, mode, ratio, pl, num_pairs, max_n, out_ptr ? out_count : nullptr, rf, st);
     if (rc != B200M_OK) return rc;
     if (out_ptr) {
@@ -315,7 +317,7 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
     RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr};
     if (kind == B200M_KIND_L2_I8)
         rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D, nullptr};
-    return launch_knn2_emit(kind == B200M_KIND_HAMMING_TC ? B200M_KIND_HAMMING : kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
+    return launch_knn2_emit(kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING : kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
 }
 
 }  // extern "C"

@@ -91,9 +91,9 @@ int launch_hamming_top2(const uint8_t* q_desc, const uint8_t* t_desc, int D, con
                         int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
                         long long total_rows, u32* colmin, cudaStream_t st);
 // Tensor-core Hamming (hamming_tc.cu): knn over the +-1 int8 stores, then the exact per-row resolve on the packed bits
-int launch_hamming_tc_top2(const int8_t* q_pm1, int64_t q_rows, const int8_t* t_pm1, int64_t t_rows, int Dpad, int dbits,
-                           const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
-                           long long total_rows, cudaStream_t st);
+int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_store, int64_t t_rows, int Dpad, int dbits,
+                           bool fp4, const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
+                           Top2* out, long long total_rows, cudaStream_t st);
 int launch_hamming_tc_resolve(const uint8_t* q_bits, const uint8_t* t_bits, int D, const DevPair* pairs, int num_pairs,
                               int max_n, int max_m, int S, bool backward, Top2* arr, long long total_rows, cudaStream_t st);
 #define B200M_HAMMING_IDX_BITS 19   // key32 = dist << 19 | index (hamming.cu); fused column minima need n <= 2^19

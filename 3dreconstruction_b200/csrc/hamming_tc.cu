@@ -26,9 +26,20 @@
 
 namespace {
 
-constexpr int TM = 128, TN = 256, KB_BYTES = 128;
+constexpr int TM = 128, KB_BYTES = 128;
 constexpr int A_KB_BYTES = TM * KB_BYTES;      // 16 KiB
-constexpr int B_KB_BYTES = TN * KB_BYTES;      // 32 KiB
+// Two operand formats (template flag FP4):
+//   int8  : one byte per bit (+1 / -1), tcgen05.mma kind::i8, K = 32 per instruction, int32 accumulators, N = 256 per tile;
+//   e2m1  : one NIBBLE per bit (+1.0 = 0x2, -1.0 = 0xA), tcgen05.mma kind::mxf4.block_scale with every UE8M0 scale factor
+//           = 1.0, K = 64 per instruction at the same instruction rate = twice the MACs (tools/mma_peak mxf4: 16384
+//           MAC/clk/SM, 7.8 PFLOP/s sustained), fp32 accumulators (sums of +-1: exact).  The scale factors live in TMEM, and
+//           two 256-column accumulators already fill its 512 columns, so tiles are N = 240 wide: accumulator stage s at
+//           column 256 s, 16 columns of 0x7F bytes at column 240 serve as both scale-factor operands (all bytes equal, so
+//           their layout does not matter).
+__host__ __device__ constexpr int tn_of(bool fp4) { return fp4 ? 240 : 256; }          // train columns per tile (UMMA N)
+__host__ __device__ constexpr int b_kb_bytes(bool fp4) { return tn_of(fp4) * KB_BYTES; }  // one K block of a train tile
+constexpr int SF_COL = 240;
+constexpr uint32_t IDESC_MXF4 = (1u << 7) | (1u << 10) | ((uint32_t)(240 >> 3) << 17) | (1u << 23) | ((uint32_t)(TM >> 4) << 24);
 constexpr int NBF = 4;                         // train K-block ring depth
 constexpr int CTRL_WARPS = 4, EPI_WARPS = 16;
 constexpr int THREADS = (CTRL_WARPS + EPI_WARPS) * 32;
@@ -52,7 +63,8 @@ struct Item {
     bool valid;
 };
 
-__device__ __forceinline__ Item decode_tile(int p, int split, int tile, const DevPair* __restrict__ pairs, int S, int backward) {
+__device__ __forceinline__ Item decode_tile(int p, int split, int tile, const DevPair* __restrict__ pairs, int S, int backward,
+                                            int TN) {
     Item it;
     it.split = split;
     DevPair pr = pairs[p];
@@ -73,11 +85,11 @@ struct Smem {
     uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
     uint32_t* tmem_ptr;
 };
-__device__ __forceinline__ Smem carve(uint8_t* base, int nkb) {
+__device__ __forceinline__ Smem carve(uint8_t* base, int nkb, bool fp4) {
     Smem s;
     s.a = base;
     s.b = s.a + nabuf_of(nkb) * nkb * A_KB_BYTES;
-    s.xch = (int2*)(s.b + NBF * B_KB_BYTES);
+    s.xch = (int2*)(s.b + NBF * b_kb_bytes(fp4));
     uint8_t* p = (uint8_t*)(s.xch + 2 * (EPI_WARPS - 4) * 32);
     s.a_full = (uint64_t*)p; p += 2 * 8;
     s.a_empty = (uint64_t*)p; p += 2 * 8;
@@ -88,12 +100,12 @@ __device__ __forceinline__ Smem carve(uint8_t* base, int nkb) {
     s.tmem_ptr = (uint32_t*)p;
     return s;
 }
-__host__ __device__ constexpr size_t smem_bytes(int nkb) {
-    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NBF * B_KB_BYTES +
+__host__ __device__ constexpr size_t smem_bytes(int nkb, bool fp4 = false) {
+    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NBF * b_kb_bytes(fp4) +
            2 * (EPI_WARPS - 4) * 32 * sizeof(int2) + (4 + 2 * NBF + 4) * 8 + 16;
 }
 static_assert(smem_bytes(1) <= 232448 && smem_bytes(2) <= 232448 && smem_bytes(3) <= 232448 && smem_bytes(4) <= 232448,
-              "shared memory");
+              "shared memory (int8)");
 
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
 template <int O>
@@ -103,23 +115,49 @@ __device__ __forceinline__ int max16(const uint32_t (&v)[32]) {
     int a4 = max3((int)v[O + 12], (int)v[O + 13], (int)v[O + 14]);
     return max(max3(a0, a1, a2), max3(a3, a4, (int)v[O + 15]));
 }
+__device__ __forceinline__ float fmax3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }    // one FMNMX3
+template <int O>
+__device__ __forceinline__ int max16f(const uint32_t (&v)[32]) {          // fp32 accumulators holding exact integers
+#define F(i) __uint_as_float(v[O + (i)])
+    float a0 = fmax3(F(0), F(1), F(2)), a1 = fmax3(F(3), F(4), F(5)), a2 = fmax3(F(6), F(7), F(8));
+    float a3 = fmax3(F(9), F(10), F(11)), a4 = fmax3(F(12), F(13), F(14));
+    return __float2int_rn(fmaxf(fmax3(a0, a1, a2), fmax3(a3, a4, F(15))));
+#undef F
+}
+template <int O, bool FP4>
+__device__ __forceinline__ int chunk_max(const uint32_t (&v)[32]) {
+    if constexpr (FP4) return max16f<O>(v);
+    else return max16<O>(v);
+}
+template <bool FP4>
 __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {
+    constexpr uint32_t M = FP4 ? 0xC4800000u /* -1024.0f */ : (uint32_t)MASKED;
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : (uint32_t)MASKED;
+    for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : M;
+}
+__device__ __forceinline__ void mma_mxf4(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t sf,
+                                         uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%4], [%4], p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(sf), "r"(accumulate)
+        : "memory");
 }
 
 // CS = CTAs per cluster (1 or 2): the two CTAs of a cluster take adjacent query row tiles of the same pair, each fetches
 // half of every train tile and TMA-multicasts it to both (see l2_i8_fold_kernel for the protocol).
-template <int NKB, int CS>
+template <int NKB, int CS, bool FP4>
 __global__ void __launch_bounds__(THREADS, 1)
 hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
                   int dbits, Top2* __restrict__ out, long long total_rows) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const Smem sm = carve(smem, NKB);
+    const Smem sm = carve(smem, NKB, FP4);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int W_MMA = 0, W_PROD = 1;
+    constexpr int TN = tn_of(FP4), B_KB_BYTES = b_kb_bytes(FP4);
+    static_assert(!FP4 || NKB <= 2, "e2m1: 256 bits per K block, |a.b| <= 512");
     constexpr int NABUF = nabuf_of(NKB);
     constexpr bool SEP_ACC = sep_acc_of(NKB);
     constexpr uint16_t MC_MASK = (1u << CS) - 1;
@@ -128,7 +166,7 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const long long item_stride = CS > 1 ? (long long)sm100::cluster_count_x() : (long long)gridDim.x;
     auto decode = [&](long long item) -> Item {
         int tg = (int)(item % tiles_max); item /= tiles_max;     // tiles_max = tile groups per (pair, split)
-        Item it = decode_tile((int)(item / S), (int)(item % S), tg * CS + (int)crank, pairs, S, backward);
+        Item it = decode_tile((int)(item / S), (int)(item % S), tg * CS + (int)crank, pairs, S, backward, TN);
         it.valid = tg * CS * TM < it.n;        // a CTA whose own row tile lies past the pair still streams for its peer
         return it;
     };
@@ -148,6 +186,18 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     sm100::tc_fence_after();
     const uint32_t tmem_base = *sm.tmem_ptr;
     constexpr int HALF_ROWS = TN / CS;
+    if constexpr (FP4) {      // scale factors 1.0 everywhere: warps 4..7 own the four TMEM lane quarters
+        if (warp >= CTRL_WARPS && warp < CTRL_WARPS + 4) {
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + SF_COL;
+            const uint32_t v = 0x7F7F7F7Fu;
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};"
+                         ::"r"(taddr), "r"(v) : "memory");
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        sm100::tc_fence_before();
+        __syncthreads();
+        sm100::tc_fence_after();
+    }
 
     if (warp == W_PROD) {
         uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;
@@ -181,7 +231,7 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
         }
     } else if (warp == W_MMA) {
-        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
+        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, 256);
         const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
@@ -194,7 +244,7 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
                 acc_par ^= 1u << as;
                 sm100::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + as * TN;
+                const uint32_t d_tmem = tmem_base + as * 256;
 #pragma unroll
                 for (int kb = 0; kb < NKB; ++kb) {
                     sm100::mbar_wait(&sm.b_full[bs], b_par);
@@ -202,9 +252,14 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     if (sm100::elect_one()) {
                         const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
 #pragma unroll
-                        for (int k = 0; k < KB_BYTES / 32; ++k)
-                            sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                          idesc, (kb | k) ? 1u : 0u);
+                        for (int k = 0; k < KB_BYTES / 32; ++k) {
+                            if constexpr (FP4)
+                                mma_mxf4(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k), IDESC_MXF4,
+                                         tmem_base + SF_COL, (kb | k) ? 1u : 0u);
+                            else
+                                sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                              idesc, (kb | k) ? 1u : 0u);
+                        }
                         if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
                         else sm100::mma_commit(&sm.b_empty[bs]);
                         if (SEP_ACC && kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
@@ -223,7 +278,8 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         // (half a tile) of its 32 TMEM lanes
         const int e = warp - CTRL_WARPS;
         const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * (TN / 2);
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * 256 + half * 128;
+        const int width = FP4 && half ? TN - 128 : 128;      // e2m1 tiles: the upper half has 112 columns = 7 chunks
         constexpr int KOFF = (512 << KEY_SHIFT) + KEY_LOW;
         uint32_t k = 0, tc_base = 0, nitem = 0;
         for (long long item = first_item; item < total_items; item += item_stride) {
@@ -235,7 +291,7 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 v1 = max(v1, key);
             };
             for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
-                const int base = it.c_begin + j * TN + half * (TN / 2);
+                const int base = it.c_begin + j * TN + half * 128;
                 const int lim = it.c_end - base;
                 const int kc = KOFF - (base >> 4);        // key of chunk c of this warp's 8 = (max << 20) + kc - c
                 if constexpr (SEP_ACC) {
@@ -250,10 +306,10 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 sm100::tmem_ld32(taddr, acc[0]);
                 sm100::tmem_ld32(taddr + 32, acc[1]);
                 sm100::tmem_ld_wait();
-                if (lim < TN / 2) { mask32(acc[0], lim); mask32(acc[1], lim - 32); }
-                int m0 = max16<0>(acc[0]), m1 = max16<16>(acc[0]);
+                if (lim < width) { mask32<FP4>(acc[0], lim); mask32<FP4>(acc[1], lim - 32); }
+                int m0 = chunk_max<0, FP4>(acc[0]), m1 = chunk_max<16, FP4>(acc[0]);
                 sm100::tmem_ld32(taddr + 64, acc[0]);
-                int m2 = max16<0>(acc[1]), m3 = max16<16>(acc[1]);
+                int m2 = chunk_max<0, FP4>(acc[1]), m3 = chunk_max<16, FP4>(acc[1]);
                 sm100::tmem_ld32(taddr + 96, acc[1]);
                 insert((m0 << KEY_SHIFT) + kc); insert((m1 << KEY_SHIFT) + kc - 1);
                 insert((m2 << KEY_SHIFT) + kc - 2); insert((m3 << KEY_SHIFT) + kc - 3);
@@ -261,11 +317,15 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 sm100::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
-                if (lim < TN / 2) { mask32(acc[0], lim - 64); mask32(acc[1], lim - 96); }
-                m0 = max16<0>(acc[0]); m1 = max16<16>(acc[0]);
-                m2 = max16<0>(acc[1]); m3 = max16<16>(acc[1]);
+                if (lim < width) { mask32<FP4>(acc[0], lim - 64); mask32<FP4>(acc[1], lim - 96); }
+                m0 = chunk_max<0, FP4>(acc[0]); m1 = chunk_max<16, FP4>(acc[0]);
+                m2 = chunk_max<0, FP4>(acc[1]);
                 insert((m0 << KEY_SHIFT) + kc - 4); insert((m1 << KEY_SHIFT) + kc - 5);
-                insert((m2 << KEY_SHIFT) + kc - 6); insert((m3 << KEY_SHIFT) + kc - 7);
+                insert((m2 << KEY_SHIFT) + kc - 6);
+                if (!(FP4 && half)) {          // columns 240..255 of an e2m1 tile are the scale factors, not distances
+                    m3 = chunk_max<16, FP4>(acc[1]);
+                    insert((m3 << KEY_SHIFT) + kc - 7);
+                }
             }
             tc_base += (uint32_t)it.ntiles;
             // the four warps of a TMEM lane quarter hold partial top-2s of the same 32 query rows: merge in shared memory
@@ -379,57 +439,89 @@ prep_hamming_tc_kernel(const uint8_t* __restrict__ src, long long rows, int D, i
     *reinterpret_cast<uint2*>(dst + r * Dpad + 8 * k) = o;
 }
 
+// bits -> e2m1 nibbles: +1.0 = 0x2 for a set bit, -1.0 = 0xA for a clear one.  One thread per source byte: one 32-bit word
+// (nibble b of the word = bit b of the byte); nibbles past 8 D are 0.0.
+__global__ void __launch_bounds__(256)
+prep_hamming_fp4_kernel(const uint8_t* __restrict__ src, long long rows, int D, uint8_t* __restrict__ dst, int Dpad4) {
+    const int per_row = Dpad4 >> 2;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * per_row) return;
+    const long long r = idx / per_row;
+    const int k = (int)(idx - r * per_row);
+    u32 o = 0u;
+    if (k < D) {
+        const u32 x = __ldg(src + r * D + k);
+        u32 w = 0u;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) w |= ((x >> b) & 1u) << (4 * b + 3);
+        o = 0xAAAAAAAAu ^ w;                           // set bit: 0xA ^ 0x8 = 0x2
+    }
+    *reinterpret_cast<u32*>(dst + r * Dpad4 + 4 * k) = o;
+}
+
 }  // namespace
 
-int launch_hamming_tc_top2(const int8_t* q_pm1, int64_t q_rows, const int8_t* t_pm1, int64_t t_rows, int Dpad, int dbits,
-                           const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward, Top2* out,
-                           long long total_rows, cudaStream_t st) {
-    if (Dpad % KB_BYTES != 0 || Dpad < dbits) return B200M_EINVAL;
+static_assert(smem_bytes(1, true) <= 232448 && smem_bytes(2, true) <= 232448, "shared memory (e2m1)");
+
+// fp4 == false: stores are int8 [rows, Dpad], Dpad = 8 D rounded up to 128 (b200m_prep_hamming_tc);
+// fp4 == true : stores are packed e2m1 [rows, Dpad], Dpad = 4 D rounded up to 128 bytes (b200m_prep_hamming_fp4).
+int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_store, int64_t t_rows, int Dpad, int dbits,
+                           bool fp4, const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
+                           Top2* out, long long total_rows, cudaStream_t st) {
+    if (Dpad % KB_BYTES != 0 || Dpad * (fp4 ? 2 : 1) < dbits) return B200M_EINVAL;
     const int nkb = Dpad / KB_BYTES;
-    if (nkb < 1 || nkb > 4) return B200M_EUNSUPPORTED;           // |a.b| <= 512 is what the packed key holds
+    if (nkb < 1 || nkb > (fp4 ? 2 : 4)) return B200M_EUNSUPPORTED;           // |a.b| <= 512 is what the packed key holds
     if (backward) {
-        const int8_t* d = q_pm1; q_pm1 = t_pm1; t_pm1 = d;
+        const void* d = q_store; q_store = t_store; t_store = d;
         int64_t r = q_rows; q_rows = t_rows; t_rows = r;
         int mx = max_n; max_n = max_m; max_m = mx;
     }
+    const int TN = tn_of(fp4);
     if (((long long)max_m + TN) >> 4 > KEY_LOW) return B200M_EUNSUPPORTED;
     static bool attr_set = false;
-    static int cs_ok[5] = {0, 0, 0, 0, 0};       // max active 2-CTA clusters per K-block count (0: use single CTAs)
+    static int cs_ok[2][5] = {{0, 0, 0, 0, 0}, {0, 0, 0, 0, 0}};   // max active 2-CTA clusters per format and K-block count (0: single CTAs)
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    auto kern = [](int nkb_, int cs_) -> const void* {
+    auto kern = [](int nkb_, int cs_, bool f4) -> const void* {
+        if (f4) {
+            switch (nkb_ * 2 + cs_ - 1) {
+                case 2: return (const void*)hamming_tc_kernel<1, 1, true>; case 3: return (const void*)hamming_tc_kernel<1, 2, true>;
+                case 4: return (const void*)hamming_tc_kernel<2, 1, true>; default: return (const void*)hamming_tc_kernel<2, 2, true>;
+            }
+        }
         switch (nkb_ * 2 + cs_ - 1) {
-            case 2: return (const void*)hamming_tc_kernel<1, 1>; case 3: return (const void*)hamming_tc_kernel<1, 2>;
-            case 4: return (const void*)hamming_tc_kernel<2, 1>; case 5: return (const void*)hamming_tc_kernel<2, 2>;
-            case 6: return (const void*)hamming_tc_kernel<3, 1>; case 7: return (const void*)hamming_tc_kernel<3, 2>;
-            case 8: return (const void*)hamming_tc_kernel<4, 1>; default: return (const void*)hamming_tc_kernel<4, 2>;
+            case 2: return (const void*)hamming_tc_kernel<1, 1, false>; case 3: return (const void*)hamming_tc_kernel<1, 2, false>;
+            case 4: return (const void*)hamming_tc_kernel<2, 1, false>; case 5: return (const void*)hamming_tc_kernel<2, 2, false>;
+            case 6: return (const void*)hamming_tc_kernel<3, 1, false>; case 7: return (const void*)hamming_tc_kernel<3, 2, false>;
+            case 8: return (const void*)hamming_tc_kernel<4, 1, false>; default: return (const void*)hamming_tc_kernel<4, 2, false>;
         }
     };
     if (!attr_set) {
-        for (int nk = 1; nk <= 4; ++nk) {
-            for (int cs = 1; cs <= 2; ++cs)
-                B200M_CUDA_CHECK(cudaFuncSetAttribute(kern(nk, cs), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                      (int)smem_bytes(nk)), "hamming_tc smem attr");
-            cudaLaunchConfig_t qc = {};
-            cudaLaunchAttribute qa[1];
-            qa[0].id = cudaLaunchAttributeClusterDimension;
-            qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
-            qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(THREADS); qc.dynamicSmemBytes = smem_bytes(nk);
-            qc.attrs = qa; qc.numAttrs = 1;
-            int nc = 0;
-            if (cudaOccupancyMaxActiveClusters(&nc, kern(nk, 2), &qc) == cudaSuccess && nc * 2 >= sms && !getenv("B200M_NO_CLUSTER"))
-                cs_ok[nk] = nc;
-            else
-                cudaGetLastError();
-        }
+        for (int f4 = 0; f4 < 2; ++f4)
+            for (int nk = 1; nk <= (f4 ? 2 : 4); ++nk) {
+                for (int cs = 1; cs <= 2; ++cs)
+                    B200M_CUDA_CHECK(cudaFuncSetAttribute(kern(nk, cs, f4), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                          (int)smem_bytes(nk, f4)), "hamming_tc smem attr");
+                cudaLaunchConfig_t qc = {};
+                cudaLaunchAttribute qa[1];
+                qa[0].id = cudaLaunchAttributeClusterDimension;
+                qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+                qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(THREADS); qc.dynamicSmemBytes = smem_bytes(nk, f4);
+                qc.attrs = qa; qc.numAttrs = 1;
+                int nc = 0;
+                if (cudaOccupancyMaxActiveClusters(&nc, kern(nk, 2, f4), &qc) == cudaSuccess && nc * 2 >= sms && !getenv("B200M_NO_CLUSTER"))
+                    cs_ok[f4][nk] = nc;
+                else
+                    cudaGetLastError();
+            }
         attr_set = true;
     }
     CUtensorMap tq, tt;
-    const int cs = cs_ok[nkb] > 0 ? 2 : 1;
-    int rc = b200m_make_tmap_2d(&tq, q_pm1, (uint64_t)q_rows, (uint64_t)Dpad, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+    const int cs = cs_ok[fp4][nkb] > 0 ? 2 : 1;
+    int rc = b200m_make_tmap_2d(&tq, q_store, (uint64_t)q_rows, (uint64_t)Dpad, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
-    rc = b200m_make_tmap_2d(&tt, t_pm1, (uint64_t)t_rows, (uint64_t)Dpad, TN / cs, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
+    rc = b200m_make_tmap_2d(&tt, t_store, (uint64_t)t_rows, (uint64_t)Dpad, TN / cs, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
     const int tiles_max = (max_n + TM - 1) / TM;
     int groups = (tiles_max + cs - 1) / cs;
@@ -439,16 +531,16 @@ int launch_hamming_tc_top2(const int8_t* q_pm1, int64_t q_rows, const int8_t* t_
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned)cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    const long long max_units = cs == 2 ? cs_ok[nkb] : sms;
+    const long long max_units = cs == 2 ? cs_ok[fp4][nkb] : sms;
     cfg.gridDim = dim3((unsigned)((items < max_units ? items : max_units) * cs));
     cfg.blockDim = dim3(THREADS);
-    cfg.dynamicSmemBytes = smem_bytes(nkb);
+    cfg.dynamicSmemBytes = smem_bytes(nkb, fp4);
     cfg.stream = st;
     cfg.attrs = at; cfg.numAttrs = 1;
     int bw = backward ? 1 : 0;
     void* args[] = {(void*)&tq, (void*)&tt, (void*)&pairs, (void*)&items, (void*)&groups, (void*)&S, (void*)&bw,
                     (void*)&dbits, (void*)&out, (void*)&total_rows};
-    cudaError_t e = cudaLaunchKernelExC(&cfg, kern(nkb, cs), args);
+    cudaError_t e = cudaLaunchKernelExC(&cfg, kern(nkb, cs, fp4), args);
     b200m_count_launch();
     B200M_CUDA_CHECK(e, "hamming_tc_kernel launch");
     return B200M_OK;
@@ -480,6 +572,14 @@ int b200m_hamming_tc_width(int D, int* Dpad) {
     return B200M_OK;
 }
 
+int b200m_hamming_fp4_width(int D, int* Dpad4) {
+    if (D <= 0 || !Dpad4) return B200M_EINVAL;
+    const int w = (4 * D + KB_BYTES - 1) / KB_BYTES * KB_BYTES;
+    if (w > 2 * KB_BYTES) return B200M_EUNSUPPORTED;
+    *Dpad4 = w;
+    return B200M_OK;
+}
+
 int b200m_prep_hamming_tc(const uint8_t* src, int64_t rows, int D, int8_t* dst, int Dpad, void* stream) {
     int want = 0;
     int rc = b200m_hamming_tc_width(D, &want);
@@ -493,6 +593,22 @@ int b200m_prep_hamming_tc(const uint8_t* src, int64_t rows, int D, int8_t* dst, 
     prep_hamming_tc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, rows, D, dst, Dpad);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "prep_hamming_tc_kernel launch");
+    return B200M_OK;
+}
+
+int b200m_prep_hamming_fp4(const uint8_t* src, int64_t rows, int D, uint8_t* dst, int Dpad4, void* stream) {
+    int want = 0;
+    int rc = b200m_hamming_fp4_width(D, &want);
+    if (rc != B200M_OK) return rc;
+    if (rows < 0 || Dpad4 != want) return B200M_EINVAL;
+    if (rows == 0) return B200M_OK;
+    if (!src || !dst || ((uintptr_t)dst & 15)) return B200M_EINVAL;
+    const long long work = rows * (Dpad4 >> 2);
+    const long long blocks = (work + 255) / 256;
+    if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    prep_hamming_fp4_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, rows, D, dst, Dpad4);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "prep_hamming_fp4_kernel launch");
     return B200M_OK;
 }
 

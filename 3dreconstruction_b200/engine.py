@@ -34,7 +34,8 @@ class DeviceDescriptors(NamedTuple):
     kind: int
     desc: torch.Tensor                 # uint8 [rows, D] | int8 [rows, Dpad] | float32 [rows, Dpad]
     norm: Optional[torch.Tensor]       # L2_I8: int32 aux block (norms[rows], fold digits, info) | float32 [rows] | None
-                                       # HAMMING_TC: int8 [rows, Dpad] +-1 expansion of `desc` (which stays the packed bits)
+                                       # HAMMING_TC / HAMMING_FP4: int8 [rows, Dpad] / e2m1 uint8 [rows, Dpad4] +-1 expansion
+                                       # of `desc` (which stays the packed bits)
     rows: int
     width: int                         # D as passed to the C-ABI
 
@@ -52,13 +53,13 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
 
 class Engine:
     def __init__(self, device: Optional[torch.device | str | int] = None, hamming_path: Optional[str] = None):
-        """hamming_path: "tensor" (tcgen05 kind::i8 over +-1 expanded bits, descriptors up to 64 bytes), "popc"
-        (the INT-pipe kernel) or "auto" (tensor where the width allows it); default from B200M_HAMMING_PATH, else auto.
-        Both produce identical results."""
+        """hamming_path: "fp4" (tcgen05 kind::mxf4 over bits expanded to e2m1 +-1.0, descriptors up to 64 bytes), "int8"
+        (tcgen05 kind::i8 over +-1 int8, same limit), "popc" (the INT-pipe kernel, any width) or "auto" (fp4 where the
+        width allows it, else popc); default from B200M_HAMMING_PATH, else auto.  All produce identical results."""
         self.lib = L.load()
         self.hamming_path = hamming_path or os.environ.get("B200M_HAMMING_PATH", "auto")
-        if self.hamming_path not in ("auto", "tensor", "popc"):
-            raise ValueError("hamming_path must be auto, tensor or popc")
+        if self.hamming_path not in ("auto", "fp4", "int8", "popc"):
+            raise ValueError("hamming_path must be auto, fp4, int8 or popc")
         if not torch.cuda.is_available():
             raise L.B200MatchError(L.ENODEVICE, "Engine", "no CUDA device: the matcher has no CPU fallback")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
@@ -90,18 +91,23 @@ class Engine:
         if norm_type == NORM_HAMMING:
             if t.dtype != torch.uint8:
                 raise ValueError("NORM_HAMMING needs uint8 descriptors")      # cv2.error in the reference
-            if force_kind == L.KIND_HAMMING or (force_kind is None and self.hamming_path == "popc"):
+            want = force_kind
+            if want is None:
+                want = {"popc": L.KIND_HAMMING, "int8": L.KIND_HAMMING_TC}.get(self.hamming_path, L.KIND_HAMMING_FP4)
+            if want == L.KIND_HAMMING:
                 return DeviceDescriptors(L.KIND_HAMMING, t, None, rows, D)
+            fp4 = want == L.KIND_HAMMING_FP4
+            width_fn = self.lib.b200m_hamming_fp4_width if fp4 else self.lib.b200m_hamming_tc_width
+            prep_fn = self.lib.b200m_prep_hamming_fp4 if fp4 else self.lib.b200m_prep_hamming_tc
             wpad = ctypes.c_int(0)
-            rc = self.lib.b200m_hamming_tc_width(D, ctypes.byref(wpad))
+            rc = width_fn(D, ctypes.byref(wpad))
             if rc == L.EUNSUPPORTED and force_kind is None and self.hamming_path == "auto":
                 return DeviceDescriptors(L.KIND_HAMMING, t, None, rows, D)     # wider than 512 bits: INT-pipe kernel
-            L.check(rc, "b200m_hamming_tc_width")
+            L.check(rc, "b200m_hamming_*_width")
             with torch.cuda.device(self.device):
-                pm1 = torch.empty((rows, wpad.value), dtype=torch.int8, device=self.device)
-                L.check(self.lib.b200m_prep_hamming_tc(t.data_ptr(), rows, D, pm1.data_ptr(), wpad.value, self._stream()),
-                        "b200m_prep_hamming_tc")
-            return DeviceDescriptors(L.KIND_HAMMING_TC, t, pm1, rows, D)
+                ex = torch.empty((rows, wpad.value), dtype=torch.uint8 if fp4 else torch.int8, device=self.device)
+                L.check(prep_fn(t.data_ptr(), rows, D, ex.data_ptr(), wpad.value, self._stream()), "b200m_prep_hamming_*")
+            return DeviceDescriptors(want, t, ex, rows, D)
         if norm_type != NORM_L2:
             raise ValueError(f"unsupported norm_type {norm_type}")
         if t.dtype == torch.uint8:

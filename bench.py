@@ -262,7 +262,7 @@ def single_pair_extras(torch, b, eng, pk):
     a, c = b.synth.binary_pair(seed=1, n=10000, nbytes=32)
     popc_peak = 148 * 16 * pk.get("sm_max_mhz", 1965.0) * 1e6 / 8 / 1e9       # Gdist/s, 256-bit, at max clock
     orb = {}
-    for path, e in (("tensor", eng), ("popc", b.Engine(eng.device, hamming_path="popc"))):
+    for path, e in (("tensor", eng), ("int8", b.Engine(eng.device, hamming_path="int8")), ("popc", b.Engine(eng.device, hamming_path="popc"))):
         da, dc = e.prepare(a, b.NORM_HAMMING), e.prepare(c, b.NORM_HAMMING)
         ms = timed(lambda: e.match_device(da, dc, [(0, 10000, 0, 10000)], L.MODE_CROSS))
         orb[path] = {"ms_per_pair": ms, "pairs_per_s": 1e3 / ms, "gdist_per_s": 1e8 / 1e9 / (ms / 1e3)}

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 120
+#define B200M_VERSION 130
 
 #if defined(__GNUC__)
 #define B200M_API __attribute__((visibility("default")))
@@ -58,6 +58,9 @@ extern "C" {
                                  kind::i8 finds each row's two best 16-column chunks, a POPC pass over the
                                  packed bits resolves them to the exact neighbours.  Same results as
                                  B200M_KIND_HAMMING, D <= 64 bytes                              */
+#define B200M_KIND_HAMMING_FP4 4 /* the same with every bit as one e2m1 NIBBLE (+1.0 / -1.0, b200m_prep_hamming_fp4)
+                                 and tcgen05 kind::mxf4.block_scale with all scale factors 1.0: twice the MACs
+                                 per instruction, half the operand bytes; fp32 sums of +-1 are exact         */
 
 /* One image pair of a batch: rows [q_off, q_off+n) of the query store against rows
  * [t_off, t_off+m) of the train store; its matches are written at out_off.. (capacity n). */
@@ -105,6 +108,11 @@ B200M_API int b200m_prep_l2_i8_rows(const float* src, int64_t row_begin, int64_t
  * what b200m_match_pairs* / b200m_knn2_pairs take as q_norm / t_norm for this kind, next to the packed bits. */
 B200M_API int b200m_hamming_tc_width(int D, int* Dpad);
 B200M_API int b200m_prep_hamming_tc(const uint8_t* src, int64_t rows, int D, int8_t* dst, int Dpad, void* stream);
+/* e2m1 expansion for B200M_KIND_HAMMING_FP4: dst uint8 [rows, Dpad4], Dpad4 from b200m_hamming_fp4_width(D) (4 D bytes
+ * rounded up to 128; B200M_EUNSUPPORTED when D > 64): nibble 8k+b = 0x2 (+1.0) if bit b of byte k is set, else 0xA
+ * (-1.0); nibbles past 8 D are 0.  Passed as q_norm / t_norm like the int8 expansion. */
+B200M_API int b200m_hamming_fp4_width(int D, int* Dpad4);
+B200M_API int b200m_prep_hamming_fp4(const uint8_t* src, int64_t rows, int D, uint8_t* dst, int Dpad4, void* stream);
 
 /* Row squared norms for the F32 kind: norms[r] = sum_k src[r,k]^2 (fp32). */
 B200M_API int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream);
@@ -124,11 +132,12 @@ B200M_API int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t t
  *   kind           B200M_KIND_*
  *   q_desc/t_desc  descriptor stores (may be the same pointer for all-pairs over one store):
  *                    HAMMING: uint8 [rows, D]      (D = bytes per descriptor, any D >= 1)
- *                    HAMMING_TC: the same packed uint8 [rows, D], D <= 64
+ *                    HAMMING_TC, HAMMING_FP4: the same packed uint8 [rows, D], D <= 64
  *                    L2_I8  : int8  [rows, D]      (D multiple of 128, from b200m_prep_l2_i8)
  *                    L2_F32 : float [rows, D]      (D multiple of 32 floats, D <= 256)
  *   q_norm/t_norm  L2_I8: the aux block of b200m_prep_l2_i8 (int32 norms first); L2_F32: float [rows];
- *                  HAMMING: NULL; HAMMING_TC: int8 [rows, Dpad] from b200m_prep_hamming_tc
+ *                  HAMMING: NULL; HAMMING_TC: int8 [rows, Dpad] from b200m_prep_hamming_tc;
+ *                  HAMMING_FP4: uint8 [rows, Dpad4] from b200m_prep_hamming_fp4
  *   q_rows/t_rows  number of rows in each store (bounds for TMA maps)
  *   pairs_host     HOST array of num_pairs descriptors (copied to the device workspace)
  *   mode, ratio    B200M_MODE_*; ratio used by MODE_RATIO only (fp64, as Python does at :216)

@@ -25,13 +25,18 @@ def eng():
     return b.Engine()
 
 
-@pytest.fixture(scope="module", params=["auto", "popc"])
+@pytest.fixture(scope="module", params=["auto", "int8", "popc"])
 def heng(request):
-    """Hamming engines: "auto" = tensor-core kernel (+-1 int8 GEMM + POPC resolve) up to 64-byte descriptors, INT-pipe
-    kernel above; "popc" = INT-pipe kernel everywhere.  Both must be bit-exact against the oracle."""
+    """Hamming engines: "auto" = tensor-core kernel on e2m1 operands (kind::mxf4 GEMM + POPC resolve) up to 64-byte
+    descriptors, INT-pipe kernel above; "int8" = the same kernel on int8 operands (kind::i8); "popc" = INT-pipe kernel
+    everywhere.  All must be bit-exact against the oracle."""
     if not torch.cuda.is_available():
         pytest.skip("needs a GPU")
-    return b.Engine(hamming_path=request.param)
+    e = b.Engine(hamming_path=request.param)
+    if request.param == "int8":          # wider than 512 bits: the int8 engine has no kernel, the tests fall back explicitly
+        prep = e.prepare
+        e.prepare = lambda d, nt, force_kind=None: prep(d, nt, pkg("_lib").KIND_HAMMING if force_kind is None and d.shape[1] > 64 else force_kind)
+    return e
 
 
 def assert_exact(got, want, what=""):
@@ -141,14 +146,22 @@ def test_hamming_tc_kind_is_used_and_matches_popc(heng):
     a, c = synth.binary_pair(seed=9, n=1500, m=1300, nbytes=32)
     dd = heng.prepare(a, b.NORM_HAMMING)
     L = pkg("_lib")
-    assert dd.kind == (L.KIND_HAMMING_TC if heng.hamming_path == "auto" else L.KIND_HAMMING)
+    assert dd.kind == {"auto": L.KIND_HAMMING_FP4, "int8": L.KIND_HAMMING_TC, "popc": L.KIND_HAMMING}[heng.hamming_path]
+    bits = np.unpackbits(a, axis=1, bitorder="little").astype(np.int8) * 2 - 1
     if dd.kind == L.KIND_HAMMING_TC:
         pm1 = dd.norm.cpu().numpy()
-        bits = np.unpackbits(a, axis=1, bitorder="little").astype(np.int8) * 2 - 1
         assert pm1.shape == (1500, 256) and np.array_equal(pm1, bits)
         dd61 = heng.prepare(a[:, :29], b.NORM_HAMMING)          # 232 bits -> 256 dims, the last 24 are zero
         p = dd61.norm.cpu().numpy()
         assert p.shape == (1500, 256) and np.array_equal(p[:, :232], bits[:, :232]) and not p[:, 232:].any()
+    if dd.kind == L.KIND_HAMMING_FP4:
+        nib = dd.norm.cpu().numpy()                              # two e2m1 values per byte, low nibble first
+        assert nib.shape == (1500, 128)
+        lo, hi = nib & 15, nib >> 4
+        dec = np.stack([lo, hi], axis=2).reshape(1500, 256)
+        assert np.array_equal(dec, np.where(bits > 0, 0x2, 0xA))
+        p = heng.prepare(a[:, :29], b.NORM_HAMMING).norm.cpu().numpy()
+        assert p.shape == (1500, 128) and not p[:, 116:].any()
 
 
 @pytest.mark.parametrize("nbytes", [16, 32, 48, 61, 64])

@@ -59,6 +59,82 @@ __global__ void __launch_bounds__(128, 1) peak_kernel(int iters, uint32_t idesc,
     if (warp == 0) sm100::tmem_dealloc<512>(tbase);
 }
 
+// kind::mxf4 (block-scaled E2M1, K = 64 elements = 32 bytes per MMA): accumulators of N columns at TMEM columns 0 and 256,
+// scale factors (UE8M0 1.0 = 0x7F everywhere, so their layout does not matter) at columns 240..255.
+__device__ __forceinline__ void mma_k_mxf4(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t sfa, uint32_t sfb, uint32_t acc) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %6, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%4], [%5], p;\n\t}" ::"r"(d),
+                 "l"(a), "l"(b), "r"(idesc), "r"(sfa), "r"(sfb), "r"(acc) : "memory");
+}
+__global__ void __launch_bounds__(128, 1) peak_mxf4_kernel(int iters, uint32_t idesc, long long* cycles, int random_fill) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tptr;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) {
+        uint32_t v = 0x2A2A2A2Au;                                  // nibbles +1 / -1
+        if (random_fill) { v = (uint32_t)i * 2654435761u + blockIdx.x * 40503u; v ^= v >> 15; v *= 2246822519u; v ^= v >> 13;
+                           v = (v & 0x88888888u) | 0x22222222u; }  // random signs, magnitude 1.0
+        ((uint32_t*)smem)[i] = v;
+    }
+    if (threadIdx.x == 0) { sm100::mbar_init(&bar, 1); sm100::fence_barrier_init(); }
+    if (warp == 0) sm100::tmem_alloc<512>(&tptr);
+    sm100::fence_proxy_async();
+    sm100::tc_fence_before(); __syncthreads(); sm100::tc_fence_after();
+    uint32_t tbase = tptr;
+    {   // scale factors: every warp fills its 32 TMEM lanes x 16 columns with 0x7F7F7F7F
+        uint32_t taddr = tbase + ((uint32_t)(warp * 32) << 16) + 240;
+        uint32_t v = 0x7F7F7F7Fu;
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};"
+                     ::"r"(taddr), "r"(v) : "memory");
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    sm100::tc_fence_before(); __syncthreads(); sm100::tc_fence_after();
+    if (threadIdx.x == 32) {
+        uint64_t ad = sm100::make_smem_desc_sw128(sm100::smem_u32(smem));
+        uint64_t bd = sm100::make_smem_desc_sw128(sm100::smem_u32(smem + 16384));
+        long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                mma_k_mxf4(tbase + ((it & 1) ? 256 : 0), ad + 2 * k, bd + 2 * k, idesc, tbase + 240, tbase + 240, 1);
+        }
+        sm100::mma_commit(&bar);
+        sm100::mbar_wait(&bar, 0);
+        long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    }
+    sm100::tc_fence_before(); __syncthreads();
+    if (warp == 0) sm100::tmem_dealloc<512>(tbase);
+}
+// idesc of kind::mxf4: a/b format E2M1 = 1 at bits 7 and 10, N >> 3 at 17, scale format UE8M0 at bit 23, M >> 4 at 24
+static uint32_t idesc_mxf4(int N) { return (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | (1u << 23) | (8u << 24); }
+static void run_mxf4(int N, int sms, double sustained_s) {
+    long long* dcyc; cudaMalloc(&dcyc, 8);
+    cudaFuncSetAttribute(peak_mxf4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int iters = sustained_s > 0 ? 100000 : 20000;
+    peak_mxf4_kernel<<<sms, 128, 64 * 1024>>>(200, idesc_mxf4(N), dcyc, 0);
+    double elapsed = 0; int n = 0;
+    do {
+        cudaEventRecord(e0);
+        peak_mxf4_kernel<<<sms, 128, 64 * 1024>>>(iters, idesc_mxf4(N), dcyc, sustained_s > 0 ? 1 : 0);
+        cudaEventRecord(e1);
+        cudaError_t err = cudaDeviceSynchronize();
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        long long cyc = 0; cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+        double macs = (double)sms * iters * 4.0 * 128 * N * 64;
+        elapsed += ms; ++n;
+        if (sustained_s <= 0 || n % 8 == 0)
+            printf("mxf4 N%d %s t=%.2fs: %.3f ms, %.1f TOP/s, %.1f cycles per MMA (M128 K=64), %.0f MAC/clk/SM, SM clock %.0f MHz\n", N,
+                   cudaGetErrorString(err), elapsed / 1e3, ms, 2 * macs / (ms * 1e-3) / 1e12, (double)cyc / (iters * 4.0),
+                   128.0 * N * 64 / ((double)cyc / (iters * 4.0)), (double)cyc / ms / 1e3);
+        if (err != cudaSuccess) break;
+    } while (elapsed < sustained_s * 1e3);
+    cudaFree(dcyc);
+}
+
 template <int KIND>
 void run(const char* name, uint32_t idesc, int k_elems_per_mma, int sms) {
     long long* dcyc; cudaMalloc(&dcyc, 8);
@@ -284,6 +360,11 @@ static void run_sustained(int sms, double seconds) {
 int main(int argc, char** argv) {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     printf("SMs: %d\n", sms);
+    if (argc > 1 && !strcmp(argv[1], "mxf4")) {
+        run_mxf4(256, sms, 0); run_mxf4(240, sms, 0); run_mxf4(128, sms, 0);
+        run_mxf4(240, sms, argc > 2 ? atof(argv[2]) : 3.0);
+        return 0;
+    }
     if (argc > 1 && !strcmp(argv[1], "sustained")) { run_sustained(sms, argc > 2 ? atof(argv[2]) : 4.0); return 0; }
     run<0>("i8", sm100::make_idesc(2, 1, 1, 128, 256), 32, sms);
     run<1>("f16", sm100::make_idesc(1, 0, 0, 128, 256), 16, sms);

@@ -13,7 +13,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libb200match.so")
-SOURCES = ["capi.cu", "hamming.cu", "hamming_tc.cu", "l2_i8.cu", "l2_f32.cu", "tail.cu", "prep.cu", "adapter.cu"]
+SOURCES = ["capi.cu", "hamming.cu", "hamming_tc.cu", "l2_i8.cu", "l2_f32.cu", "tail.cu", "prep.cu", "adapter.cu", "ransac.cu"]
+# ransac.cu restates cv2's float32/fp64 arithmetic of findHomography: a*b+c must round twice there
+PER_SOURCE_FLAGS = {"ransac.cu": ["-fmad=false"]}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 
@@ -42,7 +44,7 @@ def build(force: bool = False, verbose: bool = False, defs=(), so: str = SO, tag
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for src in SOURCES:
         obj = os.path.join(HERE, "build", src.replace(".cu", tag + ".o"))
-        cmd = [_nvcc(), *NVCC_FLAGS, *defs, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [_nvcc(), *NVCC_FLAGS, *PER_SOURCE_FLAGS.get(src, []), *defs, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

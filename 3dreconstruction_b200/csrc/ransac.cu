@@ -1,0 +1,580 @@
+// ransac.cu — geometric verification of matched pairs: batched replacement of
+//     H, mask = cv2.findHomography(pts1, pts2, cv2.RANSAC, thr, confidence=conf, maxIters=max_iters)
+// as called per image pair by /root/reference/FeatureMatchingExtraction/utils.py:141 (enhanced_filter_matches_with_homography).
+// Input is what the matcher's hand-off already holds in HBM: the CSR `ptr` over pairs and the float32 [K, 4]
+// correspondences (x1, y1, x2, y2) of b200m_gather_correspondences.  One CTA per image pair.
+//
+// cv2's RANSAC is a deterministic sequential program (its RNG restarts from the same state on every call), so the
+// result is reproducible and parity is testable; the kernel keeps that sequence and parallelises inside it:
+//   * the random stream is a geometry-independent sequence of 4-tuples (distinct indices by rejection); tuples that
+//     fail checkSubset are skipped, the others are hypotheses 0, 1, 2 ... .  One thread draws TUPLES tuples per
+//     round, TUPLES threads test them and fit their models side by side (normalised DLT, 9x9 Jacobi in fp64, the
+//     rotation order of OpenCV's solver), all threads count inliers of all models of the round (float32 error, no
+//     fused multiply-add: the comparison against thr^2 must see the bits cv2 sees), then one thread replays the
+//     sequential decisions in order: "strictly more inliers wins", the shrinking iteration limit, the stop.
+//     Models drawn past the stop are discarded, exactly as if they had never been drawn.
+//   * after the loop: DLT over the winner's inliers and <= 10 Levenberg-Marquardt iterations on 8 parameters,
+//     normal equations by block reduction, the 8x8 eigen-solve on one thread; the returned mask is recomputed from
+//     the refined H (what cv2 4.13 returns).
+// fp64 sums run in a different order than OpenCV's serial loops: H agrees to ~1e-9 relative, the mask bit for bit
+// unless a point's error sits within rounding of the threshold (tests count such cases).
+// Compiled with -fmad=false (build.py): a*b+c must round twice, as in OpenCV's SSE2 baseline build.
+#include <float.h>
+#include <math_constants.h>
+#include "common.cuh"
+
+namespace {
+
+constexpr int RT = 256;          // threads per CTA
+constexpr int NW = RT / 32;
+constexpr int TUPLES = 64;       // 4-tuples drawn per round
+constexpr int NRED = 45;         // sums per block reduction: upper triangle of 9x9, or 36 + 8 + 1 for the LM normal equations
+
+struct Smem {
+    double red[NW][NRED + 1];    // per-warp partial sums (+1: max slot)
+    double tot[NRED + 1];
+    double Hd[TUPLES][9];        // models of the round
+    float Hf[TUPLES][8];
+    int tup[TUPLES][4];
+    int cnt[TUPLES];
+    int state[TUPLES];           // 0 = tuple failed checkSubset, 1 = hypothesis without a model, 2 = hypothesis with a model
+    double bestH[9];
+    double x[8], xd[8];
+    double nrm[8];               // cM.x cM.y cm.x cm.y sM.x sM.y sm.x sm.y of the inlier DLT
+    int flag, best_cnt, iters_run, n_inl;
+    u64 rng;
+};
+
+__device__ __forceinline__ u32 rng_next(u64& s) {
+    s = (u64)(u32)s * 4164903690ull + (s >> 32);
+    return (u32)s;
+}
+
+__device__ __forceinline__ double hypot2(double a, double b) {      // scaled form, as the solver being matched
+    a = fabs(a); b = fabs(b);
+    if (a > b) { b /= a; return a * sqrt(1.0 + b * b); }
+    if (b > 0) { a /= b; return b * sqrt(1.0 + a * a); }
+    return 0.0;
+}
+
+// Symmetric eigen-decomposition, cyclic-by-largest-pivot Jacobi with row/column pivot indices: the rotation order
+// of OpenCV's solver (core/src/lapack.cpp), so that the eigenvector of a (numerically) rank-deficient L^T L comes
+// out as cv2's does.  A: N x N row major, upper triangle used and destroyed.  Eigenvalues descending in W,
+// eigenvectors in the ROWS of V.
+template <int N>
+__device__ void jacobi_eig(double* A, double* W, double* V) {
+    int indR[N], indC[N];
+    for (int i = 0; i < N; ++i)
+        for (int j = 0; j < N; ++j) V[i * N + j] = i == j ? 1.0 : 0.0;
+    auto row_arg = [&](int k) {
+        int m = k + 1;
+        double mv = fabs(A[k * N + m]);
+        for (int i = k + 2; i < N; ++i) { double v = fabs(A[k * N + i]); if (mv < v) { mv = v; m = i; } }
+        return m;
+    };
+    auto col_arg = [&](int k) {
+        int m = 0;
+        double mv = fabs(A[k]);
+        for (int i = 1; i < k; ++i) { double v = fabs(A[i * N + k]); if (mv < v) { mv = v; m = i; } }
+        return m;
+    };
+    for (int k = 0; k < N; ++k) {
+        W[k] = A[k * N + k];
+        if (k < N - 1) indR[k] = row_arg(k);
+        if (k > 0) indC[k] = col_arg(k);
+    }
+    for (int it = 0; it < N * N * 30; ++it) {
+        int k = 0;
+        double mv = fabs(A[indR[0]]);
+        for (int i = 1; i < N - 1; ++i) { double v = fabs(A[i * N + indR[i]]); if (mv < v) { mv = v; k = i; } }
+        int l = indR[k];
+        for (int i = 1; i < N; ++i) { double v = fabs(A[indC[i] * N + i]); if (mv < v) { mv = v; k = indC[i]; l = i; } }
+        const double p = A[k * N + l];
+        if (fabs(p) <= DBL_EPSILON) break;
+        const double y = (W[l] - W[k]) * 0.5;
+        double t = fabs(y) + hypot2(p, y);
+        double s = hypot2(p, t);
+        const double c = t / s;
+        s = p / s;
+        t = (p / t) * p;
+        if (y < 0) { s = -s; t = -t; }
+        A[k * N + l] = 0.0;
+        W[k] -= t;
+        W[l] += t;
+        auto rot = [&](double& u, double& w) { const double a0 = u, b0 = w; u = a0 * c - b0 * s; w = a0 * s + b0 * c; };
+        for (int i = 0; i < k; ++i) rot(A[i * N + k], A[i * N + l]);
+        for (int i = k + 1; i < l; ++i) rot(A[k * N + i], A[i * N + l]);
+        for (int i = l + 1; i < N; ++i) rot(A[k * N + i], A[l * N + i]);
+        for (int i = 0; i < N; ++i) rot(V[k * N + i], V[l * N + i]);
+        for (int j = 0; j < 2; ++j) {
+            const int idx = j ? l : k;
+            if (idx < N - 1) indR[idx] = row_arg(idx);
+            if (idx > 0) indC[idx] = col_arg(idx);
+        }
+    }
+    for (int k = 0; k < N - 1; ++k) {
+        int m = k;
+        for (int i = k + 1; i < N; ++i) if (W[m] < W[i]) m = i;
+        if (k != m) {
+            double tw = W[m]; W[m] = W[k]; W[k] = tw;
+            for (int i = 0; i < N; ++i) { double tv = V[m * N + i]; V[m * N + i] = V[k * N + i]; V[k * N + i] = tv; }
+        }
+    }
+}
+
+// rows of the DLT system for one normalised correspondence, accumulated into the upper triangle (45 sums, row-major j <= k)
+__device__ __forceinline__ void ltl_accumulate(double* acc, double X, double Y, double x, double y) {
+    const double Lx[9] = {X, Y, 1.0, 0.0, 0.0, 0.0, -x * X, -x * Y, -x};
+    const double Ly[9] = {0.0, 0.0, 0.0, X, Y, 1.0, -y * X, -y * Y, -y};
+    int o = 0;
+#pragma unroll
+    for (int j = 0; j < 9; ++j)
+#pragma unroll
+        for (int k = j; k < 9; ++k) acc[o++] += Lx[j] * Lx[k] + Ly[j] * Ly[k];
+}
+
+// de-normalise the eigenvector of the smallest eigenvalue: H = inv(Hnorm_dst) * H0 * Hnorm_src, scaled to h33 = 1
+__device__ void dlt_finish(const double* tri, const double* nrm, double* H) {
+    double A[81], W[9], V[81];
+    int o = 0;
+    for (int j = 0; j < 9; ++j)
+        for (int k = j; k < 9; ++k) { A[j * 9 + k] = tri[o]; A[k * 9 + j] = tri[o]; ++o; }
+    jacobi_eig<9>(A, W, V);
+    const double* h0 = V + 72;
+    const double cMx = nrm[0], cMy = nrm[1], cmx = nrm[2], cmy = nrm[3], sMx = nrm[4], sMy = nrm[5], smx = nrm[6], smy = nrm[7];
+    const double inv[9] = {1.0 / smx, 0.0, cmx, 0.0, 1.0 / smy, cmy, 0.0, 0.0, 1.0};
+    const double n2[9] = {sMx, 0.0, -cMx * sMx, 0.0, sMy, -cMy * sMy, 0.0, 0.0, 1.0};
+    double T[9];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) T[r * 3 + c] = inv[r * 3] * h0[c] + inv[r * 3 + 1] * h0[3 + c] + inv[r * 3 + 2] * h0[6 + c];
+    double R[9];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) R[r * 3 + c] = T[r * 3] * n2[c] + T[r * 3 + 1] * n2[3 + c] + T[r * 3 + 2] * n2[6 + c];
+    const double sc = 1.0 / R[8];
+    for (int i = 0; i < 9; ++i) H[i] = R[i] * sc;
+}
+
+// normalised DLT of exactly four correspondences on one thread; false when a coordinate has no spread
+__device__ bool dlt_four(const float4* p, double* H) {
+    double cMx = 0, cMy = 0, cmx = 0, cmy = 0;
+    for (int i = 0; i < 4; ++i) { cmx += p[i].z; cmy += p[i].w; cMx += p[i].x; cMy += p[i].y; }
+    cmx /= 4; cmy /= 4; cMx /= 4; cMy /= 4;
+    double smx = 0, smy = 0, sMx = 0, sMy = 0;
+    for (int i = 0; i < 4; ++i) {
+        smx += fabs(p[i].z - cmx); smy += fabs(p[i].w - cmy);
+        sMx += fabs(p[i].x - cMx); sMy += fabs(p[i].y - cMy);
+    }
+    if (fabs(smx) < DBL_EPSILON || fabs(smy) < DBL_EPSILON || fabs(sMx) < DBL_EPSILON || fabs(sMy) < DBL_EPSILON) return false;
+    smx = 4 / smx; smy = 4 / smy; sMx = 4 / sMx; sMy = 4 / sMy;
+    double tri[NRED];
+    for (int i = 0; i < NRED; ++i) tri[i] = 0.0;
+    for (int i = 0; i < 4; ++i)
+        ltl_accumulate(tri, (p[i].x - cMx) * sMx, (p[i].y - cMy) * sMy, (p[i].z - cmx) * smx, (p[i].w - cmy) * smy);
+    const double nrm[8] = {cMx, cMy, cmx, cmy, sMx, sMy, smx, smy};
+    dlt_finish(tri, nrm, H);
+    return true;
+}
+
+__device__ __forceinline__ bool collinear_last(const double* x, const double* y) {
+    // only the LAST of four points is tested against the pairs before it
+    for (int j = 0; j < 3; ++j) {
+        const double dx1 = x[j] - x[3], dy1 = y[j] - y[3];
+        for (int k = 0; k < j; ++k) {
+            const double dx2 = x[k] - x[3], dy2 = y[k] - y[3];
+            if (fabs(dx2 * dy1 - dy2 * dx1) <= (double)FLT_EPSILON * (fabs(dx1) + fabs(dy1) + fabs(dx2) + fabs(dy2))) return true;
+        }
+    }
+    return false;
+}
+
+__device__ __forceinline__ double det_tri(const double* x, const double* y, int a, int b, int c) {
+    // determinant of [[xa ya 1] [xb yb 1] [xc yc 1]], cofactor expansion along the first row
+    return x[a] * (y[b] - y[c]) - y[a] * (x[b] - x[c]) + (x[b] * y[c] - y[b] * x[c]);
+}
+
+__device__ bool subset_ok(const float4* p) {
+    double sx[4], sy[4], dx[4], dy[4];
+    for (int i = 0; i < 4; ++i) { sx[i] = p[i].x; sy[i] = p[i].y; dx[i] = p[i].z; dy[i] = p[i].w; }
+    if (collinear_last(sx, sy) || collinear_last(dx, dy)) return false;
+    const int tt[4][3] = {{0, 1, 2}, {1, 2, 3}, {0, 2, 3}, {0, 1, 3}};
+    int negative = 0;
+    for (int i = 0; i < 4; ++i)
+        negative += det_tri(sx, sy, tt[i][0], tt[i][1], tt[i][2]) * det_tri(dx, dy, tt[i][0], tt[i][1], tt[i][2]) < 0;
+    return negative == 0 || negative == 4;
+}
+
+// float32 reprojection error, every operation rounded on its own
+__device__ __forceinline__ float reproj_err(const float* h, float4 p) {
+    const float ww = __fdiv_rn(1.0f, __fadd_rn(__fadd_rn(__fmul_rn(h[6], p.x), __fmul_rn(h[7], p.y)), 1.0f));
+    const float dx = __fsub_rn(__fmul_rn(__fadd_rn(__fadd_rn(__fmul_rn(h[0], p.x), __fmul_rn(h[1], p.y)), h[2]), ww), p.z);
+    const float dy = __fsub_rn(__fmul_rn(__fadd_rn(__fadd_rn(__fmul_rn(h[3], p.x), __fmul_rn(h[4], p.y)), h[5]), ww), p.w);
+    return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+}
+
+__device__ int update_num_iters(double p, double ep, int max_iters) {
+    p = fmin(fmax(p, 0.0), 1.0);
+    ep = fmin(fmax(ep, 0.0), 1.0);
+    double num = fmax(1.0 - p, DBL_MIN);
+    double denom = 1.0 - pow(1.0 - ep, 4.0);
+    if (denom < DBL_MIN) return 0;
+    num = log(num);
+    denom = log(denom);
+    return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)rint(num / denom);
+}
+
+// block-wide sums of nv <= NRED doubles per thread (fixed tree: run-to-run deterministic) and one max; result in sm.tot
+template <int NV>
+__device__ void block_reduce(Smem& sm, double* acc, double mx) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        double v = acc[i];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) sm.red[warp][i] = v;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) sm.red[warp][NRED] = mx;
+    __syncthreads();
+    if (threadIdx.x < NV) {
+        double v = 0;
+        for (int w = 0; w < NW; ++w) v += sm.red[w][threadIdx.x];
+        sm.tot[threadIdx.x] = v;
+    }
+    if (threadIdx.x == 32) {
+        double v = 0;
+        for (int w = 0; w < NW; ++w) v = fmax(v, sm.red[w][NRED]);
+        sm.tot[NRED] = v;
+    }
+    __syncthreads();
+}
+
+// residuals and normal equations of the refinement at parameters h over the inliers: acc[0..35] upper triangle of
+// J^T J, acc[36..43] J^T r, acc[44] |r|^2; returns max |r|
+__device__ __forceinline__ double lm_accumulate(double* acc, const double* h, float4 p) {
+    const double Mx = p.x, My = p.y;
+    double ww = h[6] * Mx + h[7] * My + 1.0;
+    ww = fabs(ww) > DBL_EPSILON ? 1.0 / ww : 0.0;
+    const double xi = (h[0] * Mx + h[1] * My + h[2]) * ww, yi = (h[3] * Mx + h[4] * My + h[5]) * ww;
+    const double rx = xi - p.z, ry = yi - p.w;
+    const double Jx[8] = {Mx * ww, My * ww, ww, 0.0, 0.0, 0.0, -Mx * ww * xi, -My * ww * xi};
+    const double Jy[8] = {0.0, 0.0, 0.0, Mx * ww, My * ww, ww, -Mx * ww * yi, -My * ww * yi};
+    int o = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+        for (int k = j; k < 8; ++k) acc[o++] += Jx[j] * Jx[k] + Jy[j] * Jy[k];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[36 + j] += Jx[j] * rx + Jy[j] * ry;
+    acc[44] += rx * rx + ry * ry;
+    return fmax(fabs(rx), fabs(ry));
+}
+
+struct LmState {                 // thread 0's registers/local memory across the refinement
+    double A[64], v[8], D[8], d[8], S, lam, lc, rmax;
+    int iter;
+};
+
+__device__ void unpack_normal(const double* tot, double* A, double* v) {
+    int o = 0;
+    for (int j = 0; j < 8; ++j)
+        for (int k = j; k < 8; ++k) { A[j * 8 + k] = tot[o]; A[k * 8 + j] = tot[o]; ++o; }
+    for (int j = 0; j < 8; ++j) v[j] = tot[36 + j];
+}
+
+// x = A^-1 b through the eigen-decomposition (cv::solve(..., DECOMP_EIG)); optionally the diagonal of A^-1
+__device__ void eig_solve8(const double* A, const double* b, double* x, double* inv_diag) {
+    double T[64], W[8], V[64];
+    for (int i = 0; i < 64; ++i) T[i] = A[i];
+    jacobi_eig<8>(T, W, V);
+    double y[8];
+    for (int i = 0; i < 8; ++i) {
+        double s = 0;
+        for (int j = 0; j < 8; ++j) s += V[i * 8 + j] * b[j];
+        y[i] = fabs(W[i]) > DBL_EPSILON ? s / W[i] : 0.0;
+    }
+    for (int j = 0; j < 8; ++j) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += V[i * 8 + j] * y[i];
+        x[j] = s;
+    }
+    if (inv_diag)
+        for (int j = 0; j < 8; ++j) {
+            double s = 0;
+            for (int i = 0; i < 8; ++i) s += fabs(W[i]) > DBL_EPSILON ? V[i * 8 + j] * V[i * 8 + j] / W[i] : 0.0;
+            inv_diag[j] = s;
+        }
+}
+
+__global__ void __launch_bounds__(RT)
+ransac_homography_kernel(const float4* __restrict__ corr, const long long* __restrict__ ptr, int num_pairs, float thr2,
+                         double confidence, int max_iters, double* __restrict__ H_out, uint8_t* __restrict__ mask_out,
+                         int32_t* __restrict__ inliers_out, int32_t* __restrict__ iters_out) {
+    __shared__ Smem sm;
+    const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const long long beg = ptr[pair];
+    const int count = (int)(ptr[pair + 1] - beg);
+    const float4* pts = corr + beg;
+    uint8_t* mask = mask_out + beg;
+    double* Hg = H_out + (size_t)pair * 9;
+
+    auto fail = [&]() {          // H = None
+        for (int i = tid; i < count; i += RT) mask[i] = 0;
+        if (tid < 9) Hg[tid] = CUDART_NAN;
+        if (tid == 0) { inliers_out[pair] = -1; if (iters_out) iters_out[pair] = 0; }
+    };
+    if (count < 4) { fail(); return; }       // the reference returns ([], None) before calling cv2 (utils.py:135-136)
+
+    if (count == 4) {
+        if (tid == 0) {
+            float4 p[4] = {pts[0], pts[1], pts[2], pts[3]};
+            double H[9];
+            sm.flag = dlt_four(p, H);
+            for (int i = 0; i < 9; ++i) sm.bestH[i] = H[i];
+        }
+        __syncthreads();
+        if (!sm.flag) { fail(); return; }
+        if (tid < 9) Hg[tid] = sm.bestH[tid];
+        if (tid < 4) mask[tid] = 1;
+        if (tid == 0) { inliers_out[pair] = 4; if (iters_out) iters_out[pair] = 0; }
+        return;
+    }
+
+    // ---------------------------------------------------------------- hypothesis loop
+    int niters = max(max_iters, 1), iter = 0, max_good = 0, fails = 0;      // thread 0 only
+    if (tid == 0) { sm.rng = 0xFFFFFFFFFFFFFFFFull; sm.flag = 0; sm.best_cnt = 0; }
+    __syncthreads();
+    for (;;) {
+        if (tid == 0) {
+            u64 s = sm.rng;
+            for (int t = 0; t < TUPLES; ++t) {
+                int id[4];
+                for (int i = 0; i < 4; ++i) {
+                    int v;
+                    bool dup;
+                    do {
+                        v = (int)(rng_next(s) % (u32)count);
+                        dup = false;
+                        for (int j = 0; j < i; ++j) dup |= id[j] == v;
+                    } while (dup);
+                    id[i] = v;
+                }
+                for (int i = 0; i < 4; ++i) sm.tup[t][i] = id[i];
+            }
+            sm.rng = s;
+        }
+        if (tid < TUPLES) sm.cnt[tid] = 0;
+        __syncthreads();
+        if (tid < TUPLES) {
+            float4 p[4];
+            for (int i = 0; i < 4; ++i) p[i] = __ldg(pts + sm.tup[tid][i]);
+            int st = 0;
+            if (subset_ok(p)) {
+                double H[9];
+                st = 1;
+                if (dlt_four(p, H)) {
+                    st = 2;
+                    for (int i = 0; i < 9; ++i) sm.Hd[tid][i] = H[i];
+                    for (int i = 0; i < 8; ++i) sm.Hf[tid][i] = (float)H[i];
+                }
+            }
+            sm.state[tid] = st;
+        }
+        __syncthreads();
+        for (int i0 = 0; i0 < count; i0 += RT) {
+            const int i = i0 + tid;
+            const bool in = i < count;
+            const float4 p = in ? __ldg(pts + i) : make_float4(0, 0, 0, 0);
+            for (int t = 0; t < TUPLES; ++t) {
+                if (sm.state[t] != 2) continue;
+                const bool good = in && reproj_err(sm.Hf[t], p) <= thr2;
+                const int c = __popc(__ballot_sync(0xffffffffu, good));
+                if (lane == 0 && c) atomicAdd(&sm.cnt[t], c);
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int done = 0;
+            for (int t = 0; t < TUPLES && !done; ++t) {
+                if (iter >= niters) { done = 1; break; }
+                if (sm.state[t] == 0) {
+                    if (++fails >= 10000) done = iter == 0 ? 2 : 1;       // getSubset gave up
+                    continue;
+                }
+                fails = 0;
+                if (sm.state[t] == 2) {
+                    const int good = sm.cnt[t];
+                    if (good > max(max_good, 3)) {
+                        max_good = good;
+                        for (int i = 0; i < 9; ++i) sm.bestH[i] = sm.Hd[t][i];
+                        niters = update_num_iters(confidence, (double)(count - good) / count, niters);
+                    }
+                }
+                ++iter;
+            }
+            if (!done && iter >= niters) done = 1;
+            sm.flag = done;
+            sm.best_cnt = max_good;
+            sm.iters_run = iter;
+        }
+        __syncthreads();
+        if (sm.flag) break;
+    }
+    if (sm.flag == 2 || sm.best_cnt == 0) { fail(); return; }
+
+    // ---------------------------------------------------------------- refit on the winner's inliers
+    float hf[8];
+    for (int i = 0; i < 8; ++i) hf[i] = (float)sm.bestH[i];
+    double acc[NRED];
+    for (int i = 0; i < NRED; ++i) acc[i] = 0.0;
+    for (int i = tid; i < count; i += RT) {
+        const float4 p = __ldg(pts + i);
+        const bool good = reproj_err(hf, p) <= thr2;
+        mask[i] = good;
+        if (good) { acc[0] += p.x; acc[1] += p.y; acc[2] += p.z; acc[3] += p.w; acc[4] += 1.0; }
+    }
+    block_reduce<5>(sm, acc, 0.0);
+    const int n_inl = (int)sm.tot[4];
+    const double cMx = sm.tot[0] / n_inl, cMy = sm.tot[1] / n_inl, cmx = sm.tot[2] / n_inl, cmy = sm.tot[3] / n_inl;
+    __syncthreads();
+    for (int i = 0; i < 4; ++i) acc[i] = 0.0;
+    for (int i = tid; i < count; i += RT)
+        if (mask[i]) {
+            const float4 p = __ldg(pts + i);
+            acc[0] += fabs(p.x - cMx); acc[1] += fabs(p.y - cMy); acc[2] += fabs(p.z - cmx); acc[3] += fabs(p.w - cmy);
+        }
+    block_reduce<4>(sm, acc, 0.0);
+    const bool spread = !(fabs(sm.tot[0]) < DBL_EPSILON || fabs(sm.tot[1]) < DBL_EPSILON || fabs(sm.tot[2]) < DBL_EPSILON ||
+                          fabs(sm.tot[3]) < DBL_EPSILON);
+    const double sMx = n_inl / sm.tot[0], sMy = n_inl / sm.tot[1], smx = n_inl / sm.tot[2], smy = n_inl / sm.tot[3];
+    __syncthreads();
+    if (spread) {                                  // block-uniform
+        for (int i = 0; i < NRED; ++i) acc[i] = 0.0;
+        for (int i = tid; i < count; i += RT)
+            if (mask[i]) {
+                const float4 p = __ldg(pts + i);
+                ltl_accumulate(acc, (p.x - cMx) * sMx, (p.y - cMy) * sMy, (p.z - cmx) * smx, (p.w - cmy) * smy);
+            }
+        block_reduce<NRED>(sm, acc, 0.0);
+        if (tid == 0) {
+            const double nrm[8] = {cMx, cMy, cmx, cmy, sMx, sMy, smx, smy};
+            double H[9];
+            dlt_finish(sm.tot, nrm, H);
+            for (int i = 0; i < 9; ++i) sm.bestH[i] = H[i];
+        }
+        __syncthreads();
+    }
+
+    // ---------------------------------------------------------------- Levenberg-Marquardt, 8 parameters, <= 10 iterations
+    LmState lm;
+    if (tid < 8) sm.xd[tid] = sm.bestH[tid];
+    __syncthreads();
+    for (int pass = 0;; ++pass) {
+        // normal equations at xd (pass 0: the starting point)
+        double h[8];
+        for (int i = 0; i < 8; ++i) h[i] = sm.xd[i];
+        for (int i = 0; i < NRED; ++i) acc[i] = 0.0;
+        double rmax = 0.0;
+        for (int i = tid; i < count; i += RT)
+            if (mask[i]) rmax = fmax(rmax, lm_accumulate(acc, h, __ldg(pts + i)));
+        block_reduce<NRED>(sm, acc, rmax);
+        if (tid == 0) {
+            const double eps = (double)FLT_EPSILON;
+            bool proceed = true;
+            if (pass == 0) {
+                unpack_normal(sm.tot, lm.A, lm.v);
+                for (int i = 0; i < 8; ++i) { lm.D[i] = lm.A[i * 9]; sm.x[i] = sm.xd[i]; }
+                lm.S = sm.tot[44]; lm.rmax = sm.tot[NRED];
+                lm.lam = 1.0; lm.lc = 0.75; lm.iter = 0;
+            } else {
+                const double* d = lm.d;
+                const double Sd = sm.tot[44];
+                double dS = 0, dv = 0, dmax = 0;
+                for (int i = 0; i < 8; ++i) {
+                    double t = 0;
+                    for (int j = 0; j < 8; ++j) t += lm.A[i * 8 + j] * d[j];
+                    dS += d[i] * (2.0 * lm.v[i] - t);
+                    dv += d[i] * lm.v[i];
+                    dmax = fmax(dmax, fabs(d[i]));
+                }
+                const double R = (lm.S - Sd) / (fabs(dS) > DBL_EPSILON ? dS : 1.0);
+                if (R > 0.75) {
+                    lm.lam *= 0.5;
+                    if (lm.lam < lm.lc) lm.lam = 0.0;
+                } else if (R < 0.25) {
+                    double nu = (Sd - lm.S) / (fabs(dv) > DBL_EPSILON ? dv : 1.0) + 2.0;
+                    nu = fmin(fmax(nu, 2.0), 10.0);
+                    if (lm.lam == 0.0) {
+                        double dummy[8], idg[8], mxv = DBL_EPSILON;
+                        eig_solve8(lm.A, lm.v, dummy, idg);
+                        for (int i = 0; i < 8; ++i) mxv = fmax(mxv, fabs(idg[i]));
+                        lm.lam = lm.lc = 1.0 / mxv;
+                        nu *= 0.5;
+                    }
+                    lm.lam *= nu;
+                }
+                if (Sd < lm.S) {
+                    lm.S = Sd;
+                    for (int i = 0; i < 8; ++i) sm.x[i] = sm.xd[i];
+                    unpack_normal(sm.tot, lm.A, lm.v);
+                    lm.rmax = sm.tot[NRED];
+                }
+                ++lm.iter;
+                proceed = lm.iter < 10 && dmax >= eps && lm.rmax >= eps;
+            }
+            if (proceed) {
+                double Ap[64];
+                for (int i = 0; i < 64; ++i) Ap[i] = lm.A[i];
+                for (int i = 0; i < 8; ++i) Ap[i * 9] += lm.lam * lm.D[i];
+                eig_solve8(Ap, lm.v, lm.d, nullptr);
+                for (int i = 0; i < 8; ++i) sm.xd[i] = sm.x[i] - lm.d[i];
+            }
+            sm.flag = proceed;
+        }
+        __syncthreads();
+        if (!sm.flag) break;
+    }
+
+    // ---------------------------------------------------------------- mask of the refined model
+    for (int i = 0; i < 8; ++i) hf[i] = (float)sm.x[i];
+    int c = 0;
+    for (int i = tid; i < count; i += RT) {
+        const bool good = reproj_err(hf, __ldg(pts + i)) <= thr2;
+        mask[i] = good;
+        c += good;
+    }
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) sm.cnt[tid >> 5] = c;
+    __syncthreads();
+    if (tid == 0) {
+        int tot = 0;
+        for (int w = 0; w < NW; ++w) tot += sm.cnt[w];
+        inliers_out[pair] = tot;
+        if (iters_out) iters_out[pair] = sm.iters_run;
+    }
+    if (tid < 8) Hg[tid] = sm.x[tid];
+    if (tid == 8) Hg[8] = 1.0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200m_ransac_homography(const float* corr_xyxy, const int64_t* ptr, int num_pairs, double thr, double confidence,
+                            int max_iters, double* H_out, uint8_t* mask_out, int32_t* inliers_out, int32_t* iters_out,
+                            void* stream) {
+    if (num_pairs < 0) return B200M_EINVAL;
+    if (num_pairs == 0) return B200M_OK;
+    if (!corr_xyxy || !ptr || !H_out || !mask_out || !inliers_out) return B200M_EINVAL;
+    if (!(confidence > 0.0 && confidence < 1.0)) return B200M_EINVAL;            // CV_Assert in RANSACPointSetRegistrator::run
+    if ((uintptr_t)corr_xyxy & 15) return B200M_EINVAL;
+    ransac_homography_kernel<<<(unsigned)num_pairs, RT, 0, (cudaStream_t)stream>>>(
+        (const float4*)corr_xyxy, (const long long*)ptr, num_pairs, (float)(thr * thr), confidence, max_iters, H_out, mask_out,
+        inliers_out, iters_out);
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "ransac_homography_kernel launch");
+    return B200M_OK;
+}
+
+}  // extern "C"

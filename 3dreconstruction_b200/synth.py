@@ -108,3 +108,31 @@ def all_pairs(images: int) -> np.ndarray:
     (/root/reference/FeatureMatchingExtraction/image_manager.py:491-494)."""
     i, j = np.triu_indices(images, k=1)
     return np.stack([i, j], axis=1).astype(np.int32)
+
+
+def homography_pair(seed: int = 5, n: int = 1000, inlier_frac: float = 0.5, noise: float = 1.0,
+                    width: float = 1920.0, height: float = 1080.0):
+    """Matched keypoint coordinates of one image pair for the geometric-verification stage: float32 [n, 4] rows
+    (x1, y1, x2, y2).  A fraction of the matches follows one random perspective map (+ Gaussian pixel noise), the
+    rest pairs uniformly random points (wrong matches); rows are shuffled."""
+    rng = np.random.default_rng(seed)
+    p1 = rng.random((n, 2)) * [width, height]
+    H = np.array([[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]])
+    H += rng.normal(0.0, 1.0, (3, 3)) * [[0.08, 0.08, 40.0], [0.08, 0.08, 40.0], [2e-5, 2e-5, 0.0]]
+    q = np.c_[p1, np.ones(n)] @ H.T
+    p2 = q[:, :2] / q[:, 2:]
+    k = int(round(n * inlier_frac))
+    p2[:k] += rng.normal(0.0, noise, (k, 2))
+    p2[k:] = rng.random((n - k, 2)) * [width, height]
+    out = np.concatenate([p1, p2], axis=1).astype(np.float32)
+    return out[rng.permutation(n)]
+
+
+def homography_set(seed: int = 6, pairs: int = 64, n_lo: int = 50, n_hi: int = 2000, inl_lo: float = 0.3, inl_hi: float = 0.9):
+    """`pairs` correspondence sets of varying size and inlier ratio as one CSR: (float32 [K, 4], int64 ptr [pairs + 1])."""
+    rng = np.random.default_rng(seed)
+    sets = [homography_pair(seed * 1000 + p, int(rng.integers(n_lo, n_hi + 1)), float(rng.uniform(inl_lo, inl_hi)))
+            for p in range(pairs)]
+    ptr = np.zeros(pairs + 1, np.int64)
+    ptr[1:] = np.cumsum([len(s) for s in sets])
+    return np.concatenate(sets, axis=0), ptr

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 130
+#define B200M_VERSION 140
 
 #if defined(__GNUC__)
 #define B200M_API __attribute__((visibility("default")))
@@ -183,6 +183,22 @@ B200M_API int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm,
 B200M_API int b200m_gather_correspondences(const float* kp_xy, int64_t rows, const int32_t* pair_q_off,
                      const int32_t* pair_t_off, const int64_t* ptr, int num_pairs, const int32_t* q_idx,
                      const int32_t* t_idx, float* out_xyxy, void* stream);
+
+/* Geometric verification of matched pairs: what, per image pair,
+ *     H, mask = cv2.findHomography(pts1, pts2, cv2.RANSAC, thr, confidence=confidence, maxIters=max_iters)
+ * returns at /root/reference/FeatureMatchingExtraction/utils.py:141 (enhanced_filter_matches_with_homography, :118-153),
+ * for every pair of a CSR in one launch (one CTA per pair; cv2's own random sequence, see csrc/ransac.cu).
+ *   corr_xyxy   float32 [ptr[num_pairs], 4] from b200m_gather_correspondences (device, 16-byte aligned)
+ *   ptr         int64 [num_pairs + 1] (device)
+ *   H_out       float64 [num_pairs, 9] row-major 3x3, h33 = 1; NaN where cv2 returns None
+ *   mask_out    uint8 [ptr[num_pairs]]: 1 = inlier of the refined H (cv2's mask.ravel()), 0 elsewhere
+ *   inliers_out int32 [num_pairs]: number of inliers, or -1 where the reference yields ([], None): fewer than 4
+ *               matches (utils.py:135) or no model
+ *   iters_out   int32 [num_pairs] or NULL: RANSAC iterations run (diagnostic)
+ * confidence must lie in (0, 1) (cv2 asserts the same).  No workspace. */
+B200M_API int b200m_ransac_homography(const float* corr_xyxy, const int64_t* ptr, int num_pairs, double thr,
+                     double confidence, int max_iters, double* H_out, uint8_t* mask_out, int32_t* inliers_out,
+                     int32_t* iters_out, void* stream);
 
 /* Measurement hooks for bench.py's roofline: when enabled, CUDA events are recorded on the
  * launching stream around every knn-stage kernel; collect() synchronises them and returns the summed

@@ -1,0 +1,125 @@
+"""GPU parity of the batched RANSAC homography kernel (csrc/ransac.cu) through the C-ABI
+(b200m_ransac_homography): against the committed outputs of the reference's enhanced_filter_matches_with_homography
+(tests/golden/ransac_golden.npz), against the oracle on seeded inputs, and through size-independent properties
+on a large batch.  Bar: the inlier mask bit for bit, H within 1e-6 relative (fp64 sums run in another order than
+OpenCV's serial loops; observed <= 1e-8)."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ransac_oracle as ro
+
+b = importlib.import_module("3dreconstruction_b200")
+verify = importlib.import_module("3dreconstruction_b200.verify")
+synth = b.synth
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "ransac_golden.npz")
+pytestmark = pytest.mark.gpu
+H_TOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def eng():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return b.Engine()
+
+
+def h_close(H, Hg, tol=H_TOL):
+    return np.abs(H - Hg).max() <= tol * np.abs(Hg).max()
+
+
+def test_golden_cases_in_one_batch(eng):
+    g = np.load(GOLD)
+    names = [str(n) for n in g["names"]]
+    groups = {}
+    for nm in names:                                     # one launch per parameter set
+        groups.setdefault(tuple(g[nm + "_params"]), []).append(nm)
+    for (thr, conf, iters), nms in groups.items():
+        corr = np.concatenate([g[nm + "_corr"] for nm in nms], axis=0)
+        ptr = np.zeros(len(nms) + 1, np.int64)
+        ptr[1:] = np.cumsum([len(g[nm + "_corr"]) for nm in nms])
+        v = verify.verify_pairs(corr, ptr, thr, conf, int(iters), engine=eng)
+        for p, nm in enumerate(nms):
+            Hg = g[nm + "_H"]
+            if np.isnan(Hg).any():
+                assert v.inliers[p] == -1 and v.homography(p) is None and len(v.kept(p)) == 0, nm
+                continue
+            assert np.array_equal(v.kept(p), g[nm + "_kept"]), nm
+            assert v.inliers[p] == len(g[nm + "_kept"]), nm
+            assert h_close(v.H[p], Hg), (nm, v.H[p], Hg)
+
+
+def test_against_oracle_seeded(eng):
+    cases = [(200, 0.8, 5.0, 0.99, 2000), (150, 0.6, 3.0, 0.99, 2000), (64, 0.7, 4.0, 0.995, 500), (30, 0.9, 5.0, 0.99, 2000),
+             (7, 1.0, 5.0, 0.99, 2000), (4, 1.0, 5.0, 0.99, 2000), (2, 1.0, 5.0, 0.99, 2000), (0, 1.0, 5.0, 0.99, 2000)]
+    for seed, (n, inl, thr, conf, iters) in enumerate(cases):
+        c = synth.homography_pair(seed=70 + seed, n=max(n, 1), inlier_frac=inl)[:n]
+        v = verify.verify_pairs(c, np.array([0, n], np.int64), thr, conf, iters, engine=eng)
+        kept, H = ro.reference_filter(c[:, :2], c[:, 2:], thr, conf, iters)
+        assert np.array_equal(v.kept(0), kept), (n, inl)
+        if H is None:
+            assert v.inliers[0] == -1
+        else:
+            assert h_close(v.H[0], H), (n, inl)
+            _, _, it = ro.ransac_homography(c[:, :2], c[:, 2:], thr, conf, iters)
+            assert v.iters[0] == it
+
+
+def test_degenerate_inputs(eng):
+    # all points identical / collinear: cv2 finds no subset that passes its checks -> (None, None)
+    same = np.tile(np.array([[10.0, 20.0, 30.0, 40.0]], np.float32), (20, 1))
+    line = np.stack([np.arange(30), np.arange(30) * 2, np.arange(30) + 5, np.arange(30) * 2 + 1], axis=1).astype(np.float32)
+    corr = np.concatenate([same, line], axis=0)
+    v = verify.verify_pairs(corr, np.array([0, 20, 50], np.int64), 5.0, 0.99, 50, engine=eng)
+    for p, c in enumerate((same, line)):
+        kept, H = ro.reference_filter(c[:, :2], c[:, 2:], 5.0, 0.99, 50)
+        assert H is None and v.inliers[p] == -1 and not v.mask[v.ptr[p]:v.ptr[p + 1]].any()
+
+
+def test_reference_function_mirror(eng):
+    """enhanced_filter_matches_with_homography / adaptive_match_filtering with the reference's argument shapes."""
+    contracts = b.contracts.resolve()
+    g = np.load(GOLD)
+    c = g["half_1000_corr"]
+    n = len(c)
+
+    class KP:
+        def __init__(self, x, y):
+            self.pt = (float(x), float(y))
+    kp1 = [KP(x, y) for x, y in c[:, :2]]
+    kp2 = [KP(x, y) for x, y in c[:, 2:]]
+    dist_t = contracts.ScoreType.DISTANCE
+    ms = [contracts.EnhancedDMatch(queryIdx=i, trainIdx=i, score=float(i), score_type=dist_t) for i in range(n)]
+    md = contracts.MatchData(matches=ms, method="BF", score_type=dist_t)
+    kept, H = verify.enhanced_filter_matches_with_homography(kp1, kp2, ms, md, ransac_threshold=5.0, engine=eng)
+    assert [m.queryIdx for m in kept] == g["half_1000_kept"].tolist() and all(k is ms[k.queryIdx] for k in kept)
+    assert H.shape == (3, 3) and h_close(H, g["half_1000_H"])
+    kept2, H2, info = verify.adaptive_match_filtering(kp1, kp2, ms, md, ransac_threshold=4.0, engine=eng)
+    assert info["method"] == "homography_ransac" and info["original_count"] == n and info["filtered_count"] == len(kept2)
+    assert info["homography_found"] and H2 is not None
+    md3 = contracts.MatchData(matches=ms[:3], method="BF", score_type=dist_t)
+    assert verify.enhanced_filter_matches_with_homography(kp1, kp2, ms[:3], md3, engine=eng) == ([], None)
+    assert verify.adaptive_match_filtering(kp1, kp2, ms[:3], md3, engine=eng)[2]["reason"] == "insufficient_matches"
+
+
+def test_large_batch_properties(eng):
+    """2000 pairs in one launch: run-to-run identical, a pair's result does not depend on its neighbours, the mask is
+    exactly the float32 error test of the returned H, counts agree."""
+    corr, ptr = synth.homography_set(seed=6, pairs=2000, n_lo=20, n_hi=1500)
+    v1 = verify.verify_pairs(corr, ptr, 4.0, 0.99, 2000, engine=eng)
+    v2 = verify.verify_pairs(corr, ptr, 4.0, 0.99, 2000, engine=eng)
+    assert np.array_equal(v1.mask, v2.mask) and np.array_equal(v1.inliers, v2.inliers)
+    assert np.array_equal(v1.H, v2.H, equal_nan=True)
+    assert (v1.inliers >= 4).mean() > 0.95
+    t = np.float32(16.0)
+    for p in range(0, 2000, 97):
+        s = slice(int(ptr[p]), int(ptr[p + 1]))
+        alone = verify.verify_pairs(corr[s], np.array([0, s.stop - s.start], np.int64), 4.0, 0.99, 2000, engine=eng)
+        assert np.array_equal(alone.mask, v1.mask[s]) and np.array_equal(alone.H[0], v1.H[p], equal_nan=True)
+        if v1.inliers[p] >= 0:
+            want = ro.compute_error(corr[s, :2], corr[s, 2:], v1.H[p]) <= t
+            assert np.array_equal(want.astype(np.uint8), v1.mask[s])
+            assert v1.inliers[p] == int(want.sum())

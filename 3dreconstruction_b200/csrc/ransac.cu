@@ -25,10 +25,22 @@
 
 namespace {
 
-constexpr int RT = 256;          // threads per CTA
+#ifndef RANSAC_TUPLES
+#define RANSAC_TUPLES 64
+#endif
+#ifndef RANSAC_MINB
+#define RANSAC_MINB 2
+#endif
+constexpr int RT = 128;          // threads per CTA
 constexpr int NW = RT / 32;
-constexpr int TUPLES = 64;       // 4-tuples drawn per round
+constexpr int TUPLES = RANSAC_TUPLES;   // 4-tuples drawn per round
+constexpr int TS = TUPLES;       // stride between the elements of one thread's scratch matrix
 constexpr int NRED = 45;         // sums per block reduction: upper triangle of 9x9, or 36 + 8 + 1 for the LM normal equations
+
+struct LmState {                 // thread 0's state across the refinement (shared memory)
+    double A[64], v[8], D[8], d[8], S, lam, lc, rmax;
+    int iter;
+};
 
 struct Smem {
     double red[NW][NRED + 1];    // per-warp partial sums (+1: max slot)
@@ -40,9 +52,9 @@ struct Smem {
     int state[TUPLES];           // 0 = tuple failed checkSubset, 1 = hypothesis without a model, 2 = hypothesis with a model
     double bestH[9];
     double x[8], xd[8];
-    double nrm[8];               // cM.x cM.y cm.x cm.y sM.x sM.y sm.x sm.y of the inlier DLT
     int flag, best_cnt, iters_run, n_inl;
     u64 rng;
+    LmState lm;
 };
 
 __device__ __forceinline__ u32 rng_next(u64& s) {
@@ -57,69 +69,113 @@ __device__ __forceinline__ double hypot2(double a, double b) {      // scaled fo
     return 0.0;
 }
 
-// Symmetric eigen-decomposition, cyclic-by-largest-pivot Jacobi with row/column pivot indices: the rotation order
-// of OpenCV's solver (core/src/lapack.cpp), so that the eigenvector of a (numerically) rank-deficient L^T L comes
-// out as cv2's does.  A: N x N row major, upper triangle used and destroyed.  Eigenvalues descending in W,
-// eigenvectors in the ROWS of V.
+// Per-thread scratch matrices live in SHARED memory, element-major: element e of thread t's matrix is at
+// base[e * TS + t] (TS = TUPLES threads side by side), so lanes with different pivots still hit different banks.
+// (A first version kept them in local memory: 2.6 KB per thread thrashed L1, ncu showed 2.5 GB of DRAM writes.)
+template <int N> struct Scratch {
+    double* m;                                    // this thread's column
+    __device__ __forceinline__ double& A(int i, int j) const { return m[(i * N + j) * TS]; }
+    __device__ __forceinline__ double& V(int i, int j) const { return m[(N * N + i * N + j) * TS]; }
+    __device__ __forceinline__ double& W(int i) const { return m[(2 * N * N + i) * TS]; }
+};
+constexpr int SCRATCH_DOUBLES = 2 * 81 + 9;       // per thread, N = 9
+
+__device__ __forceinline__ int nib_get(u64 w, int i) { return (int)((w >> (4 * i)) & 15u); }
+__device__ __forceinline__ u64 nib_set(u64 w, int i, int v) { return (w & ~(15ull << (4 * i))) | ((u64)v << (4 * i)); }
+
+// Symmetric eigen-decomposition, Jacobi with the pivot = largest off-diagonal element tracked through per-row and
+// per-column argmax indices: the rotation order of OpenCV's solver (core/src/lapack.cpp), so that the eigenvector of
+// a (numerically) rank-deficient L^T L comes out as cv2's does.  Upper triangle of A used and destroyed, eigenvectors
+// in the ROWS of V, eigenvalues in W (unsorted; sorted_index() gives the order OpenCV's selection sort would).
+// All loops have fixed trip counts and predicated bodies: lanes of a warp work on different matrices with
+// different pivots.  The index arrays are nibbles of two registers.
 template <int N>
-__device__ void jacobi_eig(double* A, double* W, double* V) {
-    int indR[N], indC[N];
-    for (int i = 0; i < N; ++i)
-        for (int j = 0; j < N; ++j) V[i * N + j] = i == j ? 1.0 : 0.0;
-    auto row_arg = [&](int k) {
+__device__ void jacobi_eig(const Scratch<N>& S) {
+    u64 indR = 0, indC = 0;
+    auto row_arg = [&](int k) {                    // first maximum of |A[k][i]|, i > k
         int m = k + 1;
-        double mv = fabs(A[k * N + m]);
-        for (int i = k + 2; i < N; ++i) { double v = fabs(A[k * N + i]); if (mv < v) { mv = v; m = i; } }
+        double mv = -1.0;
+#pragma unroll
+        for (int i = 1; i < N; ++i)
+            if (i > k) { const double v = fabs(S.A(k, i)); if (mv < v) { mv = v; m = i; } }
         return m;
     };
-    auto col_arg = [&](int k) {
+    auto col_arg = [&](int k) {                    // first maximum of |A[i][k]|, i < k
         int m = 0;
-        double mv = fabs(A[k]);
-        for (int i = 1; i < k; ++i) { double v = fabs(A[i * N + k]); if (mv < v) { mv = v; m = i; } }
+        double mv = -1.0;
+#pragma unroll
+        for (int i = 0; i < N - 1; ++i)
+            if (i < k) { const double v = fabs(S.A(i, k)); if (mv < v) { mv = v; m = i; } }
         return m;
     };
-    for (int k = 0; k < N; ++k) {
-        W[k] = A[k * N + k];
-        if (k < N - 1) indR[k] = row_arg(k);
-        if (k > 0) indC[k] = col_arg(k);
+#pragma unroll 1
+    for (int i = 0; i < N; ++i) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) S.V(i, j) = i == j ? 1.0 : 0.0;
+        S.W(i) = S.A(i, i);
+        if (i < N - 1) indR = nib_set(indR, i, row_arg(i));
+        if (i > 0) indC = nib_set(indC, i, col_arg(i));
     }
+#pragma unroll 1
     for (int it = 0; it < N * N * 30; ++it) {
         int k = 0;
-        double mv = fabs(A[indR[0]]);
-        for (int i = 1; i < N - 1; ++i) { double v = fabs(A[i * N + indR[i]]); if (mv < v) { mv = v; k = i; } }
-        int l = indR[k];
-        for (int i = 1; i < N; ++i) { double v = fabs(A[indC[i] * N + i]); if (mv < v) { mv = v; k = indC[i]; l = i; } }
-        const double p = A[k * N + l];
+        double mv = fabs(S.A(0, nib_get(indR, 0)));
+#pragma unroll
+        for (int i = 1; i < N - 1; ++i) { const double v = fabs(S.A(i, nib_get(indR, i))); if (mv < v) { mv = v; k = i; } }
+        int l = nib_get(indR, k);
+#pragma unroll
+        for (int i = 1; i < N; ++i) {
+            const int ci = nib_get(indC, i);
+            const double v = fabs(S.A(ci, i));
+            if (mv < v) { mv = v; k = ci; l = i; }
+        }
+        const double p = S.A(k, l);
         if (fabs(p) <= DBL_EPSILON) break;
-        const double y = (W[l] - W[k]) * 0.5;
+        const double y = (S.W(l) - S.W(k)) * 0.5;
         double t = fabs(y) + hypot2(p, y);
         double s = hypot2(p, t);
         const double c = t / s;
         s = p / s;
         t = (p / t) * p;
         if (y < 0) { s = -s; t = -t; }
-        A[k * N + l] = 0.0;
-        W[k] -= t;
-        W[l] += t;
-        auto rot = [&](double& u, double& w) { const double a0 = u, b0 = w; u = a0 * c - b0 * s; w = a0 * s + b0 * c; };
-        for (int i = 0; i < k; ++i) rot(A[i * N + k], A[i * N + l]);
-        for (int i = k + 1; i < l; ++i) rot(A[k * N + i], A[i * N + l]);
-        for (int i = l + 1; i < N; ++i) rot(A[k * N + i], A[l * N + i]);
-        for (int i = 0; i < N; ++i) rot(V[k * N + i], V[l * N + i]);
-        for (int j = 0; j < 2; ++j) {
-            const int idx = j ? l : k;
-            if (idx < N - 1) indR[idx] = row_arg(idx);
-            if (idx > 0) indC[idx] = col_arg(idx);
+        S.A(k, l) = 0.0;
+        S.W(k) -= t;
+        S.W(l) += t;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            {   // eigenvector rows k and l
+                double& u = S.V(k, i); double& w = S.V(l, i);
+                const double a0 = u, b0 = w;
+                u = a0 * c - b0 * s; w = a0 * s + b0 * c;
+            }
+            if (i != k && i != l) {                // the upper-triangle elements that pair i with k and with l
+                double& u = S.A(min(i, k), max(i, k)); double& w = S.A(min(i, l), max(i, l));
+                const double a0 = u, b0 = w;
+                u = a0 * c - b0 * s; w = a0 * s + b0 * c;
+            }
         }
+        if (k < N - 1) indR = nib_set(indR, k, row_arg(k));
+        if (k > 0) indC = nib_set(indC, k, col_arg(k));
+        if (l < N - 1) indR = nib_set(indR, l, row_arg(l));
+        if (l > 0) indC = nib_set(indC, l, col_arg(l));
     }
+}
+
+// position (row of V) that OpenCV's descending selection sort leaves LAST: the eigenvector DLT keeps
+template <int N>
+__device__ int last_after_sort(const Scratch<N>& S) {
+    u64 perm = 0;
+    for (int i = 0; i < N; ++i) perm = nib_set(perm, i, i);
     for (int k = 0; k < N - 1; ++k) {
         int m = k;
-        for (int i = k + 1; i < N; ++i) if (W[m] < W[i]) m = i;
+        for (int i = k + 1; i < N; ++i) if (S.W(m) < S.W(i)) m = i;
         if (k != m) {
-            double tw = W[m]; W[m] = W[k]; W[k] = tw;
-            for (int i = 0; i < N; ++i) { double tv = V[m * N + i]; V[m * N + i] = V[k * N + i]; V[k * N + i] = tv; }
+            const double tw = S.W(m); S.W(m) = S.W(k); S.W(k) = tw;
+            const int pm = nib_get(perm, m), pk = nib_get(perm, k);
+            perm = nib_set(nib_set(perm, m, pk), k, pm);
         }
     }
+    return nib_get(perm, N - 1);
 }
 
 // rows of the DLT system for one normalised correspondence, accumulated into the upper triangle (45 sums, row-major j <= k)
@@ -133,33 +189,38 @@ __device__ __forceinline__ void ltl_accumulate(double* acc, double X, double Y, 
         for (int k = j; k < 9; ++k) acc[o++] += Lx[j] * Lx[k] + Ly[j] * Ly[k];
 }
 
-// de-normalise the eigenvector of the smallest eigenvalue: H = inv(Hnorm_dst) * H0 * Hnorm_src, scaled to h33 = 1
-__device__ void dlt_finish(const double* tri, const double* nrm, double* H) {
-    double A[81], W[9], V[81];
-    int o = 0;
-    for (int j = 0; j < 9; ++j)
-        for (int k = j; k < 9; ++k) { A[j * 9 + k] = tri[o]; A[k * 9 + j] = tri[o]; ++o; }
-    jacobi_eig<9>(A, W, V);
-    const double* h0 = V + 72;
+// A (upper triangle filled) -> eigenvector of the smallest eigenvalue, de-normalised: H = inv(Hnorm_dst) * H0 * Hnorm_src, h33 = 1
+__device__ void dlt_finish(const Scratch<9>& S, const double* nrm, double* H) {
+    jacobi_eig<9>(S);
+    const int r8 = last_after_sort<9>(S);
+    double h0[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) h0[i] = S.V(r8, i);
     const double cMx = nrm[0], cMy = nrm[1], cmx = nrm[2], cmy = nrm[3], sMx = nrm[4], sMy = nrm[5], smx = nrm[6], smy = nrm[7];
     const double inv[9] = {1.0 / smx, 0.0, cmx, 0.0, 1.0 / smy, cmy, 0.0, 0.0, 1.0};
     const double n2[9] = {sMx, 0.0, -cMx * sMx, 0.0, sMy, -cMy * sMy, 0.0, 0.0, 1.0};
-    double T[9];
+    double T[9], R[9];
+#pragma unroll
     for (int r = 0; r < 3; ++r)
+#pragma unroll
         for (int c = 0; c < 3; ++c) T[r * 3 + c] = inv[r * 3] * h0[c] + inv[r * 3 + 1] * h0[3 + c] + inv[r * 3 + 2] * h0[6 + c];
-    double R[9];
+#pragma unroll
     for (int r = 0; r < 3; ++r)
+#pragma unroll
         for (int c = 0; c < 3; ++c) R[r * 3 + c] = T[r * 3] * n2[c] + T[r * 3 + 1] * n2[3 + c] + T[r * 3 + 2] * n2[6 + c];
     const double sc = 1.0 / R[8];
+#pragma unroll
     for (int i = 0; i < 9; ++i) H[i] = R[i] * sc;
 }
 
 // normalised DLT of exactly four correspondences on one thread; false when a coordinate has no spread
-__device__ bool dlt_four(const float4* p, double* H) {
+__device__ bool dlt_four(const Scratch<9>& S, const float4* p, double* H) {
     double cMx = 0, cMy = 0, cmx = 0, cmy = 0;
+#pragma unroll
     for (int i = 0; i < 4; ++i) { cmx += p[i].z; cmy += p[i].w; cMx += p[i].x; cMy += p[i].y; }
     cmx /= 4; cmy /= 4; cMx /= 4; cMy /= 4;
     double smx = 0, smy = 0, sMx = 0, sMy = 0;
+#pragma unroll
     for (int i = 0; i < 4; ++i) {
         smx += fabs(p[i].z - cmx); smy += fabs(p[i].w - cmy);
         sMx += fabs(p[i].x - cMx); sMy += fabs(p[i].y - cMy);
@@ -167,11 +228,18 @@ __device__ bool dlt_four(const float4* p, double* H) {
     if (fabs(smx) < DBL_EPSILON || fabs(smy) < DBL_EPSILON || fabs(sMx) < DBL_EPSILON || fabs(sMy) < DBL_EPSILON) return false;
     smx = 4 / smx; smy = 4 / smy; sMx = 4 / sMx; sMy = 4 / sMy;
     double tri[NRED];
+#pragma unroll
     for (int i = 0; i < NRED; ++i) tri[i] = 0.0;
+#pragma unroll
     for (int i = 0; i < 4; ++i)
         ltl_accumulate(tri, (p[i].x - cMx) * sMx, (p[i].y - cMy) * sMy, (p[i].z - cmx) * smx, (p[i].w - cmy) * smy);
+    int o = 0;
+#pragma unroll
+    for (int j = 0; j < 9; ++j)
+#pragma unroll
+        for (int k = j; k < 9; ++k) S.A(j, k) = tri[o++];
     const double nrm[8] = {cMx, cMy, cmx, cmy, sMx, sMy, smx, smy};
-    dlt_finish(tri, nrm, H);
+    dlt_finish(S, nrm, H);
     return true;
 }
 
@@ -271,10 +339,6 @@ __device__ __forceinline__ double lm_accumulate(double* acc, const double* h, fl
     return fmax(fabs(rx), fabs(ry));
 }
 
-struct LmState {                 // thread 0's registers/local memory across the refinement
-    double A[64], v[8], D[8], d[8], S, lam, lc, rmax;
-    int iter;
-};
 
 __device__ void unpack_normal(const double* tot, double* A, double* v) {
     int o = 0;
@@ -283,35 +347,45 @@ __device__ void unpack_normal(const double* tot, double* A, double* v) {
     for (int j = 0; j < 8; ++j) v[j] = tot[36 + j];
 }
 
-// x = A^-1 b through the eigen-decomposition (cv::solve(..., DECOMP_EIG)); optionally the diagonal of A^-1
-__device__ void eig_solve8(const double* A, const double* b, double* x, double* inv_diag) {
-    double T[64], W[8], V[64];
-    for (int i = 0; i < 64; ++i) T[i] = A[i];
-    jacobi_eig<8>(T, W, V);
+// x = (A + lam diag(D))^-1 b through the eigen-decomposition (cv::solve(..., DECOMP_EIG)); optionally the diagonal of the inverse
+__device__ void eig_solve8(const Scratch<8>& S, const double* A, double lam, const double* D, const double* b, double* x,
+                           double* inv_diag) {
+    for (int i = 0; i < 8; ++i)
+        for (int j = i; j < 8; ++j) S.A(i, j) = A[i * 8 + j] + (i == j ? lam * D[i] : 0.0);
+    jacobi_eig<8>(S);
     double y[8];
+#pragma unroll
     for (int i = 0; i < 8; ++i) {
-        double s = 0;
-        for (int j = 0; j < 8; ++j) s += V[i * 8 + j] * b[j];
-        y[i] = fabs(W[i]) > DBL_EPSILON ? s / W[i] : 0.0;
+        double t = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t += S.V(i, j) * b[j];
+        const double w = S.W(i);
+        y[i] = fabs(w) > DBL_EPSILON ? t / w : 0.0;
     }
-    for (int j = 0; j < 8; ++j) {
-        double s = 0;
-        for (int i = 0; i < 8; ++i) s += V[i * 8 + j] * y[i];
-        x[j] = s;
-    }
+    if (x)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            double t = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) t += S.V(i, j) * y[i];
+            x[j] = t;
+        }
     if (inv_diag)
         for (int j = 0; j < 8; ++j) {
-            double s = 0;
-            for (int i = 0; i < 8; ++i) s += fabs(W[i]) > DBL_EPSILON ? V[i * 8 + j] * V[i * 8 + j] / W[i] : 0.0;
-            inv_diag[j] = s;
+            double t = 0;
+            for (int i = 0; i < 8; ++i) { const double w = S.W(i), e = S.V(i, j); t += fabs(w) > DBL_EPSILON ? e * e / w : 0.0; }
+            inv_diag[j] = t;
         }
 }
 
-__global__ void __launch_bounds__(RT)
+__global__ void __launch_bounds__(RT, RANSAC_MINB)
 ransac_homography_kernel(const float4* __restrict__ corr, const long long* __restrict__ ptr, int num_pairs, float thr2,
                          double confidence, int max_iters, double* __restrict__ H_out, uint8_t* __restrict__ mask_out,
                          int32_t* __restrict__ inliers_out, int32_t* __restrict__ iters_out) {
     __shared__ Smem sm;
+    extern __shared__ double scratch[];          // [SCRATCH_DOUBLES][TUPLES]: one Jacobi workspace per hypothesis thread
+    const Scratch<9> S9{scratch + (threadIdx.x < TUPLES ? threadIdx.x : 0)};
+    const Scratch<8> S8{scratch};
     const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
     const long long beg = ptr[pair];
     const int count = (int)(ptr[pair + 1] - beg);
@@ -330,7 +404,7 @@ ransac_homography_kernel(const float4* __restrict__ corr, const long long* __res
         if (tid == 0) {
             float4 p[4] = {pts[0], pts[1], pts[2], pts[3]};
             double H[9];
-            sm.flag = dlt_four(p, H);
+            sm.flag = dlt_four(S9, p, H);
             for (int i = 0; i < 9; ++i) sm.bestH[i] = H[i];
         }
         __syncthreads();
@@ -373,7 +447,7 @@ ransac_homography_kernel(const float4* __restrict__ corr, const long long* __res
             if (subset_ok(p)) {
                 double H[9];
                 st = 1;
-                if (dlt_four(p, H)) {
+                if (dlt_four(S9, p, H)) {
                     st = 2;
                     for (int i = 0; i < 9; ++i) sm.Hd[tid][i] = H[i];
                     for (int i = 0; i < 8; ++i) sm.Hf[tid][i] = (float)H[i];
@@ -460,14 +534,17 @@ ransac_homography_kernel(const float4* __restrict__ corr, const long long* __res
         if (tid == 0) {
             const double nrm[8] = {cMx, cMy, cmx, cmy, sMx, sMy, smx, smy};
             double H[9];
-            dlt_finish(sm.tot, nrm, H);
+            int o = 0;
+            for (int j = 0; j < 9; ++j)
+                for (int k = j; k < 9; ++k) S9.A(j, k) = sm.tot[o++];
+            dlt_finish(S9, nrm, H);
             for (int i = 0; i < 9; ++i) sm.bestH[i] = H[i];
         }
         __syncthreads();
     }
 
     // ---------------------------------------------------------------- Levenberg-Marquardt, 8 parameters, <= 10 iterations
-    LmState lm;
+    LmState& lm = sm.lm;
     if (tid < 8) sm.xd[tid] = sm.bestH[tid];
     __syncthreads();
     for (int pass = 0;; ++pass) {
@@ -506,8 +583,8 @@ ransac_homography_kernel(const float4* __restrict__ corr, const long long* __res
                     double nu = (Sd - lm.S) / (fabs(dv) > DBL_EPSILON ? dv : 1.0) + 2.0;
                     nu = fmin(fmax(nu, 2.0), 10.0);
                     if (lm.lam == 0.0) {
-                        double dummy[8], idg[8], mxv = DBL_EPSILON;
-                        eig_solve8(lm.A, lm.v, dummy, idg);
+                        double idg[8], mxv = DBL_EPSILON;
+                        eig_solve8(S8, lm.A, 0.0, lm.D, lm.v, nullptr, idg);
                         for (int i = 0; i < 8; ++i) mxv = fmax(mxv, fabs(idg[i]));
                         lm.lam = lm.lc = 1.0 / mxv;
                         nu *= 0.5;
@@ -524,10 +601,7 @@ ransac_homography_kernel(const float4* __restrict__ corr, const long long* __res
                 proceed = lm.iter < 10 && dmax >= eps && lm.rmax >= eps;
             }
             if (proceed) {
-                double Ap[64];
-                for (int i = 0; i < 64; ++i) Ap[i] = lm.A[i];
-                for (int i = 0; i < 8; ++i) Ap[i * 9] += lm.lam * lm.D[i];
-                eig_solve8(Ap, lm.v, lm.d, nullptr);
+                eig_solve8(S8, lm.A, lm.lam, lm.D, lm.v, lm.d, nullptr);
                 for (int i = 0; i < 8; ++i) sm.xd[i] = sm.x[i] - lm.d[i];
             }
             sm.flag = proceed;
@@ -569,7 +643,10 @@ int b200m_ransac_homography(const float* corr_xyxy, const int64_t* ptr, int num_
     if (!corr_xyxy || !ptr || !H_out || !mask_out || !inliers_out) return B200M_EINVAL;
     if (!(confidence > 0.0 && confidence < 1.0)) return B200M_EINVAL;            // CV_Assert in RANSACPointSetRegistrator::run
     if ((uintptr_t)corr_xyxy & 15) return B200M_EINVAL;
-    ransac_homography_kernel<<<(unsigned)num_pairs, RT, 0, (cudaStream_t)stream>>>(
+    constexpr size_t dyn = (size_t)SCRATCH_DOUBLES * TUPLES * sizeof(double);
+    B200M_CUDA_CHECK(cudaFuncSetAttribute(ransac_homography_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn),
+                     "ransac_homography_kernel smem attribute");      // per device; microseconds
+    ransac_homography_kernel<<<(unsigned)num_pairs, RT, dyn, (cudaStream_t)stream>>>(
         (const float4*)corr_xyxy, (const long long*)ptr, num_pairs, (float)(thr * thr), confidence, max_iters, H_out, mask_out,
         inliers_out, iters_out);
     b200m_count_launch();

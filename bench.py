@@ -274,6 +274,7 @@ def single_pair_extras(torch, b, eng, pk):
                                               "speedup_over_popc_path": orb["popc"]["ms_per_pair"] / orb["tensor"]["ms_per_pair"]}
     out.update(allpairs_extras(torch, b, eng, pk))
     out.update(sfm_extras(torch, b, eng, pk))
+    out.update(ransac_extras(torch, b, eng, pk))
     return out
 
 
@@ -331,6 +332,54 @@ def sfm_extras(torch, b, eng, pk):
         "reference_python_assembly_ms_for_these_matches": cpu_us_per_match * K / 1e3,
         "note": "feature cache + all-pairs + device gather of keypoint coordinates into N x 4 correspondences; "
                 "the gather is latency-bound at this size (40 algorithmic bytes per match)"}}
+
+
+def ransac_extras(torch, b, eng, pk):
+    """RANSAC homography verification of 2048 pairs in one launch (csrc/ransac.cu), device-resident
+    correspondences; beside it cv2.findHomography (what utils.py:141 calls) on a sample of the same pairs on this host."""
+    import time
+    import numpy as np
+    verify = importlib.import_module("3dreconstruction_b200.verify")
+    P = 2048
+    corr, ptr = b.synth.homography_set(seed=6, pairs=P, n_lo=200, n_hi=4000, inl_lo=0.3, inl_hi=0.9)
+    dc, dp = eng.to_device(corr), eng.to_device(ptr)
+    run = lambda: verify.verify_pairs_device(eng, dc, dp, 4.0, 0.99, 2000)        # noqa: E731
+    for _ in range(3):
+        v = run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(5):
+        v = run()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    iters = v.iters.cpu().numpy()
+    inl = v.inliers.cpu().numpy()
+    mask = v.mask.cpu().numpy()
+    out = {"pairs": P, "matches": int(ptr[-1]), "ms_per_launch": ms, "pairs_per_s": P / (ms / 1e3),
+           "ransac_iterations_total": int(iters.sum()), "hypotheses_per_s": float(iters.sum()) / (ms / 1e3),
+           "point_model_tests_per_s": float((iters.astype(np.float64) * np.diff(ptr)).sum()) / (ms / 1e3),
+           "pairs_with_model": int((inl >= 0).sum()),
+           "note": "one CTA per pair; cv2's own random sequence replayed (64 tuples per round), fp64 DLT/Jacobi per hypothesis, float32 "
+                   "inlier test, inlier refit + Levenberg-Marquardt, mask of the refined H; threshold 4 px, confidence 0.99, maxIters 2000"}
+    try:
+        import cv2
+        sample = list(range(0, P, P // 64))
+        same = 0
+        t0 = time.perf_counter()
+        res = []
+        for p in sample:
+            c = corr[ptr[p]:ptr[p + 1]]
+            res.append(cv2.findHomography(c[:, :2].reshape(-1, 1, 2), c[:, 2:].reshape(-1, 1, 2), cv2.RANSAC, 4.0,
+                                          confidence=0.99, maxIters=2000))
+        t = time.perf_counter() - t0
+        for p, (Hc, mc) in zip(sample, res):
+            same += Hc is not None and np.array_equal(mc.ravel(), mask[ptr[p]:ptr[p + 1]])
+        out["cpu_cv2_findHomography"] = {"sample_pairs": len(sample), "pairs_per_s": len(sample) / t, "threads": cv2.getNumThreads(),
+                                         "masks_identical_to_gpu": int(same), "speedup": out["pairs_per_s"] / (len(sample) / t)}
+    except ImportError:
+        out["cpu_cv2_findHomography"] = None
+    return {"ransac_homography_2048_pairs": out}
 
 
 def superpoint_set_gpu(torch, device, images, n, d=256, seed=2, pool=8192, shared=0.5, sigma=0.05):

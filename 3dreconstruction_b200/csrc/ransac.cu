@@ -34,6 +34,7 @@ namespace {
 constexpr int RT = 128;          // threads per CTA
 constexpr int NW = RT / 32;
 constexpr int TUPLES = RANSAC_TUPLES;   // 4-tuples drawn per round
+constexpr int GMAX = 512;        // tuples drawn per batch
 constexpr int TS = TUPLES;       // stride between the elements of one thread's scratch matrix
 constexpr int NRED = 45;         // sums per block reduction: upper triangle of 9x9, or 36 + 8 + 1 for the LM normal equations
 
@@ -47,9 +48,12 @@ struct Smem {
     double tot[NRED + 1];
     double Hd[TUPLES][9];        // models of the round
     float Hf[TUPLES][8];
-    int tup[TUPLES][4];
+    alignas(16) int tup[GMAX][4];   // tuples of the batch
+    short hlist[GMAX];           // the ones that passed checkSubset, in order
+    uint8_t pass[GMAX];
+    int npass;
     int cnt[TUPLES];
-    int state[TUPLES];           // 0 = tuple failed checkSubset, 1 = hypothesis without a model, 2 = hypothesis with a model
+    int state[TUPLES];           // 1 = hypothesis without a model (no spread), 2 = hypothesis with a model
     double bestH[9];
     double x[8], xd[8];
     int flag, best_cnt, iters_run, n_inl;
@@ -416,84 +420,124 @@ ransac_homography_kernel(const float4* __restrict__ corr, const long long* __res
     }
 
     // ---------------------------------------------------------------- hypothesis loop
+    // Batches of tuples (128 in the first, GMAX afterwards: easy pairs stop within the first few hypotheses); only the
+    // tuples that pass checkSubset (often ~10 %) become hypotheses, compacted in order into sub-rounds of TUPLES models.
     int niters = max(max_iters, 1), iter = 0, max_good = 0, fails = 0;      // thread 0 only
     if (tid == 0) { sm.rng = 0xFFFFFFFFFFFFFFFFull; sm.flag = 0; sm.best_cnt = 0; }
+    const u32 recip = 0xFFFFFFFFu / (u32)count;
+    int G = 128;
     __syncthreads();
     for (;;) {
         if (tid == 0) {
             u64 s = sm.rng;
-            for (int t = 0; t < TUPLES; ++t) {
+#pragma unroll 1
+            for (int t = 0; t < G; ++t) {
                 int id[4];
+#pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     int v;
                     bool dup;
                     do {
-                        v = (int)(rng_next(s) % (u32)count);
+                        const u32 x = rng_next(s);
+                        u32 r = x - __umulhi(x, recip) * (u32)count;       // x % count: the estimate is low by at most 2
+                        while (r >= (u32)count) r -= (u32)count;
+                        v = (int)r;
                         dup = false;
-                        for (int j = 0; j < i; ++j) dup |= id[j] == v;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) dup |= j < i && id[j] == v;
                     } while (dup);
                     id[i] = v;
                 }
-                for (int i = 0; i < 4; ++i) sm.tup[t][i] = id[i];
+                *(int4*)sm.tup[t] = make_int4(id[0], id[1], id[2], id[3]);
             }
             sm.rng = s;
         }
-        if (tid < TUPLES) sm.cnt[tid] = 0;
         __syncthreads();
-        if (tid < TUPLES) {
+        for (int t = tid; t < G; t += RT) {
             float4 p[4];
-            for (int i = 0; i < 4; ++i) p[i] = __ldg(pts + sm.tup[tid][i]);
-            int st = 0;
-            if (subset_ok(p)) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) p[i] = __ldg(pts + sm.tup[t][i]);
+            sm.pass[t] = subset_ok(p);
+        }
+        __syncthreads();
+        if (tid < 32) {                         // ordered compaction: hlist[k] = k-th passing tuple of the batch
+            int base = 0;
+            for (int c = 0; c < G; c += 32) {
+                const bool f = sm.pass[c + lane];
+                const u32 bal = __ballot_sync(0xffffffffu, f);
+                if (f) sm.hlist[base + __popc(bal & ((1u << lane) - 1u))] = (short)(c + lane);
+                base += __popc(bal);
+            }
+            if (lane == 0) sm.npass = base;
+        }
+        __syncthreads();
+        const int npass = sm.npass;
+        int prev_tuple = -1;                    // thread 0: last tuple of the batch already replayed
+        for (int h0 = 0; h0 < npass; h0 += TUPLES) {
+            const int nh = min(TUPLES, npass - h0);
+            if (tid < TUPLES) sm.cnt[tid] = 0;
+            if (tid < nh) {
+                const int t = sm.hlist[h0 + tid];
+                float4 p[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) p[i] = __ldg(pts + sm.tup[t][i]);
                 double H[9];
-                st = 1;
+                int st = 1;
                 if (dlt_four(S9, p, H)) {
                     st = 2;
+#pragma unroll
                     for (int i = 0; i < 9; ++i) sm.Hd[tid][i] = H[i];
+#pragma unroll
                     for (int i = 0; i < 8; ++i) sm.Hf[tid][i] = (float)H[i];
                 }
+                sm.state[tid] = st;
             }
-            sm.state[tid] = st;
-        }
-        __syncthreads();
-        for (int i0 = 0; i0 < count; i0 += RT) {
-            const int i = i0 + tid;
-            const bool in = i < count;
-            const float4 p = in ? __ldg(pts + i) : make_float4(0, 0, 0, 0);
-            for (int t = 0; t < TUPLES; ++t) {
-                if (sm.state[t] != 2) continue;
-                const bool good = in && reproj_err(sm.Hf[t], p) <= thr2;
-                const int c = __popc(__ballot_sync(0xffffffffu, good));
-                if (lane == 0 && c) atomicAdd(&sm.cnt[t], c);
-            }
-        }
-        __syncthreads();
-        if (tid == 0) {
-            int done = 0;
-            for (int t = 0; t < TUPLES && !done; ++t) {
-                if (iter >= niters) { done = 1; break; }
-                if (sm.state[t] == 0) {
-                    if (++fails >= 10000) done = iter == 0 ? 2 : 1;       // getSubset gave up
-                    continue;
+            __syncthreads();
+            for (int i0 = 0; i0 < count; i0 += RT) {
+                const int i = i0 + tid;
+                const bool in = i < count;
+                const float4 p = in ? __ldg(pts + i) : make_float4(0, 0, 0, 0);
+                for (int h = 0; h < nh; ++h) {
+                    if (sm.state[h] != 2) continue;
+                    const bool good = in && reproj_err(sm.Hf[h], p) <= thr2;
+                    const int c = __popc(__ballot_sync(0xffffffffu, good));
+                    if (lane == 0 && c) atomicAdd(&sm.cnt[h], c);
                 }
-                fails = 0;
-                if (sm.state[t] == 2) {
-                    const int good = sm.cnt[t];
-                    if (good > max(max_good, 3)) {
-                        max_good = good;
-                        for (int i = 0; i < 9; ++i) sm.bestH[i] = sm.Hd[t][i];
-                        niters = update_num_iters(confidence, (double)(count - good) / count, niters);
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int done = 0;
+                for (int h = 0; h < nh && !done; ++h) {
+                    if (iter >= niters) { done = 1; break; }
+                    const int t = sm.hlist[h0 + h];
+                    fails += t - prev_tuple - 1;                 // tuples that failed checkSubset before this one
+                    prev_tuple = t;
+                    if (fails >= 10000) { done = iter == 0 ? 2 : 1; break; }     // getSubset gave up
+                    fails = 0;
+                    if (sm.state[h] == 2) {
+                        const int good = sm.cnt[h];
+                        if (good > max(max_good, 3)) {
+                            max_good = good;
+                            for (int i = 0; i < 9; ++i) sm.bestH[i] = sm.Hd[h][i];
+                            niters = update_num_iters(confidence, (double)(count - good) / count, niters);
+                        }
                     }
+                    ++iter;
                 }
-                ++iter;
+                if (!done && iter >= niters) done = 1;
+                sm.flag = done;
             }
-            if (!done && iter >= niters) done = 1;
-            sm.flag = done;
-            sm.best_cnt = max_good;
-            sm.iters_run = iter;
+            __syncthreads();
+            if (sm.flag) break;
         }
+        if (tid == 0 && !sm.flag) {             // the batch's trailing failures
+            fails += G - 1 - prev_tuple;
+            if (fails >= 10000) sm.flag = iter == 0 ? 2 : 1;
+        }
+        if (tid == 0) { sm.best_cnt = max_good; sm.iters_run = iter; }
         __syncthreads();
         if (sm.flag) break;
+        G = GMAX;
     }
     if (sm.flag == 2 || sm.best_cnt == 0) { fail(); return; }
 

@@ -138,6 +138,23 @@ class SfMMatches:
                                  self.distance[s].astype(np.float64).tolist())]
         return c.MatchData(matches=ms, method=self.method, score_type=dist_t)
 
+    # ---- N3: geometric verification (FeatureProcessingPipeline._apply_filtering, pipeline.py:289-320, for every pair at once)
+    def verify_homography(self, ransac_threshold: float = 4.0, confidence: float = 0.99, max_iters: int = 2000, engine=None):
+        """RANSAC homography per pair on the GPU (verify.verify_pairs): what `enhanced_filter_matches_with_homography`
+        (utils.py:118-153) returns for each pair's matches — mask, H, inlier count (-1: the reference's ([], None))."""
+        from . import verify
+        return verify.verify_pairs(self.correspondences, self.ptr, ransac_threshold, confidence, max_iters, engine)
+
+    def filtered(self, verification) -> "SfMMatches":
+        """The matches the reference would store in `match_data.filtered_matches` (pipeline.py:309, :322): inliers of
+        each pair's homography, order kept; pairs without a model keep nothing."""
+        keep = verification.mask.astype(bool)
+        no_model = np.repeat(verification.inliers < 0, np.diff(self.ptr))
+        keep &= ~no_model
+        ptr = np.concatenate([[0], np.cumsum(keep, dtype=np.int64)])[self.ptr]       # kept matches before each pair
+        return SfMMatches(self.names, self.sizes, self.pairs, ptr, self.query_idx[keep], self.train_idx[keep],
+                          self.distance[keep], self.correspondences[keep], self.method, self.feature_type)
+
     # ---- N4: array-native persistence
     def save(self, path) -> None:
         sizes = np.array([(-1, -1) if s is None else tuple(s) for s in self.sizes], np.int64).reshape(-1, 2)

@@ -123,3 +123,22 @@ def test_large_batch_properties(eng):
             want = ro.compute_error(corr[s, :2], corr[s, 2:], v1.H[p]) <= t
             assert np.array_equal(want.astype(np.uint8), v1.mask[s])
             assert v1.inliers[p] == int(want.sum())
+
+
+def test_sfm_matches_verification_plumbing(eng):
+    """SfMMatches.verify_homography + filtered: per pair what the reference's filter keeps (oracle), CSR re-packed."""
+    sfm = importlib.import_module("3dreconstruction_b200.sfm")
+    corr, ptr = synth.homography_set(seed=11, pairs=6, n_lo=40, n_hi=160, inl_lo=0.75, inl_hi=0.95)
+    ptr = np.concatenate([ptr, [ptr[-1]]])                       # a seventh pair without matches
+    K = int(ptr[-1])
+    m = sfm.SfMMatches([f"im{i}" for i in range(8)], [None] * 8, [(0, j + 1) for j in range(7)], ptr, np.arange(K), np.arange(K),
+                       np.zeros(K, np.float32), corr)
+    v = m.verify_homography(4.0, 0.99, 2000, engine=eng)
+    f = m.filtered(v)
+    for p in range(7):
+        s = m.pair_slice(p)
+        kept, H = ro.reference_filter(corr[s, :2], corr[s, 2:], 4.0, 0.99, 2000)
+        assert np.array_equal(f.query_idx[f.pair_slice(p)] - s.start, kept)
+        assert (H is None) == (v.homography(p) is None)
+        if H is not None:
+            assert h_close(v.H[p], H)

@@ -81,3 +81,19 @@ def test_keypoints_xy_accepts_cv2_keypoints_and_arrays():
     xy = sfm.keypoints_xy([KP(1.5, 2.0), KP(3.0, 4.25)])
     assert xy.dtype == np.float32 and xy.tolist() == [[1.5, 2.0], [3.0, 4.25]]
     assert np.array_equal(sfm.keypoints_xy(np.array([[1, 2], [3, 4]], np.float64)), np.array([[1, 2], [3, 4]], np.float32))
+
+
+def test_filtered_by_verification_host_logic():
+    """SfMMatches.filtered (N3 hand-off): inliers kept in order, pairs without a model emptied, empty pairs stay empty."""
+    verify = pkg("verify")
+    ptr = np.array([0, 3, 3, 8, 10, 10], np.int64)
+    K = 10
+    m = sfm.SfMMatches(list("abcdef"), [None] * 6, [(0, 1), (0, 2), (0, 3), (0, 4), (0, 5)], ptr, np.arange(K), np.arange(K) + 100,
+                       np.arange(K, dtype=np.float32), np.arange(4 * K).reshape(K, 4))
+    mask = np.array([1, 0, 1, 1, 1, 0, 0, 1, 1, 1], np.uint8)
+    v = verify.Verification(ptr, np.zeros((5, 3, 3)), mask, np.array([2, -1, 3, -1, -1], np.int32), np.zeros(5, np.int32))
+    f = m.filtered(v)
+    assert f.ptr.tolist() == [0, 2, 2, 5, 5, 5]
+    assert f.query_idx.tolist() == [0, 2, 3, 4, 7] and f.train_idx.tolist() == [100, 102, 103, 104, 107]
+    assert np.array_equal(f.correspondences, m.correspondences[[0, 2, 3, 4, 7]])
+    assert v.kept(2).tolist() == [0, 1, 4] and v.kept(1).tolist() == [] and v.homography(3) is None

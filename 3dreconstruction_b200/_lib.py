@@ -14,14 +14,14 @@ SO_PATH = os.environ.get("B200MATCH_SO") or os.path.join(HERE, "libb200match.so"
 
 OK, EINVAL, EWORKSPACE, ECUDA, ENODEVICE, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
 MODE_RATIO, MODE_CROSS, MODE_NN = 0, 1, 2
-KIND_HAMMING, KIND_L2_I8, KIND_L2_F32, KIND_HAMMING_TC, KIND_HAMMING_FP4 = 0, 1, 2, 3, 4
+KIND_HAMMING, KIND_L2_I8, KIND_L2_F32, KIND_HAMMING_TC, KIND_HAMMING_FP4, KIND_L2_F16C = 0, 1, 2, 3, 4, 5
 
 EXPORTS = ["b200m_version", "b200m_error_string", "b200m_last_cuda_error", "b200m_device_info",
            "b200m_prep_l2_i8", "b200m_prep_l2_f32", "b200m_workspace_bytes", "b200m_match_pairs",
            "b200m_knn2_pairs", "b200m_launch_count", "b200m_reset_launch_count", "b200m_match_pairs_csr",
            "b200m_timing_enable", "b200m_timing_collect", "b200m_f32_stats", "b200m_l2_i8_aux_bytes",
            "b200m_l2_i8_aux_init", "b200m_prep_l2_i8_rows", "b200m_hamming_tc_width", "b200m_prep_hamming_tc",
-           "b200m_gather_correspondences", "b200m_hamming_fp4_width", "b200m_prep_hamming_fp4", "b200m_ransac_homography"]
+           "b200m_gather_correspondences", "b200m_hamming_fp4_width", "b200m_prep_hamming_fp4", "b200m_ransac_homography", "b200m_l2_f16_aux_bytes", "b200m_prep_l2_f16"]
 
 
 class Pair(ctypes.Structure):
@@ -63,6 +63,8 @@ def load() -> ctypes.CDLL:
     lib.b200m_hamming_fp4_width.argtypes = [i32, ctypes.POINTER(i32)]
     lib.b200m_prep_hamming_fp4.argtypes = [vp, i64, i32, vp, i32, vp]
     lib.b200m_gather_correspondences.argtypes = [vp, i64, vp, vp, vp, i32, vp, vp, vp, vp]
+    lib.b200m_l2_f16_aux_bytes.argtypes = [i64, i32, ctypes.POINTER(ctypes.c_size_t)]
+    lib.b200m_prep_l2_f16.argtypes = [vp, i64, i32, vp, vp]
     lib.b200m_ransac_homography.argtypes = [vp, vp, i32, dbl, dbl, i32, vp, vp, vp, vp, vp]
     lib.b200m_workspace_bytes.argtypes = [i32, i32, i32, i64, i64, i32, i32, i32, ctypes.POINTER(ctypes.c_size_t)]
     lib.b200m_match_pairs.argtypes = [i32, vp, vp, i64, vp, vp, i64, i32, ctypes.POINTER(Pair), i32, i32, dbl,

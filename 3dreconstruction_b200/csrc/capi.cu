@@ -65,7 +65,7 @@ static void make_plan(MatchPlan& pl, char* base, int kind, int mode, int num_pai
     pl.sortbuf = (u64*)(base + off);   off = align_up(off + sizeof(u64) * (size_t)total_pad, 256);
     pl.tbest = (int32_t*)(base + off); off = align_up(off + sizeof(int32_t) * (size_t)total_n, 256);
     pl.cand = nullptr; pl.pmax = nullptr;
-    if (kind == B200M_KIND_L2_F32) {
+    if (kind == B200M_KIND_L2_F32 || kind == B200M_KIND_L2_F16C) {
         long long rows = need_bwd && total_m > total_n ? total_m : total_n;
         pl.cand = (void*)(base + off);  off = align_up(off + (8ull * B200M_F32_CAND + 4ull) * 2 * (size_t)S * rows + 8ull * rows + 64, 256);
         pl.pmax = (float*)(base + off); off = align_up(off + sizeof(float) * (size_t)num_pairs, 256);
@@ -161,7 +161,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
     if (num_pairs < 0 || D <= 0 || (num_pairs > 0 && (!pairs_host || !q_desc || !t_desc || !workspace)))
         return B200M_EINVAL;
     if (kind != B200M_KIND_HAMMING && kind != B200M_KIND_L2_I8 && kind != B200M_KIND_L2_F32 && kind != B200M_KIND_HAMMING_TC &&
-        kind != B200M_KIND_HAMMING_FP4)
+        kind != B200M_KIND_HAMMING_FP4 && kind != B200M_KIND_L2_F16C)
         return B200M_EINVAL;
     if (kind != B200M_KIND_HAMMING && (!q_norm || !t_norm) && num_pairs > 0) return B200M_EINVAL;
     int htc_pad = 0;                                  // HAMMING_TC: width of the +-1 stores
@@ -236,7 +236,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         else
             rc = launch_l2_f32_top2((const float*)q_desc, (const float*)q_norm, q_rows, (const float*)t_desc,
                                     (const float*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
-                                    back, need2, pl.cand, pl.pmax, out, rows, st);
+                                    back, need2, pl.cand, pl.pmax, out, rows, st, kind == B200M_KIND_L2_F16C);
         if (e1) cudaEventRecord(e1, st);
         if (rc != B200M_OK) return rc;
     }
@@ -273,7 +273,8 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D,
                       mode == B200M_MODE_RATIO ? (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows)) : nullptr};
     // CSR mode counts survivors in finalize (into out_count), scans them into tight offsets, then emits.
-    const int tail_kind = kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING : kind;   // integer bit counts either way
+    const int tail_kind = kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING    // integer bit counts either way
+                          : kind == B200M_KIND_L2_F16C ? B200M_KIND_L2_F32 : kind;                               // exact fp32 d^2 bits either way
     rc = launch_finalize(tail_kind, mode, ratio, pl, num_pairs, max_n, out_ptr ? out_count : nullptr, rf, st);
     if (rc != B200M_OK) return rc;
     if (out_ptr) {
@@ -317,7 +318,8 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
     RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr};
     if (kind == B200M_KIND_L2_I8)
         rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D, nullptr};
-    return launch_knn2_emit(kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING : kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
+    return launch_knn2_emit(kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING
+                            : kind == B200M_KIND_L2_F16C ? B200M_KIND_L2_F32 : kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
 }
 
 }  // extern "C"

@@ -38,6 +38,14 @@ __host__ __device__ inline size_t b200m_aux_info_off(long long rows) {
     return b200m_aux_fold_off(rows) + ((size_t)rows * B200M_FOLD_K + 255) / 256 * 256;
 }
 __host__ __device__ inline size_t b200m_aux_bytes(long long rows) { return b200m_aux_info_off(rows) + 256; }
+// Auxiliary block of b200m_prep_l2_f16 (kind L2_F16C): float norms[rows] | __half copy[rows][Dh] at half_off |
+// float info[64] at info_off: [0] scale s (a power of two, max |x| * s <= 1), [1] 1 / s, [2] max |x|.  Dh = D rounded up to 64.
+__host__ __device__ inline int b200m_f16_width(int D) { return (D + 63) / 64 * 64; }
+__host__ __device__ inline size_t b200m_f16_half_off(long long rows) { return ((size_t)rows * 4 + 255) / 256 * 256; }
+__host__ __device__ inline size_t b200m_f16_info_off(long long rows, int D) {
+    return b200m_f16_half_off(rows) + ((size_t)rows * b200m_f16_width(D) * 2 + 255) / 256 * 256;
+}
+__host__ __device__ inline size_t b200m_f16_aux_bytes(long long rows, int D) { return b200m_f16_info_off(rows, D) + 256; }
 #define B200M_HTC_CHUNK 16   // columns per key chunk of the tensor-core Hamming kernel (hamming_tc.cu); resolve recomputes two chunks per row
 #define B200M_F32_CAND 32    // TF32 candidate list capacity per (query row, column half, column split) (l2_f32.cu)
 
@@ -104,7 +112,7 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
 int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
                        const float* t_desc, const float* t_norm, int64_t t_rows, int D,
                        const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
-                       bool need2, void* cand_ws, float* pmax, Top2* out, long long total_rows, cudaStream_t st);
+                       bool need2, void* cand_ws, float* pmax, Top2* out, long long total_rows, cudaStream_t st, bool h16 = false);
 int b200m_f32_stats_read(unsigned long long out[2], bool reset);
 // L2_I8 descriptors for the fused exact runner-up refinement (null for the other kinds)
 struct RefineI8 {

@@ -35,6 +35,30 @@ constexpr int EPI_THREADS = 256;
 constexpr int THREADS = EPI_THREADS + 64;
 constexpr int KC = B200M_F32_CAND; // list capacity per (row, column half, column split)
 constexpr float C_EPS = 0.0042f;
+// fp16 candidates (kind L2_F16C): operands ROUNDED to 11 significant bits (relative 2^-11 each): |error of a.b| <=
+// (2^-10 + 2^-22) ||a|| ||b||, d^2 carries twice that = 0.001953; C_H16 adds the same 7.5 % margin for the fp32
+// accumulation and the norms.  Scaled elements below 2^-14 are fp16 subnormals with ABSOLUTE error <= 2^-25: the dot
+// product moves by at most 2^-25 sqrt(Dh) (||b|| / s_a + ||a|| / s_b) in unscaled units (Cauchy-Schwarz on the 1-norm),
+// d^2 by twice that -- the `sub` term of the window.
+constexpr float C_H16 = 0.0021f;
+
+struct Window {                 // eps(a) = c * ||a|| * bmax + sub_b * bmax + sub_a * ||a||;  window = 2 eps
+    float c, sub_a, sub_b;
+    __device__ __forceinline__ float operator()(float a_norm2, float bmax) const {
+        const float an = sqrtf(a_norm2);
+        return 2.0f * (c * an * bmax + sub_b * bmax + sub_a * an);
+    }
+};
+// q_info / t_info: info words of the two stores' aux blocks (scale, 1 / scale, max |x|), null for the TF32 kind
+__device__ __forceinline__ Window make_window(const float* q_info, const float* t_info, int Dh) {
+    Window w;
+    if (!q_info) { w.c = C_EPS; w.sub_a = 0.0f; w.sub_b = 0.0f; return w; }
+    const float g = 5.9604645e-8f * sqrtf((float)Dh);        // 2 * 2^-25 sqrt(Dh)
+    w.c = C_H16;
+    w.sub_b = g * __ldg(q_info + 1);                          // ||b|| / s_a
+    w.sub_a = g * __ldg(t_info + 1);                          // ||a|| / s_b
+    return w;
+}
 constexpr float BIG_F = 3.0e38f;   // ||b||^2 of a masked column: never appended, never a minimum that matters
 
 struct Item {
@@ -94,12 +118,16 @@ __host__ __device__ constexpr size_t smem_bytes(int nkb) {
            (8 + 2 * NB) * 8 + 16;
 }
 
+// H16: the tensor maps address the scaled fp16 copies (K block = 64 halves), the MMA is kind::f16 and the accumulator
+// is s_q s_t a.b; everything else (pipeline, epilogue, lists) is shared with the TF32 kind.
+template <bool H16>
 __global__ void __launch_bounds__(THREADS, 1)
 l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                    const float* __restrict__ t_norm, const DevPair* __restrict__ pairs, long long total_items,
                    int tiles_max, int S, int backward, int nkb, const float* __restrict__ q_norm,
                    const float* __restrict__ pmax, float2* __restrict__ cand, int* __restrict__ cand_cnt,
-                   long long total_rows) {
+                   long long total_rows, const float* __restrict__ q_info, const float* __restrict__ t_info) {
+    constexpr int KB_ELEMS = H16 ? KB_BYTES / 2 : KB_BYTES / 4;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const SmemLayout sm = carve(smem, nkb);
@@ -131,7 +159,7 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
                 for (int kb = 0; kb < nkb; ++kb)
                     sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
-                                       kb * (KB_BYTES / 4), it.q_off + it.r0);
+                                       kb * KB_ELEMS, it.q_off + it.r0);
             }
             __syncwarp();
             if (++ab == (uint32_t)nabuf) { ab = 0; a_par ^= 1; }
@@ -140,7 +168,7 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     sm100::mbar_wait(&sm.b_empty[bs], b_par);
                     if (sm100::elect_one()) {
                         sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
-                        sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * (KB_BYTES / 4),
+                        sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * KB_ELEMS,
                                            it.t_off + c0);
                     }
                     __syncwarp();
@@ -152,7 +180,8 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         // ===================== MMA issuer: lockstep warp, one elected lane issues =====================
         // (a single thread with per-tile modulo arithmetic and 64-bit descriptor maths was the bottleneck of
         // the int8 kernel; descriptors here are a constant high word and a running 32-bit low word)
-        constexpr uint32_t idesc = sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
+        constexpr uint32_t idesc = H16 ? sm100::make_idesc(/*F32*/ 1, /*f16*/ 0, /*f16*/ 0, TM, TN)
+                                       : sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
         const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
@@ -172,9 +201,14 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     if (sm100::elect_one()) {
                         const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
 #pragma unroll
-                        for (int k = 0; k < KB_BYTES / 32; ++k)      // UMMA K = 8 tf32 = 32 bytes; +2 = 32 B >> 4
-                            sm100::mma_tf32(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                            idesc, (kb | k) ? 1u : 0u);
+                        for (int k = 0; k < KB_BYTES / 32; ++k) {    // UMMA K = 8 tf32 or 16 halves = 32 bytes; +2 = 32 B >> 4
+                            if constexpr (H16)
+                                sm100::mma_f16(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                               idesc, (kb | k) ? 1u : 0u);
+                            else
+                                sm100::mma_tf32(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                                idesc, (kb | k) ? 1u : 0u);
+                        }
                         sm100::mma_commit(&sm.b_empty[bs]);
                         if (kb == nkb - 1) sm100::mma_commit(&sm.acc_full[as]);
                     }
@@ -194,6 +228,8 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         const int row_in_tile = quarter * 32 + lane;
         constexpr int HC = TN / 2;                 // columns per half
         uint32_t acc_cnt = 0;
+        const Window window = make_window(H16 ? q_info : nullptr, t_info, nkb * KB_ELEMS);
+        const float neg2 = H16 ? -2.0f * __ldg(q_info + 1) * __ldg(t_info + 1) : -2.0f;     // -2 / (s_q s_t), exact
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward);
             if (!it.valid) continue;
@@ -201,16 +237,19 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             const int row = it.r0 + row_in_tile;
             const bool row_ok = row < it.n;
             float v1 = CUDART_INF_F, v2 = CUDART_INF_F;
-            const float win = row_ok ? 2.0f * C_EPS * sqrtf(__ldg(q_norm + it.q_off + (row_ok ? row : 0))) * __ldg(pmax + it.pair)
-                                     : -CUDART_INF_F;
+            const float win = row_ok ? window(__ldg(q_norm + it.q_off + (row_ok ? row : 0)), __ldg(pmax + it.pair)) : -CUDART_INF_F;
             const long long lrow = (long long)(it.split * 2 + half) * total_rows + it.row_base + (row_ok ? row : 0);
             float2* list = cand + lrow * KC;
             int cnt = 0;
+            // ||b||^2 of the NEXT tile's columns is fetched while this tile is reduced (the load's latency used to sit in
+            // front of every tile: 12 % of the stall samples at the barrier below)
+            float nb = e < TN ? (it.c_begin + e < it.c_end ? __ldg(t_norm + it.t_off + it.c_begin + e) : BIG_F) : 0.0f;
             for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                 const uint32_t as = acc_cnt & 1;
                 if (e < TN) {
-                    int col = c0 + e;
-                    sm.cb[as * TN + e] = col < it.c_end ? __ldg(t_norm + it.t_off + col) : BIG_F;
+                    sm.cb[as * TN + e] = nb;
+                    const int col = c0 + TN + e;
+                    nb = col < it.c_end ? __ldg(t_norm + it.t_off + col) : BIG_F;
                 }
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
@@ -230,21 +269,27 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     float h0 = CUDART_INF_F, h1 = CUDART_INF_F;
 #pragma unroll
                     for (int i = 0; i < 32; ++i) {
-                        ev[i] = fmaf(-2.0f, __uint_as_float(acc[ch][i]), cbv[ch * 32 + i]);
+                        ev[i] = fmaf(neg2, __uint_as_float(acc[ch][i]), cbv[ch * 32 + i]);
                         if (i < 16) h0 = fminf(h0, ev[i]); else h1 = fminf(h1, ev[i]);
                     }
                     // top-2 of group minima first (the tighter, still valid bound), then the append test
                     v2 = fminf(v2, fmaxf(v1, h0)); v1 = fminf(v1, h0);
                     v2 = fminf(v2, fmaxf(v1, h1)); v1 = fminf(v1, h1);
-                    const float tau = v2 + win;
-                    if (fminf(h0, h1) <= tau) {
-                        const int colb = c0 + half * HC + ch * 32;
+                    const float tau = fminf(v2 + win, BIG_F * 0.5f);      // masked columns (||b||^2 = BIG_F) never pass
+                    const int colb = c0 + half * HC + ch * 32;
+                    // per 16-column group, and only where the group's minimum passes; the body is predicated, not
+                    // branched (one lane's row passing makes the whole warp walk the group)
 #pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (ev[i] <= tau && ev[i] < BIG_F * 0.5f) {
-                                if (cnt < KC) list[cnt] = make_float2(ev[i], __int_as_float(colb + i));
-                                ++cnt;
+                    for (int g = 0; g < 2; ++g) {
+                        if ((g ? h1 : h0) <= tau) {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) {
+                                const float x = ev[g * 16 + i];
+                                const bool pass = x <= tau;
+                                if (pass & (cnt < KC)) list[cnt] = make_float2(x, __int_as_float(colb + g * 16 + i));
+                                cnt += pass;
                             }
+                        }
                     }
                 }
                 ++acc_cnt;
@@ -285,7 +330,8 @@ refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, in
                   const float2* __restrict__ cand, const int* __restrict__ cand_cnt, long long total_rows, int S,
                   const float* __restrict__ q_desc,
                   const float* __restrict__ q_norm, const float* __restrict__ t_desc, int D,
-                  const float* __restrict__ pmax, Top2* __restrict__ out, u64* __restrict__ fbq, int* __restrict__ fb_count) {
+                  const float* __restrict__ pmax, Top2* __restrict__ out, u64* __restrict__ fbq, int* __restrict__ fb_count,
+                  const float* __restrict__ q_info, const float* __restrict__ t_info, int Dh) {
     const int lane = threadIdx.x & 31;
     const int p = blockIdx.x / blocks_per_pair;
     const int i = (blockIdx.x - p * blocks_per_pair) * 8 + (threadIdx.x >> 5);
@@ -338,7 +384,7 @@ refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, in
     u64 k1 = B200M_SENTINEL, k2 = B200M_SENTINEL;
     const bool fallback = overflow;
     if (m > 0 && !fallback) {
-        const float win = 2.0f * C_EPS * sqrtf(__ldg(q_norm + q_off + i)) * __ldg(pmax + p);
+        const float win = make_window(q_info, t_info, Dh)(__ldg(q_norm + q_off + i), __ldg(pmax + p));
         const float bound = (need2 ? m2 : m1) + win;       // m2 == +inf with a single column: everything passes
         for (int l = 0; l < nlist; ++l) {
             const long long lrow = (long long)l * total_rows + row;
@@ -448,10 +494,11 @@ int b200m_f32_stats_read(unsigned long long out[2], bool reset) {
 int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows, const float* t_desc,
                        const float* t_norm, int64_t t_rows, int D, const DevPair* pairs, int num_pairs, int max_n,
                        int max_m, int S, bool backward, bool need2, void* cand_ws, float* pmax, Top2* out,
-                       long long total_rows, cudaStream_t st) {
+                       long long total_rows, cudaStream_t st, bool h16) {
     if (D % (KB_BYTES / 4) != 0) return B200M_EINVAL;
-    const int nkb = D / (KB_BYTES / 4);
-    if (nkb > MAX_NKB) return B200M_EUNSUPPORTED;       // query tile must stay resident in shared memory
+    const int Dh = h16 ? b200m_f16_width(D) : D;        // width of the operand rows the tensor cores read
+    const int nkb = h16 ? Dh / (KB_BYTES / 2) : D / (KB_BYTES / 4);
+    if (D > 256 || nkb > MAX_NKB) return B200M_EUNSUPPORTED;       // query tile must stay resident in shared memory
     if (!cand_ws || !pmax) return B200M_EINVAL;
     if (backward) {
         const float* d = q_desc; q_desc = t_desc; t_desc = d;
@@ -459,15 +506,30 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
         int64_t r = q_rows; q_rows = t_rows; t_rows = r;
         int mx = max_n; max_n = max_m; max_m = mx;
     }
+    // L2_F16C: q_norm / t_norm are aux blocks (norms first, then the fp16 copy and the info words)
+    const float* q_info = h16 ? (const float*)((const char*)q_norm + b200m_f16_info_off(q_rows, D)) : nullptr;
+    const float* t_info = h16 ? (const float*)((const char*)t_norm + b200m_f16_info_off(t_rows, D)) : nullptr;
     CUtensorMap tq, tt;
-    int rc = b200m_make_tmap_2d(&tq, q_desc, (uint64_t)q_rows, (uint64_t)D * 4, TM, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
-    if (rc != B200M_OK) return rc;
-    rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D * 4, TN, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
+    int rc;
+    if (h16) {
+        if (((uintptr_t)q_norm & 255) || ((uintptr_t)t_norm & 255)) return B200M_EINVAL;
+        rc = b200m_make_tmap_2d(&tq, (const char*)q_norm + b200m_f16_half_off(q_rows), (uint64_t)q_rows, (uint64_t)Dh * 2, TM,
+                                CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2);
+        if (rc != B200M_OK) return rc;
+        rc = b200m_make_tmap_2d(&tt, (const char*)t_norm + b200m_f16_half_off(t_rows), (uint64_t)t_rows, (uint64_t)Dh * 2, TN,
+                                CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2);
+    } else {
+        rc = b200m_make_tmap_2d(&tq, q_desc, (uint64_t)q_rows, (uint64_t)D * 4, TM, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
+        if (rc != B200M_OK) return rc;
+        rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D * 4, TN, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
+    }
     if (rc != B200M_OK) return rc;
     static bool attr_set = false;
     if (!attr_set) {
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(MAX_NKB)), "l2_f16c smem attr");
         attr_set = true;
     }
     int tiles_max = (max_n + TM - 1) / TM;
@@ -484,14 +546,18 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     B200M_CUDA_CHECK(cudaMemsetAsync(fb_count, 0, sizeof(int), st), "fallback counter");
     pair_max_norm_kernel<<<num_pairs, 256, 0, st>>>(pairs, t_norm, backward ? 1 : 0, pmax);
     B200M_CUDA_CHECK(cudaGetLastError(), "pair_max_norm_kernel launch");
-    l2_f32_cand_kernel<<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S,
-                                                              backward ? 1 : 0, nkb, q_norm, pmax, cand, cand_cnt, total_rows);
+    if (h16)
+        l2_f32_cand_kernel<true><<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S, backward ? 1 : 0,
+                                                                        nkb, q_norm, pmax, cand, cand_cnt, total_rows, q_info, t_info);
+    else
+        l2_f32_cand_kernel<false><<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S, backward ? 1 : 0,
+                                                                         nkb, q_norm, pmax, cand, cand_cnt, total_rows, nullptr, nullptr);
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_f32_cand_kernel launch");
     int bpp = (max_n + 7) / 8;
     long long rgrid = (long long)num_pairs * bpp;
     if (rgrid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
     refine_f32_kernel<<<(unsigned)rgrid, 256, 0, st>>>(backward ? 1 : 0, need2 ? 1 : 0, pairs, bpp, cand, cand_cnt, total_rows, S,
-                                                       q_desc, q_norm, t_desc, D, pmax, out, fbq, fb_count);
+                                                       q_desc, q_norm, t_desc, D, pmax, out, fbq, fb_count, q_info, t_info, Dh);
     B200M_CUDA_CHECK(cudaGetLastError(), "refine_f32_kernel launch");
     fallback_f32_kernel<<<4 * sms, 256, 0, st>>>(backward ? 1 : 0, pairs, fbq, fb_count, q_desc, t_desc, D, out);
     B200M_CUDA_CHECK(cudaGetLastError(), "fallback_f32_kernel launch");

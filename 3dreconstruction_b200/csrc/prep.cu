@@ -8,6 +8,7 @@
 //                out-of-range element so the caller can route to the fp32 path instead.
 //   prep_l2_f32: fp32 row norms for the TF32 candidate kernel.
 // HBM-bound streaming kernels: one warp per row, coalesced 128-bit loads.
+#include <cuda_fp16.h>
 #include "common.cuh"
 
 namespace {
@@ -113,9 +114,77 @@ prep_l2_f32_kernel(const float* __restrict__ src, long long rows, int D, float* 
     if (lane == 0) norms[row] = acc;
 }
 
+// L2_F16C, pass 1: row norms (fp32) and the store's max |x| (atomicMax on the bits of a non-negative float)
+__global__ void __launch_bounds__(256)
+prep_l2_f16_norm_kernel(const float* __restrict__ src, long long rows, int D, float* __restrict__ norms,
+                        unsigned int* __restrict__ maxbits) {
+    const int lane = threadIdx.x & 31;
+    long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const float* s = src + row * D;
+    float acc = 0.0f, mx = 0.0f;
+    for (int k = lane; k < D; k += 32) { float f = __ldg(s + k); acc = fmaf(f, f, acc); mx = fmaxf(mx, fabsf(f)); }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, off);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    }
+    if (lane == 0) {
+        norms[row] = acc;
+        if (mx == mx && mx < 3.0e38f) atomicMax(maxbits, __float_as_uint(mx));
+    }
+}
+
+// pass 2: dst = half(src * s), s = 2^-ceil(log2 max|x|) (exact scaling; max |x| * s <= 1, so nothing overflows and the
+// fp32 accumulator of a 256-term dot product stays below 256); columns D..Dh-1 are zero
+__global__ void __launch_bounds__(256)
+prep_l2_f16_convert_kernel(const float* __restrict__ src, long long rows, int D, int Dh, __half* __restrict__ dst,
+                           float* __restrict__ info) {
+    const float mx = __uint_as_float(*(const unsigned int*)(info + 2));
+    int e = 0;
+    if (mx > 0.0f) { frexpf(mx, &e); if (ldexpf(1.0f, e - 1) == mx) e -= 1; }     // mx <= 2^e, tight
+    e = max(-100, min(100, e));
+    const float s = ldexpf(1.0f, -e);
+    if (blockIdx.x == 0 && threadIdx.x == 0) { info[0] = s; info[1] = ldexpf(1.0f, e); }
+    const long long total = rows * (long long)(Dh / 2);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / (Dh / 2);
+        const int k = (int)(i - r * (Dh / 2)) * 2;
+        const float a = k < D ? __ldg(src + r * D + k) * s : 0.0f, b = k + 1 < D ? __ldg(src + r * D + k + 1) * s : 0.0f;
+        *reinterpret_cast<__half2*>(dst + r * Dh + k) = __floats2half2_rn(a, b);
+    }
+}
+
 }  // namespace
 
 extern "C" {
+
+int b200m_l2_f16_aux_bytes(int64_t rows, int D, size_t* bytes) {
+    if (rows < 0 || D <= 0 || !bytes) return B200M_EINVAL;
+    *bytes = b200m_f16_aux_bytes(rows, D);
+    return B200M_OK;
+}
+
+int b200m_prep_l2_f16(const float* src, int64_t rows, int D, void* aux, void* stream) {
+    if (rows < 0 || D <= 0) return B200M_EINVAL;
+    if (!aux || ((uintptr_t)aux & 255)) return B200M_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* info = (float*)((char*)aux + b200m_f16_info_off(rows, D));
+    B200M_CUDA_CHECK(cudaMemsetAsync(info, 0, 256, st), "l2_f16 info memset");
+    if (rows == 0) return B200M_OK;
+    if (!src) return B200M_EINVAL;
+    long long blocks = (rows + 7) / 8;
+    if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    prep_l2_f16_norm_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, rows, D, (float*)aux, (unsigned int*)(info + 2));
+    B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_f16_norm_kernel launch");
+    const int Dh = b200m_f16_width(D);
+    long long want = (rows * (long long)(Dh / 2) + 255) / 256;
+    prep_l2_f16_convert_kernel<<<(unsigned)(want < 148 * 16 ? want : 148 * 16), 256, 0, st>>>(
+        src, rows, D, Dh, (__half*)((char*)aux + b200m_f16_half_off(rows)), info);
+    B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_f16_convert_kernel launch");
+    b200m_count_launch(2);
+    return B200M_OK;
+}
 
 int b200m_l2_i8_aux_bytes(int64_t rows, size_t* bytes) {
     if (rows < 0 || !bytes) return B200M_EINVAL;

@@ -739,8 +739,12 @@ int b200m_ransac_homography(const float* corr_xyxy, const int64_t* ptr, int num_
     if (!(confidence > 0.0 && confidence < 1.0)) return B200M_EINVAL;            // CV_Assert in RANSACPointSetRegistrator::run
     if ((uintptr_t)corr_xyxy & 15) return B200M_EINVAL;
     constexpr size_t dyn = (size_t)SCRATCH_DOUBLES * TUPLES * sizeof(double);
-    B200M_CUDA_CHECK(cudaFuncSetAttribute(ransac_homography_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn),
-                     "ransac_homography_kernel smem attribute");      // per device; microseconds
+    static bool attr_set = false;                 // one process per GPU (as everywhere in this library)
+    if (!attr_set) {
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(ransac_homography_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn),
+                         "ransac_homography_kernel smem attribute");
+        attr_set = true;
+    }
     ransac_homography_kernel<<<(unsigned)num_pairs, RT, dyn, (cudaStream_t)stream>>>(
         (const float4*)corr_xyxy, (const long long*)ptr, num_pairs, (float)(thr * thr), confidence, max_iters, H_out, mask_out,
         inliers_out, iters_out);

@@ -52,11 +52,17 @@ def _ptr(t: Optional[torch.Tensor]) -> int:
 
 
 class Engine:
-    def __init__(self, device: Optional[torch.device | str | int] = None, hamming_path: Optional[str] = None):
+    def __init__(self, device: Optional[torch.device | str | int] = None, hamming_path: Optional[str] = None,
+                 float_path: Optional[str] = None):
         """hamming_path: "fp4" (tcgen05 kind::mxf4 over bits expanded to e2m1 +-1.0, descriptors up to 64 bytes), "int8"
         (tcgen05 kind::i8 over +-1 int8, same limit), "popc" (the INT-pipe kernel, any width) or "auto" (fp4 where the
         width allows it, else popc); default from B200M_HAMMING_PATH, else auto.  All produce identical results."""
         self.lib = L.load()
+        # non-integer float descriptors: "f16" = tcgen05 kind::f16 candidates over a scaled fp16 copy (default), "tf32" =
+        # kind::tf32 candidates straight from the fp32 rows; the exact fp32 re-rank makes the results identical.
+        self.float_path = float_path or os.environ.get("B200M_FLOAT_PATH", "f16")
+        if self.float_path not in ("f16", "tf32"):
+            raise ValueError("float_path must be f16 or tf32")
         self.hamming_path = hamming_path or os.environ.get("B200M_HAMMING_PATH", "auto")
         if self.hamming_path not in ("auto", "fp4", "int8", "popc"):
             raise ValueError("hamming_path must be auto, fp4, int8 or popc")
@@ -115,7 +121,7 @@ class Engine:
         if t.dtype != torch.float32:
             raise ValueError("NORM_L2 needs float32 (or uint8) descriptors")
         with torch.cuda.device(self.device):
-            if force_kind != L.KIND_L2_F32:
+            if force_kind not in (L.KIND_L2_F32, L.KIND_L2_F16C):
                 Dpad = (D + 127) // 128 * 128
                 d8 = torch.empty((rows, Dpad), dtype=torch.int8, device=self.device)
                 nb = ctypes.c_size_t(0)
@@ -129,6 +135,13 @@ class Engine:
             Dpad = (D + 31) // 32 * 32
             if Dpad != D:
                 t = torch.nn.functional.pad(t, (0, Dpad - D))
+            t = t.contiguous()
+            if force_kind == L.KIND_L2_F16C or (force_kind != L.KIND_L2_F32 and self.float_path == "f16"):
+                nb = ctypes.c_size_t(0)
+                L.check(self.lib.b200m_l2_f16_aux_bytes(rows, Dpad, ctypes.byref(nb)), "b200m_l2_f16_aux_bytes")
+                aux = torch.empty((nb.value // 4,), dtype=torch.float32, device=self.device)   # norms | fp16 copy | info
+                L.check(self.lib.b200m_prep_l2_f16(t.data_ptr(), rows, Dpad, aux.data_ptr(), self._stream()), "b200m_prep_l2_f16")
+                return DeviceDescriptors(L.KIND_L2_F16C, t, aux, rows, Dpad)
             nrm = torch.empty((rows,), dtype=torch.float32, device=self.device)
             L.check(self.lib.b200m_prep_l2_f32(t.data_ptr(), rows, Dpad, nrm.data_ptr(), self._stream()),
                     "b200m_prep_l2_f32")
@@ -229,8 +242,9 @@ class Engine:
         a = self.prepare(desc1, norm_type)
         b = self.prepare(desc2, norm_type)
         if a.kind != b.kind:      # one side integer-valued, the other not: both go the fp32 way
-            a = self.prepare(desc1, norm_type, force_kind=L.KIND_L2_F32)
-            b = self.prepare(desc2, norm_type, force_kind=L.KIND_L2_F32)
+            fk = L.KIND_L2_F16C if self.float_path == "f16" else L.KIND_L2_F32
+            a = self.prepare(desc1, norm_type, force_kind=fk)
+            b = self.prepare(desc2, norm_type, force_kind=fk)
         return a, b
 
     def match_arrays(self, desc1: np.ndarray, desc2: np.ndarray, norm_type: int = NORM_L2,

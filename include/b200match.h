@@ -62,6 +62,11 @@ extern "C" {
                                  and tcgen05 kind::mxf4.block_scale with all scale factors 1.0: twice the MACs
                                  per instruction, half the operand bytes; fp32 sums of +-1 are exact         */
 
+#define B200M_KIND_L2_F16C 5     /* float32 rows as L2_F32, candidates from tcgen05 kind::f16 over a scaled fp16 copy of the
+                                 rows (b200m_prep_l2_f16): operands rounded to 11 significant bits instead of TF32's
+                                 truncation to 11, twice the MMA rate, half the operand bytes; the same proven error
+                                 window + exact fp32 re-rank, so the results are those of L2_F32                  */
+
 /* One image pair of a batch: rows [q_off, q_off+n) of the query store against rows
  * [t_off, t_off+m) of the train store; its matches are written at out_off.. (capacity n). */
 typedef struct b200m_pair {
@@ -114,6 +119,12 @@ B200M_API int b200m_prep_hamming_tc(const uint8_t* src, int64_t rows, int D, int
 B200M_API int b200m_hamming_fp4_width(int D, int* Dpad4);
 B200M_API int b200m_prep_hamming_fp4(const uint8_t* src, int64_t rows, int D, uint8_t* dst, int Dpad4, void* stream);
 
+/* Aux block for B200M_KIND_L2_F16C: b200m_l2_f16_aux_bytes(rows, D) bytes, 256-byte aligned, passed as q_norm / t_norm:
+ * float32 norms[rows] (as b200m_prep_l2_f32) | fp16 copy [rows, D rounded up to 64] of src * s | info (s, 1/s, max |x|);
+ * s is the power of two with max |x| * s in (1/2, 1].  Two launches, no host synchronisation. */
+B200M_API int b200m_l2_f16_aux_bytes(int64_t rows, int D, size_t* bytes);
+B200M_API int b200m_prep_l2_f16(const float* src, int64_t rows, int D, void* aux, void* stream);
+
 /* Row squared norms for the F32 kind: norms[r] = sum_k src[r,k]^2 (fp32). */
 B200M_API int b200m_prep_l2_f32(const float* src, int64_t rows, int D, float* norms, void* stream);
 
@@ -134,8 +145,8 @@ B200M_API int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t t
  *                    HAMMING: uint8 [rows, D]      (D = bytes per descriptor, any D >= 1)
  *                    HAMMING_TC, HAMMING_FP4: the same packed uint8 [rows, D], D <= 64
  *                    L2_I8  : int8  [rows, D]      (D multiple of 128, from b200m_prep_l2_i8)
- *                    L2_F32 : float [rows, D]      (D multiple of 32 floats, D <= 256)
- *   q_norm/t_norm  L2_I8: the aux block of b200m_prep_l2_i8 (int32 norms first); L2_F32: float [rows];
+ *                    L2_F32, L2_F16C : float [rows, D]      (D multiple of 32 floats, D <= 256)
+ *   q_norm/t_norm  L2_I8: the aux block of b200m_prep_l2_i8 (int32 norms first); L2_F32: float [rows]; L2_F16C: the aux block of b200m_prep_l2_f16;
  *                  HAMMING: NULL; HAMMING_TC: int8 [rows, Dpad] from b200m_prep_hamming_tc;
  *                  HAMMING_FP4: uint8 [rows, Dpad4] from b200m_prep_hamming_fp4
  *   q_rows/t_rows  number of rows in each store (bounds for TMA maps)

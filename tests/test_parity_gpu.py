@@ -39,6 +39,15 @@ def heng(request):
     return e
 
 
+@pytest.fixture(scope="module", params=["f16", "tf32"])
+def feng(request):
+    """Float-descriptor engines: "f16" = tcgen05 kind::f16 candidates over the scaled fp16 copy (default), "tf32" =
+    kind::tf32 candidates from the fp32 rows.  Both re-rank exactly in fp32."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    return b.Engine(float_path=request.param)
+
+
 def assert_exact(got, want, what=""):
     assert len(got.query_idx) == len(want.query_idx), f"{what}: count {len(got.query_idx)} != {len(want.query_idx)}"
     assert np.array_equal(got.query_idx, want.query_idx), what
@@ -313,15 +322,15 @@ def test_l2_uint8_descriptors(eng):
 
 # ------------------------------------------------------------------ non-integer float L2 (SuperPoint) — TF32 + fp32 re-rank
 @pytest.mark.parametrize("mode", [(True, None), (False, 0.8), (False, None)])
-def test_l2_f32_vs_oracle(eng, mode):
+def test_l2_f32_vs_oracle(feng, mode):
     s = synth.superpoint_set(seed=21, images=2, n=1500, d=256, pool=2500)
-    flips = assert_close_float(eng.match_arrays(s[0], s[1], b.NORM_L2, *mode),
+    flips = assert_close_float(feng.match_arrays(s[0], s[1], b.NORM_L2, *mode),
                                O.reference_match(s[0], s[1], O.NORM_L2, *mode), f"f32 {mode}")
     print(f"f32 mode={mode}: near-tie flips={flips}")
     rng = np.random.default_rng(4)
     a = rng.normal(size=(333, 100)).astype(np.float32) * 3.0          # not unit norm, D not a multiple of 32
     c = (a[rng.permutation(333)[:290]] + rng.normal(size=(290, 100)).astype(np.float32) * 0.05).astype(np.float32)
-    assert_close_float(eng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"f32 generic {mode}")
+    assert_close_float(feng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"f32 generic {mode}")
 
 
 def assert_knn2_close(got, want, what=""):
@@ -335,16 +344,16 @@ def assert_knn2_close(got, want, what=""):
     return
 
 
-def test_l2_f32_knn2_raw(eng):
+def test_l2_f32_knn2_raw(feng):
     s = synth.superpoint_set(seed=22, images=2, n=1200, d=256, pool=2000)
-    assert_knn2_close(eng.knn2_arrays(s[0], s[1], b.NORM_L2), O.knn2_c(s[0], s[1], O.NORM_L2), "f32 knn2")
-    got = eng.knn2_arrays(s[0], s[1][:1], b.NORM_L2)
+    assert_knn2_close(feng.knn2_arrays(s[0], s[1], b.NORM_L2), O.knn2_c(s[0], s[1], O.NORM_L2), "f32 knn2")
+    got = feng.knn2_arrays(s[0], s[1][:1], b.NORM_L2)
     assert np.all(got.idx2 == -1) and np.all(got.idx1 == 0)
     d128 = synth.superpoint_set(seed=23, images=2, n=700, d=128, pool=1000)      # DISK / ALIKED width
-    assert_knn2_close(eng.knn2_arrays(d128[0], d128[1], b.NORM_L2), O.knn2_c(d128[0], d128[1], O.NORM_L2), "f32 d128")
+    assert_knn2_close(feng.knn2_arrays(d128[0], d128[1], b.NORM_L2), O.knn2_c(d128[0], d128[1], O.NORM_L2), "f32 d128")
 
 
-def test_l2_f32_dense_cluster_takes_exhaustive_fallback(eng):
+def test_l2_f32_dense_cluster_takes_exhaustive_fallback(feng):
     """Many train rows within the TF32 error window of each other: the 8-candidate list cannot be proven
     sufficient, so the rows are re-scanned exhaustively in fp32 — results must still match the oracle."""
     rng = np.random.default_rng(11)
@@ -352,9 +361,9 @@ def test_l2_f32_dense_cluster_takes_exhaustive_fallback(eng):
     base /= np.linalg.norm(base)
     c = (base + 1e-4 * rng.normal(size=(400, 64))).astype(np.float32)          # 400 near-duplicates
     a = (base + 1e-4 * rng.normal(size=(200, 64))).astype(np.float32)
-    eng.f32_stats(reset=True)
-    got = eng.knn2_arrays(a, c, b.NORM_L2)
-    rows, evals = eng.f32_stats()
+    feng.f32_stats(reset=True)
+    got = feng.knn2_arrays(a, c, b.NORM_L2)
+    rows, evals = feng.f32_stats()
     assert rows == 200 and evals == 200 * 400
     want = O.knn2_c(a, c, O.NORM_L2)
     # distances ~1e-3 with gaps ~1e-6: compare distances, and indices where the oracle's gap is resolvable in fp32
@@ -363,9 +372,47 @@ def test_l2_f32_dense_cluster_takes_exhaustive_fallback(eng):
     assert np.array_equal(got.idx1[clear], want.idx1[clear])
     # well separated data never needs the fallback
     s = synth.superpoint_set(seed=24, images=2, n=2000, d=256, pool=3000)
-    eng.f32_stats(reset=True)
-    eng.match_arrays(s[0], s[1], b.NORM_L2, True, None)
-    assert eng.f32_stats()[0] == 0
+    feng.f32_stats(reset=True)
+    feng.match_arrays(s[0], s[1], b.NORM_L2, True, None)
+    assert feng.f32_stats()[0] == 0
+
+
+def test_l2_f16c_kind_is_default_and_identical_to_tf32():
+    """The fp16 copy is round-to-nearest of src * s with s the power of two that brings max |x| into (1/2, 1]; the two
+    candidate kinds return the same bits (both finish with the exact fp32 re-rank), also for rows whose elements span
+    the fp16 subnormal range and for large magnitudes."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    L = pkg("_lib")
+    e16, e32 = b.Engine(float_path="f16"), b.Engine(float_path="tf32")
+    rng = np.random.default_rng(31)
+    a = rng.normal(size=(500, 96)).astype(np.float32) * 37.0
+    dd = e16.prepare(a, b.NORM_L2)
+    assert dd.kind == L.KIND_L2_F16C and e32.prepare(a, b.NORM_L2).kind == L.KIND_L2_F32
+    aux = dd.norm.cpu().numpy()
+    half_off, Dh = (500 * 4 + 255) // 256 * 256, 128
+    info_off = half_off + (500 * Dh * 2 + 255) // 256 * 256
+    s = aux[info_off // 4]
+    mx = np.abs(a).max()
+    assert 0.5 < mx * s <= 1.0 and np.log2(s) == np.round(np.log2(s)) and aux[info_off // 4 + 1] == 1.0 / s
+    assert np.allclose(aux[:500], (a.astype(np.float64) ** 2).sum(1), rtol=1e-5)
+    h = aux.view(np.uint8)[half_off:half_off + 500 * Dh * 2].view(np.float16).reshape(500, Dh)
+    assert np.array_equal(h[:, :96], (a * s).astype(np.float16)) and not h[:, 96:].any()
+    cases = {"generic": (a, (a[rng.permutation(500)[:420]] + rng.normal(size=(420, 96)) * 0.5).astype(np.float32))}
+    wide = (rng.normal(size=(400, 256)) * np.exp(rng.uniform(-14, 0, size=(1, 256)))).astype(np.float32)       # columns down to 1e-6
+    cases["wide_range"] = (wide, (wide[rng.permutation(400)[:350]] * (1 + 0.01 * rng.normal(size=(350, 256)))).astype(np.float32))
+    big = (rng.normal(size=(300, 128)) * 1e4).astype(np.float32)
+    cases["large"] = (big, (big[rng.permutation(300)] + rng.normal(size=(300, 128)) * 50).astype(np.float32))
+    sp = synth.superpoint_set(seed=33, images=2, n=1800, d=256, pool=3000)
+    cases["superpoint"] = (sp[0], sp[1])
+    for name, (x, y) in cases.items():
+        for mode in [(False, 0.8), (True, None), (False, None)]:
+            g16, g32 = e16.match_arrays(x, y, b.NORM_L2, *mode), e32.match_arrays(x, y, b.NORM_L2, *mode)
+            assert_exact(g16, g32, f"f16 vs tf32 {name} {mode}")
+            assert_close_float(g16, O.reference_match(x, y, O.NORM_L2, *mode), f"f16 {name} {mode}")
+        k16, k32 = e16.knn2_arrays(x, y, b.NORM_L2), e32.knn2_arrays(x, y, b.NORM_L2)
+        for u, v in zip(k16, k32):
+            assert np.array_equal(u, v), name
 
 
 def test_l2_f32_config3_shape(eng):

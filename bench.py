@@ -453,18 +453,33 @@ def allpairs_extras(torch, b, eng, pk):
     store = ap.build_store(eng, desc.view(I * n, D), b.NORM_L2, counts=[n] * I)
     del desc
     pairs = ap.all_pairs(I)
-    eng.f32_stats(reset=True)
-    ms, knn_ms, matches = timed_pass(store, pairs, 2)
-    fb_rows, _ = eng.f32_stats()
     flops = 2.0 * n * n * D * len(pairs) * 2                  # both directions are computed for the mutual check
-    peak = 0.5 * pk["bf16_tflops_sustained"]
+    sp = {}
+    for path in ("f16", "tf32"):
+        e = eng if eng.float_path == path else b.Engine(eng.device, float_path=path)
+        if path != eng.float_path:
+            store = ap.build_store(e, store.dd.desc, b.NORM_L2, counts=[n] * I)
+        timed_eng[0] = e
+        e.f32_stats(reset=True)
+        ms, knn_ms, matches = timed_pass(store, pairs, 2)
+        fb_rows, _ = e.f32_stats()
+        sp[path] = {"ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3),
+                    "gdist_per_s_one_direction": len(pairs) * n * n / 1e9 / (ms / 1e3), "matches": matches,
+                    "knn_stage_ms": knn_ms, "tflops_achieved_knn_stage": flops / (knn_ms / 1e3) / 1e12,
+                    "exhaustive_fallback_rows": fb_rows}
+    timed_eng[0] = eng
+    peak16, peak32 = pk["bf16_tflops_sustained"], 0.5 * pk["bf16_tflops_sustained"]
+    sp["f16"].update({"f16_peak_tflops": peak16, "frac_of_f16_roofline": sp["f16"]["tflops_achieved_knn_stage"] / peak16,
+                      "frac_of_tf32_roofline_survey_8d": sp["f16"]["tflops_achieved_knn_stage"] / peak32,
+                      "peak_source": "bf16_tflops_sustained of MEASURED_PEAKS.json (kind::f16 runs at the bf16 rate); SURVEY 8d names "
+                                     "0.5 x that (TF32) for this config: both fractions given; tools/mma_peak: 2233 / 1117 TFLOP/s burst",
+                      "note": "default float path (B200M_KIND_L2_F16C): tcgen05 kind::f16 candidates over a scaled fp16 copy of the rows + "
+                              "exact fp32 re-rank; knn stage = candidate + refine + fallback kernels, both directions"})
+    sp["tf32"].update({"tf32_peak_tflops": peak32, "frac_of_tf32_roofline": sp["tf32"]["tflops_achieved_knn_stage"] / peak32,
+                       "note": "B200M_KIND_L2_F32 (Engine(float_path='tf32')): kind::tf32 candidates from the fp32 rows; same results, bit for bit"})
     out["superpoint_allpairs_100x4096x256_mutual"] = {
-        "pairs": len(pairs), "ms_per_pass": ms, "pairs_per_s": len(pairs) / (ms / 1e3),
-        "gdist_per_s_one_direction": len(pairs) * n * n / 1e9 / (ms / 1e3), "matches": matches,
-        "knn_stage_ms": knn_ms, "tf32_tflops_achieved_knn_stage": flops / (knn_ms / 1e3) / 1e12,
-        "tf32_peak_tflops": peak, "frac_of_tf32_roofline": flops / (knn_ms / 1e3) / 1e12 / peak,
-        "peak_source": "0.5 x bf16_tflops_sustained (SURVEY 8d); tools/mma_peak measures 1117 TFLOP/s burst tf32",
-        "exhaustive_fallback_rows": fb_rows, "rows_total": 2 * n * len(pairs)}
+        "pairs": len(pairs), "rows_total": 2 * n * len(pairs), **sp["f16"], "tf32_path": sp["tf32"],
+        "speedup_over_tf32_path": sp["tf32"]["ms_per_pass"] / sp["f16"]["ms_per_pass"]}
     del store
     # ---- configs[4], bounded: 48 of the 1000 images (1128 of 499500 pairs), AKAZE 61 bytes padded to 64
     I, n, nb = 48, 16384, 61
@@ -484,13 +499,18 @@ def allpairs_extras(torch, b, eng, pk):
                      "knn_stage_ms": knn_ms, "full_config_estimate_s_1gpu": 499500 / (len(pairs) / (ms / 1e3))}
         del store
     timed_eng[0] = eng
-    tops = 2.0 * 2 * len(pairs) * n * n * 512 / (res["tensor"]["knn_stage_ms"] / 1e3) / 1e12     # both directions, 512 int8 dims
+    tops = 2.0 * 2 * len(pairs) * n * n * 512 / (res["tensor"]["knn_stage_ms"] / 1e3) / 1e12     # both directions, 512 one-bit dims
+    fp4_peak = 4.0 * pk["bf16_tflops_sustained"]
     res["tensor"].update({
-        "int8_tops_achieved_knn_stage": tops, "int8_peak_tops": int8_peak, "frac_of_int8_roofline": tops / int8_peak,
-        "frac_of_hw_int8_microbench": tops / 4590.0,
-        "peak_source": "2 x bf16_tflops_sustained of MEASURED_PEAKS.json; 4590 = tools/mma_peak.cu issue peak at 1965 MHz",
-        "note": "default path (hamming_tc.cu): bits as +-1 int8, K = 512, forward and backward knn on the tensor cores, "
-                "exact POPC resolve of two 16-column chunks per row; knn stage = both directions + resolve"})
+        "tops_achieved_knn_stage": tops, "fp4_peak_tops": fp4_peak, "frac_of_fp4_roofline": tops / fp4_peak,
+        "frac_of_hw_mxf4_sustained_microbench": tops / 7850.0, "frac_of_hw_mxf4_burst_microbench": tops / 8876.0,
+        "int8_peak_tops": int8_peak, "frac_of_int8_roofline": tops / int8_peak,
+        "peak_source": "4 x bf16_tflops_sustained of MEASURED_PEAKS.json (nominal fp4 : bf16 = 4 : 1); tools/mma_peak.cu kind::mxf4 issue rate "
+                       "16384 MAC/clk/SM = 8876 TOP/s burst, 7850 sustained under the power cap (profiles/r01_mma_mxf4_peak.txt); the "
+                       "int8 denominators (2 x bf16 sustained) are what the kind::i8 variant of the kernel is held to",
+        "note": "default path (hamming_tc.cu, B200M_KIND_HAMMING_FP4): bits as e2m1 +-1.0 nibbles, tcgen05 kind::mxf4 with unit scale factors, "
+                "K = 512, forward and backward knn on the tensor cores, exact POPC resolve of two 16-column chunks per row; "
+                "knn stage = both directions + resolve"})
     res["popc"].update({
         "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": res["popc"]["gdist_per_s"] / popc_peak,
         "note": "INT-pipe kernel (hamming.cu): each distance computed once (fused row top-2 + column minima); POPC roofline at 1965 MHz"})

@@ -19,6 +19,7 @@
 //      survivors of the final bound get the direct fp32 sum (a-b)^2 — what cv2 computes.
 // Result: Top2 keys (IEEE bits of the exact fp32 d^2 << 32 | column), ties -> lowest column.
 #include <math_constants.h>
+#include <stdlib.h>
 #include "common.cuh"
 #include "sm100.cuh"
 
@@ -68,7 +69,7 @@ struct Item {
 };
 
 __device__ __forceinline__ Item decode_item(long long item, const DevPair* __restrict__ pairs, int tiles_max, int S,
-                                            int backward) {
+                                            int backward, int rows_per_item = TM) {
     Item it;
     int tile = (int)(item % tiles_max); item /= tiles_max;
     it.split = (int)(item % S);
@@ -77,7 +78,7 @@ __device__ __forceinline__ Item decode_item(long long item, const DevPair* __res
     DevPair pr = pairs[p];
     if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
     else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
-    it.r0 = tile * TM;
+    it.r0 = tile * rows_per_item;
     int cols_per = ((it.m + S - 1) / S + TN - 1) / TN * TN;
     it.c_begin = it.split * cols_per;
     it.c_end = min(it.m, it.c_begin + cols_per);
@@ -120,7 +121,13 @@ __host__ __device__ constexpr size_t smem_bytes(int nkb) {
 
 // H16: the tensor maps address the scaled fp16 copies (K block = 64 halves), the MMA is kind::f16 and the accumulator
 // is s_q s_t a.b; everything else (pipeline, epilogue, lists) is shared with the TF32 kind.
-template <bool H16>
+// MT = query row tiles per work item (1 or 2).  With MT = 2 the two buffers that otherwise double-buffer one query tile
+// hold two row tiles, and every train K block is issued against both, into two TMEM accumulators per stage pair: half
+// the train bytes from L2 per MMA.  Used when the query tile is small enough (nkb <= 4: fp16 up to D = 256) and the
+// batch still fills the SMs.  Measured: 2.46 -> 2.37 ms per 276-pair launch only -- the epilogue's instruction count
+// (8 warps, ~0.5 IPC per scheduler; adding instructions slows the kernel proportionally), not the L2 -> SM path,
+// bounds the fp16 kernel.
+template <bool H16, int MT>
 __global__ void __launch_bounds__(THREADS, 1)
 l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                    const float* __restrict__ t_norm, const DevPair* __restrict__ pairs, long long total_items,
@@ -132,7 +139,9 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const SmemLayout sm = carve(smem, nkb);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nabuf = nabuf_of(nkb);
+    const int nabuf = MT == 2 ? 1 : nabuf_of(nkb);      // MT == 2: both buffers hold the item's two row tiles
+    constexpr int ROWS_ITEM = TM * MT;
+    constexpr uint32_t ACC_COLS = TN * MT;              // TMEM columns of one stage (MT accumulators side by side)
 
     if (warp == 8 && lane == 0) {
         sm100::tma_prefetch_desc(&tmap_q);
@@ -142,7 +151,7 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_THREADS / 32); }
         sm100::fence_barrier_init();
     }
-    if (warp == 9) sm100::tmem_alloc<256>(sm.tmem_ptr);
+    if (warp == 9) sm100::tmem_alloc<2 * ACC_COLS>(sm.tmem_ptr);
     sm100::tc_fence_before();
     __syncthreads();
     sm100::tc_fence_after();
@@ -152,14 +161,15 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         // ===================== TMA producer: lockstep warp, one elected lane issues =====================
         uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;     // parities to wait for on a_empty / b_empty
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_empty[ab], a_par);
             if (sm100::elect_one()) {
-                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(nkb * A_KB_BYTES));
-                for (int kb = 0; kb < nkb; ++kb)
-                    sm100::tma_load_2d(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
-                                       kb * KB_ELEMS, it.q_off + it.r0);
+                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(MT * nkb * A_KB_BYTES));
+                for (int t = 0; t < MT; ++t)
+                    for (int kb = 0; kb < nkb; ++kb)
+                        sm100::tma_load_2d(sm.a + (size_t)((ab * MT + t) * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                           kb * KB_ELEMS, it.q_off + it.r0 + t * TM);
             }
             __syncwarp();
             if (++ab == (uint32_t)nabuf) { ab = 0; a_par ^= 1; }
@@ -186,28 +196,32 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_full[ab], a_par);
-            const uint32_t a_lo = a_lo0 + ab * (uint32_t)(nkb * (A_KB_BYTES >> 4));
+            const uint32_t a_lo = a_lo0 + ab * (uint32_t)(MT * nkb * (A_KB_BYTES >> 4));
             for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
                 sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
                 acc_par ^= 1u << as;
                 sm100::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + as * TN;
+                const uint32_t d_tmem = tmem_base + as * ACC_COLS;
                 for (int kb = 0; kb < nkb; ++kb) {
                     sm100::mbar_wait(&sm.b_full[bs], b_par);
                     sm100::tc_fence_after();
                     if (sm100::elect_one()) {
-                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
+                        const uint32_t bl = b_lo0 + bs * (B_KB_BYTES >> 4);
 #pragma unroll
-                        for (int k = 0; k < KB_BYTES / 32; ++k) {    // UMMA K = 8 tf32 or 16 halves = 32 bytes; +2 = 32 B >> 4
-                            if constexpr (H16)
-                                sm100::mma_f16(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                               idesc, (kb | k) ? 1u : 0u);
-                            else
-                                sm100::mma_tf32(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                                idesc, (kb | k) ? 1u : 0u);
+                        for (int t = 0; t < MT; ++t) {               // every train K block against each resident row tile
+                            const uint32_t al = a_lo + (t * nkb + kb) * (A_KB_BYTES >> 4);
+#pragma unroll
+                            for (int k = 0; k < KB_BYTES / 32; ++k) {    // UMMA K = 8 tf32 or 16 halves = 32 bytes; +2 = 32 B >> 4
+                                if constexpr (H16)
+                                    sm100::mma_f16(d_tmem + t * TN, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                                   idesc, (kb | k) ? 1u : 0u);
+                                else
+                                    sm100::mma_tf32(d_tmem + t * TN, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                                    idesc, (kb | k) ? 1u : 0u);
+                            }
                         }
                         sm100::mma_commit(&sm.b_empty[bs]);
                         if (kb == nkb - 1) sm100::mma_commit(&sm.acc_full[as]);
@@ -231,16 +245,24 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         const Window window = make_window(H16 ? q_info : nullptr, t_info, nkb * KB_ELEMS);
         const float neg2 = H16 ? -2.0f * __ldg(q_info + 1) * __ldg(t_info + 1) : -2.0f;     // -2 / (s_q s_t), exact
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward);
+            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
             if (!it.valid) continue;
-            // per-row state: running top-2 of 16-column minima, append window, list cursor
-            const int row = it.r0 + row_in_tile;
-            const bool row_ok = row < it.n;
-            float v1 = CUDART_INF_F, v2 = CUDART_INF_F;
-            const float win = row_ok ? window(__ldg(q_norm + it.q_off + (row_ok ? row : 0)), __ldg(pmax + it.pair)) : -CUDART_INF_F;
-            const long long lrow = (long long)(it.split * 2 + half) * total_rows + it.row_base + (row_ok ? row : 0);
-            float2* list = cand + lrow * KC;
-            int cnt = 0;
+            // per-row state (one set per resident row tile): running top-2 of 16-column minima, append window, list cursor
+            bool row_ok[MT];
+            float v1[MT], v2[MT], win[MT];
+            long long lrow[MT];
+            float2* list[MT];
+            int cnt[MT];
+#pragma unroll
+            for (int t = 0; t < MT; ++t) {
+                const int row = it.r0 + t * TM + row_in_tile;
+                row_ok[t] = row < it.n;
+                v1[t] = CUDART_INF_F; v2[t] = CUDART_INF_F;
+                win[t] = row_ok[t] ? window(__ldg(q_norm + it.q_off + row), __ldg(pmax + it.pair)) : -CUDART_INF_F;
+                lrow[t] = (long long)(it.split * 2 + half) * total_rows + it.row_base + (row_ok[t] ? row : 0);
+                list[t] = cand + lrow[t] * KC;
+                cnt[t] = 0;
+            }
             // ||b||^2 of the NEXT tile's columns is fetched while this tile is reduced (the load's latency used to sit in
             // front of every tile: 12 % of the stall samples at the barrier below)
             float nb = e < TN ? (it.c_begin + e < it.c_end ? __ldg(t_norm + it.t_off + it.c_begin + e) : BIG_F) : 0.0f;
@@ -254,53 +276,60 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
                 sm100::tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * TN + half * HC;
                 const float* cbv = sm.cb + as * TN + half * HC;
-                uint32_t acc[2][32];
-                sm100::tmem_ld32(taddr, acc[0]);
-                sm100::tmem_ld32(taddr + 32, acc[1]);
-                sm100::tmem_ld_wait();
-                sm100::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);    // whole half-tile is in registers
 #pragma unroll
-                for (int ch = 0; ch < 2; ++ch) {
-                    float ev[32];
-                    float h0 = CUDART_INF_F, h1 = CUDART_INF_F;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        ev[i] = fmaf(neg2, __uint_as_float(acc[ch][i]), cbv[ch * 32 + i]);
-                        if (i < 16) h0 = fminf(h0, ev[i]); else h1 = fminf(h1, ev[i]);
+                for (int t = 0; t < MT; ++t) {
+                    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * ACC_COLS + t * TN + half * HC;
+                    uint32_t acc[2][32];
+                    sm100::tmem_ld32(taddr, acc[0]);
+                    sm100::tmem_ld32(taddr + 32, acc[1]);
+                    sm100::tmem_ld_wait();
+                    if (t == MT - 1) {
+                        sm100::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);    // the stage's accumulators are in registers
                     }
-                    // top-2 of group minima first (the tighter, still valid bound), then the append test
-                    v2 = fminf(v2, fmaxf(v1, h0)); v1 = fminf(v1, h0);
-                    v2 = fminf(v2, fmaxf(v1, h1)); v1 = fminf(v1, h1);
-                    const float tau = fminf(v2 + win, BIG_F * 0.5f);      // masked columns (||b||^2 = BIG_F) never pass
-                    const int colb = c0 + half * HC + ch * 32;
-                    // per 16-column group, and only where the group's minimum passes; the body is predicated, not
-                    // branched (one lane's row passing makes the whole warp walk the group)
 #pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        if ((g ? h1 : h0) <= tau) {
+                    for (int ch = 0; ch < 2; ++ch) {
+                        float ev[32];
+                        float h0 = CUDART_INF_F, h1 = CUDART_INF_F;
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) {
-                                const float x = ev[g * 16 + i];
-                                const bool pass = x <= tau;
-                                if (pass & (cnt < KC)) list[cnt] = make_float2(x, __int_as_float(colb + g * 16 + i));
-                                cnt += pass;
+                        for (int i = 0; i < 32; ++i) {
+                            ev[i] = fmaf(neg2, __uint_as_float(acc[ch][i]), cbv[ch * 32 + i]);
+                            if (i < 16) h0 = fminf(h0, ev[i]); else h1 = fminf(h1, ev[i]);
+                        }
+                        // top-2 of group minima first (the tighter, still valid bound), then the append test
+                        v2[t] = fminf(v2[t], fmaxf(v1[t], h0)); v1[t] = fminf(v1[t], h0);
+                        v2[t] = fminf(v2[t], fmaxf(v1[t], h1)); v1[t] = fminf(v1[t], h1);
+                        const float tau = fminf(v2[t] + win[t], BIG_F * 0.5f);      // masked columns (||b||^2 = BIG_F) never pass
+                        const int colb = c0 + half * HC + ch * 32;
+                        // per 16-column group, and only where the group's minimum passes; the body is predicated, not
+                        // branched (one lane's row passing makes the whole warp walk the group)
+#pragma unroll
+                        for (int g = 0; g < 2; ++g) {
+                            if ((g ? h1 : h0) <= tau) {
+#pragma unroll
+                                for (int i = 0; i < 16; ++i) {
+                                    const float x = ev[g * 16 + i];
+                                    const bool pass = x <= tau;
+                                    if (pass & (cnt[t] < KC)) list[t][cnt[t]] = make_float2(x, __int_as_float(colb + g * 16 + i));
+                                    cnt[t] += pass;
+                                }
                             }
                         }
                     }
                 }
                 ++acc_cnt;
             }
-            if (row_ok) cand_cnt[lrow] = cnt;
+#pragma unroll
+            for (int t = 0; t < MT; ++t)
+                if (row_ok[t]) cand_cnt[lrow[t]] = cnt[t];
         }
     }
 
     sm100::tc_fence_before();
     __syncthreads();
-    if (warp == 9) sm100::tmem_dealloc<256>(tmem_base);
+    if (warp == 9) sm100::tmem_dealloc<2 * ACC_COLS>(tmem_base);
 }
 
 // max ||b|| over the train rows of each pair (for the TF32 error window)
@@ -526,18 +555,27 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     if (rc != B200M_OK) return rc;
     static bool attr_set = false;
     if (!attr_set) {
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(MAX_NKB)), "l2_f16c smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(MAX_NKB)), "l2_f16c smem attr");
         attr_set = true;
     }
-    int tiles_max = (max_n + TM - 1) / TM;
-    long long total_items = (long long)num_pairs * S * tiles_max;
-    if (total_items <= 0) return B200M_OK;
+    // two resident row tiles per work item when both fit (nkb <= 4) and the pairs are tall enough to fill the SMs that way
+    static const int mt_env = getenv("B200M_F32_MT") ? atoi(getenv("B200M_F32_MT")) : 0;
+    const int MTr = mt_env ? mt_env : 2;
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int MT = nabuf_of(nkb) == 2 && MTr == 2 && max_n > TM ? 2 : 1;
+    if (MT == 2 && !mt_env && (long long)num_pairs * S * ((max_n + 2 * TM - 1) / (2 * TM)) < sms) MT = 1;   // too few items to fill the SMs
+    int tiles_max = (max_n + TM * MT - 1) / (TM * MT);
+    long long total_items = (long long)num_pairs * S * tiles_max;
+    if (total_items <= 0) return B200M_OK;
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
     float2* cand = (float2*)cand_ws;
     int* cand_cnt = (int*)((char*)cand_ws + 8ull * KC * 2 * (size_t)S * (size_t)total_rows);
@@ -546,12 +584,12 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     B200M_CUDA_CHECK(cudaMemsetAsync(fb_count, 0, sizeof(int), st), "fallback counter");
     pair_max_norm_kernel<<<num_pairs, 256, 0, st>>>(pairs, t_norm, backward ? 1 : 0, pmax);
     B200M_CUDA_CHECK(cudaGetLastError(), "pair_max_norm_kernel launch");
-    if (h16)
-        l2_f32_cand_kernel<true><<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S, backward ? 1 : 0,
-                                                                        nkb, q_norm, pmax, cand, cand_cnt, total_rows, q_info, t_info);
-    else
-        l2_f32_cand_kernel<false><<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S, backward ? 1 : 0,
-                                                                         nkb, q_norm, pmax, cand, cand_cnt, total_rows, nullptr, nullptr);
+#define B200M_LAUNCH_CAND(H, M, QI, TI)                                                                                        \
+    l2_f32_cand_kernel<H, M><<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S,          \
+                                                                    backward ? 1 : 0, nkb, q_norm, pmax, cand, cand_cnt, total_rows, QI, TI)
+    if (h16) { if (MT == 2) B200M_LAUNCH_CAND(true, 2, q_info, t_info); else B200M_LAUNCH_CAND(true, 1, q_info, t_info); }
+    else     { if (MT == 2) B200M_LAUNCH_CAND(false, 2, nullptr, nullptr); else B200M_LAUNCH_CAND(false, 1, nullptr, nullptr); }
+#undef B200M_LAUNCH_CAND
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_f32_cand_kernel launch");
     int bpp = (max_n + 7) / 8;
     long long rgrid = (long long)num_pairs * bpp;

@@ -45,7 +45,13 @@ __host__ __device__ inline size_t b200m_f16_half_off(long long rows) { return ((
 __host__ __device__ inline size_t b200m_f16_info_off(long long rows, int D) {
     return b200m_f16_half_off(rows) + ((size_t)rows * b200m_f16_width(D) * 2 + 255) / 256 * 256;
 }
-__host__ __device__ inline size_t b200m_f16_aux_bytes(long long rows, int D) { return b200m_f16_info_off(rows, D) + 256; }
+// ... | "folded norm" rows x[rows][16 halves] at x_off: {hi, mid, lo, 0 x13} with hi + mid + lo = -(s^2 / 2) ||b||^2 (three
+// fp16 terms hold the fp32 value exactly); one extra K = 16 MMA step against the constant query-side row {r, r, r, 0 ...},
+// r = s_q / s_t, adds -(s_q s_t / 2) ||b||^2 to the accumulator (l2_f32.cu, FOLD kernels)
+__host__ __device__ inline size_t b200m_f16_x_off(long long rows, int D) { return b200m_f16_info_off(rows, D) + 256; }
+__host__ __device__ inline size_t b200m_f16_aux_bytes(long long rows, int D) {
+    return b200m_f16_x_off(rows, D) + ((size_t)rows * 32 + 255) / 256 * 256;
+}
 #define B200M_HTC_CHUNK 16   // columns per key chunk of the tensor-core Hamming kernel (hamming_tc.cu); resolve recomputes two chunks per row
 #define B200M_F32_CAND 32    // TF32 candidate list capacity per (query row, column half, column split) (l2_f32.cu)
 

@@ -18,6 +18,7 @@
 //      unless it overflows (counted -> the row is re-scanned exhaustively in fp32).  The few
 //      survivors of the final bound get the direct fp32 sum (a-b)^2 — what cv2 computes.
 // Result: Top2 keys (IEEE bits of the exact fp32 d^2 << 32 | column), ties -> lowest column.
+#include <cuda_fp16.h>
 #include <math_constants.h>
 #include <stdlib.h>
 #include "common.cuh"
@@ -43,19 +44,20 @@ constexpr float C_EPS = 0.0042f;
 // d^2 by twice that -- the `sub` term of the window.
 constexpr float C_H16 = 0.0021f;
 
-struct Window {                 // eps(a) = c * ||a|| * bmax + sub_b * bmax + sub_a * ||a||;  window = 2 eps
-    float c, sub_a, sub_b;
+struct Window {                 // eps(a) = c * ||a|| * bmax + sub_b * bmax + sub_a * ||a|| + quad * bmax^2;  window = 2 eps
+    float c, sub_a, sub_b, quad;
     __device__ __forceinline__ float operator()(float a_norm2, float bmax) const {
         const float an = sqrtf(a_norm2);
-        return 2.0f * (c * an * bmax + sub_b * bmax + sub_a * an);
+        return 2.0f * (c * an * bmax + sub_b * bmax + sub_a * an + quad * bmax * bmax);
     }
 };
 // q_info / t_info: info words of the two stores' aux blocks (scale, 1 / scale, max |x|), null for the TF32 kind
 __device__ __forceinline__ Window make_window(const float* q_info, const float* t_info, int Dh) {
     Window w;
-    if (!q_info) { w.c = C_EPS; w.sub_a = 0.0f; w.sub_b = 0.0f; return w; }
+    if (!q_info) { w.c = C_EPS; w.sub_a = 0.0f; w.sub_b = 0.0f; w.quad = 0.0f; return w; }
     const float g = 5.9604645e-8f * sqrtf((float)Dh);        // 2 * 2^-25 sqrt(Dh)
     w.c = C_H16;
+    w.quad = 4.8e-7f;       // 2^-21: fp32 rounding of -(||b||^2 / 2) riding in the accumulator (FOLD kernels), with margin
     w.sub_b = g * __ldg(q_info + 1);                          // ||b|| / s_a
     w.sub_a = g * __ldg(t_info + 1);                          // ||a|| / s_b
     return w;
@@ -86,9 +88,15 @@ __device__ __forceinline__ Item decode_item(long long item, const DevPair* __res
     return it;
 }
 
+constexpr int NB_FOLD = 5;         // ring depth of the FOLD kernels (20 KiB go to the folded-norm tiles)
+constexpr int X_BYTES = TN * 32;   // folded-norm rows of one train tile (SWIZZLE_32B, 16 halves per row)
+constexpr int AX_BYTES = TM * 32;  // the constant query-side block
+
 struct SmemLayout {
     uint8_t* a;        // [nabuf][nkb][16 KiB]
-    uint8_t* b;        // [NB][16 KiB]
+    uint8_t* b;        // [nb][16 KiB]
+    uint8_t* x;        // FOLD: [2][X_BYTES]
+    uint8_t* ax;       // FOLD: [AX_BYTES]
     float* cb;         // [2][TN]   ||b||^2 of the tile's columns (+inf when masked)
     uint64_t* a_full; uint64_t* a_empty;   // [2]
     uint64_t* b_full; uint64_t* b_empty;   // [NB]
@@ -98,11 +106,13 @@ struct SmemLayout {
 
 __host__ __device__ constexpr int nabuf_of(int nkb) { return nkb <= MAX_NKB / 2 ? 2 : 1; }
 
-__device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
+__device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb, bool fold = false) {
     SmemLayout s;
     s.a = base;
     s.b = s.a + nabuf_of(nkb) * nkb * A_KB_BYTES;
-    uint8_t* p = s.b + NB * B_KB_BYTES;
+    uint8_t* p = s.b + (fold ? NB_FOLD : NB) * B_KB_BYTES;
+    s.x = p; s.ax = p;
+    if (fold) { s.ax = p + 2 * X_BYTES; p += 2 * X_BYTES + AX_BYTES; }
     s.cb = (float*)p; p += 2 * TN * sizeof(float);
     s.a_full = (uint64_t*)p; p += 2 * 8;
     s.a_empty = (uint64_t*)p; p += 2 * 8;
@@ -114,9 +124,9 @@ __device__ __forceinline__ SmemLayout carve(uint8_t* base, int nkb) {
     return s;
 }
 
-__host__ __device__ constexpr size_t smem_bytes(int nkb) {
-    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NB * B_KB_BYTES + 2 * TN * sizeof(float) +
-           (8 + 2 * NB) * 8 + 16;
+__host__ __device__ constexpr size_t smem_bytes(int nkb, bool fold = false) {
+    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)(fold ? NB_FOLD : NB) * B_KB_BYTES +
+           (fold ? 2 * X_BYTES + AX_BYTES : 0) + 2 * TN * sizeof(float) + (8 + 2 * NB) * 8 + 16;
 }
 
 // H16: the tensor maps address the scaled fp16 copies (K block = 64 halves), the MMA is kind::f16 and the accumulator
@@ -127,17 +137,29 @@ __host__ __device__ constexpr size_t smem_bytes(int nkb) {
 // batch still fills the SMs.  Measured: 2.46 -> 2.37 ms per 276-pair launch only -- the epilogue's instruction count
 // (8 warps, ~0.5 IPC per scheduler; adding instructions slows the kernel proportionally), not the L2 -> SM path,
 // bounds the fp16 kernel.
-template <bool H16, int MT>
+// FOLD (fp16 only): -(||b||^2 / 2) rides in the accumulator through one extra K = 16 step against a constant query-side
+// row (the aux block's folded-norm rows, see common.cuh), so the epilogue compares RAW accumulators -- larger = closer --
+// with no per-column constant: no shared-memory norm staging, no barrier per tile, one FMNMX instead of FMA + LDS + FMNMX
+// per element.  fold_mode: 0 = run; 1 = run only if r = s_q / s_t is a small power of two (the FOLD kernel's own gate);
+// 2 = return if it is (the plain kernel launched right behind a FOLD kernel: device-side dispatch, no host sync).
+template <bool H16, int MT, bool FOLD>
 __global__ void __launch_bounds__(THREADS, 1)
 l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
+                   const __grid_constant__ CUtensorMap tmap_x, int fold_mode,
                    const float* __restrict__ t_norm, const DevPair* __restrict__ pairs, long long total_items,
                    int tiles_max, int S, int backward, int nkb, const float* __restrict__ q_norm,
                    const float* __restrict__ pmax, float2* __restrict__ cand, int* __restrict__ cand_cnt,
                    long long total_rows, const float* __restrict__ q_info, const float* __restrict__ t_info) {
     constexpr int KB_ELEMS = H16 ? KB_BYTES / 2 : KB_BYTES / 4;
+    constexpr int NBK = FOLD ? NB_FOLD : NB;            // train K-block ring depth
+    if (fold_mode) {
+        const float r = __ldg(q_info) * __ldg(t_info + 1);          // s_q / s_t, a power of two
+        const bool foldable = r >= 0.00390625f && r <= 256.0f;
+        if ((fold_mode == 1) != foldable) return;
+    }
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const SmemLayout sm = carve(smem, nkb);
+    const SmemLayout sm = carve(smem, nkb, FOLD);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nabuf = MT == 2 ? 1 : nabuf_of(nkb);      // MT == 2: both buffers hold the item's two row tiles
     constexpr int ROWS_ITEM = TM * MT;
@@ -147,9 +169,21 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         sm100::tma_prefetch_desc(&tmap_q);
         sm100::tma_prefetch_desc(&tmap_t);
         for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
-        for (int i = 0; i < NB; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
+        for (int i = 0; i < NBK; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_THREADS / 32); }
         sm100::fence_barrier_init();
+        if constexpr (FOLD) sm100::tma_prefetch_desc(&tmap_x);
+    }
+    if constexpr (FOLD) {
+        if (warp == 0) {
+            // query side of the folded-norm step: every row {r, r, r, 0 x5} twice -- both 16-byte halves equal, so the tile is
+            // invariant under the 16-byte chunk permutation of SWIZZLE_32B
+            const uint32_t rb = (uint32_t)__half_as_ushort(__float2half_rn(__ldg(q_info) * __ldg(t_info + 1)));
+            const uint32_t ax = sm100::smem_u32(sm.ax);
+            for (int w = lane; w < AX_BYTES / 4; w += 32)
+                sm100::sts32(ax + 4 * w, (w & 3) == 0 ? (int)(rb | (rb << 16)) : (w & 3) == 1 ? (int)rb : 0);
+            sm100::fence_proxy_async();            // generic-proxy stores -> visible to tcgen05.mma (async proxy)
+        }
     }
     if (warp == 9) sm100::tmem_alloc<2 * ACC_COLS>(sm.tmem_ptr);
     sm100::tc_fence_before();
@@ -160,6 +194,7 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     if (warp == 8) {
         // ===================== TMA producer: lockstep warp, one elected lane issues =====================
         uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;     // parities to wait for on a_empty / b_empty
+        uint32_t xs = 0;                                   // folded-norm slot = tile parity (the MMA warp's `as`)
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
             if (!it.valid) continue;
@@ -177,13 +212,16 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 for (int kb = 0; kb < nkb; ++kb) {
                     sm100::mbar_wait(&sm.b_empty[bs], b_par);
                     if (sm100::elect_one()) {
-                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
+                        const bool withx = FOLD && kb == nkb - 1;      // the tile's folded-norm rows travel with its last K block
+                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (withx ? X_BYTES : 0)));
                         sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * KB_ELEMS,
                                            it.t_off + c0);
+                        if (withx) sm100::tma_load_2d(sm.x + (size_t)xs * X_BYTES, &tmap_x, &sm.b_full[bs], 0, it.t_off + c0);
                     }
                     __syncwarp();
-                    if (++bs == NB) { bs = 0; b_par ^= 1; }
+                    if (++bs == NBK) { bs = 0; b_par ^= 1; }
                 }
+                xs ^= 1;
             }
         }
     } else if (warp == 9) {
@@ -194,6 +232,8 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                                        : sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
         const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
+        const uint32_t x_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.x));      // same low-word format
+        const uint64_t ax_desc = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.ax)));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
         for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
             Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
@@ -223,11 +263,18 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                                                     idesc, (kb | k) ? 1u : 0u);
                             }
                         }
+                        if constexpr (FOLD) {
+                            if (kb == nkb - 1) {                     // + r (hi + mid + lo) = -(s_q s_t / 2) ||b||^2, into every accumulator
+                                const uint64_t xd = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + as * (X_BYTES >> 4));
+#pragma unroll
+                                for (int t = 0; t < MT; ++t) sm100::mma_f16(d_tmem + t * TN, ax_desc, xd, idesc, 1u);
+                            }
+                        }
                         sm100::mma_commit(&sm.b_empty[bs]);
                         if (kb == nkb - 1) sm100::mma_commit(&sm.acc_full[as]);
                     }
                     __syncwarp();
-                    if (++bs == NB) { bs = 0; b_par ^= 1; }
+                    if (++bs == NBK) { bs = 0; b_par ^= 1; }
                 }
                 as ^= 1;
             }
@@ -263,6 +310,63 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 list[t] = cand + lrow[t] * KC;
                 cnt[t] = 0;
             }
+            if constexpr (FOLD) {
+                // raw accumulators y = s_q s_t (a.b - ||b||^2 / 2): larger = closer, estimate e = neg2 * y
+                constexpr float NEG_BIG = -3.0e38f;
+                const float half_ss = -1.0f / neg2;                  // s_q s_t / 2: the window in accumulator units
+#pragma unroll
+                for (int t = 0; t < MT; ++t) { v1[t] = NEG_BIG; v2[t] = NEG_BIG; win[t] *= half_ss; }
+                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                    const uint32_t as = acc_cnt & 1;
+                    const bool tail = c0 + TN > it.c_end;            // columns past the pair's last train row: other images' rows
+                    sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
+                    sm100::tc_fence_after();
+#pragma unroll
+                    for (int t = 0; t < MT; ++t) {
+                        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * ACC_COLS + t * TN + half * HC;
+                        uint32_t acc[2][32];
+                        sm100::tmem_ld32(taddr, acc[0]);
+                        sm100::tmem_ld32(taddr + 32, acc[1]);
+                        sm100::tmem_ld_wait();
+                        if (t == MT - 1) {
+                            sm100::tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
+                        }
+#pragma unroll
+                        for (int ch = 0; ch < 2; ++ch) {
+                            const int colb = c0 + half * HC + ch * 32;
+                            float y[32];
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(acc[ch][i]);
+                            if (tail) {
+#pragma unroll
+                                for (int i = 0; i < 32; ++i) y[i] = colb + i < it.c_end ? y[i] : NEG_BIG;
+                            }
+                            float h0 = y[0], h1 = y[16];
+#pragma unroll
+                            for (int i = 1; i < 16; ++i) { h0 = fmaxf(h0, y[i]); h1 = fmaxf(h1, y[16 + i]); }
+                            v2[t] = fmaxf(v2[t], fminf(v1[t], h0)); v1[t] = fmaxf(v1[t], h0);
+                            v2[t] = fmaxf(v2[t], fminf(v1[t], h1)); v1[t] = fmaxf(v1[t], h1);
+                            // rows past the pair (window -inf) never append; masked columns (NEG_BIG) never pass
+                            const float tau = row_ok[t] ? fmaxf(v2[t] - win[t], 0.5f * NEG_BIG) : CUDART_INF_F;
+#pragma unroll
+                            for (int g = 0; g < 2; ++g) {
+                                if ((g ? h1 : h0) >= tau) {
+#pragma unroll
+                                    for (int i = 0; i < 16; ++i) {
+                                        const float x = y[g * 16 + i];
+                                        const bool pass = x >= tau;
+                                        if (pass & (cnt[t] < KC)) list[t][cnt[t]] = make_float2(neg2 * x, __int_as_float(colb + g * 16 + i));
+                                        cnt[t] += pass;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    ++acc_cnt;
+                }
+            } else {
             // ||b||^2 of the NEXT tile's columns is fetched while this tile is reduced (the load's latency used to sit in
             // front of every tile: 12 % of the stall samples at the barrier below)
             float nb = e < TN ? (it.c_begin + e < it.c_end ? __ldg(t_norm + it.t_off + it.c_begin + e) : BIG_F) : 0.0f;
@@ -320,6 +424,7 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                     }
                 }
                 ++acc_cnt;
+            }
             }
 #pragma unroll
             for (int t = 0; t < MT; ++t)
@@ -555,14 +660,12 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     if (rc != B200M_OK) return rc;
     static bool attr_set = false;
     if (!attr_set) {
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem_bytes(MAX_NKB)), "l2_f16c smem attr");
-        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)smem_bytes(MAX_NKB)), "l2_f16c smem attr");
+#define B200M_CAND_ATTR(H, M, F)                                                                                             \
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<H, M, F>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+                                              (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr")
+        B200M_CAND_ATTR(false, 1, false); B200M_CAND_ATTR(false, 2, false); B200M_CAND_ATTR(true, 1, false);
+        B200M_CAND_ATTR(true, 2, false); B200M_CAND_ATTR(true, 1, true); B200M_CAND_ATTR(true, 2, true);
+#undef B200M_CAND_ATTR
         attr_set = true;
     }
     // two resident row tiles per work item when both fit (nkb <= 4) and the pairs are tall enough to fill the SMs that way
@@ -584,11 +687,26 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     B200M_CUDA_CHECK(cudaMemsetAsync(fb_count, 0, sizeof(int), st), "fallback counter");
     pair_max_norm_kernel<<<num_pairs, 256, 0, st>>>(pairs, t_norm, backward ? 1 : 0, pmax);
     B200M_CUDA_CHECK(cudaGetLastError(), "pair_max_norm_kernel launch");
-#define B200M_LAUNCH_CAND(H, M, QI, TI)                                                                                        \
-    l2_f32_cand_kernel<H, M><<<grid, THREADS, smem_bytes(nkb), st>>>(tq, tt, t_norm, pairs, total_items, tiles_max, S,          \
-                                                                    backward ? 1 : 0, nkb, q_norm, pmax, cand, cand_cnt, total_rows, QI, TI)
-    if (h16) { if (MT == 2) B200M_LAUNCH_CAND(true, 2, q_info, t_info); else B200M_LAUNCH_CAND(true, 1, q_info, t_info); }
-    else     { if (MT == 2) B200M_LAUNCH_CAND(false, 2, nullptr, nullptr); else B200M_LAUNCH_CAND(false, 1, nullptr, nullptr); }
+    // fp16 kind with at least 3 K blocks (the folded-norm slots are reused every second tile: 2 nkb >= ring depth): the FOLD
+    // kernel, gated on the device by the two stores' scale ratio, with the plain kernel behind it for the other case
+    static const int fold_env = getenv("B200M_F32_FOLD") ? atoi(getenv("B200M_F32_FOLD")) : 1;
+    const bool fold = h16 && fold_env && 2 * nkb >= NB_FOLD;
+    CUtensorMap tx = tt;
+    if (fold) {
+        rc = b200m_make_tmap_2d_ex(&tx, (const char*)t_norm + b200m_f16_x_off(t_rows, D), (uint64_t)t_rows, 32, TN,
+                                   CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, 32, CU_TENSOR_MAP_SWIZZLE_32B);
+        if (rc != B200M_OK) return rc;
+    }
+#define B200M_LAUNCH_CAND(H, M, F, MODE, QI, TI)                                                                                 \
+    l2_f32_cand_kernel<H, M, F><<<grid, THREADS, smem_bytes(nkb, F), st>>>(tq, tt, tx, MODE, t_norm, pairs, total_items, tiles_max, S, \
+                                                                          backward ? 1 : 0, nkb, q_norm, pmax, cand, cand_cnt, total_rows, QI, TI)
+    if (h16) {
+        if (fold) { if (MT == 2) B200M_LAUNCH_CAND(true, 2, true, 1, q_info, t_info); else B200M_LAUNCH_CAND(true, 1, true, 1, q_info, t_info); }
+        const int mode = fold ? 2 : 0;
+        if (MT == 2) B200M_LAUNCH_CAND(true, 2, false, mode, q_info, t_info); else B200M_LAUNCH_CAND(true, 1, false, mode, q_info, t_info);
+    } else {
+        if (MT == 2) B200M_LAUNCH_CAND(false, 2, false, 0, nullptr, nullptr); else B200M_LAUNCH_CAND(false, 1, false, 0, nullptr, nullptr);
+    }
 #undef B200M_LAUNCH_CAND
     B200M_CUDA_CHECK(cudaGetLastError(), "l2_f32_cand_kernel launch");
     int bpp = (max_n + 7) / 8;

@@ -139,7 +139,7 @@ prep_l2_f16_norm_kernel(const float* __restrict__ src, long long rows, int D, fl
 // fp32 accumulator of a 256-term dot product stays below 256); columns D..Dh-1 are zero
 __global__ void __launch_bounds__(256)
 prep_l2_f16_convert_kernel(const float* __restrict__ src, long long rows, int D, int Dh, __half* __restrict__ dst,
-                           float* __restrict__ info) {
+                           float* __restrict__ info, const float* __restrict__ norms, __half* __restrict__ xrows) {
     const float mx = __uint_as_float(*(const unsigned int*)(info + 2));
     int e = 0;
     if (mx > 0.0f) { frexpf(mx, &e); if (ldexpf(1.0f, e - 1) == mx) e -= 1; }     // mx <= 2^e, tight
@@ -152,6 +152,18 @@ prep_l2_f16_convert_kernel(const float* __restrict__ src, long long rows, int D,
         const int k = (int)(i - r * (Dh / 2)) * 2;
         const float a = k < D ? __ldg(src + r * D + k) * s : 0.0f, b = k + 1 < D ? __ldg(src + r * D + k + 1) * s : 0.0f;
         *reinterpret_cast<__half2*>(dst + r * Dh + k) = __floats2half2_rn(a, b);
+        if (k == 0) {                               // the row's folded norm: three fp16 terms of w = -(s^2 / 2) ||b||^2
+            const float w = -0.5f * s * s * norms[r];
+            const __half hi = __float2half_rn(w);
+            const float r1 = w - __half2float(hi);
+            const __half mid = __float2half_rn(r1);
+            const __half lo = __float2half_rn(r1 - __half2float(mid));
+            __half2* x = reinterpret_cast<__half2*>(xrows + r * 16);
+            x[0] = __halves2half2(hi, mid);
+            x[1] = __halves2half2(lo, __float2half_rn(0.0f));
+#pragma unroll
+            for (int j = 2; j < 8; ++j) x[j] = __floats2half2_rn(0.0f, 0.0f);
+        }
     }
 }
 
@@ -180,7 +192,8 @@ int b200m_prep_l2_f16(const float* src, int64_t rows, int D, void* aux, void* st
     const int Dh = b200m_f16_width(D);
     long long want = (rows * (long long)(Dh / 2) + 255) / 256;
     prep_l2_f16_convert_kernel<<<(unsigned)(want < 148 * 16 ? want : 148 * 16), 256, 0, st>>>(
-        src, rows, D, Dh, (__half*)((char*)aux + b200m_f16_half_off(rows)), info);
+        src, rows, D, Dh, (__half*)((char*)aux + b200m_f16_half_off(rows)), info, (const float*)aux,
+        (__half*)((char*)aux + b200m_f16_x_off(rows, D)));
     B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_f16_convert_kernel launch");
     b200m_count_launch(2);
     return B200M_OK;

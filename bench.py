@@ -530,9 +530,13 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    json_out = sys.stdout
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line (NCCL prints its version there)
+        # stdout must hold the ONE JSON line: NCCL prints its version banner on file descriptor 1 (at NCCL_DEBUG=VERSION and
+        # above, WARN included), so fd 1 is pointed at stderr for the run and the line goes to a saved copy of the real stdout
+        sys.stdout.flush()
+        json_out = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=device)
     eng = b.Engine(device)
     lib = eng.lib
@@ -695,7 +699,7 @@ def run_b200(args):
                                               "oracle/bf_oracle.cv2_match (restates EnhancedBFMatcher.match)"}
             if not args.no_also:
                 line["also"] = single_pair_extras(torch, b, eng, pk)
-        print(json.dumps(line))
+        print(json.dumps(line), file=json_out, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

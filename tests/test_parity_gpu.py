@@ -398,6 +398,11 @@ def test_l2_f16c_kind_is_default_and_identical_to_tf32():
     assert np.allclose(aux[:500], (a.astype(np.float64) ** 2).sum(1), rtol=1e-5)
     h = aux.view(np.uint8)[half_off:half_off + 500 * Dh * 2].view(np.float16).reshape(500, Dh)
     assert np.array_equal(h[:, :96], (a * s).astype(np.float16)) and not h[:, 96:].any()
+    # folded-norm rows behind the info words: three fp16 terms that sum to -(s^2 / 2) ||b||^2 (the fp32 value, exactly)
+    x_off = info_off + 256
+    x = aux.view(np.uint8)[x_off:x_off + 500 * 32].view(np.float16).reshape(500, 16).astype(np.float64)
+    assert not x[:, 3:].any()
+    assert np.array_equal(x[:, :3].sum(1).astype(np.float32), (np.float32(-0.5) * s * s * aux[:500]).astype(np.float32))
     cases = {"generic": (a, (a[rng.permutation(500)[:420]] + rng.normal(size=(420, 96)) * 0.5).astype(np.float32))}
     wide = (rng.normal(size=(400, 256)) * np.exp(rng.uniform(-14, 0, size=(1, 256)))).astype(np.float32)       # columns down to 1e-6
     cases["wide_range"] = (wide, (wide[rng.permutation(400)[:350]] * (1 + 0.01 * rng.normal(size=(350, 256)))).astype(np.float32))
@@ -405,6 +410,11 @@ def test_l2_f16c_kind_is_default_and_identical_to_tf32():
     cases["large"] = (big, (big[rng.permutation(300)] + rng.normal(size=(300, 128)) * 50).astype(np.float32))
     sp = synth.superpoint_set(seed=33, images=2, n=1800, d=256, pool=3000)
     cases["superpoint"] = (sp[0], sp[1])
+    # two stores with different scales: s_q / s_t = 2^-5 rides in the folded-norm step; 2^-14 is outside its gate (plain kernel)
+    cases["scale_ratio_32"] = (sp[0][:900], (sp[1][:1000] * 37.0).astype(np.float32))
+    cases["scale_ratio_gate"] = ((sp[0][:700] * 3.0e-4).astype(np.float32), (sp[1][:800] * 4.0).astype(np.float32))
+    d192 = synth.superpoint_set(seed=34, images=2, n=1100, d=192, pool=1700)
+    cases["d192"] = (d192[0], d192[1])
     for name, (x, y) in cases.items():
         for mode in [(False, 0.8), (True, None), (False, None)]:
             g16, g32 = e16.match_arrays(x, y, b.NORM_L2, *mode), e32.match_arrays(x, y, b.NORM_L2, *mode)

@@ -254,8 +254,16 @@ class StreamingAllPairs:
         np.cumsum(counts, out=offsets[1:])
         rows = int(offsets[-1])
         D = int(host.shape[1]) if host is not None else int(D)
-        if rank == 0:
+        if host is not None:
             assert host.dtype == torch.float32 and host.shape[0] == rows
+        # world > 1: when EVERY rank passes the host rows (each needs only the rows of the images it uploads), the upload is
+        # sharded -- rank k sends a 1/world block of each image group over its own PCIe link, re-encodes it and broadcasts the
+        # encoded rows from k; otherwise rank 0 uploads everything (839 MB per step on one link bounded the 8-GPU run)
+        sharded = False
+        if world > 1:
+            have = torch.tensor([1 if host is not None else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(have, op=dist.ReduceOp.MIN)
+            sharded = bool(have.item())
         mode = mode_of(cross_check, ratio_threshold)
         ratio = float(ratio_threshold or 0.0)
         cur = torch.cuda.current_stream(dev)
@@ -265,7 +273,7 @@ class StreamingAllPairs:
             mt._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
         cs = self._copy_stream
         key = (rows, D)
-        if rank == 0 and self._dev.get("key") != key:   # device staging buffer, reused across calls of the same shape
+        if (rank == 0 or sharded) and self._dev.get("key") != key:   # device staging buffer, reused across calls of the same shape
             self._dev = {"key": key, "f32": torch.empty((rows, D), dtype=torch.float32, device=dev)}
         cs.wait_stream(cur)
         with torch.cuda.stream(cs):
@@ -309,15 +317,30 @@ class StreamingAllPairs:
         for j_end, gp in plan:
             with torch.cuda.stream(cs):                  # upload + re-encode (+ broadcast) images [uploaded, j_end)
                 r0, r1 = int(offsets[uploaded]), int(offsets[j_end])
-                if rank == 0:
-                    f32 = self._dev["f32"]
-                    f32[r0:r1].copy_(host[r0:r1], non_blocking=True)
-                    eng.prepare_l2_i8_rows(dd, flag, f32[r0:r1], r0)
-                if world > 1:                            # encoded rows, their norms, fold digits and the info words
-                    aux = dd.norm
-                    for piece in (dd.desc[r0:r1], aux[r0:r1], aux[fold_off + r0 * 8:fold_off + r1 * 8],
-                                  aux[info_off:info_off + 8]):
-                        dist.broadcast(piece, src=0)     # enqueued after the prep on this stream; ordered on it
+                aux = dd.norm
+                if sharded:                              # image block k of the group belongs to rank k
+                    cuts = [uploaded + (j_end - uploaded) * k // world for k in range(world + 1)]
+                    a0, a1 = int(offsets[cuts[rank]]), int(offsets[cuts[rank + 1]])
+                    if a1 > a0:
+                        f32 = self._dev["f32"]
+                        f32[a0:a1].copy_(host[a0:a1], non_blocking=True)
+                        eng.prepare_l2_i8_rows(dd, flag, f32[a0:a1], a0)
+                    for k in range(world):               # every owner broadcasts its encoded rows, norms and fold digits
+                        b0, b1 = int(offsets[cuts[k]]), int(offsets[cuts[k + 1]])
+                        if b1 > b0:
+                            for piece in (dd.desc[b0:b1], aux[b0:b1], aux[fold_off + b0 * 8:fold_off + b1 * 8]):
+                                dist.broadcast(piece, src=k)
+                    # info words: the bias is a constant of the width (set on every rank); "digits usable" must hold for all rows
+                    dist.all_reduce(aux[info_off + 3:info_off + 4], op=dist.ReduceOp.MIN)
+                else:
+                    if rank == 0:
+                        f32 = self._dev["f32"]
+                        f32[r0:r1].copy_(host[r0:r1], non_blocking=True)
+                        eng.prepare_l2_i8_rows(dd, flag, f32[r0:r1], r0)
+                    if world > 1:                        # encoded rows, their norms, fold digits and the info words
+                        for piece in (dd.desc[r0:r1], aux[r0:r1], aux[fold_off + r0 * 8:fold_off + r1 * 8],
+                                      aux[info_off:info_off + 8]):
+                            dist.broadcast(piece, src=0)     # enqueued after the prep on this stream; ordered on it
                 ev = torch.cuda.Event()
                 ev.record(cs)
             uploaded = j_end
@@ -338,7 +361,10 @@ class StreamingAllPairs:
             cur.wait_stream(st)
         bad = flag.clone()
         if world > 1:
-            dist.broadcast(bad, src=0)
+            if sharded:
+                dist.all_reduce(bad, op=dist.ReduceOp.MAX)       # any rank's block held a non-integer element
+            else:
+                dist.broadcast(bad, src=0)
         cur.synchronize()                                # results are host arrays: the D2H copies must have landed
         if int(bad.item()) != 0:                         # not integer-valued: the int8 encoding is not exact -> generic path
             st2 = None

@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--chunk-pairs", type=int, default=2048)
     ap.add_argument("--cpu-sample-pairs", type=int, default=24)
     ap.add_argument("--no-also", action="store_true")
+    ap.add_argument("--e2e-upload", default="sharded", choices=["sharded", "rank0"],
+                    help="N > 1: every rank uploads its block of each image group (default) or rank 0 uploads everything")
     return ap.parse_args()
 
 
@@ -546,13 +548,15 @@ def run_b200(args):
     P = len(pairs)
 
     # ---- inputs: rank 0 synthesises float32 SIFT-like descriptors, prepares the int8 store, broadcasts it
+    # every rank holds the host rows (same seed): the e2e arm uploads 1/N of each image group per rank over its own PCIe link
     host_pinned = None
     store = None
-    if rank == 0:
+    if rank == 0 or args.e2e_upload == "sharded":
         desc = sift_set_gpu(torch, device, I, n)                       # [I, n, 128] float32 on the device
         host_pinned = torch.empty((I * n, D), dtype=torch.float32, pin_memory=True)
         host_pinned.copy_(desc.view(I * n, D))                          # the e2e arm starts from HOST buffers
-        store = ap.build_store(eng, desc.view(I * n, D), b.NORM_L2, counts=[n] * I)
+        if rank == 0:
+            store = ap.build_store(eng, desc.view(I * n, D), b.NORM_L2, counts=[n] * I)
         del desc
     if world > 1:
         store = ap.broadcast_store(store, b.NORM_L2, device)
@@ -686,9 +690,12 @@ def run_b200(args):
                         "path": ("pinned host float32 descriptors -> H2D in image groups on a copy stream -> b200m_prep_l2_i8_rows -> "
                                  "b200m_match_pairs_csr on the resident groups (two compute streams) -> per-chunk D2H of the CSR into pinned memory"
                                  if world == 1 else
-                                 "rank 0: pinned host float32 descriptors -> H2D in image groups -> b200m_prep_l2_i8_rows -> NCCL broadcast of the "
-                                 "encoded group; every rank: b200m_match_pairs_csr on its slice of the resident groups' pairs; gather of the CSRs to "
-                                 "rank 0 -> D2H")},
+                                 ("every rank: its 1/N block of each image group, pinned host float32 -> H2D on its own PCIe link -> "
+                                  "b200m_prep_l2_i8_rows -> NCCL broadcast of the encoded block from its owner; " if args.e2e_upload == "sharded" else
+                                  "rank 0: pinned host float32 descriptors -> H2D in image groups -> b200m_prep_l2_i8_rows -> NCCL broadcast of the "
+                                  "encoded group; ") +
+                                 "every rank: b200m_match_pairs_csr on its slice of the resident groups' pairs; gather of the CSRs to rank 0 -> D2H"),
+                        "upload": "n/a" if world == 1 else args.e2e_upload},
                 "gpu_launches": int(launches.item()), "clocks": clocks}
         if world == 1:
             imgs = host_sample_images(args, 4)

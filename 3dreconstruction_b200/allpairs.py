@@ -258,7 +258,8 @@ class StreamingAllPairs:
             assert host.dtype == torch.float32 and host.shape[0] == rows
         # world > 1: when EVERY rank passes the host rows (each needs only the rows of the images it uploads), the upload is
         # sharded -- rank k sends a 1/world block of each image group over its own PCIe link, re-encodes it and broadcasts the
-        # encoded rows from k; otherwise rank 0 uploads everything (839 MB per step on one link bounded the 8-GPU run)
+        # encoded rows from k; otherwise rank 0 uploads everything.  (Measured at 8 GPUs: no difference, 689k vs 696k pairs/s end to
+        # end -- the gather of the CSRs and their D2H after the last chunk, not the upload, is what the e2e step adds.)
         sharded = False
         if world > 1:
             have = torch.tensor([1 if host is not None else 0], dtype=torch.int32, device=dev)

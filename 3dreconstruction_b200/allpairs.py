@@ -438,7 +438,7 @@ def broadcast_store(store: Optional[Store], norm_type: int, device: torch.device
 
 
 def gather_csr(local: PairCSR, device: torch.device, dst: int = 0) -> Optional[PairCSR]:
-    """Variable-length gather of every rank's CSR to `dst` (all_gather of sizes, then send/recv)."""
+    """Variable-length gather of every rank's CSR to `dst` (all_gather of sizes, then one grouped send/recv exchange)."""
     import torch.distributed as dist
     rank, world = dist.get_rank(), dist.get_world_size()
     P = len(local.pairs)
@@ -447,26 +447,29 @@ def gather_csr(local: PairCSR, device: torch.device, dst: int = 0) -> Optional[P
     dist.all_gather(all_sizes, sizes)
     all_sizes = [tuple(int(v) for v in s.tolist()) for s in all_sizes]
     pairs_dev = torch.from_numpy(np.ascontiguousarray(local.pairs)).to(device)
+    # one grouped exchange (ncclGroup): posted one by one, the 5 x (world - 1) transfers ran serialised behind each other
     if rank != dst:
-        for t in (pairs_dev, local.ptr, local.query_idx, local.train_idx, local.distance):
-            if t.numel():
-                dist.send(t.contiguous(), dst=dst)
+        ops = [dist.P2POp(dist.isend, t.contiguous(), dst)
+               for t in (pairs_dev, local.ptr, local.query_idx, local.train_idx, local.distance) if t.numel()]
+        for req in (dist.batch_isend_irecv(ops) if ops else []):
+            req.wait()
         return None
+    bufs, ops = {}, []
+    for r in range(world):
+        Pr, Kr = all_sizes[r]
+        if r == dst:
+            continue
+        bufs[r] = (torch.empty((Pr, 2), dtype=torch.int32, device=device), torch.empty(Pr + 1, dtype=torch.int64, device=device),
+                   torch.empty(Kr, dtype=torch.int32, device=device), torch.empty(Kr, dtype=torch.int32, device=device),
+                   torch.empty(Kr, dtype=torch.float32, device=device))
+        ops += [dist.P2POp(dist.irecv, buf, r) for buf in bufs[r] if buf.numel()]
+    for req in (dist.batch_isend_irecv(ops) if ops else []):
+        req.wait()
     parts_pairs, parts_ptr, parts_q, parts_t, parts_d = [], [], [], [], []
     base = 0
     for r in range(world):
         Pr, Kr = all_sizes[r]
-        if r == dst:
-            pr, ptr, q, t, d = pairs_dev, local.ptr, local.query_idx, local.train_idx, local.distance
-        else:
-            pr = torch.empty((Pr, 2), dtype=torch.int32, device=device)
-            ptr = torch.empty(Pr + 1, dtype=torch.int64, device=device)
-            q = torch.empty(Kr, dtype=torch.int32, device=device)
-            t = torch.empty(Kr, dtype=torch.int32, device=device)
-            d = torch.empty(Kr, dtype=torch.float32, device=device)
-            for buf in (pr, ptr, q, t, d):
-                if buf.numel():
-                    dist.recv(buf, src=r)
+        pr, ptr, q, t, d = (pairs_dev, local.ptr, local.query_idx, local.train_idx, local.distance) if r == dst else bufs[r]
         parts_pairs.append(pr); parts_ptr.append(ptr[:Pr] + base); parts_q.append(q); parts_t.append(t); parts_d.append(d)
         base += Kr
     parts_ptr.append(torch.tensor([base], dtype=torch.int64, device=device))

@@ -142,3 +142,15 @@ def test_sfm_matches_verification_plumbing(eng):
         assert (H is None) == (v.homography(p) is None)
         if H is not None:
             assert h_close(v.H[p], H)
+
+
+def test_c_abi_argument_errors(eng):
+    """confidence outside (0, 1) is cv2's CV_Assert; the C-ABI answers B200M_EINVAL instead of running."""
+    L = importlib.import_module("3dreconstruction_b200._lib")
+    c = synth.homography_pair(seed=1, n=20)
+    for conf in (0.0, 1.0, 1.5):
+        with pytest.raises(L.B200MatchError) as ei:
+            verify.verify_pairs(c, np.array([0, 20], np.int64), 4.0, conf, 100, engine=eng)
+        assert ei.value.code == L.EINVAL
+    v = verify.verify_pairs(np.zeros((0, 4), np.float32), np.array([0], np.int64), engine=eng)      # no pairs at all
+    assert len(v.inliers) == 0 and len(v.mask) == 0

@@ -175,9 +175,11 @@ class SfMMatches:
 
 def match_feature_set(engine: Engine, fs: FeatureSet, pairs: Optional[np.ndarray] = None, cross_check: bool = False,
                       ratio_threshold: Optional[float] = None, chunk_pairs: int = 2048,
-                      matcher: Optional[AllPairsMatcher] = None) -> SfMMatches:
+                      matcher: Optional[AllPairsMatcher] = None, ransac: Optional[Tuple[float, float, int]] = None):
     """Match `pairs` (default: all i < j, the reference's pair_mode='all', image_manager.py:491-494) and gather the
-    matched keypoint coordinates on the device; one D2H of the finished arrays."""
+    matched keypoint coordinates on the device; one D2H of the finished arrays.
+    ransac = (threshold, confidence, max_iters): also verify every pair by RANSAC homography (N3) on the correspondences
+    while they are still in HBM; returns (SfMMatches, verify.Verification) instead of SfMMatches alone."""
     if pairs is None:
         pairs = all_pairs(len(fs.names))
     pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
@@ -195,9 +197,18 @@ def match_feature_set(engine: Engine, fs: FeatureSet, pairs: Optional[np.ndarray
                 fs.kp_xy.data_ptr(), int(fs.kp_xy.shape[0]), q_off.data_ptr(), t_off.data_ptr(), csr.ptr.data_ptr(),
                 len(pairs), csr.query_idx.data_ptr(), csr.train_idx.data_ptr(), corr.data_ptr(), engine._stream()),
                 "b200m_gather_correspondences")
+    ver = None
+    if ransac is not None:
+        from . import verify
+        ver = verify.verify_pairs_device(engine, corr[:K], csr.ptr, *ransac)
     h = csr.to_host()
-    return SfMMatches(fs.names, fs.sizes, pairs, h.ptr, h.query_idx, h.train_idx, h.distance, corr[:K].cpu().numpy(),
-                      method="BF", feature_type=fs.method)
+    res = SfMMatches(fs.names, fs.sizes, pairs, h.ptr, h.query_idx, h.train_idx, h.distance, corr[:K].cpu().numpy(),
+                     method="BF", feature_type=fs.method)
+    if ver is None:
+        return res
+    from . import verify
+    return res, verify.Verification(h.ptr, ver.H.cpu().numpy().reshape(-1, 3, 3), ver.mask.cpu().numpy(),
+                                    ver.inliers.cpu().numpy(), ver.iters.cpu().numpy())
 
 
 def match_all_pairs(features: Mapping[str, object], norm_type: int, cross_check: bool = False,

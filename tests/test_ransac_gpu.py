@@ -154,3 +154,31 @@ def test_c_abi_argument_errors(eng):
         assert ei.value.code == L.EINVAL
     v = verify.verify_pairs(np.zeros((0, 4), np.float32), np.array([0], np.int64), engine=eng)      # no pairs at all
     assert len(v.inliers) == 0 and len(v.mask) == 0
+
+
+def test_match_gather_verify_on_device(eng):
+    """sfm.match_feature_set(..., ransac=...): the verification of every pair equals verifying its correspondences alone;
+    images related by one perspective map give a model, unrelated ones few inliers."""
+    sfm = importlib.import_module("3dreconstruction_b200.sfm")
+    rng = np.random.default_rng(3)
+    n = 600
+    base = synth.binary_pair(seed=21, n=n, nbytes=32)[0]
+    xy0 = (rng.random((n, 2)) * [1600, 1200]).astype(np.float32)
+    Hm = np.array([[0.95, 0.04, 25.0], [-0.03, 1.02, -14.0], [1e-5, -2e-5, 1.0]])
+    q = np.c_[xy0, np.ones(n)] @ Hm.T
+    xy1 = (q[:, :2] / q[:, 2:]).astype(np.float32)
+    perm = rng.permutation(n)
+    d1 = base[perm].copy()
+    d1[:, 0] ^= 1                                               # same features, one bit flipped, shuffled
+    other = synth.binary_pair(seed=22, n=n, nbytes=32)[0]
+    F = b.contracts.FeatureData
+    feats = {"a": F(keypoints=xy0, descriptors=base, method="ORB"), "b": F(keypoints=xy1[perm], descriptors=d1, method="ORB"),
+             "c": F(keypoints=(rng.random((n, 2)) * [1600, 1200]).astype(np.float32), descriptors=other, method="ORB")}
+    fs = sfm.build_feature_set(eng, feats, b.NORM_HAMMING)
+    res, ver = sfm.match_feature_set(eng, fs, None, True, None, ransac=(3.0, 0.99, 2000))
+    assert len(res) == 3 and ver.inliers[0] == n and np.abs(ver.H[0] - Hm).max() < 1e-3 * np.abs(Hm).max()
+    for p in range(3):
+        s = res.pair_slice(p)
+        alone = verify.verify_pairs(res.correspondences[s], np.array([0, s.stop - s.start], np.int64), 3.0, 0.99, 2000, engine=eng)
+        assert np.array_equal(alone.mask, ver.mask[s]) and alone.inliers[0] == ver.inliers[p]
+    assert ver.inliers[1] < 30 and ver.inliers[2] < 30

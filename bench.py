@@ -275,10 +275,48 @@ def single_pair_extras(torch, b, eng, pk):
                         "note": "INT-pipe kernel (hamming.cu): single fused pass, row top-2 and column minima from the same distances"})
     out["orb_pair_10000x10000_crosscheck"] = {**orb["tensor"], "popc_path": orb["popc"],
                                               "speedup_over_popc_path": orb["popc"]["ms_per_pair"] / orb["tensor"]["ms_per_pair"]}
+    out.update(plugin_call_extras(torch, b, eng))
     out.update(allpairs_extras(torch, b, eng, pk))
     out.update(sfm_extras(torch, b, eng, pk))
     out.update(ransac_extras(torch, b, eng, pk))
     return out
+
+
+def plugin_call_extras(torch, b, eng):
+    """configs[0] through the drop-in plugin call a user of the reference makes: B200BFMatcher(norm, cross_check, ratio).match(
+    FeatureData, FeatureData) -> MatchData, HOST numpy descriptors in, a Python list of EnhancedDMatch out (wall clock: H2D, int8
+    re-encoding, kernels, D2H, the per-match Python objects).  Beside it the reference's way on this host: cv2.BFMatcher driven as
+    EnhancedBFMatcher.match drives it (arrays out; the reference then builds the same Python objects on top)."""
+    import time
+    a, c = b.synth.sift_pair(seed=0, n=8192)
+    F = b.contracts.FeatureData
+    f1, f2 = F(keypoints=list(range(len(a))), descriptors=a, method="SIFT"), F(keypoints=list(range(len(c))), descriptors=c, method="SIFT")
+    m = b.B200BFMatcher(norm_type=b.NORM_L2, cross_check=False, ratio_threshold=RATIO)
+    m._engine = eng
+    md = m.match(f1, f2)
+    torch.cuda.synchronize()
+    reps = 10
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        md = m.match(f1, f2)
+    ms = (time.perf_counter() - t0) / reps * 1e3
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        arr = m.match_arrays(a, c)
+    ms_arr = (time.perf_counter() - t0) / reps * 1e3
+    fn, cores, engine = cpu_match_fn()
+    fn(a, c)
+    t0 = time.perf_counter()
+    want = fn(a, c)
+    ms_cpu = (time.perf_counter() - t0) * 1e3
+    same = len(md.matches) == len(want.query_idx) and all(x.queryIdx == int(q) and x.trainIdx == int(t) for x, q, t in
+                                                          zip(md.matches, want.query_idx, want.train_idx))
+    return {"plugin_call_sift_pair_8192x8192": {
+        "ms_per_match_call": ms, "ms_per_match_arrays_call": ms_arr, "matches": len(md.matches),
+        "h2d_bytes_per_call": int(a.nbytes + c.nbytes), "reference_cpu_ms_per_call": ms_cpu, "reference_engine": engine,
+        "reference_threads": cores, "identical_to_reference": bool(same), "speedup": ms_cpu / ms,
+        "note": "B200BFMatcher.match(FeatureData, FeatureData) -> MatchData with host numpy descriptors (pageable): the drop-in call; "
+                "match_arrays = the same without building the list of EnhancedDMatch objects"}}
 
 
 def sfm_extras(torch, b, eng, pk):

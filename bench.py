@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--chunk-pairs", type=int, default=2048)
     ap.add_argument("--cpu-sample-pairs", type=int, default=24)
     ap.add_argument("--no-also", action="store_true")
+    ap.add_argument("--group-images", type=int, default=25, help="images per upload group of the e2e arm (StreamingAllPairs)")
     ap.add_argument("--e2e-upload", default="rank0", choices=["sharded", "rank0"],
                     help="N > 1: rank 0 uploads everything (default) or every rank uploads its block of each image group "
                          "(measured equal at N = 8: 689k vs 696k pairs/s -- the end-of-step CSR gather + D2H, not the upload, is the tail)")
@@ -664,7 +665,7 @@ def run_b200(args):
     value = P * args.steps / (ms_total / 1e3)
 
     # ---- end to end: HOST float32 descriptors -> H2D -> prep -> (broadcast) -> match -> (gather) -> D2H CSR
-    streaming = ap.StreamingAllPairs(eng, chunk_pairs=args.chunk_pairs)
+    streaming = ap.StreamingAllPairs(eng, chunk_pairs=args.chunk_pairs, group_images=args.group_images)
     matches_all = torch.tensor([matches_total], dtype=torch.int64, device=device)
     if world > 1:
         dist.all_reduce(matches_all, op=dist.ReduceOp.SUM)

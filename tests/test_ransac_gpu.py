@@ -218,3 +218,33 @@ def test_against_live_cv2_random_batch(eng):
                 assert np.abs(qa[:, :2] / qa[:, 2:] - qb[:, :2] / qb[:, 2:])[mc.ravel() > 0].max() <= 0.01, (thr, p)
     print("points at the threshold that flipped:", borderline)
     assert borderline <= 3
+
+
+def test_against_c_oracle_hard_batch(eng):
+    """120 pairs that need many iterations (inlier ratio 0.1..0.4, some capped at maxIters) in one launch against
+    oracle/ransac_oracle.c: iterations run, masks (same stated tolerance at the threshold), H."""
+    rng = np.random.default_rng(99)
+    sets = [synth.homography_pair(seed=int(rng.integers(1 << 30)), n=int(rng.integers(60, 700)), inlier_frac=float(rng.uniform(0.1, 0.4)))
+            for _ in range(120)]
+    ptr = np.zeros(len(sets) + 1, np.int64)
+    ptr[1:] = np.cumsum([len(s) for s in sets])
+    v = verify.verify_pairs(np.concatenate(sets), ptr, 3.0, 0.99, 1500, engine=eng)
+    borderline = 0
+    for p, c in enumerate(sets):
+        H, m, it = ro.find_homography_ransac_c(c[:, :2], c[:, 2:], 3.0, 0.99, 1500)
+        assert (H is None) == (v.inliers[p] < 0), p
+        if H is None:
+            continue
+        assert v.iters[p] == it, (p, v.iters[p], it)
+        s = slice(int(ptr[p]), int(ptr[p + 1]))
+        diff = np.flatnonzero(m.ravel() != v.mask[s])
+        if len(diff):
+            err = ro.compute_error(c[:, :2], c[:, 2:], H).astype(np.float64)[diff]
+            assert np.all(np.abs(err - 9.0) <= 9e-3), (p, err)
+            borderline += len(diff)
+        if not h_close(v.H[p], H):
+            a = np.c_[c[:, :2], np.ones(len(c))]
+            qa, qb = a @ v.H[p].T, a @ H.T
+            assert np.abs(qa[:, :2] / qa[:, 2:] - qb[:, :2] / qb[:, 2:])[m.ravel() > 0].max() <= 0.01, p
+    print("points at the threshold that flipped:", borderline)
+    assert borderline <= 3

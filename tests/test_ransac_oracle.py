@@ -71,3 +71,40 @@ def test_oracle_against_live_cv2():
         if Hc is not None:
             assert np.array_equal(mc, mo)
             assert np.abs(Hc - Ho).max() <= 1e-8 * np.abs(Hc).max()
+
+
+def test_c_oracle_reproduces_every_golden_case():
+    """oracle/ransac_oracle.c on all 12 outputs of the reference's function, the iteration-capped ones included."""
+    g = np.load(GOLD)
+    for name in [str(n) for n in g["names"]]:
+        c = g[name + "_corr"]
+        thr, conf, iters = g[name + "_params"]
+        H, mask, _ = ro.find_homography_ransac_c(c[:, :2], c[:, 2:], thr, conf, int(iters))
+        Hg = g[name + "_H"]
+        if np.isnan(Hg).any():
+            assert H is None, name
+            continue
+        assert np.array_equal(np.flatnonzero(mask.ravel()), g[name + "_kept"]), name
+        assert np.abs(H - Hg).max() <= 1e-8 * np.abs(Hg).max(), name
+
+
+def test_c_oracle_equals_python_oracle():
+    for seed, (n, inl, thr, iters) in enumerate([(150, 0.7, 4.0, 2000), (80, 0.5, 3.0, 300), (40, 0.9, 5.0, 2000), (6, 1.0, 5.0, 50)]):
+        c = synth.homography_pair(seed=90 + seed, n=n, inlier_frac=inl)
+        Hp, mp, itp = ro.ransac_homography(c[:, :2], c[:, 2:], thr, 0.99, iters)
+        H2, m2 = ro.find_homography_ransac(c[:, :2], c[:, 2:], thr, 0.99, iters)
+        Hc, mc, itc = ro.find_homography_ransac_c(c[:, :2], c[:, 2:], thr, 0.99, iters)
+        assert itc == itp and np.array_equal(mc, m2) and np.abs(Hc - H2).max() <= 1e-6 * np.abs(H2).max()   # numpy sums in another order
+
+
+def test_c_oracle_against_live_cv2_many():
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(7)
+    for _ in range(150):
+        c = synth.homography_pair(seed=int(rng.integers(1 << 30)), n=int(rng.integers(5, 900)), inlier_frac=float(rng.uniform(0.2, 0.95)))
+        thr = float(rng.choice([1.5, 3.0, 5.0]))
+        Hc, mc = cv2.findHomography(c[:, :2].reshape(-1, 1, 2), c[:, 2:].reshape(-1, 1, 2), cv2.RANSAC, thr, confidence=0.99, maxIters=2000)
+        H, m, _ = ro.find_homography_ransac_c(c[:, :2], c[:, 2:], thr, 0.99, 2000)
+        assert (Hc is None) == (H is None)
+        if Hc is not None:
+            assert np.array_equal(mc, m)

@@ -2,6 +2,7 @@
 // carve the caller's workspace, copy the pair table, enqueue the kernels.  No allocation, no
 // exceptions, no CPU compute path.
 #include <atomic>
+#include <mutex>
 #include <cstdio>
 #include <cstring>
 #include <vector>
@@ -37,19 +38,29 @@ static int choose_splits(int kind, int num_pairs, int max_n, int max_m, int mode
 
 // Optional device timing of the dominant (knn) kernels for bench.py's roofline: CUDA events recorded on
 // the launching stream around each knn launch, summed by b200m_timing_collect().
+// A measurement facility, not part of the data path: one process-wide list guarded by a mutex (the events themselves
+// belong to whichever device was current when they were created; bench.py drives one device per process).
+static std::mutex g_timing_mu;
 static bool g_timing = false;
 static std::vector<std::pair<cudaEvent_t, cudaEvent_t>> g_events;
 static size_t g_events_used = 0;
 
-static int g_sm_count = 0;
-static int device_sm_count() {
-    if (g_sm_count == 0) {
-        int dev = 0, sm = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-        if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-        g_sm_count = sm;
+static std::atomic<int> g_sm_count[B200M_MAX_DEVICES];      // per device ordinal; 0 = not queried yet
+bool b200m_current_device(int* dev_out, int* sm_out) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= B200M_MAX_DEVICES) return false;
+    int sm = g_sm_count[dev].load(std::memory_order_relaxed);
+    if (sm == 0) {
+        if (cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sm <= 0) return false;
+        g_sm_count[dev].store(sm, std::memory_order_relaxed);
     }
-    return g_sm_count;
+    if (dev_out) *dev_out = dev;
+    if (sm_out) *sm_out = sm;
+    return true;
+}
+static int device_sm_count() {
+    int sm = 0;
+    return b200m_current_device(nullptr, &sm) ? sm : 0;
 }
 
 // Lay the workspace out.  base may be null (size query).
@@ -59,6 +70,7 @@ static void make_plan(MatchPlan& pl, char* base, int kind, int mode, int num_pai
     pl.S = S; pl.total_n = total_n; pl.total_m = total_m; pl.total_pad = total_pad;
     pl.slices = kind == B200M_KIND_L2_I8 ? S * B200M_I8_GROUPS : S;
     const size_t SL = (size_t)pl.slices;
+    pl.flags = (int32_t*)(base + off); off = align_up(off + 64 * sizeof(int32_t), 256);
     pl.pairs = (DevPair*)(base + off); off = align_up(off + sizeof(DevPair) * (size_t)num_pairs, 256);
     pl.fwd = (Top2*)(base + off);      off = align_up(off + sizeof(Top2) * SL * total_n, 256);
     pl.bwd = (Top2*)(base + off);      off = align_up(off + (need_bwd ? sizeof(Top2) * SL * total_m : 0), 256);
@@ -107,12 +119,14 @@ int b200m_device_info(int* sm_count, int* cc_major, int* cc_minor) {
 }
 
 int b200m_timing_enable(int on) {
+    std::lock_guard<std::mutex> lk(g_timing_mu);
     g_timing = on != 0;
     g_events_used = 0;
     return B200M_OK;
 }
 
 int b200m_timing_collect(double* knn_ms, int* knn_launches) {
+    std::lock_guard<std::mutex> lk(g_timing_mu);
     double total = 0.0;
     for (size_t i = 0; i < g_events_used; ++i) {
         float ms = 0.f;
@@ -200,6 +214,11 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
     B200M_CUDA_CHECK(cudaMemcpyAsync(pl.pairs, dp.data(), sizeof(DevPair) * (size_t)num_pairs,
                                      cudaMemcpyHostToDevice, st), "pair table upload");
     // pageable source: the copy is staged before the call returns, so `dp` may go out of scope.
+    // MODE_RATIO on int8 rows: decide ONCE, on this stream, whether the fold kernel's digits cover the train store
+    const bool fold_ok = kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO;
+    if (fold_ok)
+        B200M_CUDA_CHECK(cudaMemcpyAsync(pl.flags, (const char*)t_norm + b200m_aux_info_off(t_rows) + 3 * sizeof(int32_t),
+                                         sizeof(int32_t), cudaMemcpyDeviceToDevice, st), "fold flag snapshot");
     pl.colmin = fused_cross ? (u32*)pl.bwd : nullptr;
     if (fused_cross)
         B200M_CUDA_CHECK(cudaMemsetAsync(pl.colmin, 0xFF, sizeof(u32) * (size_t)total_m, st), "colmin memset");
@@ -210,6 +229,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         int rc;
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (g_timing) {
+            std::lock_guard<std::mutex> lk(g_timing_mu);
             if (g_events_used == g_events.size()) {
                 cudaEvent_t a, b;
                 B200M_CUDA_CHECK(cudaEventCreate(&a), "event create");
@@ -232,7 +252,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
         } else if (kind == B200M_KIND_L2_I8)
             rc = launch_l2_i8_top2((const int8_t*)q_desc, (const int32_t*)q_norm, q_rows, (const int8_t*)t_desc,
                                    (const int32_t*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
-                                   back, mode == B200M_MODE_RATIO, out, rows, st);
+                                   back, fold_ok && !back ? pl.flags : nullptr, out, rows, st);
         else
             rc = launch_l2_f32_top2((const float*)q_desc, (const float*)q_norm, q_rows, (const float*)t_desc,
                                     (const float*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,
@@ -268,10 +288,11 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         return B200M_OK;
     }
     // L2_I8: the exact runner-up refinement (inside the winner's 64-column chunk) is fused into finalize.
-    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr};
+    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr};
     if (kind == B200M_KIND_L2_I8)
         rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D,
-                      mode == B200M_MODE_RATIO ? (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows)) : nullptr};
+                      (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows)),
+                      mode == B200M_MODE_RATIO ? pl.flags : nullptr};
     // CSR mode counts survivors in finalize (into out_count), scans them into tight offsets, then emits.
     const int tail_kind = kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING    // integer bit counts either way
                           : kind == B200M_KIND_L2_F16C ? B200M_KIND_L2_F32 : kind;                               // exact fp32 d^2 bits either way
@@ -315,9 +336,9 @@ int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q
                            B200M_MODE_NN, true, workspace, workspace_bytes, st, pl, max_n, max_npad);
     if (rc != B200M_OK) return rc;
     if (num_pairs == 0 || pl.total_n == 0) return B200M_OK;
-    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr};
+    RefineI8 rf = {nullptr, nullptr, nullptr, nullptr, 0, nullptr, nullptr};
     if (kind == B200M_KIND_L2_I8)
-        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D, nullptr};
+        rf = RefineI8{(const int8_t*)q_desc, (const int32_t*)q_norm, (const int8_t*)t_desc, (const int32_t*)t_norm, D, nullptr, nullptr};
     return launch_knn2_emit(kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? B200M_KIND_HAMMING
                             : kind == B200M_KIND_L2_F16C ? B200M_KIND_L2_F32 : kind, pl, num_pairs, max_n, idx1, idx2, d1, d2, rf, st);
 }

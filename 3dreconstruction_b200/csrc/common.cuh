@@ -67,6 +67,9 @@ struct DevPair {
 };
 
 struct MatchPlan {       // host-side carve-up of the caller's workspace
+    int32_t* flags;      // [64] per-call device words: [0] = snapshot of the train store's "fold digits usable" word, taken
+                         // on the call's stream before the knn launches, so that the keyed kernel, the fold kernel and
+                         // finalize all act on ONE decision even if another stream re-encodes rows of the store meanwhile
     DevPair* pairs;      // [P]
     Top2* fwd;           // [slices][total_n]
     Top2* bwd;           // [slices][total_m]   (MODE_CROSS)
@@ -93,6 +96,17 @@ __device__ __forceinline__ void top2_insert32(u32& k1, u32& k2, u32 k) {
 
 // host helpers implemented in capi.cu
 void b200m_count_launch(int n = 1);
+// One-time setup that is a fact of a DEVICE, not of the process (cudaFuncSetAttribute applies to the current device's
+// context only; cluster occupancy and SM counts differ between devices): every launcher keeps one of these per kernel
+// family, indexed by the ordinal of the current device, so an Engine("cuda:0") and an Engine("cuda:1") in one process
+// each get their own opt-in.  Two threads racing on the same device both run the (idempotent) setup.
+#define B200M_MAX_DEVICES 64
+struct B200mPerDevice {
+    int done[B200M_MAX_DEVICES];     // 0 = setup not run on this device yet
+    int val[B200M_MAX_DEVICES][12];  // whatever the setup measured (cluster sizes, resident cluster counts)
+};
+// ordinal and SM count of the current device; returns false when there is none (or the ordinal is out of range)
+bool b200m_current_device(int* dev, int* sm_count);
 int b200m_set_cuda_error(cudaError_t e, const char* where);
 #define B200M_CUDA_CHECK(expr, where)                                   \
     do {                                                                \
@@ -114,7 +128,7 @@ int launch_hamming_tc_resolve(const uint8_t* q_bits, const uint8_t* t_bits, int 
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows,
                       const int8_t* t_desc, const int32_t* t_norm, int64_t t_rows, int D,
                       const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
-                      bool allow_fold, Top2* out, long long total_rows, cudaStream_t st);
+                      const int32_t* fold_flag, Top2* out, long long total_rows, cudaStream_t st);
 int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
                        const float* t_desc, const float* t_norm, int64_t t_rows, int D,
                        const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
@@ -123,7 +137,8 @@ int b200m_f32_stats_read(unsigned long long out[2], bool reset);
 // L2_I8 descriptors for the fused exact runner-up refinement (null for the other kinds)
 struct RefineI8 {
     const int8_t* q_desc; const int32_t* q_norm; const int8_t* t_desc; const int32_t* t_norm; int D;
-    const int32_t* t_info;      // info words of the train store's aux block (fold kernel results iff t_info[3])
+    const int32_t* t_info;      // info words of the train store's aux block ([2] = fold bias, a constant of the width)
+    const int32_t* fold_flag;   // MatchPlan::flags: fold kernel results iff fold_flag[0] (null: keyed kernel results)
 };
 int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int num_pairs, int max_n,
                     int32_t* counts, const RefineI8& rf, cudaStream_t st);

@@ -478,11 +478,10 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
     }
     const int TN = tn_of(fp4);
     if (((long long)max_m + TN) >> 4 > KEY_LOW) return B200M_EUNSUPPORTED;
-    static bool attr_set = false;
-    static int cs_ok[2][5] = {{0, 0, 0, 0, 0}, {0, 0, 0, 0, 0}};   // max active 2-CTA clusters per format and K-block count (0: single CTAs)
+    static B200mPerDevice once;          // val[f4 * 5 + nkb] = max active 2-CTA clusters per format and K-block count (0: single CTAs)
     int dev = 0, sms = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (!b200m_current_device(&dev, &sms)) return B200M_ENODEVICE;
+    int (&cs_ok)[12] = once.val[dev];
     auto kern = [](int nkb_, int cs_, bool f4) -> const void* {
         if (f4) {
             switch (nkb_ * 2 + cs_ - 1) {
@@ -497,7 +496,7 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
             case 8: return (const void*)hamming_tc_kernel<4, 1, false>; default: return (const void*)hamming_tc_kernel<4, 2, false>;
         }
     };
-    if (!attr_set) {
+    if (!once.done[dev]) {
         for (int f4 = 0; f4 < 2; ++f4)
             for (int nk = 1; nk <= (f4 ? 2 : 4); ++nk) {
                 for (int cs = 1; cs <= 2; ++cs)
@@ -511,14 +510,14 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
                 qc.attrs = qa; qc.numAttrs = 1;
                 int nc = 0;
                 if (cudaOccupancyMaxActiveClusters(&nc, kern(nk, 2, f4), &qc) == cudaSuccess && nc * 2 >= sms && !getenv("B200M_NO_CLUSTER"))
-                    cs_ok[f4][nk] = nc;
+                    cs_ok[f4 * 5 + nk] = nc;
                 else
                     cudaGetLastError();
             }
-        attr_set = true;
+        once.done[dev] = 1;
     }
     CUtensorMap tq, tt;
-    const int cs = cs_ok[fp4][nkb] > 0 ? 2 : 1;
+    const int cs = cs_ok[(fp4 ? 5 : 0) + nkb] > 0 ? 2 : 1;
     int rc = b200m_make_tmap_2d(&tq, q_store, (uint64_t)q_rows, (uint64_t)Dpad, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
     rc = b200m_make_tmap_2d(&tt, t_store, (uint64_t)t_rows, (uint64_t)Dpad, TN / cs, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
@@ -531,7 +530,7 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = (unsigned)cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-    const long long max_units = cs == 2 ? cs_ok[fp4][nkb] : sms;
+    const long long max_units = cs == 2 ? cs_ok[(fp4 ? 5 : 0) + nkb] : sms;
     cfg.gridDim = dim3((unsigned)((items < max_units ? items : max_units) * cs));
     cfg.blockDim = dim3(THREADS);
     cfg.dynamicSmemBytes = smem_bytes(nkb, fp4);

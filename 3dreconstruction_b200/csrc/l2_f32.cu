@@ -658,22 +658,21 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
         rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D * 4, TN, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
     }
     if (rc != B200M_OK) return rc;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static B200mPerDevice once;
+    int dev = 0, sms = 0;
+    if (!b200m_current_device(&dev, &sms)) return B200M_ENODEVICE;
+    if (!once.done[dev]) {
 #define B200M_CAND_ATTR(H, M, F)                                                                                             \
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<H, M, F>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
                                               (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr")
         B200M_CAND_ATTR(false, 1, false); B200M_CAND_ATTR(false, 2, false); B200M_CAND_ATTR(true, 1, false);
         B200M_CAND_ATTR(true, 2, false); B200M_CAND_ATTR(true, 1, true); B200M_CAND_ATTR(true, 2, true);
 #undef B200M_CAND_ATTR
-        attr_set = true;
+        once.done[dev] = 1;
     }
     // two resident row tiles per work item when both fit (nkb <= 4) and the pairs are tall enough to fill the SMs that way
     static const int mt_env = getenv("B200M_F32_MT") ? atoi(getenv("B200M_F32_MT")) : 0;
     const int MTr = mt_env ? mt_env : 2;
-    int dev = 0, sms = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int MT = nabuf_of(nkb) == 2 && MTr == 2 && max_n > TM ? 2 : 1;
     if (MT == 2 && !mt_env && (long long)num_pairs * S * ((max_n + 2 * TM - 1) / (2 * TM)) < sms) MT = 1;   // too few items to fill the SMs
     int tiles_max = (max_n + TM * MT - 1) / (TM * MT);

@@ -127,8 +127,8 @@ __global__ void __launch_bounds__(THREADS, 1)
 l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const int32_t* __restrict__ q_norm, const int32_t* __restrict__ t_norm,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
-                  Top2* __restrict__ out, long long total_rows, const int32_t* __restrict__ fold_info) {
-    if (fold_info && __ldg(fold_info + 3)) return;      // MODE_RATIO with usable fold digits: l2_i8_fold_kernel runs instead
+                  Top2* __restrict__ out, long long total_rows, const int32_t* __restrict__ fold_flag) {
+    if (fold_flag && __ldg(fold_flag)) return;          // MODE_RATIO with usable fold digits (the call's snapshot): l2_i8_fold_kernel runs instead
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1 KiB alignment
     const SmemLayout sm = carve(smem, NKB);
@@ -429,10 +429,10 @@ __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // colu
 template <int NKB, int CS>
 __global__ void __launch_bounds__(FOLD_THREADS, 1)
 l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
-                  const __grid_constant__ CUtensorMap tmap_x, const int32_t* __restrict__ t_info,
+                  const __grid_constant__ CUtensorMap tmap_x, const int32_t* __restrict__ fold_flag,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S,
                   Top2* __restrict__ out, long long total_rows) {
-    if (__ldg(t_info + 3) == 0) return;            // digits do not cover this store: the keyed kernel runs instead
+    if (__ldg(fold_flag) == 0) return;             // digits do not cover this store (the call's snapshot): the keyed kernel runs instead
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const SmemFold sm = carve_fold(smem, NKB);
@@ -678,7 +678,8 @@ int b200m_make_tmap_2d_ex(CUtensorMap* out, const void* base, uint64_t rows, uin
 
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows, const int8_t* t_desc,
                       const int32_t* t_norm, int64_t t_rows, int D, const DevPair* pairs, int num_pairs, int max_n,
-                      int max_m, int S, bool backward, bool allow_fold, Top2* out, long long total_rows, cudaStream_t st) {
+                      int max_m, int S, bool backward, const int32_t* fold_flag, Top2* out, long long total_rows, cudaStream_t st) {
+    bool allow_fold = fold_flag != nullptr;        // MatchPlan::flags: [0] = this call's snapshot of "fold digits usable"
     if (D % KB_BYTES != 0) return B200M_EINVAL;
     const int nkb = D / KB_BYTES;
     if (nkb > 2) return B200M_EUNSUPPORTED;      // d^2 must stay < 2^24 (exact in fp32, as in cv2) and keys in int32
@@ -694,16 +695,12 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
     if (rc != B200M_OK) return rc;
     rc = b200m_make_tmap_2d(&tt, t_desc, (uint64_t)t_rows, (uint64_t)D, TN, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
-    // the train store's aux block (b200m_prep_l2_i8): fold digits + info words behind the norms
-    const int32_t* t_info = (const int32_t*)((const char*)t_norm + b200m_aux_info_off(t_rows));
     const size_t smem = smem_bytes(nkb);
-    static bool attr_set = false;
-    static int fold_cs = 1;                          // CTAs per cluster of the fold kernel (2 when the device co-schedules pairs)
-    static int fold_clusters = 0;
-    int dev = 0, sms = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (!attr_set) {
+    static B200mPerDevice once;                      // val[0] = CTAs per cluster of the fold kernel (2 when the device co-schedules pairs),
+    int dev = 0, sms = 0;                            // val[1] = resident 2-CTA clusters
+    if (!b200m_current_device(&dev, &sms)) return B200M_ENODEVICE;
+    if (!once.done[dev]) {
+        int fold_cs = 1, fold_clusters = 0;
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes(1)), "l2_i8 smem attr");
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_top2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -731,16 +728,18 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
         } else {
             cudaGetLastError();
         }
-        if (getenv("B200M_VERBOSE")) fprintf(stderr, "b200match: fold kernel clusters of %d (max active 2-CTA clusters %d, SMs %d)\n", fold_cs, nc, sms);
-        attr_set = true;
+        if (getenv("B200M_VERBOSE")) fprintf(stderr, "b200match: device %d: fold kernel clusters of %d (max active 2-CTA clusters %d, SMs %d)\n", dev, fold_cs, nc, sms);
+        once.val[dev][0] = fold_cs; once.val[dev][1] = fold_clusters;
+        once.done[dev] = 1;
     }
+    const int fold_cs = once.val[dev][0], fold_clusters = once.val[dev][1];
     int tiles_max = (max_n + TM - 1) / TM;
     long long total_items = (long long)num_pairs * S * tiles_max;
     if (total_items <= 0) return B200M_OK;
     unsigned grid = (unsigned)(total_items < sms ? total_items : sms);
     // Device-side dispatch (no host sync): with allow_fold both kernels are enqueued and exactly one of them
     // finds its precondition in t_info[3]; the other returns at once.
-    const int32_t* fold_info = allow_fold ? t_info : nullptr;
+    const int32_t* fold_info = allow_fold ? fold_flag : nullptr;
     if (nkb == 1)
         l2_i8_top2_kernel<1><<<grid, THREADS, smem, st>>>(tq, tt, q_norm, t_norm, pairs, total_items, tiles_max, S,
                                                           backward ? 1 : 0, out, total_rows, fold_info);
@@ -771,11 +770,11 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
         cfg.attrs = at; cfg.numAttrs = 1;
         cudaError_t e;
         if (cs == 2)
-            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 2>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows)
-                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 2>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows);
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 2>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 2>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows);
         else
-            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 1>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows)
-                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 1>, tq, tth, tx, t_info, pairs, fitems, groups, S, out, total_rows);
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 1>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 1>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows);
         b200m_count_launch();
         B200M_CUDA_CHECK(e, "l2_i8_fold_kernel launch");
     }

@@ -739,11 +739,13 @@ int b200m_ransac_homography(const float* corr_xyxy, const int64_t* ptr, int num_
     if (!(confidence > 0.0 && confidence < 1.0)) return B200M_EINVAL;            // CV_Assert in RANSACPointSetRegistrator::run
     if ((uintptr_t)corr_xyxy & 15) return B200M_EINVAL;
     constexpr size_t dyn = (size_t)SCRATCH_DOUBLES * TUPLES * sizeof(double);
-    static bool attr_set = false;                 // one process per GPU (as everywhere in this library)
-    if (!attr_set) {
+    static B200mPerDevice once;                   // the shared-memory opt-in is per device
+    int dev = 0;
+    if (!b200m_current_device(&dev, nullptr)) return B200M_ENODEVICE;
+    if (!once.done[dev]) {
         B200M_CUDA_CHECK(cudaFuncSetAttribute(ransac_homography_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn),
                          "ransac_homography_kernel smem attribute");
-        attr_set = true;
+        once.done[dev] = 1;
     }
     ransac_homography_kernel<<<(unsigned)num_pairs, RT, dyn, (cudaStream_t)stream>>>(
         (const float4*)corr_xyxy, (const long long*)ptr, num_pairs, (float)(thr * thr), confidence, max_iters, H_out, mask_out,

@@ -239,7 +239,7 @@ finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pa
     DevPair pr = pairs[p];
     const bool active = i < pr.n;
     Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
-    const bool fold = kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO && rf.t_info && __ldg(rf.t_info + 3);
+    const bool fold = kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO && rf.fold_flag && __ldg(rf.fold_flag);
     // S counts Top2 slices: splits x B200M_I8_GROUPS for the keyed L2_I8 kernel, splits x B200M_FOLD_SLICES when the fold kernel ran
     if (active) t = merge_splits(fwd, total_n, fold ? S / B200M_I8_GROUPS * B200M_FOLD_SLICES : S, pr.fwd_off + i);
     bool keep_fold = false;
@@ -452,12 +452,14 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
 int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
                      int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st) {
     if (num_pairs <= 0) return B200M_OK;
-    static bool attr_set = false;
+    static B200mPerDevice once;                           // the shared-memory opt-in is per device
     const int kMaxSmemKeys = 16384;                       // 128 KiB of 64-bit keys
-    if (!attr_set) {
+    int dev = 0;
+    if (!b200m_current_device(&dev, nullptr)) return B200M_ENODEVICE;
+    if (!once.done[dev]) {
         B200M_CUDA_CHECK(cudaFuncSetAttribute(sort_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               kMaxSmemKeys * (int)sizeof(u64)), "sort_emit smem attr");
-        attr_set = true;
+        once.done[dev] = 1;
     }
     // MODE_RATIO usually keeps a few percent of the rows: a 16 KiB slice (2048 keys) and 256 threads are enough, and such
     // a block fits beside a resident knn CTA of the next chunk.  Pairs that keep more (and the other modes, which keep

@@ -195,210 +195,23 @@ class AllPairsMatcher:
 
 
 class StreamingAllPairs:
-    """All pairs of ONE host-resident set of integer-valued float32 descriptors (SIFT), with the upload hidden
-    behind the matching: images go up in groups on a copy stream (pinned host -> HBM -> b200m_prep_l2_i8_rows),
-    and as soon as group g is resident the pairs (i < j, j in group g) are matched, chunk by chunk, on two
-    compute streams; each chunk's CSR goes back to pinned host memory as it completes.
+    """All pairs of ONE host-resident set of float32 descriptors with the upload hidden behind the matching.
+    Kept as the round-1 name of the end-to-end path: it now delegates to distributed.DistributedAllPairs (any
+    descriptor kind, 1..N GPUs, packed match records); see that module for the data path.
 
-    The result is a host PairCSR whose `pairs` are in PROCESSING order (by group of j, then j, then i) — the same
-    set as itertools.combinations, permuted (look a pair up through `pairs`).  Its arrays are views of a pinned
-    arena owned by this object: valid until the next match_host() call.
-    Single GPU only; anything that is not integer-valued 0..255 falls back to build_store + AllPairsMatcher."""
+    The result's `pairs` are in PROCESSING order (by group of j) -- the same set as itertools.combinations, permuted
+    (look a pair up through `pairs`).  Its arrays are views of a pinned arena owned by this object: valid until the
+    next match_host() call."""
 
-    def __init__(self, engine: Engine, chunk_pairs: int = 2048, group_images: int = 25):
+    def __init__(self, engine: Engine, chunk_pairs: int = 2048, group_images: int = 25, **kw):
+        from .distributed import DistributedAllPairs
         self.engine = engine
-        self.matcher = AllPairsMatcher(engine, chunk_pairs)
-        self.group_images = int(group_images)
-        self._copy_stream = None
-        self._pinned = {}
-        self._dev = {}
-
-    def _host_buf(self, name: str, numel: int, dtype) -> torch.Tensor:
-        t = self._pinned.get(name)
-        if t is None or t.numel() < numel:
-            new = torch.empty(max(numel, 1 << 22, 0 if t is None else 2 * t.numel()), dtype=dtype, pin_memory=True)
-            if t is not None:
-                torch.cuda.synchronize(self.engine.device)     # copies into the old arena must have landed
-                new[:t.numel()].copy_(t)           # growth keeps what is already there
-            self._pinned[name] = t = new
-        return t
-
-    @staticmethod
-    def group_major_pairs(num_images: int, group_images: int):
-        """[(j_end, pairs[K,2])]: for every group of images [j0, j_end), the pairs (i, j), i < j, j in the group."""
-        out = []
-        for j0 in range(0, num_images, group_images):
-            j1 = min(num_images, j0 + group_images)
-            js = np.arange(max(j0, 1), j1)
-            if len(js) == 0:
-                continue
-            i = np.concatenate([np.arange(0, j) for j in js])
-            j = np.repeat(js, js)
-            out.append((j1, np.stack([i, j], axis=1).astype(np.int32)))
-        return out
+        self.impl = DistributedAllPairs(engine, chunk_pairs=chunk_pairs, group_images=group_images, **kw)
 
     def match_host(self, host: Optional[torch.Tensor], counts: Sequence[int], ratio_threshold: Optional[float] = None,
-                   cross_check: bool = False, D: Optional[int] = None) -> Optional[PairCSR]:
-        """host: pinned float32 [sum(counts), D] (rank 0; other ranks pass None and D).  Under torch.distributed
-        (world > 1) rank 0 uploads and re-encodes each image group and broadcasts the encoded rows (NCCL) while every
-        rank matches its 1/world slice of the pairs of the groups already resident; the per-rank CSRs are gathered to
-        rank 0, which returns the host CSR (other ranks return None)."""
-        import torch.distributed as dist
-        eng, mt = self.engine, self.matcher
-        dev = eng.device
-        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
-        rank = dist.get_rank() if world > 1 else 0
-        counts = [int(c) for c in counts]
-        I = len(counts)
-        offsets = np.zeros(I + 1, np.int64)
-        np.cumsum(counts, out=offsets[1:])
-        rows = int(offsets[-1])
-        D = int(host.shape[1]) if host is not None else int(D)
-        if host is not None:
-            assert host.dtype == torch.float32 and host.shape[0] == rows
-        # world > 1: when EVERY rank passes the host rows (each needs only the rows of the images it uploads), the upload is
-        # sharded -- rank k sends a 1/world block of each image group over its own PCIe link, re-encodes it and broadcasts the
-        # encoded rows from k; otherwise rank 0 uploads everything.  (Measured at 8 GPUs: no difference, 689k vs 696k pairs/s end to
-        # end -- the gather of the CSRs and their D2H after the last chunk, not the upload, is what the e2e step adds.)
-        sharded = False
-        if world > 1:
-            have = torch.tensor([1 if host is not None else 0], dtype=torch.int32, device=dev)
-            dist.all_reduce(have, op=dist.ReduceOp.MIN)
-            sharded = bool(have.item())
-        mode = mode_of(cross_check, ratio_threshold)
-        ratio = float(ratio_threshold or 0.0)
-        cur = torch.cuda.current_stream(dev)
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(device=dev)
-        if mt._streams is None:
-            mt._streams = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)]
-        cs = self._copy_stream
-        key = (rows, D)
-        if (rank == 0 or sharded) and self._dev.get("key") != key:   # device staging buffer, reused across calls of the same shape
-            self._dev = {"key": key, "f32": torch.empty((rows, D), dtype=torch.float32, device=dev)}
-        cs.wait_stream(cur)
-        with torch.cuda.stream(cs):
-            dd, flag = eng.alloc_l2_i8_store(rows, D)
-        store = Store(dd, offsets, NORM_L2)
-        for st in mt._streams:
-            st.wait_stream(cur)
-        fold_off = (rows * 4 + 255) // 256 * 256 // 4   # aux block layout (csrc/common.cuh), in int32 words
-        info_off = fold_off + (rows * 32 + 255) // 256 * 256 // 4
-
-        plan = self.group_major_pairs(I, self.group_images)
-        if world > 1:                                    # every rank takes a contiguous 1/world slice of each group's pairs
-            plan = [(j_end, np.array_split(gp, world)[rank]) for j_end, gp in plan]
-        P = sum(len(p) for _, p in plan)
-        ptr_host = np.zeros(P + 1, np.int64)
-        pairs_out = np.concatenate([p for _, p in plan]) if plan else np.zeros((0, 2), np.int32)
-        state = {"base": 0, "pbase": 0}
-        dev_out = {"q": [], "t": [], "d": [], "p": []}  # world > 1: per-chunk device results, gathered at the end
-
-        def finish(slot, C, optr, oq, ot, od):
-            st = mt._streams[slot]
-            with torch.cuda.stream(st):
-                cnts = optr[:C + 1].cpu().numpy()      # waits for this chunk only
-                total = int(cnts[C])
-                b0 = state["base"]
-                if world == 1:
-                    for name, src, dt in (("q", oq, torch.int32), ("t", ot, torch.int32), ("d", od, torch.float32)):
-                        self._host_buf(name, b0 + total, dt)[b0:b0 + total].copy_(src[:total], non_blocking=True)
-                else:
-                    for name, src in (("q", oq), ("t", ot), ("d", od)):
-                        t = src[:total].clone()
-                        t.record_stream(cur)
-                        dev_out[name].append(t)
-            ptr_host[state["pbase"]:state["pbase"] + C] = cnts[:C] + b0
-            state["base"] = b0 + total
-            state["pbase"] += C
-
-        pending = None
-        ci = 0
-        uploaded = 0                                     # images whose upload + prep (+ broadcast) is enqueued
-        for j_end, gp in plan:
-            with torch.cuda.stream(cs):                  # upload + re-encode (+ broadcast) images [uploaded, j_end)
-                r0, r1 = int(offsets[uploaded]), int(offsets[j_end])
-                aux = dd.norm
-                if sharded:                              # image block k of the group belongs to rank k
-                    cuts = [uploaded + (j_end - uploaded) * k // world for k in range(world + 1)]
-                    a0, a1 = int(offsets[cuts[rank]]), int(offsets[cuts[rank + 1]])
-                    if a1 > a0:
-                        f32 = self._dev["f32"]
-                        f32[a0:a1].copy_(host[a0:a1], non_blocking=True)
-                        eng.prepare_l2_i8_rows(dd, flag, f32[a0:a1], a0)
-                    for k in range(world):               # every owner broadcasts its encoded rows, norms and fold digits
-                        b0, b1 = int(offsets[cuts[k]]), int(offsets[cuts[k + 1]])
-                        if b1 > b0:
-                            for piece in (dd.desc[b0:b1], aux[b0:b1], aux[fold_off + b0 * 8:fold_off + b1 * 8]):
-                                dist.broadcast(piece, src=k)
-                    # info words: the bias is a constant of the width (set on every rank); "digits usable" must hold for all rows
-                    dist.all_reduce(aux[info_off + 3:info_off + 4], op=dist.ReduceOp.MIN)
-                else:
-                    if rank == 0:
-                        f32 = self._dev["f32"]
-                        f32[r0:r1].copy_(host[r0:r1], non_blocking=True)
-                        eng.prepare_l2_i8_rows(dd, flag, f32[r0:r1], r0)
-                    if world > 1:                        # encoded rows, their norms, fold digits and the info words
-                        for piece in (dd.desc[r0:r1], aux[r0:r1], aux[fold_off + r0 * 8:fold_off + r1 * 8],
-                                      aux[info_off:info_off + 8]):
-                            dist.broadcast(piece, src=0)     # enqueued after the prep on this stream; ordered on it
-                ev = torch.cuda.Event()
-                ev.record(cs)
-            uploaded = j_end
-            for st in mt._streams:
-                st.wait_event(ev)
-            for c0 in range(0, len(gp), mt.chunk_pairs):
-                slot = ci & 1
-                ci += 1
-                with torch.cuda.stream(mt._streams[slot]):
-                    job = mt._enqueue_chunk(store, gp[c0:c0 + mt.chunk_pairs], mode, ratio, slot,
-                                            mt._streams[slot].cuda_stream)
-                if pending is not None:
-                    finish(*pending)
-                pending = (slot, *job)
-        if pending is not None:
-            finish(*pending)
-        for st in mt._streams + [cs]:
-            cur.wait_stream(st)
-        bad = flag.clone()
-        if world > 1:
-            if sharded:
-                dist.all_reduce(bad, op=dist.ReduceOp.MAX)       # any rank's block held a non-integer element
-            else:
-                dist.broadcast(bad, src=0)
-        cur.synchronize()                                # results are host arrays: the D2H copies must have landed
-        if int(bad.item()) != 0:                         # not integer-valued: the int8 encoding is not exact -> generic path
-            st2 = None
-            if rank == 0:
-                st2 = build_store(eng, host.to(dev), NORM_L2, counts=counts)
-            if world > 1:
-                st2 = broadcast_store(st2, NORM_L2, dev)
-            r = self.matcher.match(st2, pairs_out, cross_check, ratio_threshold)
-            if world > 1:
-                r = gather_csr(r, dev)
-            return r.to_host() if r is not None else None
-        total = state["base"]
-        ptr_host[P] = total
-        if world == 1:
-            q = self._host_buf("q", total, torch.int32)[:total].numpy()
-            t = self._host_buf("t", total, torch.int32)[:total].numpy()
-            d = self._host_buf("d", total, torch.float32)[:total].numpy()
-            return PairCSR(pairs_out, ptr_host, q, t, d)
-        cat = lambda xs, dt: torch.cat(xs) if xs else torch.empty(0, dtype=dt, device=dev)   # noqa: E731
-        local = PairCSR(pairs_out, torch.from_numpy(ptr_host).to(dev), cat(dev_out["q"], torch.int32),
-                        cat(dev_out["t"], torch.int32), cat(dev_out["d"], torch.float32))
-        full = gather_csr(local, dev)
-        if full is None:
-            return None
-        K = int(full.query_idx.numel())                  # rank 0: D2H into the pinned arena (pageable copies are ~3x slower)
-        outs = []
-        for name, src, dt in (("q", full.query_idx, torch.int32), ("t", full.train_idx, torch.int32),
-                              ("d", full.distance, torch.float32)):
-            hb = self._host_buf(name, K, dt)[:K]
-            hb.copy_(src, non_blocking=True)
-            outs.append(hb)
-        ptr = full.ptr.cpu().numpy()                     # synchronises the stream: the copies above have landed
-        return PairCSR(full.pairs, ptr, outs[0].numpy(), outs[1].numpy(), outs[2].numpy())
+                   cross_check: bool = False, D: Optional[int] = None, norm_type: int = NORM_L2, **kw):
+        dtype = torch.uint8 if norm_type == NORM_HAMMING else torch.float32
+        return self.impl.match_host(host, counts, norm_type, cross_check, ratio_threshold, D=D, dtype=dtype, **kw)
 
 
 # ---------------------------------------------------------------------------------- multi-GPU

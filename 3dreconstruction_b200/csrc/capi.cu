@@ -270,9 +270,16 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
                             const void* t_desc, const void* t_norm, int64_t t_rows, int D,
                             const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
                             int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count, int64_t* out_ptr,
-                            void* workspace, size_t workspace_bytes, void* stream) {
+                            void* workspace, size_t workspace_bytes, void* stream, int rec_format = 0, void* out_rec = nullptr) {
     if (mode != B200M_MODE_RATIO && mode != B200M_MODE_CROSS && mode != B200M_MODE_NN) return B200M_EINVAL;
-    if (num_pairs > 0 && (!out_q || !out_t || !out_d || !out_count)) return B200M_EINVAL;
+    if (num_pairs > 0 && !out_count) return B200M_EINVAL;
+    if (num_pairs > 0 && (rec_format ? !out_rec : (!out_q || !out_t || !out_d))) return B200M_EINVAL;
+    if (rec_format == B200M_REC_Q16T16D32 || rec_format == B200M_REC_Q16T16D16) {
+        for (int p = 0; p < num_pairs; ++p)                  // 16-bit row indices
+            if (pairs_host && (pairs_host[p].n > 65536 || pairs_host[p].m > 65536)) return B200M_EUNSUPPORTED;
+        const bool ham = kind == B200M_KIND_HAMMING || kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4;
+        if (rec_format == B200M_REC_Q16T16D16 && (!ham || D > 8191)) return B200M_EUNSUPPORTED;   // the distance must be a bit count < 2^16
+    }
     cudaStream_t st = (cudaStream_t)stream;
     MatchPlan pl; int max_n = 0, max_npad = 1;
     int rc = run_knn_stage(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs,
@@ -302,7 +309,8 @@ static int match_pairs_impl(int kind, const void* q_desc, const void* q_norm, in
         rc = launch_scan_offsets(pl, out_count, num_pairs, (long long*)out_ptr, st);
         if (rc != B200M_OK) return rc;
     }
-    return launch_sort_emit(mode, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, out_ptr ? out_count : nullptr, st);
+    return launch_sort_emit(mode, pl, num_pairs, max_npad, out_q, out_t, out_d, out_count, out_ptr ? out_count : nullptr, st,
+                            rec_format, out_rec);
 }
 
 int b200m_match_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
@@ -322,6 +330,21 @@ int b200m_match_pairs_csr(int kind, const void* q_desc, const void* q_norm, int6
     if (num_pairs >= 0 && !out_ptr) return B200M_EINVAL;
     return match_pairs_impl(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs, mode,
                             ratio, out_q, out_t, out_d, out_count, out_ptr, workspace, workspace_bytes, stream);
+}
+
+int b200m_rec_bytes(int rec_format) {
+    return rec_format == B200M_REC_Q32T32D32 ? 12 : rec_format == B200M_REC_Q16T16D32 ? 8 : rec_format == B200M_REC_Q16T16D16 ? 6 : 0;
+}
+
+int b200m_match_pairs_rec(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                          const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                          const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                          int rec_format, void* out_rec, int32_t* out_count, int64_t* out_ptr,
+                          void* workspace, size_t workspace_bytes, void* stream) {
+    if (b200m_rec_bytes(rec_format) == 0 || (num_pairs >= 0 && !out_ptr)) return B200M_EINVAL;
+    if (((uintptr_t)out_rec & 7)) return B200M_EINVAL;
+    return match_pairs_impl(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs, mode, ratio,
+                            nullptr, nullptr, nullptr, out_count, out_ptr, workspace, workspace_bytes, stream, rec_format, out_rec);
 }
 
 int b200m_knn2_pairs(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,

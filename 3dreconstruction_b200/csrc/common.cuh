@@ -145,6 +145,7 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
 int launch_scan_offsets(const MatchPlan& plan, const int32_t* counts, int num_pairs, long long* out_ptr,
                         cudaStream_t st);
 int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
-                     int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st);
+                     int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st,
+                     int rec_format = 0, void* out_rec = nullptr);
 int launch_knn2_emit(int kind, const MatchPlan& plan, int num_pairs, int max_n, int32_t* idx1, int32_t* idx2,
                      float* d1, float* d2, const RefineI8& rf, cudaStream_t st);

@@ -19,6 +19,9 @@ namespace {
 // the descriptor width (info[2], set by fold_init_kernel): the digit range is anchored at the largest possible h,
 // so it covers every row whose norm is above ~13 % of the maximum (SIFT-like rows always are); a row below that
 // clears info[3] and the matcher then uses the keyed kernel for this store.
+// FROM_I8: the int8 rows are already in `dst` (they arrived from another rank, allpairs.DistributedAllPairs); only the norms,
+// digits and info words are (re)computed from them -- every rank derives identical aux data, no second collective.
+template <bool FROM_I8>
 __global__ void __launch_bounds__(256)
 prep_l2_i8_kernel(const float* __restrict__ src, long long row0, long long rows, int D, int8_t* __restrict__ dst, int Dpad,
                   int32_t* __restrict__ norms, int8_t* __restrict__ fold, int32_t* __restrict__ not_integer,
@@ -34,6 +37,11 @@ prep_l2_i8_kernel(const float* __restrict__ src, long long row0, long long rows,
     int acc = 0, bad = 0;
     // Dpad is a multiple of 128: each lane converts 4 consecutive elements per step.
     for (int k = lane * 4; k < Dpad; k += 128) {
+        if constexpr (FROM_I8) {
+            const u32 w = *reinterpret_cast<const u32*>(d + k);
+            acc = __dp4a((int)w, (int)w, acc);          // sum of squares of four int8
+            continue;
+        }
         int v[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -81,7 +89,7 @@ prep_l2_i8_kernel(const float* __restrict__ src, long long row0, long long rows,
     }
     if (lane == 0) {
         if (valid) norms[row] = acc;
-        if (bad) atomicOr(not_integer, 1);
+        if (!FROM_I8 && bad) atomicOr(not_integer, 1);
         if (!fits) atomicAnd(info + 3, 0);
         s_min[warp] = s_max[warp] = h;
     }
@@ -223,11 +231,28 @@ int b200m_prep_l2_i8_rows(const float* src, int64_t row_begin, int64_t row_count
     if (!src || !dst || !aux || !not_integer) return B200M_EINVAL;
     long long blocks = (row_count + 7) / 8;
     if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
-    prep_l2_i8_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+    prep_l2_i8_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
         src, row_begin, row_count, D, dst, Dpad, (int32_t*)aux, (int8_t*)aux + b200m_aux_fold_off(total_rows), not_integer,
         (int32_t*)((char*)aux + b200m_aux_info_off(total_rows)));
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_i8_kernel launch");
+    return B200M_OK;
+}
+
+int b200m_l2_i8_aux_rows(const int8_t* dst, int64_t row_begin, int64_t row_count, int64_t total_rows, int Dpad, void* aux,
+                         void* stream) {
+    if (row_begin < 0 || row_count < 0 || row_begin + row_count > total_rows || Dpad <= 0 || Dpad % 128 != 0 ||
+        ((uintptr_t)aux & 255) || ((uintptr_t)dst & 3))
+        return B200M_EINVAL;
+    if (row_count == 0) return B200M_OK;
+    if (!dst || !aux) return B200M_EINVAL;
+    long long blocks = (row_count + 7) / 8;
+    if (blocks > 0x7fffffffLL) return B200M_EUNSUPPORTED;
+    prep_l2_i8_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        nullptr, row_begin, row_count, Dpad, const_cast<int8_t*>(dst), Dpad, (int32_t*)aux,
+        (int8_t*)aux + b200m_aux_fold_off(total_rows), nullptr, (int32_t*)((char*)aux + b200m_aux_info_off(total_rows)));
+    b200m_count_launch();
+    B200M_CUDA_CHECK(cudaGetLastError(), "prep_l2_i8_kernel<from int8> launch");
     return B200M_OK;
 }
 

@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(1024)
 sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
                  const int32_t* __restrict__ tbest, int smem_keys, int32_t* __restrict__ out_q,
                  int32_t* __restrict__ out_t, float* __restrict__ out_d, int32_t* __restrict__ out_count,
-                 const int32_t* __restrict__ counts, int lo_count, int hi_count) {
+                 const int32_t* __restrict__ counts, int lo_count, int hi_count, int rec_format, void* __restrict__ out_rec) {
     // This launch handles the pairs with lo_count < survivors <= hi_count (two launches with different block shapes
     // split the pairs between them); `counts` (CSR mode: finalize's survivor counts) lets the others leave at once.
     extern __shared__ u64 skeys[];
@@ -396,9 +396,22 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
     for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
         u64 k = a[t];
         int q = (int)(u32)k;
-        out_q[pr.out_off + t] = q;
-        out_t[pr.out_off + t] = tbest[pr.fwd_off + q];
-        out_d[pr.out_off + t] = __uint_as_float((u32)(k >> 32));
+        const int tr = tbest[pr.fwd_off + q];
+        const u32 dbits = (u32)(k >> 32);
+        const long long o = pr.out_off + t;
+        if (rec_format == 0) {                               // three arrays (b200m_match_pairs / _csr)
+            out_q[o] = q;
+            out_t[o] = tr;
+            out_d[o] = __uint_as_float(dbits);
+        } else if (rec_format == B200M_REC_Q32T32D32) {      // one record per match (b200m_match_pairs_rec)
+            int32_t* r = (int32_t*)out_rec + 3 * o;
+            r[0] = q; r[1] = tr; r[2] = (int32_t)dbits;
+        } else if (rec_format == B200M_REC_Q16T16D32) {
+            ((uint2*)out_rec)[o] = make_uint2((u32)q | ((u32)tr << 16), dbits);
+        } else {                                             // B200M_REC_Q16T16D16: Hamming bit counts are small integers
+            unsigned short* r = (unsigned short*)out_rec + 3 * o;
+            r[0] = (unsigned short)q; r[1] = (unsigned short)tr; r[2] = (unsigned short)(int)__uint_as_float(dbits);
+        }
     }
     if (threadIdx.x == 0) out_count[blockIdx.x] = cnt;
 }
@@ -450,7 +463,8 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
 }
 
 int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npad, int32_t* out_q,
-                     int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st) {
+                     int32_t* out_t, float* out_d, int32_t* out_count, const int32_t* counts, cudaStream_t st,
+                     int rec_format, void* out_rec) {
     if (num_pairs <= 0) return B200M_OK;
     static B200mPerDevice once;                           // the shared-memory opt-in is per device
     const int kMaxSmemKeys = 16384;                       // 128 KiB of 64-bit keys
@@ -469,12 +483,13 @@ int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npa
     const int big_threads = max_npad >= 2048 ? 1024 : (max_npad >= 512 ? 256 : 64);
     if (few) {
         sort_emit_kernel<<<num_pairs, 256, 2048 * sizeof(u64), st>>>(plan.pairs, plan.sortbuf, plan.tbest, 2048, out_q, out_t,
-                                                                     out_d, out_count, counts, -1, 2048);
+                                                                     out_d, out_count, counts, -1, 2048, rec_format, out_rec);
         b200m_count_launch();
         B200M_CUDA_CHECK(cudaGetLastError(), "sort_emit_kernel launch");
     }
     sort_emit_kernel<<<num_pairs, big_threads, (size_t)big_keys * sizeof(u64), st>>>(
-        plan.pairs, plan.sortbuf, plan.tbest, big_keys, out_q, out_t, out_d, out_count, counts, few ? 2048 : -1, 0x7fffffff);
+        plan.pairs, plan.sortbuf, plan.tbest, big_keys, out_q, out_t, out_d, out_count, counts, few ? 2048 : -1, 0x7fffffff,
+        rec_format, out_rec);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "sort_emit_kernel launch");
     return B200M_OK;

@@ -30,8 +30,10 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 RATIO = 0.75
-HW_INT8_TOPS = 4590.0
-NCU_DRAM_BYTES_PER_PAIR = (468.655872e6 + 539.030272e6) / 1128.0     # profiles/r01_l2i8_v8_fold_ncu_full.md      # measured issue-rate peak of tcgen05.mma kind::i8 (tools/mma_peak.cu)
+HW_INT8_TOPS = 4590.0                 # burst issue-rate peak of tcgen05.mma kind::i8 at 1965 MHz (tools/mma_peak.cu, profiles/r01_mma_peak_microbench.txt)
+HW_INT8_TOPS_SUSTAINED = 3730.0       # the same instruction stream back to back for 6 s: the chip settles at its 1000 W cap,
+                                      # SM clock ~1540 MHz (profiles/r01_mma_int8_sustained.txt) -- SURVEY 8(d)'s "measured int8 peak"
+NCU_DRAM_BYTES_PER_PAIR = (191.9e6 + 111.4e6) / 1128.0     # ncu --set full of the shipped fold kernel (profiles/r01_l2i8_v9_fold_cluster_ncu_full.md)
 
 
 def parse_args():
@@ -45,10 +47,15 @@ def parse_args():
     ap.add_argument("--chunk-pairs", type=int, default=2048)
     ap.add_argument("--cpu-sample-pairs", type=int, default=24)
     ap.add_argument("--no-also", action="store_true")
-    ap.add_argument("--group-images", type=int, default=25, help="images per upload group of the e2e arm (StreamingAllPairs)")
-    ap.add_argument("--e2e-upload", default="rank0", choices=["sharded", "rank0"],
-                    help="N > 1: rank 0 uploads everything (default) or every rank uploads its block of each image group "
-                         "(measured equal at N = 8: 689k vs 696k pairs/s -- the end-of-step CSR gather + D2H, not the upload, is the tail)")
+    ap.add_argument("--group-images", type=int, default=24, help="images per upload group of the e2e arm (StreamingAllPairs)")
+    ap.add_argument("--e2e-upload", default="auto", choices=["auto", "sharded", "rank0"],
+                    help="N > 1: every rank uploads its block of each image group over its own PCIe link (default) or rank 0 uploads everything")
+    ap.add_argument("--e2e-gather", default="rank0", choices=["rank0", "local"],
+                    help="N > 1: match records return to rank 0 by NCCL, streamed per image group (default), or stay in every rank's host memory")
+    ap.add_argument("--no-parity", action="store_true", help="skip the element-wise check of the e2e result against the resident path")
+    ap.add_argument("--workload", default="sift", choices=["sift", "akaze"],
+                    help="sift: BASELINE configs[3] (the headline); akaze: configs[4], binary all-pairs with mutual check "
+                         "(--images 1000 --keypoints 16384 for the full configuration)")
     return ap.parse_args()
 
 
@@ -601,7 +608,7 @@ def run_b200(args):
     # every rank holds the host rows (same seed): the e2e arm uploads 1/N of each image group per rank over its own PCIe link
     host_pinned = None
     store = None
-    if rank == 0 or args.e2e_upload == "sharded":
+    if rank == 0 or args.e2e_upload != "rank0":
         desc = sift_set_gpu(torch, device, I, n)                       # [I, n, 128] float32 on the device
         host_pinned = torch.empty((I * n, D), dtype=torch.float32, pin_memory=True)
         host_pinned.copy_(desc.view(I * n, D))                          # the e2e arm starts from HOST buffers
@@ -664,38 +671,29 @@ def run_b200(args):
     ms_total = float(ms.item())
     value = P * args.steps / (ms_total / 1e3)
 
-    # ---- end to end: HOST float32 descriptors -> H2D -> prep -> (broadcast) -> match -> (gather) -> D2H CSR
-    streaming = ap.StreamingAllPairs(eng, chunk_pairs=args.chunk_pairs, group_images=args.group_images)
+    # ---- end to end: HOST float32 descriptors -> H2D -> prep -> all-gather -> match -> gather to rank 0 -> D2H records
+    dmod = importlib.import_module("3dreconstruction_b200.distributed")
+    streaming = dmod.DistributedAllPairs(eng, chunk_pairs=args.chunk_pairs, group_images=args.group_images,
+                                         gather=args.e2e_gather, upload=args.e2e_upload)
     matches_all = torch.tensor([matches_total], dtype=torch.int64, device=device)
     if world > 1:
         dist.all_reduce(matches_all, op=dist.ReduceOp.SUM)
     matches_all = int(matches_all.item())
+    last = {}
 
-    def e2e_step():
-        if streaming is not None:         # upload in image groups (rank 0), hidden behind the matching of resident groups
-            h = streaming.match_host(host_pinned, [n] * I, ratio_threshold=RATIO, D=D)
-            if rank != 0:
-                return 0
-            if int(h.ptr[-1]) != matches_all or len(h.pairs) != P:
-                raise RuntimeError(f"e2e path found {int(h.ptr[-1])} matches, device-resident path {matches_all}")
-            return h.ptr.nbytes + h.query_idx.nbytes + h.train_idx.nbytes + h.distance.nbytes
-        st = None
-        if rank == 0:
-            dev_desc = host_pinned.to(device, non_blocking=True)
-            st = ap.build_store(eng, dev_desc, b.NORM_L2, counts=[n] * I)
-        if world > 1:
-            st = ap.broadcast_store(st, b.NORM_L2, device)
-        r = matcher.match(st, mine, cross_check=False, ratio_threshold=RATIO)
-        if world > 1:
-            r = ap.gather_csr(r, device)
-        if rank == 0:
-            h = r.to_host()
-            return h.ptr.nbytes + h.query_idx.nbytes + h.train_idx.nbytes + h.distance.nbytes
-        return 0
+    def e2e_step(timing=False):
+        h = streaming.match_host(host_pinned, [n] * I, b.NORM_L2, False, RATIO, D=D, dtype=torch.float32, timing=timing)
+        if h is None:
+            return 0
+        last["h"] = h
+        if args.e2e_gather == "rank0" and (int(h.ptr[-1]) != matches_all or len(h.pairs) != P):
+            raise RuntimeError(f"e2e path found {int(h.ptr[-1])} matches, device-resident path {matches_all}")
+        return h.nbytes
 
     e2e_step()
+    e2e_step()
     barrier()
-    e2e_steps = max(1, min(args.steps, 3))
+    e2e_steps = max(1, args.steps)
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         d2h = e2e_step()
@@ -704,12 +702,33 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
     e2e_value = P * e2e_steps / float(t_e2e.item())
+    e2e_step(timing=True)                                  # one more step with per-phase CUDA events (outside the timed region)
+    barrier()
+    phases = dict(streaming.last_phases)
+    ph_all = [None] * world
+    if world > 1:
+        dist.all_gather_object(ph_all, phases)
+    else:
+        ph_all = [phases]
+    # element-wise parity of the sharded end-to-end result with the single-GPU resident path (rank 0 matches ALL pairs once)
+    parity = None
+    if rank == 0 and args.e2e_gather == "rank0" and not args.no_parity:
+        full = matcher.match(store, pairs, cross_check=False, ratio_threshold=RATIO).to_host()
+        h = last["h"].sorted_by_pair()
+        same = (np.array_equal(h.pairs, pairs) and np.array_equal(h.ptr, full.ptr) and np.array_equal(h.rec["q"], full.query_idx)
+                and np.array_equal(h.rec["t"], full.train_idx)
+                and np.array_equal(h.rec["d"].view(np.uint32), full.distance.view(np.uint32)))
+        if not same:
+            raise RuntimeError("end-to-end (sharded) result differs from the single-GPU resident result")
+        parity = f"identical to the single-GPU resident result: {len(pairs)} pairs, ptr, queryIdx, trainIdx, distance bits of {int(full.ptr[-1])} matches"
+        del full, h
 
     if rank == 0:
         my_pairs = len(mine)
         ops = 2.0 * n * n * D * my_pairs * args.steps                 # int8 MACs x2, rank 0's share
         achieved = ops / (knn_ms.value / 1e3) / 1e12 if knn_ms.value > 0 else None
-        peak = 2.0 * pk["bf16_tflops_sustained"]
+        peak = HW_INT8_TOPS_SUSTAINED
+        peak_bf16x2 = 2.0 * pk["bf16_tflops_sustained"]
         line = {"metric": "image pairs/s (SIFT-L2 all-pairs, knn k=2 + ratio 0.75)", "value": value, "unit": "pairs/s",
                 "gdist_per_s": value * n * n / 1e9, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -718,7 +737,12 @@ def run_b200(args):
                 "roofline": {"bound": "tensor", "kernel": "l2_i8_fold_kernel (tcgen05 kind::i8 M128 N256; 4 descriptor K-steps + 1 folded-norm K-step, "
                                                         "achieved counts the 4 algorithmic ones)", "achieved": achieved,
                              "peak": peak, "unit": "TOP/s int8 (TFLOP/s-equivalent)", "frac": achieved / peak if achieved else None,
-                             "peak_source": f"2 x bf16_tflops_sustained of {pk_src} MEASURED_PEAKS.json (int8 peak not measured by the driver)",
+                             "peak_source": "measured int8 tensor peak of this pool's B200, sustained under the 1000 W power cap: tools/mma_peak.cu, "
+                                            "back-to-back tcgen05.mma kind::i8 M128 N256 for 6 s (profiles/r01_mma_int8_sustained.txt); SURVEY 8(d) "
+                                            "prescribes the measured int8 peak once it exists, 2 x bf16_tflops_sustained before that (kept beside it)",
+                             "peak_2x_bf16_sustained": peak_bf16x2,
+                             "frac_of_2x_bf16_sustained": achieved / peak_bf16x2 if achieved else None,
+                             "peak_2x_bf16_source": f"2 x bf16_tflops_sustained of {pk_src} MEASURED_PEAKS.json",
                              "peak_hw_int8_microbench": HW_INT8_TOPS,
                              "frac_of_hw_int8_microbench": achieved / HW_INT8_TOPS if achieved else None,
                              "peak_hw_source": "tools/mma_peak.cu on this pool's B200: back-to-back tcgen05.mma kind::i8 M128 N256, "
@@ -732,20 +756,30 @@ def run_b200(args):
                              "algorithmic_ops_per_pair": 2.0 * n * n * D,
                              "algorithmic_hbm_bytes_per_pair": 2 * n * (D + 36) + 64 * n,
                              "traffic": NCU_DRAM_BYTES_PER_PAIR * my_pairs * args.steps / max(knn_launches.value, 1),
-                             "traffic_source": "ncu --set full of l2_i8_fold_kernel, 1128-pair launch: dram read 468.7 MB + write 539.0 MB "
-                                               "(profiles/r01_l2i8_v8_fold_ncu_full.md) = 0.893 MB/pair, scaled to this run's pairs per launch; "
-                                               "the write side is the 4 x 16 B Top2 slices per query row (0.52 MB/pair)"},
+                             "traffic_source": "ncu --set full of the shipped l2_i8_fold_kernel, 1128-pair launch: dram read 191.9 MB + write 111.4 MB "
+                                               "(profiles/r01_l2i8_v9_fold_cluster_ncu_full.md) = 0.269 MB/pair, scaled to this run's pairs per launch; "
+                                               "below the algorithmic bytes because the store's rows are re-read from L2 (hit rate 99 %)"},
                 "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel() * 4),
-                        "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
-                        "path": ("pinned host float32 descriptors -> H2D in image groups on a copy stream -> b200m_prep_l2_i8_rows -> "
-                                 "b200m_match_pairs_csr on the resident groups (two compute streams) -> per-chunk D2H of the CSR into pinned memory"
-                                 if world == 1 else
+                        "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * float(t_e2e.item()) / e2e_steps,
+                        "record_bytes_per_match": 8,
+                        "path": ("distributed.DistributedAllPairs.match_host: pinned host float32 descriptors -> H2D in image groups on a copy "
+                                 "stream -> b200m_prep_l2_i8_rows -> b200m_match_pairs_rec on the resident groups (two compute streams) -> "
+                                 "per-chunk D2H of packed 8-byte records into pinned memory" if world == 1 else
                                  ("every rank: its 1/N block of each image group, pinned host float32 -> H2D on its own PCIe link -> "
-                                  "b200m_prep_l2_i8_rows -> NCCL broadcast of the encoded block from its owner; " if args.e2e_upload == "sharded" else
-                                  "rank 0: pinned host float32 descriptors -> H2D in image groups -> b200m_prep_l2_i8_rows -> NCCL broadcast of the "
-                                  "encoded group; ") +
-                                 "every rank: b200m_match_pairs_csr on its slice of the resident groups' pairs; gather of the CSRs to rank 0 -> D2H"),
-                        "upload": "n/a" if world == 1 else args.e2e_upload},
+                                  "b200m_prep_l2_i8_rows -> ONE in-place NCCL all-gather of the int8 rows per group -> norms / fold digits "
+                                  "derived locally (b200m_l2_i8_aux_rows); " if args.e2e_upload != "rank0" else
+                                  "rank 0: pinned host float32 descriptors -> H2D in image groups -> b200m_prep_l2_i8_rows -> NCCL broadcast "
+                                  "of the int8 rows per group -> aux derived locally; ") +
+                                 "every rank: b200m_match_pairs_rec on its slice of the resident groups' pairs; per group, one group behind the "
+                                 "matching: NCCL send of the packed records to rank 0 -> D2H into pinned memory" +
+                                 ("" if args.e2e_gather == "rank0" else " [gather=local: every rank keeps its records in its own host memory]")),
+                        "upload": "n/a" if world == 1 else ("sharded" if args.e2e_upload != "rank0" else "rank0"),
+                        "gather": "n/a" if world == 1 else args.e2e_gather, "group_images": args.group_images,
+                        "parity_vs_single_gpu": parity,
+                        "phases_rank0": ph_all[0],
+                        "phases_max_over_ranks": {k: max(p.get(k, 0.0) for p in ph_all) for k in ph_all[0]},
+                        "phases_note": "CUDA events per phase over one extra step (sum of the phase's spans on its own stream; phases overlap): "
+                                       "front_ms = call start -> first matching kernel, tail_ms = last matching kernel -> last byte in host memory"},
                 "gpu_launches": int(launches.item()), "clocks": clocks}
         if world == 1:
             imgs = host_sample_images(args, 4)

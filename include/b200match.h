@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B200M_VERSION 140
+#define B200M_VERSION 200
 
 #if defined(__GNUC__)
 #define B200M_API __attribute__((visibility("default")))
@@ -102,6 +102,11 @@ B200M_API int b200m_prep_l2_i8(const float* src, int64_t rows, int D, int8_t* ds
  * b200m_prep_l2_i8_rows() per piece: src = float32 [row_count, D] (the piece only), written to rows
  * [row_begin, row_begin + row_count) of dst / aux.  b200m_prep_l2_i8 == init + one piece of all rows. */
 B200M_API int b200m_l2_i8_aux_init(void* aux, int64_t total_rows, int D, void* stream);
+/* Norms, fold digits and info words of rows [row_begin, row_begin + row_count) recomputed from int8 rows that are ALREADY
+ * in dst (they were encoded on another GPU and arrived by NCCL all-gather): every rank derives identical aux data from
+ * the rows themselves, so the descriptor rows are the only thing that crosses NVLink.  After b200m_l2_i8_aux_init. */
+B200M_API int b200m_l2_i8_aux_rows(const int8_t* dst, int64_t row_begin, int64_t row_count, int64_t total_rows, int Dpad,
+                     void* aux, void* stream);
 B200M_API int b200m_prep_l2_i8_rows(const float* src, int64_t row_begin, int64_t row_count, int64_t total_rows,
                      int D, int8_t* dst, int Dpad, void* aux, int32_t* not_integer, void* stream);
 
@@ -172,6 +177,25 @@ B200M_API int b200m_match_pairs_csr(int kind, const void* q_desc, const void* q_
                           const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
                           int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
                           int64_t* out_ptr, void* workspace, size_t workspace_bytes, void* stream);
+
+/* The same with ONE record per match instead of three arrays, so that a block of matches is one contiguous byte range
+ * (one device-to-host copy, one NCCL message) and the 1000-image binary workload moves 6 instead of 12 bytes per match
+ * (SURVEY 7.2(6)).  Replaces the per-match EnhancedDMatch objects of feature_matchers.py:213-238 as a wire format.
+ *   rec_format  B200M_REC_Q32T32D32: {int32 queryIdx, int32 trainIdx, float32 distance}           12 bytes
+ *               B200M_REC_Q16T16D32: {uint16 queryIdx, uint16 trainIdx, float32 distance}          8 bytes, n, m <= 65536
+ *               B200M_REC_Q16T16D16: {uint16 queryIdx, uint16 trainIdx, uint16 distance}           6 bytes, Hamming kinds only
+ *                                    (the distance is a bit count), n, m <= 65536; else B200M_EUNSUPPORTED
+ *   out_rec     records of pair p at [out_ptr[p], out_ptr[p+1]) (record index), capacity sum(pair.n), 8-byte aligned
+ * Order inside a pair: (distance asc, queryIdx asc), as b200m_match_pairs. */
+#define B200M_REC_Q32T32D32 1
+#define B200M_REC_Q16T16D32 2
+#define B200M_REC_Q16T16D16 3
+B200M_API int b200m_rec_bytes(int rec_format);
+B200M_API int b200m_match_pairs_rec(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                          const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                          const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                          int rec_format, void* out_rec, int32_t* out_count, int64_t* out_ptr,
+                          void* workspace, size_t workspace_bytes, void* stream);
 
 /* Raw k=2 neighbours per query row (what cv2.BFMatcher.knnMatch(k=2) returns at :210), for
  * parity checks of the knn stage itself.  Arrays of length sum(pair.n), pair p at out_off:

@@ -29,7 +29,7 @@ def test_header_symbols_all_exported():
 
 def test_version_and_error_strings():
     lib = b._lib.load()
-    assert lib.b200m_version() == 140
+    assert lib.b200m_version() == 200
     assert lib.b200m_error_string(0) == b"ok"
     assert b"workspace" in lib.b200m_error_string(-2)
     assert b"CPU" in lib.b200m_error_string(-4)

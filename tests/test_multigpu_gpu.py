@@ -1,0 +1,129 @@
+"""Multi-rank GPU parity: the sharded end-to-end path of 3dreconstruction_b200/distributed.py under
+NCCL, world size 2 (spawned from pytest, one process per GPU), compared ELEMENT-WISE — pairs, ptr, queryIdx, trainIdx,
+distance bits — with the single-GPU resident path (allpairs.AllPairsMatcher) and with the oracle, pair by pair, in the
+reference's pair order (itertools.combinations, /root/reference/FeatureMatchingExtraction/image_manager.py:491-494).
+Skipped on a box with fewer than two GPUs (run it with `gpurun --gpus 2`)."""
+import itertools
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import bf_oracle as O
+
+pytestmark = pytest.mark.gpu
+b = pkg()
+synth = b.synth
+SIZES = [300, 129, 1, 640, 77, 256, 18, 500, 64, 333]
+
+
+def _case_images(case):
+    if case.startswith("sift"):
+        imgs = [synth.sift_pair(seed=260 + i, n=max(s, 2))[0][:s] for i, s in enumerate(SIZES)]
+        imgs[3][:200] = np.clip(imgs[0][:200] + np.random.default_rng(1).integers(-4, 5, size=(200, 128)), 0, 255)
+        imgs[5][:60] = imgs[1][:60]
+        if case == "sift_late_low_norm":          # an all-128 row (norm 0 after the -128 shift) in the LAST image only:
+            imgs[-1][7] = 128.0                   # the fold digits stop covering the store once that group is encoded
+        return imgs, b.NORM_L2, (False, 0.8)
+    if case == "superpoint":
+        full = synth.superpoint_set(seed=81, images=len(SIZES), n=max(SIZES), d=256, pool=900, shared=0.6)
+        return [np.ascontiguousarray(full[i][:s]) for i, s in enumerate(SIZES)], b.NORM_L2, (True, None)
+    nb = 32 if case.startswith("orb") else 61
+    imgs = [synth.binary_pair(seed=270 + i, n=max(s, 2), nbytes=nb)[0][:s] for i, s in enumerate(SIZES)]
+    imgs[3][:200] = imgs[0][:200]
+    imgs[3][:200, 0] ^= 1
+    return imgs, b.NORM_HAMMING, ((False, 0.7) if case == "orb_ratio" else (True, None))
+
+
+CASES = ["sift", "sift_late_low_norm", "orb_cross", "orb_ratio", "akaze_cross", "superpoint"]
+VARIANTS = [dict(upload="auto", gather="rank0"), dict(upload="rank0", gather="rank0"), dict(upload="auto", gather="local")]
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        D = pkg("distributed")
+        eng = b.Engine(dev)
+        for case in CASES:
+            imgs, norm, (cc, ratio) = _case_images(case)
+            host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+            for vi, var in enumerate(VARIANTS):
+                dap = D.DistributedAllPairs(eng, chunk_pairs=5, group_images=4, **var)
+                for rep in range(2):                              # twice: buffer / arena reuse
+                    give = host if (var["upload"] != "rank0" or rank == 0) else None
+                    r = dap.match_host(give, SIZES, norm, cc, ratio, D=host.shape[1], dtype=host.dtype, timing=rep == 1)
+                    if r is not None:
+                        tag = f"{case}_v{vi}_r{rep}" + (f"_rank{rank}" if var["gather"] == "local" else "")
+                        q, t, d = r.rec["q"].astype(np.int32), r.rec["t"].astype(np.int32), r.rec["d"].astype(np.float32)
+                        np.savez(os.path.join(out_dir, tag + ".npz"), pairs=r.pairs, ptr=r.ptr, q=q, t=t, d=d)
+                    else:
+                        assert var["gather"] == "rank0" and rank != 0
+                if rank == 0:
+                    assert dap.last_phases.get("total_ms", 0) > 0 and "match_ms" in dap.last_phases
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.fixture(scope="module")
+def sharded_results(tmp_path_factory):
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    out = str(tmp_path_factory.mktemp("sharded"))
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    return out
+
+
+def _load(path):
+    z = np.load(path)
+    return {k: z[k] for k in z.files}
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_sharded_equals_single_gpu_and_oracle(sharded_results, case):
+    ap = pkg("allpairs")
+    imgs, norm, mode = _case_images(case)
+    want_pairs = list(itertools.combinations(range(len(SIZES)), 2))
+    eng = b.Engine("cuda:0")
+    store = ap.build_store(eng, imgs, norm)
+    single = ap.AllPairsMatcher(eng, chunk_pairs=7).match(store, ap.all_pairs(len(imgs)), *mode).to_host()
+    exact = case != "superpoint"
+    for vi, var in enumerate(VARIANTS):
+        for rep in range(2):
+            if var["gather"] == "local":
+                parts = [_load(os.path.join(sharded_results, f"{case}_v{vi}_r{rep}_rank{r}.npz")) for r in range(2)]
+                z = {"pairs": np.concatenate([p["pairs"] for p in parts]),
+                     "ptr": np.concatenate([[0], np.cumsum(np.concatenate([np.diff(p["ptr"]) for p in parts]))]),
+                     **{k: np.concatenate([p[k] for p in parts]) for k in "qtd"}}
+            else:
+                z = _load(os.path.join(sharded_results, f"{case}_v{vi}_r{rep}.npz"))
+            assert sorted(map(tuple, z["pairs"])) == want_pairs, (case, var)          # every pair once, none lost
+            assert z["ptr"][0] == 0 and z["ptr"][-1] == len(z["q"]) == len(z["t"]) == len(z["d"])
+            where = {tuple(p): k for k, p in enumerate(z["pairs"])}
+            for p, (i, j) in enumerate(want_pairs):
+                k = where[(i, j)]
+                s, e = int(z["ptr"][k]), int(z["ptr"][k + 1])
+                gq, gt, gd = z["q"][s:e], z["t"][s:e], z["d"][s:e]
+                sq, st_, sd = single.pair(p)
+                what = f"{case} {var} rep {rep} pair {i},{j}"
+                # the sharded run against the single-GPU resident run: element-wise, bit for bit
+                assert np.array_equal(gq, sq) and np.array_equal(gt, st_), what
+                assert np.array_equal(gd.view(np.uint32), sd.view(np.uint32)), what
+                if exact and rep == 0 and vi == 0:                 # and against the oracle
+                    w = O.reference_match(imgs[i], imgs[j], O.NORM_HAMMING if norm == b.NORM_HAMMING else O.NORM_L2, *mode)
+                    assert np.array_equal(gq, w.query_idx) and np.array_equal(gt, w.train_idx), what
+                    assert np.array_equal(gd.view(np.uint32), w.distance.view(np.uint32)), what

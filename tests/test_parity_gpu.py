@@ -524,6 +524,68 @@ def test_streaming_all_pairs_non_integer_falls_back_to_generic_path(eng):
         assert_close_float(O.Matches(*res.pair(p)), want, f"streaming fallback pair {i},{j}", 0.05)
 
 
+def test_streaming_late_low_norm_row_switches_kernels_consistently(eng):
+    """a row whose norm falls outside the fold digits' range arrives only with the LAST image group, while
+    chunks of earlier groups are in flight.  Every chunk must act on one snapshot of the store's flag (capi.cu): the
+    results stay exact whichever kernel each chunk ran."""
+    ap = pkg("allpairs")
+    sizes = [200, 150, 128, 90, 260, 64]
+    imgs = [synth.sift_pair(seed=190 + i, n=max(s, 2))[0][:s] for i, s in enumerate(sizes)]
+    imgs[-1][5] = 128.0                         # x - 128 = 0 everywhere: norm 0, far below the digit range
+    imgs[-1][6] = 0.0                           # and the other extreme (every element -128)
+    host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+    for group, chunk in [(1, 2), (2, 3), (5, 100)]:
+        res = ap.StreamingAllPairs(eng, chunk_pairs=chunk, group_images=group).match_host(host, sizes, ratio_threshold=0.85)
+        for p, (i, j) in enumerate(res.pairs):
+            want = O.reference_match(imgs[i], imgs[j], O.NORM_L2, False, 0.85)
+            assert_exact(O.Matches(*res.pair(p)), want, f"late low-norm row: pair {i},{j} group={group} chunk={chunk}")
+
+
+@pytest.mark.parametrize("kind,fmt", [("orb", None), ("akaze61", None), ("orb", 1), ("sift", 1), ("sift", 2), ("superpoint", None)])
+def test_end_to_end_host_path_all_kinds_and_record_formats(eng, kind, fmt):
+    """distributed.DistributedAllPairs on one GPU: host rows in, packed records out (6 / 8 / 12 bytes per match), every pair
+    against the oracle; with a consumer and keep=False (the streamed mode of the 1000-image workload) the blocks handed
+    over are the same records."""
+    import itertools
+    D = pkg("distributed")
+    sizes = [300, 129, 1, 640, 77, 256, 18]
+    if kind == "sift":
+        imgs = [synth.sift_pair(seed=160 + i, n=max(s, 2))[0][:s] for i, s in enumerate(sizes)]
+        norm, mode = b.NORM_L2, (False, 0.8)
+    elif kind == "superpoint":
+        full = synth.superpoint_set(seed=80, images=len(sizes), n=max(sizes), d=256, pool=900, shared=0.6)
+        imgs = [np.ascontiguousarray(full[i][:s]) for i, s in enumerate(sizes)]
+        norm, mode = b.NORM_L2, (True, None)
+    else:
+        nb = 32 if kind == "orb" else 61
+        imgs = [synth.binary_pair(seed=70 + i, n=max(s, 2), nbytes=nb)[0][:s] for i, s in enumerate(sizes)]
+        imgs[3][:200] = imgs[0][:200]
+        norm, mode = b.NORM_HAMMING, (True, None)
+    host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+    dap = D.DistributedAllPairs(eng, chunk_pairs=4, group_images=3, rec_format=fmt)
+    res = dap.match_host(host, sizes, norm, *mode, timing=True)
+    want_fmt = fmt or (3 if norm == b.NORM_HAMMING else 2)
+    assert res.rec_format == want_fmt and res.rec.dtype.itemsize == {1: 12, 2: 8, 3: 6}[want_fmt]
+    assert sorted(map(tuple, res.pairs)) == list(itertools.combinations(range(len(sizes)), 2))
+    assert dap.last_phases["total_ms"] > 0 and dap.last_phases["h2d_ms"] > 0
+    onorm = O.NORM_HAMMING if norm == b.NORM_HAMMING else O.NORM_L2
+    for p, (i, j) in enumerate(res.pairs):
+        want = O.reference_match(imgs[i], imgs[j], onorm, *mode)
+        if kind == "superpoint":
+            assert_close_float(O.Matches(*res.pair(p)), want, f"e2e {kind} pair {i},{j}", 0.02)
+        else:
+            assert_exact(O.Matches(*res.pair(p)), want, f"e2e {kind} fmt={fmt} pair {i},{j}")
+    got = []
+    r2 = dap.match_host(host, sizes, norm, *mode, keep=False,
+                        consumer=lambda pr, cn, rec: got.append((pr.copy(), cn.copy(), rec.copy())))
+    assert len(r2.rec) == 0 and np.array_equal(r2.ptr, res.ptr) and np.array_equal(r2.pairs, res.pairs)
+    assert np.array_equal(np.concatenate([g[0] for g in got]), res.pairs)
+    assert np.array_equal(np.concatenate([g[1] for g in got]), np.diff(res.ptr))
+    assert np.array_equal(np.concatenate([g[2] for g in got]), res.rec)
+    s = res.sorted_by_pair()
+    assert [tuple(x) for x in s.pairs] == list(itertools.combinations(range(len(sizes)), 2)) and s.ptr[-1] == res.ptr[-1]
+
+
 # ------------------------------------------------------------------ SfM hand-off (feature cache -> all pairs -> correspondences)
 @pytest.mark.parametrize("name", ["orb_cross", "orb_ratio07", "sift_ratio075"])
 def test_sfm_handoff_equals_reference_converter(eng, name):

@@ -12,7 +12,8 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get("B200MATCH_SO") or os.path.join(HERE, "libb200match.so")   # override: experiment builds only
 
-OK, EINVAL, EWORKSPACE, ECUDA, ENODEVICE, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
+OK, EINVAL, EWORKSPACE, ECUDA, ENODEVICE, EUNSUPPORTED, ESCRATCH = 0, -1, -2, -3, -4, -5, -6
+STATIC_SCRATCH_BYTES = 32 << 20
 MODE_RATIO, MODE_CROSS, MODE_NN = 0, 1, 2
 REC_Q32T32D32, REC_Q16T16D32, REC_Q16T16D16 = 1, 2, 3
 KIND_HAMMING, KIND_L2_I8, KIND_L2_F32, KIND_HAMMING_TC, KIND_HAMMING_FP4, KIND_L2_F16C = 0, 1, 2, 3, 4, 5
@@ -23,7 +24,7 @@ EXPORTS = ["b200m_version", "b200m_error_string", "b200m_last_cuda_error", "b200
            "b200m_timing_enable", "b200m_timing_collect", "b200m_f32_stats", "b200m_l2_i8_aux_bytes",
            "b200m_l2_i8_aux_init", "b200m_prep_l2_i8_rows", "b200m_hamming_tc_width", "b200m_prep_hamming_tc",
            "b200m_gather_correspondences", "b200m_hamming_fp4_width", "b200m_prep_hamming_fp4", "b200m_ransac_homography", "b200m_l2_f16_aux_bytes", "b200m_prep_l2_f16",
-           "b200m_l2_i8_aux_rows", "b200m_rec_bytes", "b200m_match_pairs_rec"]
+           "b200m_l2_i8_aux_rows", "b200m_rec_bytes", "b200m_match_pairs_rec", "b200m_match_pairs_static"]
 
 
 class Pair(ctypes.Structure):
@@ -78,6 +79,8 @@ def load() -> ctypes.CDLL:
     lib.b200m_match_pairs_rec.argtypes = [i32, vp, vp, i64, vp, vp, i64, i32, ctypes.POINTER(Pair), i32, i32, dbl,
                                           i32, vp, vp, vp, vp, ctypes.c_size_t, vp]
     lib.b200m_rec_bytes.argtypes = [i32]
+    lib.b200m_match_pairs_static.argtypes = [i32, vp, vp, i64, vp, vp, i64, i32, ctypes.POINTER(Pair), i32, i32, dbl,
+                                             vp, vp, vp, vp, vp]
     lib.b200m_l2_i8_aux_rows.argtypes = [vp, i64, i64, i64, i32, vp, vp]
     lib.b200m_timing_enable.argtypes = [i32]
     lib.b200m_timing_collect.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(i32)]
@@ -92,6 +95,6 @@ def check(rc: int, where: str) -> None:
     if rc != OK:
         lib = load()
         detail = lib.b200m_error_string(rc).decode()
-        if rc == ECUDA:
+        if rc in (ECUDA, ESCRATCH):
             detail += ": " + lib.b200m_last_cuda_error().decode()
         raise B200MatchError(rc, where, detail)

@@ -98,6 +98,7 @@ const char* b200m_error_string(int code) {
         case B200M_ECUDA: return "CUDA error";
         case B200M_ENODEVICE: return "no sm_100 device (this library has no CPU path)";
         case B200M_EUNSUPPORTED: return "unsupported shape";
+        case B200M_ESCRATCH: return "problem exceeds the library's static scratch (B200M_STATIC_SCRATCH_BYTES): see b200m_last_cuda_error()";
         default: return "unknown error";
     }
 }
@@ -330,6 +331,46 @@ int b200m_match_pairs_csr(int kind, const void* q_desc, const void* q_norm, int6
     if (num_pairs >= 0 && !out_ptr) return B200M_EINVAL;
     return match_pairs_impl(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs, mode,
                             ratio, out_q, out_t, out_d, out_count, out_ptr, workspace, workspace_bytes, stream);
+}
+
+// ---- b200m_match_pairs_static: the workspace lives in this library, not in the caller --------------------------------
+// File-scope scratch: every GPU that loads the library holds these bytes until the process exits.  In HOST code the name
+// g_static_scratch is a host-side stand-in, not a device address; the address a kernel may use comes from
+// cudaGetSymbolAddress, once per device, with that device current (static_scratch_ptr below).
+static __device__ __align__(256) unsigned char g_static_scratch[B200M_STATIC_SCRATCH_BYTES];
+static void* g_static_scratch_ptr[B200M_MAX_DEVICES];      // per device ordinal; null = not looked up yet
+
+static int static_scratch_ptr(void** out) {
+    int dev = 0;
+    if (!b200m_current_device(&dev, nullptr)) return B200M_ENODEVICE;
+    void* p = g_static_scratch_ptr[dev];
+    if (!p) {
+        B200M_CUDA_CHECK(cudaGetSymbolAddress(&p, g_static_scratch), "cudaGetSymbolAddress(static scratch)");
+        if (!p || ((uintptr_t)p & 255)) return b200m_set_cuda_error(cudaErrorInvalidSymbol, "static scratch address");
+        g_static_scratch_ptr[dev] = p;         // two threads racing here store the same address
+    }
+    *out = p;
+    return B200M_OK;
+}
+
+int b200m_match_pairs_static(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                             const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                             const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                             int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count, void* stream) {
+    void* ws = nullptr;
+    int rc = static_scratch_ptr(&ws);
+    if (rc != B200M_OK) return rc;
+    // Nothing in the scratch has to start at zero across calls: the plan re-initialises what it reads before writing
+    // (flag words, column minima, the caller's out_count) on `stream`, exactly as it does for a caller-owned workspace
+    // that is reused dirty.
+    rc = match_pairs_impl(kind, q_desc, q_norm, q_rows, t_desc, t_norm, t_rows, D, pairs_host, num_pairs, mode, ratio,
+                          out_q, out_t, out_d, out_count, nullptr, ws, (size_t)B200M_STATIC_SCRATCH_BYTES, stream);
+    if (rc == B200M_EWORKSPACE) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "b200m_match_pairs_static: this batch needs more than the %u-byte static scratch "
+                 "(B200M_STATIC_SCRATCH_BYTES); use b200m_match_pairs with a caller-owned workspace", (unsigned)B200M_STATIC_SCRATCH_BYTES);
+        return B200M_ESCRATCH;
+    }
+    return rc;
 }
 
 int b200m_rec_bytes(int rec_format) {

@@ -42,6 +42,8 @@ extern "C" {
 #define B200M_ECUDA      -3   /* a CUDA runtime call / launch failed                            */
 #define B200M_ENODEVICE  -4   /* no sm_100 device: this library has no CPU path                 */
 #define B200M_EUNSUPPORTED -5 /* shape outside what the kernels implement (stated per call)     */
+#define B200M_ESCRATCH   -6   /* b200m_match_pairs_static only: the batch needs more than
+                                 B200M_STATIC_SCRATCH_BYTES of workspace                        */
 
 /* The three behaviours of EnhancedBFMatcher.match. */
 #define B200M_MODE_RATIO  0   /* feature_matchers.py:208-224: knn k=2 + `d1 < ratio*d2` in fp64 */
@@ -177,6 +179,24 @@ B200M_API int b200m_match_pairs_csr(int kind, const void* q_desc, const void* q_
                           const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
                           int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count,
                           int64_t* out_ptr, void* workspace, size_t workspace_bytes, void* stream);
+
+/* b200m_match_pairs with NO caller workspace and no allocation of any kind (no cudaMalloc / cudaFree, no allocating
+ * library routine): for callers that cannot allocate -- code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it.  This entry point has no counterpart in the reference.
+ * Same arguments, results and order as b200m_match_pairs (the caller still passes every input and output); the workspace
+ * is a file-scope `static __device__` array of B200M_STATIC_SCRATCH_BYTES (32 MiB) inside the library, which every GPU
+ * that loads the library holds until the process exits.
+ *   - a batch whose plan needs more than that returns B200M_ESCRATCH (b200m_last_cuda_error() says so); nothing is
+ *     enqueued.  b200m_workspace_bytes() gives an upper bound of the need: one 8192 x 8192 SIFT pair 4.4 MB, one ORB
+ *     10k x 10k cross-check pair 1.5 MB, one 4096 x 4096 x 256 float pair with mutual check 18.2 MB.
+ *   - every call on a device shares the ONE array, which keeps the last call's contents (the plan re-initialises what it
+ *     needs on `stream`).  Calls that overlap on the GPU -- different streams, or different host threads on one device --
+ *     RACE on it: serialise them (one stream, or events between them). */
+#define B200M_STATIC_SCRATCH_BYTES (32u << 20)
+B200M_API int b200m_match_pairs_static(int kind, const void* q_desc, const void* q_norm, int64_t q_rows,
+                             const void* t_desc, const void* t_norm, int64_t t_rows, int D,
+                             const b200m_pair* pairs_host, int num_pairs, int mode, double ratio,
+                             int32_t* out_q, int32_t* out_t, float* out_d, int32_t* out_count, void* stream);
 
 /* The same with ONE record per match instead of three arrays, so that a block of matches is one contiguous byte range
  * (one device-to-host copy, one NCCL message) and the 1000-image binary workload moves 6 instead of 12 bytes per match

@@ -98,3 +98,40 @@ def test_partition_is_balanced_contiguous_and_complete():
         assert max(loads) <= work.sum() / world + work.max()         # within one pair of the ideal share
     assert all(len(s) == 0 for s in ap.partition_pairs(pairs[:0], offsets, 4))
     assert [len(s) for s in ap.partition_pairs(pairs[:2], offsets, 4)].count(0) >= 2   # more ranks than pairs
+
+
+def _board_worker(rank, world, port):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        D = pkg("distributed")
+        bd = D._HostBoard(world, rank, dist.new_group(backend="gloo"))
+        for k in range(3 * D._HostBoard.SLOTS):                 # more exchanges than slots: the ring wraps
+            got = bd.exchange(rank * 100000 + k)
+            if rank == 0:
+                assert got == [r * 100000 + k for r in range(world)]
+            else:
+                assert got is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_host_board_rendezvous(world):
+    """distributed._HostBoard: the shared-memory count exchange of the streamed return path (rank 0 learns every rank's
+    record count per image group without a device collective)."""
+    mp.spawn(_board_worker, args=(world, _free_port()), nprocs=world, join=True)
+
+
+def test_group_plan_covers_every_pair_once_and_blocks_tile_groups():
+    D = pkg("distributed")
+    for I, G in [(1, 4), (2, 1), (7, 3), (10, 4), (25, 24), (50, 8)]:
+        plan = D.group_plan(I, G)
+        assert [(a, c) for a, c, _ in plan] == [(j, min(I, j + G)) for j in range(0, I, G)]
+        got = sorted(tuple(p) for _, _, gp in plan for p in gp)
+        assert got == list(itertools.combinations(range(I), 2))
+        for j0, j1, gp in plan:
+            assert all(j0 <= j < j1 and i < j for i, j in gp)       # a group's pairs need only images < j1: resident by then
+    for world in (1, 2, 8):
+        cuts = D.block_cuts(24, 48, world)
+        assert cuts[0] == 24 and cuts[-1] == 48 and len(cuts) == world + 1 and cuts == sorted(cuts)

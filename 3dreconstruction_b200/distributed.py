@@ -73,11 +73,24 @@ class RecCSR:
         return RecCSR(self.pairs[order], ptr, self.rec[idx], self.rec_format)
 
 
-def group_plan(num_images: int, group_images: int):
+def group_sizes(num_images: int, group_images: int, first: Optional[int] = None) -> List[int]:
+    """Images per upload group.  With `first` the groups ramp up -- first, 2 first, 4 first, ... until group_images -- so
+    that matching starts after a SMALL first upload (the step's exposed front is the first group's H2D + re-encoding +
+    all-gather) while later groups are large enough to keep launches and collectives few."""
+    sizes, g, left = [], (first or group_images), num_images
+    g = max(1, min(g, group_images))
+    while left > 0:
+        sizes.append(min(g, left))
+        left -= sizes[-1]
+        g = min(2 * g, group_images)
+    return sizes
+
+
+def group_plan(num_images: int, group_images: int, first: Optional[int] = None):
     """[(j0, j1, pairs[K, 2])]: for every group of images [j0, j1), the pairs (i, j), i < j, j in the group."""
-    out = []
-    for j0 in range(0, num_images, group_images):
-        j1 = min(num_images, j0 + group_images)
+    out, j0 = [], 0
+    for size in group_sizes(num_images, group_images, first):
+        j1 = j0 + size
         js = np.arange(max(j0, 1), j1)
         if len(js):
             i = np.concatenate([np.arange(0, j) for j in js])
@@ -85,6 +98,7 @@ def group_plan(num_images: int, group_images: int):
         else:
             gp = np.zeros((0, 2), np.int32)
         out.append((j0, j1, gp))
+        j0 = j1
     return out
 
 
@@ -180,7 +194,7 @@ class DistributedAllPairs:
     """See the module docstring.  One instance per process; buffers (device stores, pinned arenas) are kept between calls."""
 
     def __init__(self, engine: Engine, chunk_pairs: int = 2048, group_images: int = 24, rec_format: Optional[int] = None,
-                 gather: str = "rank0", upload: str = "auto"):
+                 gather: str = "rank0", upload: str = "auto", ramp: bool = True):
         if gather not in ("rank0", "local"):
             raise ValueError("gather must be rank0 or local")
         if upload not in ("auto", "sharded", "rank0"):
@@ -189,7 +203,7 @@ class DistributedAllPairs:
         self.chunk_pairs = int(chunk_pairs)
         self.group_images = int(group_images)
         self.rec_format = rec_format
-        self.gather, self.upload = gather, upload
+        self.gather, self.upload, self.ramp = gather, upload, bool(ramp)
         self._dev = {}
         self._pinned = {}
         self._streams = None
@@ -375,14 +389,16 @@ class DistributedAllPairs:
     def match_host(self, host: Optional[torch.Tensor], counts: Sequence[int], norm_type: int = NORM_L2,
                    cross_check: bool = False, ratio_threshold: Optional[float] = None, D: Optional[int] = None,
                    dtype: Optional[torch.dtype] = None, consumer: Optional[Callable] = None, keep: bool = True,
-                   timing: bool = False, assume_float: bool = False) -> Optional[RecCSR]:
+                   timing: bool = False, assume_float: bool = False, done_mask: Optional[np.ndarray] = None) -> Optional[RecCSR]:
         """host: pinned [sum(counts), D] float32 (NORM_L2) or uint8 (NORM_HAMMING) rows of all images, image after image.
         Under torch.distributed every rank may pass them (sharded upload: rank k only reads the rows of the image
         blocks it owns) or only rank 0 (the others pass None plus D and dtype; rank 0 then uploads and broadcasts).
         consumer(pairs[K, 2], counts[K], rec) is called on the returning rank for every block of pairs as soon as its
         records are in host memory (`rec` is only valid during the call unless keep=True).
         Returns the RecCSR on rank 0 (gather="rank0"; other ranks: None) or this rank's shard (gather="local");
-        with keep=False the returned `rec` is empty and only `pairs` / `ptr` are filled."""
+        with keep=False the returned `rec` is empty and only `pairs` / `ptr` are filled.
+        done_mask: bool [I (I - 1) / 2] over itertools.combinations order; pairs marked True are skipped (a resumed job:
+        checkpoint.AllPairsCheckpoint.done_mask()).  Every rank must pass the same mask."""
         import torch.distributed as dist
         eng = self.engine
         dev = eng.device
@@ -421,12 +437,21 @@ class DistributedAllPairs:
         G = max(1, self.group_images)
         if world > 1 and sharded:
             G = (G + world - 1) // world * world               # equal upload blocks -> in-place all-gather
-        groups = group_plan(I, I if float_path else G)
+        first = max(8, world)                                   # ramp: 8, 16, 32, ... images per group up to G
+        if world > 1 and sharded:
+            first = (first + world - 1) // world * world
+        groups = group_plan(I, I, None) if float_path else group_plan(I, G, min(first, G) if self.ramp else None)
+        if done_mask is not None:
+            from .checkpoint import pair_index
+            done_mask = np.asarray(done_mask, bool)
+            if done_mask.shape != (I * (I - 1) // 2,):
+                raise ValueError("done_mask must have one entry per pair of itertools.combinations(range(I), 2)")
+            groups = [(j0, j1, gp[~done_mask[pair_index(gp[:, 0], gp[:, 1], I)]] if len(gp) else gp) for j0, j1, gp in groups]
         res = self._run(host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, mode, ratio, fmt,
                         consumer, keep, timing)
         if res == "not-integer":                              # the int8 encoding is not exact for these rows: fp16/tf32 candidates
             return self.match_host(host, counts, norm_type, cross_check, ratio_threshold, D, dtype, consumer, keep, timing,
-                                   assume_float=True)
+                                   assume_float=True, done_mask=done_mask)
         return res
 
     def _run(self, host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, mode, ratio, fmt,

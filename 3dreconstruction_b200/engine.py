@@ -16,6 +16,11 @@ from . import _lib as L
 NORM_L2, NORM_HAMMING = 4, 6      # cv2.NORM_L2, cv2.NORM_HAMMING
 
 
+class UnsupportedNormError(NotImplementedError):
+    """A cv2 norm type the reference's matcher accepts (NORM_L1, NORM_L2SQR, NORM_HAMMING2, ...) and this library does not
+    implement: raised, never turned into an empty result."""
+
+
 class MatchArrays(NamedTuple):
     query_idx: np.ndarray    # int32 [K]
     train_idx: np.ndarray    # int32 [K]
@@ -115,7 +120,7 @@ class Engine:
                 L.check(prep_fn(t.data_ptr(), rows, D, ex.data_ptr(), wpad.value, self._stream()), "b200m_prep_hamming_*")
             return DeviceDescriptors(want, t, ex, rows, D)
         if norm_type != NORM_L2:
-            raise ValueError(f"unsupported norm_type {norm_type}")
+            raise UnsupportedNormError(f"norm_type {norm_type}: only cv2.NORM_L2 (4) and cv2.NORM_HAMMING (6) are implemented")
         if t.dtype == torch.uint8:
             t = t.to(torch.float32)
         if t.dtype != torch.float32:

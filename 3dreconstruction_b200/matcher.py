@@ -17,7 +17,8 @@ from typing import Optional
 import numpy as np
 
 from . import contracts
-from .engine import NORM_HAMMING, NORM_L2, Engine, MatchArrays, default_engine
+from ._lib import ECUDA, ENODEVICE, EUNSUPPORTED, EWORKSPACE, B200MatchError
+from .engine import NORM_HAMMING, NORM_L2, Engine, MatchArrays, UnsupportedNormError, default_engine
 
 
 def _materialise(c: contracts.Contracts, arr: MatchArrays) -> list:
@@ -80,7 +81,17 @@ class B200BFMatcher(contracts.BaseFeatureMatcher):
             self.last_arrays = arr
             return c.MatchData(matches=_materialise(c, arr), method="BF",
                                matching_time=time.time() - start, score_type=c.ScoreType.DISTANCE)
-        except Exception as e:                   # reference convention: print and return empty
+        except B200MatchError as e:
+            # Shapes THIS library does not implement (L2 descriptors wider than 256, B200M_EUNSUPPORTED) and device /
+            # environment failures are not input errors: the reference's cv2 path returns real matches for them, so an
+            # empty MatchData here would silently lose them.  They propagate (limits: INTEGRATION.md 7).
+            if e.code in (EUNSUPPORTED, ENODEVICE, ECUDA, EWORKSPACE):
+                raise
+            print(f"BF matching failed: {e}")
+            return c.MatchData([], method="BF", score_type=c.ScoreType.DISTANCE)
+        except UnsupportedNormError:
+            raise                                 # NORM_L1 / NORM_L2SQR / NORM_HAMMING2: cv2 matches these, this library does not
+        except Exception as e:                   # reference convention for genuine input errors (:250-252): print and return empty
             print(f"BF matching failed: {e}")
             return c.MatchData([], method="BF", score_type=c.ScoreType.DISTANCE)
 

@@ -47,7 +47,7 @@ def parse_args():
     ap.add_argument("--chunk-pairs", type=int, default=2048)
     ap.add_argument("--cpu-sample-pairs", type=int, default=24)
     ap.add_argument("--no-also", action="store_true")
-    ap.add_argument("--group-images", type=int, default=24, help="images per upload group of the e2e arm (StreamingAllPairs)")
+    ap.add_argument("--group-images", type=int, default=48, help="images per upload group of the e2e arm (StreamingAllPairs)")
     ap.add_argument("--e2e-upload", default="auto", choices=["auto", "sharded", "rank0"],
                     help="N > 1: every rank uploads its block of each image group over its own PCIe link (default) or rank 0 uploads everything")
     ap.add_argument("--e2e-gather", default="rank0", choices=["rank0", "local"],
@@ -795,10 +795,214 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_b200_akaze(args):
+    """BASELINE configs[4]: AKAZE 61-byte (486-bit) descriptors, all pairs of `--images` images x `--keypoints` keypoints with
+    the mutual check, sharded over the ranks.  `value`: device-resident store, every rank matches its balanced block of the
+    pair list (results stay on the device and are dropped).  `e2e`: distributed.DistributedAllPairs from pinned host rows
+    (sharded upload, one all-gather of the packed bits per image group, e2m1 expansion derived locally), 6-byte match
+    records streamed to rank 0 per image group and handed to a consumer there (rank 0 never holds the whole result)."""
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    b = importlib.import_module("3dreconstruction_b200")
+    ap = importlib.import_module("3dreconstruction_b200.allpairs")
+    dmod = importlib.import_module("3dreconstruction_b200.distributed")
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    json_out = sys.stdout
+    if world > 1:
+        sys.stdout.flush()
+        json_out = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+        dist.init_process_group("nccl", device_id=device)
+    eng = b.Engine(device)
+    lib = eng.lib
+    pk, pk_src = peaks()
+    I, n, nb = args.images, args.keypoints, 61
+    pairs = ap.all_pairs(I)
+    P = len(pairs)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    # every rank synthesises the same set (same seed) on its GPU and keeps a pinned host copy: the e2e arm starts from HOST rows
+    desc = binary_set_gpu(torch, device, I, n, nb)                        # [I, n, 61] uint8
+    host_pinned = torch.empty((I * n, nb), dtype=torch.uint8, pin_memory=True)
+    host_pinned.copy_(desc.view(I * n, nb))
+    store = ap.build_store(eng, torch.nn.functional.pad(desc.view(I * n, nb), (0, 3)), b.NORM_HAMMING, counts=[n] * I)
+    del desc
+    mine = ap.partition_pairs(pairs, store.offsets, world)[rank]
+    matcher = ap.AllPairsMatcher(eng, chunk_pairs=args.chunk_pairs)
+    SUPER = 8 * args.chunk_pairs                                          # results of this many pairs live on the device at a time
+
+    def step():
+        total = 0
+        for c0 in range(0, len(mine), SUPER):
+            r = matcher.match(store, mine[c0:c0 + SUPER], cross_check=True)
+            total += int(r.query_idx.numel())
+            del r
+        return total
+
+    matcher.match(store, mine[:min(len(mine), 2 * args.chunk_pairs + 1)], cross_check=True)     # bounded warm-up (buffers, attributes)
+    for _ in range(max(args.warmup, 0)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.b200m_reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        matches_mine = step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    launches = torch.tensor([lib.b200m_launch_count()], dtype=torch.int64, device=device)
+    matches_all = torch.tensor([matches_mine], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(launches, op=dist.ReduceOp.SUM)
+        dist.all_reduce(matches_all, op=dist.ReduceOp.SUM)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total, matches_all = float(ms.item()), int(matches_all.item())
+    value = P * args.steps / (ms_total / 1e3)
+    # the dominant kernel alone on a bounded sample of this rank's pairs (pipeline off: events bracket the kernel only)
+    sample = mine[:min(len(mine), 2 * args.chunk_pairs)]
+    seq = ap.AllPairsMatcher(eng, chunk_pairs=args.chunk_pairs, pipeline=False)
+    seq.match(store, sample, cross_check=True)
+    barrier()
+    lib.b200m_timing_enable(1)
+    seq.match(store, sample, cross_check=True)
+    torch.cuda.synchronize()
+    knn_ms, knn_l = ctypes.c_double(0), ctypes.c_int(0)
+    lib.b200m_timing_collect(ctypes.byref(knn_ms), ctypes.byref(knn_l))
+    lib.b200m_timing_enable(0)
+    tops = 2.0 * 2 * len(sample) * n * n * 512 / (knn_ms.value / 1e3) / 1e12 if knn_ms.value > 0 else None   # both directions, 512 one-bit dims
+    del store, seq
+    matcher._bufs.clear()
+    torch.cuda.empty_cache()
+
+    # ---- end to end from host rows; rank 0 consumes the records group by group (counts them, keeps three sampled pairs for the oracle)
+    dap = dmod.DistributedAllPairs(eng, chunk_pairs=args.chunk_pairs, group_images=args.group_images, gather=args.e2e_gather,
+                                   upload=args.e2e_upload)
+    seen = {"matches": 0, "pairs": 0, "blocks": 0, "keep": {}}
+    want_keys = np.array([0 * I + 1, (I // 3) * I + I // 2, (I - 2) * I + I - 1], np.int64)
+
+    def consumer(pr, cn, rec):
+        seen["matches"] += int(cn.sum(dtype=np.int64))
+        seen["pairs"] += len(pr)
+        seen["blocks"] += 1
+        if args.no_parity:
+            return
+        hit = np.nonzero(np.isin(pr[:, 0].astype(np.int64) * I + pr[:, 1], want_keys))[0]
+        if len(hit):
+            ptr = np.concatenate([[0], np.cumsum(cn, dtype=np.int64)])
+            for k in hit:
+                seen["keep"][(int(pr[k, 0]), int(pr[k, 1]))] = rec[ptr[k]:ptr[k + 1]].copy()
+
+    def e2e_step(timing=False):
+        seen.update({"matches": 0, "pairs": 0, "blocks": 0})
+        r = dap.match_host(host_pinned, [n] * I, b.NORM_HAMMING, True, None, D=nb, dtype=torch.uint8, consumer=consumer, keep=False,
+                           timing=timing)
+        if rank == 0 and args.e2e_gather == "rank0" and (seen["pairs"] != P or seen["matches"] != matches_all or int(r.ptr[-1]) != matches_all):
+            raise RuntimeError(f"e2e path returned {seen['matches']} matches of {seen['pairs']} pairs, resident path {matches_all} of {P}")
+        return seen["matches"] * 6 + (0 if r is None else r.ptr.nbytes)
+
+    if args.warmup > 0 or I <= 64:
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        d2h = e2e_step(timing=args.steps == 1)
+    barrier()
+    t_e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    e2e_value = P * args.steps / float(t_e2e.item())
+    if args.steps != 1:
+        e2e_step(timing=True)
+        barrier()
+    ph_all = [None] * world
+    if world > 1:
+        dist.all_gather_object(ph_all, dict(dap.last_phases))
+    else:
+        ph_all = [dict(dap.last_phases)]
+    if rank == 0:
+        parity = None
+        if not args.no_parity and args.e2e_gather == "rank0":
+            from oracle import bf_oracle as O
+            O.set_threads(os.cpu_count() or 1)
+            hp = host_pinned.numpy().reshape(I, n, nb)
+            for (i, j), rec in seen["keep"].items():
+                w = O.reference_match(hp[i], hp[j], O.NORM_HAMMING, True, None)
+                ok = (np.array_equal(rec["q"].astype(np.int32), w.query_idx) and np.array_equal(rec["t"].astype(np.int32), w.train_idx)
+                      and np.array_equal(rec["d"].astype(np.float32), w.distance))
+                if not ok:
+                    raise RuntimeError(f"e2e records of pair {(i, j)} differ from the oracle")
+            parity = f"pairs {sorted(seen['keep'])} of the streamed result identical to the oracle (queryIdx, trainIdx, distance, order)"
+        fp4_peak = 4.0 * pk["bf16_tflops_sustained"]
+        full = (I, n) == (1000, 16384)
+        line = {"metric": "image pairs/s (AKAZE-Hamming all-pairs, mutual cross-check)", "value": value, "unit": "pairs/s",
+                "gdist_per_s": value * n * n / 1e9, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "e2m1 (+-1.0 per descriptor bit; fp32 sums of +-1 are exact)", "data": "synthetic",
+                "config": {"workload": f"AKAZE binary all-pairs: {I} images x {n} keypoints x 61 B, {P} pairs, mutual cross-check "
+                                       f"(BASELINE configs[4]{'' if full else ', REDUCED size'})",
+                           "pairs": P, "l2_flush": "inputs larger than L2 (e2m1 store %.2f GB)" % (I * n * 256 / 1e9),
+                           "parallelism": f"pair-list sharding x{world}"},
+                "matches_per_step": matches_all,
+                "roofline": {"bound": "tensor", "kernel": "hamming_tc_kernel<2, CS, FP4> (tcgen05 kind::mxf4.block_scale, forward + backward) + POPC resolve",
+                             "achieved": tops, "peak": 7850.0, "unit": "TOP/s (one-bit MACs x 2)", "frac": tops / 7850.0 if tops else None,
+                             "peak_source": "tools/mma_peak.cu kind::mxf4 issue rate sustained under the power cap on this pool's B200 "
+                                            "(profiles/r01_mma_mxf4_peak.txt; 8876 burst); 4 x bf16_tflops_sustained = %.0f beside it" % fp4_peak,
+                             "frac_of_4x_bf16_sustained": tops / fp4_peak if tops else None,
+                             "sample": f"{len(sample)} pairs of rank 0's block, pipeline off, library CUDA events around the knn stage",
+                             "kernel_ms_sample": knn_ms.value, "kernel_launches_sample": knn_l.value, "traffic": None},
+                "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel()), "d2h_bytes_per_step": int(d2h),
+                        "steps": args.steps, "ms_per_step": 1e3 * float(t_e2e.item()) / args.steps, "record_bytes_per_match": 6,
+                        "blocks_streamed_to_rank0": seen["blocks"],
+                        "upload": "n/a" if world == 1 else ("sharded" if args.e2e_upload != "rank0" else "rank0"),
+                        "gather": "n/a" if world == 1 else args.e2e_gather, "group_images": args.group_images,
+                        "path": "pinned host uint8 rows -> H2D per image group (every rank its block) -> NCCL all-gather of the packed bits -> "
+                                "e2m1 expansion derived locally -> b200m_match_pairs_rec (6-byte records) -> per group NCCL send to rank 0 -> "
+                                "D2H into a two-slot pinned ring -> consumer (rank 0 never holds the whole result)",
+                        "parity_vs_oracle": parity, "phases_rank0": ph_all[0],
+                        "phases_max_over_ranks": {k: max(p.get(k, 0.0) for p in ph_all) for k in ph_all[0]}},
+                "gpu_launches": int(launches.item()), "clocks": clocks}
+        if world == 1 and not args.no_also:
+            try:
+                import cv2
+                cv2.setNumThreads(os.cpu_count() or 1)
+                hp = host_pinned.numpy().reshape(I, n, nb)
+                bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True)
+                bf.match(hp[0][:512], hp[1][:512])
+                k = max(1, min(args.cpu_sample_pairs // 6, I - 1))
+                t0 = time.perf_counter()
+                for j in range(1, k + 1):
+                    bf.match(hp[0], hp[j])
+                t = time.perf_counter() - t0
+                line["cpu_baseline"] = {"value": k / t, "unit": "pairs/s", "cores": cv2.getNumThreads(), "kind": "reference",
+                                        "sample": f"{k} pairs of {n}x{n}x61 B on this host, cv2.BFMatcher(NORM_HAMMING, crossCheck=True).match "
+                                                  f"{cv2.__version__} (what EnhancedBFMatcher.match calls at feature_matchers.py:227)"}
+            except ImportError:
+                line["cpu_baseline"] = None
+        print(json.dumps(line), file=json_out, flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "akaze":
+        run_b200_akaze(args)
     else:
         run_b200(args)
 

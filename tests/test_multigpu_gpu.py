@@ -39,7 +39,8 @@ def _case_images(case):
 
 
 CASES = ["sift", "sift_late_low_norm", "orb_cross", "orb_ratio", "akaze_cross", "superpoint"]
-VARIANTS = [dict(upload="auto", gather="rank0"), dict(upload="rank0", gather="rank0"), dict(upload="auto", gather="local")]
+VARIANTS = [dict(upload="auto", gather="rank0"), dict(upload="rank0", gather="rank0"), dict(upload="auto", gather="local"),
+            dict(upload="auto", gather="rank0", group_images=16)]       # 10 images in ramped groups of 8 + 2
 
 
 def _free_port():
@@ -61,7 +62,7 @@ def _worker(rank, world, port, out_dir):
             imgs, norm, (cc, ratio) = _case_images(case)
             host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
             for vi, var in enumerate(VARIANTS):
-                dap = D.DistributedAllPairs(eng, chunk_pairs=5, group_images=4, **var)
+                dap = D.DistributedAllPairs(eng, chunk_pairs=5, **{"group_images": 4, **var})
                 for rep in range(2):                              # twice: buffer / arena reuse
                     give = host if (var["upload"] != "rank0" or rank == 0) else None
                     r = dap.match_host(give, SIZES, norm, cc, ratio, D=host.shape[1], dtype=host.dtype, timing=rep == 1)

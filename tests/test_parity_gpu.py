@@ -586,6 +586,80 @@ def test_end_to_end_host_path_all_kinds_and_record_formats(eng, kind, fmt):
     assert [tuple(x) for x in s.pairs] == list(itertools.combinations(range(len(sizes)), 2)) and s.ptr[-1] == res.ptr[-1]
 
 
+def test_checkpointed_job_interrupted_and_resumed_equals_uninterrupted(eng, tmp_path):
+    """an all-pairs job that dies after some blocks and is started again (a new AllPairsCheckpoint on the
+    same directory) matches only the unfinished pairs and ends with the same result as one uninterrupted job -- with the
+    single-GPU block driver and with the streamed host path (consumer + done_mask); progress.json lists every pair."""
+    import itertools
+    ap, ckm, D = pkg("allpairs"), pkg("checkpoint"), pkg("distributed")
+    sizes = [300, 129, 64, 640, 77, 256, 18]
+    I = len(sizes)
+    imgs = [synth.binary_pair(seed=370 + i, n=max(s, 2), nbytes=32)[0][:s] for i, s in enumerate(sizes)]
+    imgs[3][:200] = imgs[0][:200]
+    combos = list(itertools.combinations(range(I), 2))
+    want = [O.reference_match(imgs[i], imgs[j], O.NORM_HAMMING, True, None) for i, j in combos]
+
+    def check(c):
+        pairs, ptr, rec = c.load()
+        assert [tuple(p) for p in pairs] == combos and c.done_mask().all()
+        assert sorted(c.progress.completed_pairs) == sorted(ckm.pair_id(p) for p in range(len(combos)))
+        for p, w in enumerate(want):
+            r = rec[ptr[p]:ptr[p + 1]]
+            got = O.Matches(r["q"].astype(np.int32), r["t"].astype(np.int32), r["d"].astype(np.float32))
+            assert_exact(got, w, f"checkpointed pair {combos[p]}")
+
+    # (1) block driver over a resident store
+    store = ap.build_store(eng, imgs, b.NORM_HAMMING)
+    m = ap.AllPairsMatcher(eng, chunk_pairs=3)
+    c = ckm.AllPairsCheckpoint(tmp_path / "blocks", I)
+    assert ckm.run_checkpointed(m, store, I, c, cross_check=True, block_pairs=5, stop_after_blocks=2) == 10     # "dies" after 2 blocks
+    c = ckm.AllPairsCheckpoint(tmp_path / "blocks", I)
+    assert c.done_mask().sum() == 10
+    assert ckm.run_checkpointed(m, store, I, c, cross_check=True, block_pairs=5) == len(combos) - 10          # the rest only
+    assert ckm.run_checkpointed(m, store, I, c, cross_check=True, block_pairs=5) == 0
+    check(ckm.AllPairsCheckpoint(tmp_path / "blocks", I))
+    # (2) streamed host path: the consumer raises in the third block
+    host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+    dap = D.DistributedAllPairs(eng, chunk_pairs=4, group_images=3)
+    c = ckm.AllPairsCheckpoint(tmp_path / "stream", I)
+    seen = []
+
+    def dying(pr, cn, rec):
+        if len(seen) == 2:
+            raise KeyboardInterrupt("power cut")
+        seen.append(len(pr))
+        c.consumer(pr, cn, rec)
+
+    with pytest.raises(KeyboardInterrupt):
+        dap.match_host(host, sizes, b.NORM_HAMMING, True, None, consumer=dying, keep=False)
+    torch.cuda.synchronize()
+    c = ckm.AllPairsCheckpoint(tmp_path / "stream", I)
+    assert c.done_mask().sum() == sum(seen) and 0 < sum(seen) < len(combos)
+    r = D.DistributedAllPairs(eng, chunk_pairs=4, group_images=3).match_host(host, sizes, b.NORM_HAMMING, True, None,
+                                                                             consumer=c.consumer, keep=False, done_mask=c.done_mask())
+    assert len(r.pairs) == len(combos) - sum(seen)
+    check(ckm.AllPairsCheckpoint(tmp_path / "stream", I))
+
+
+def test_plugin_raises_for_what_cv2_would_match_but_the_library_does_not(eng):
+    """shapes the kernels do not implement must not become an empty MatchData (the reference's cv2 path returns
+    real matches for them); genuine input errors still do (feature_matchers.py:250-252)."""
+    F = b.contracts.FeatureData
+    rng = np.random.default_rng(3)
+    wide = rng.integers(0, 256, size=(40, 300)).astype(np.float32)
+    f = F(keypoints=list(range(40)), descriptors=wide, method="x")
+    m = b.B200BFMatcher(norm_type=b.NORM_L2, ratio_threshold=0.8, engine=eng)
+    with pytest.raises(pkg("_lib").B200MatchError):
+        m.match(f, f)
+    u8 = rng.integers(0, 256, size=(40, 32), dtype=np.uint8)
+    fu = F(keypoints=list(range(40)), descriptors=u8, method="x")
+    with pytest.raises(pkg("engine").UnsupportedNormError):
+        b.B200BFMatcher(norm_type=2, engine=eng).match(fu, fu)            # cv2.NORM_L1
+    narrow = F(keypoints=list(range(40)), descriptors=u8[:, :16], method="x")
+    md = b.B200BFMatcher(norm_type=b.NORM_HAMMING, engine=eng).match(fu, narrow)   # width mismatch: cv2 fails too -> empty
+    assert md.matches == [] and md.method == "BF"
+
+
 # ------------------------------------------------------------------ SfM hand-off (feature cache -> all pairs -> correspondences)
 @pytest.mark.parametrize("name", ["orb_cross", "orb_ratio07", "sift_ratio075"])
 def test_sfm_handoff_equals_reference_converter(eng, name):

@@ -205,6 +205,24 @@ def cpu_time_pairs(host_images, pair_list):
     return time.perf_counter() - t0, cores, engine
 
 
+def cv2_pair_baseline(pairs, norm, cross_check, ratio, what):
+    """cpu_baseline of an `also` entry: cv2.BFMatcher on this box's host cores, driven as EnhancedBFMatcher.match drives it
+    (oracle/bf_oracle.cv2_match), on `pairs` = [(desc1, desc2)].  Returns (dict for the JSON line, [Matches])."""
+    from oracle import bf_oracle as O
+    try:
+        import cv2
+    except ImportError:
+        return None, None
+    cv2.setNumThreads(os.cpu_count() or 1)
+    O.cv2_match(pairs[0][0][:256], pairs[0][1][:256], norm, cross_check, ratio)        # warm the thread pool
+    t0 = time.perf_counter()
+    res = [O.cv2_match(a, c, norm, cross_check, ratio) for a, c in pairs]
+    t = time.perf_counter() - t0
+    return {"value": len(pairs) / t, "unit": "pairs/s", "ms_per_pair": 1e3 * t / len(pairs), "cores": cv2.getNumThreads(),
+            "kind": "reference", "sample": f"{len(pairs)} pair(s) of {what} on this host, cv2.BFMatcher {cv2.__version__} driven by "
+                                           "oracle/bf_oracle.cv2_match (restates EnhancedBFMatcher.match)"}, res
+
+
 def host_sample_images(args, count):
     synth = importlib.import_module("3dreconstruction_b200.synth")
     return synth.sift_set(seed=3, images=count, n=args.keypoints)
@@ -281,8 +299,14 @@ def single_pair_extras(torch, b, eng, pk):
                              "16-column chunks per row (hamming_tc.cu); one pair = 79 row tiles, launch/tail latency-bound")
     orb["popc"].update({"popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": orb["popc"]["gdist_per_s"] / popc_peak,
                         "note": "INT-pipe kernel (hamming.cu): single fused pass, row top-2 and column minima from the same distances"})
+    cpu, cres = cv2_pair_baseline([(a, c)] * 3, 6, True, None, "10000 x 10000 x 256-bit ORB, crossCheck=True (BASELINE configs[1])")
+    if cpu:
+        got = eng.match_arrays(a, c, b.NORM_HAMMING, True, None)
+        cpu["identical_to_gpu"] = bool(np.array_equal(got.query_idx, cres[0].query_idx) and np.array_equal(got.train_idx, cres[0].train_idx)
+                                       and np.array_equal(got.distance, cres[0].distance))
     out["orb_pair_10000x10000_crosscheck"] = {**orb["tensor"], "popc_path": orb["popc"],
-                                              "speedup_over_popc_path": orb["popc"]["ms_per_pair"] / orb["tensor"]["ms_per_pair"]}
+                                              "speedup_over_popc_path": orb["popc"]["ms_per_pair"] / orb["tensor"]["ms_per_pair"],
+                                              "cpu_baseline": cpu}
     out.update(plugin_call_extras(torch, b, eng))
     out.update(allpairs_extras(torch, b, eng, pk))
     out.update(sfm_extras(torch, b, eng, pk))
@@ -536,9 +560,30 @@ def allpairs_extras(torch, b, eng, pk):
                               "exact fp32 re-rank; knn stage = candidate + refine + fallback kernels, both directions"})
     sp["tf32"].update({"tf32_peak_tflops": peak32, "frac_of_tf32_roofline": sp["tf32"]["tflops_achieved_knn_stage"] / peak32,
                        "note": "B200M_KIND_L2_F32 (Engine(float_path='tf32')): kind::tf32 candidates from the fp32 rows; same results, bit for bit"})
+    # cv2 on the same box for a sample of the same pairs, and the near-tie accounting north_star asks for: rows where the
+    # GPU result and cv2 disagree (membership of the mutual set, or the train index)
+    sample_pairs = pairs[:: max(1, len(pairs) // 6)][:6]
+    host_rows = {int(i): store.dd.desc[i * n:(i + 1) * n, :D].cpu().numpy() for i in np.unique(sample_pairs)}
+    cpu, cres = cv2_pair_baseline([(host_rows[int(i)], host_rows[int(j)]) for i, j in sample_pairs], 4, True, None,
+                                  "4096 x 4096 x 256 float (BASELINE configs[2]), crossCheck=True")
+    if cpu:
+        rs = ap.AllPairsMatcher(eng, chunk_pairs=1024).match(store, sample_pairs, cross_check=True).to_host()
+        flips, total, max_rel = 0, 0, 0.0
+        for p, w in enumerate(cres):
+            gq, gt, gd = rs.pair(p)
+            g = dict(zip(gq.tolist(), zip(gt.tolist(), gd.tolist())))
+            wd = dict(zip(w.query_idx.tolist(), zip(w.train_idx.tolist(), w.distance.tolist())))
+            flips += len(set(g) ^ set(wd)) + sum(1 for q in set(g) & set(wd) if g[q][0] != wd[q][0])
+            total += len(wd)
+            same = [q for q in set(g) & set(wd) if g[q][0] == wd[q][0]]
+            if same:
+                max_rel = max(max_rel, max(abs(g[q][1] - wd[q][1]) / max(wd[q][1], 1e-12) for q in same))
+        cpu.update({"near_tie_flips": flips, "matches_compared": total, "max_rel_distance_error": max_rel,
+                    "tolerance": "north_star: relative distance error <= 1e-5, index differences only at near ties (counted here; "
+                                 "each one is verified against the oracle's float64 margin in tests/test_parity_gpu.py)"})
     out["superpoint_allpairs_100x4096x256_mutual"] = {
         "pairs": len(pairs), "rows_total": 2 * n * len(pairs), **sp["f16"], "tf32_path": sp["tf32"],
-        "speedup_over_tf32_path": sp["tf32"]["ms_per_pass"] / sp["f16"]["ms_per_pass"]}
+        "speedup_over_tf32_path": sp["tf32"]["ms_per_pass"] / sp["f16"]["ms_per_pass"], "cpu_baseline": cpu}
     del store
     # ---- configs[4], bounded: 48 of the 1000 images (1128 of 499500 pairs), AKAZE 61 bytes padded to 64
     I, n, nb = 48, 16384, 61
@@ -573,8 +618,11 @@ def allpairs_extras(torch, b, eng, pk):
     res["popc"].update({
         "popc_roofline_gdist_per_s": popc_peak, "frac_of_popc_roofline": res["popc"]["gdist_per_s"] / popc_peak,
         "note": "INT-pipe kernel (hamming.cu): each distance computed once (fused row top-2 + column minima); POPC roofline at 1965 MHz"})
+    hp = desc[:3 * n, :nb].cpu().numpy().reshape(3, n, nb)
+    cpu, _ = cv2_pair_baseline([(hp[0], hp[1]), (hp[0], hp[2]), (hp[1], hp[2])], 6, True, None,
+                               "16384 x 16384 x 61 B AKAZE (BASELINE configs[4]), crossCheck=True")
     out["akaze_allpairs_sample_48x16384x61B_mutual"] = {
-        "pairs": len(pairs), "of_pairs": 499500, **res["tensor"], "popc_path": res["popc"],
+        "pairs": len(pairs), "of_pairs": 499500, "cpu_baseline": cpu, **res["tensor"], "popc_path": res["popc"],
         "speedup_over_popc_path": res["popc"]["ms_per_pass"] / res["tensor"]["ms_per_pass"],
         "matches_d2h_bytes_compact": res["tensor"]["matches"] * 6}
     return out

@@ -101,3 +101,71 @@ def test_install_into_reference_modules():
     finally:
         b.uninstall()
     assert ref.matcher_factory.EnhancedBFMatcher is ref.matcher_factory._CV2_EnhancedBFMatcher
+
+
+def test_reference_class_path_end_to_end_with_the_reference_imported():
+    """VERDICT r1 parity hole 2: everything that only runs when the REFERENCE's package is imported -- install(), the factory
+    building our class, validate_features inherited from the reference's ABC, contracts.resolve() handing back the
+    reference's own MatchData / EnhancedDMatch, the positional fast path of matcher._materialise keyed on the reference's
+    field order, ResultConverter._convert_method and a pickle round trip -- against the reference's own EnhancedBFMatcher on
+    the same inputs, field by field.  The reference tree cannot travel to the GPU box (its setup.py installs no modules:
+    DESIGN.md 2), so the kernels are replaced here by the oracle's arrays behind Engine.match_arrays; the kernels themselves
+    are compared with the same oracle in tests/test_parity_gpu.py."""
+    import pickle
+    import cv2
+    from oracle import bf_oracle as O
+    from oracle import ref_loader
+    if not ref_loader.available():
+        pytest.skip("reference tree not present on this box")
+    ref_loader._MODULES = tuple(dict.fromkeys(ref_loader._MODULES + ("utils", "result_types", "result_converters")))
+    ref = ref_loader.load()
+    cds, rt = ref.core_data_structures, ref.result_types
+    conv = ref.result_converters.ResultConverter()
+
+    class OracleEngine:                                  # stands in for the GPU: same signature as Engine.match_arrays
+        def match_arrays(self, d1, d2, norm, cc, ratio):
+            m = O.reference_match(d1, d2, norm, cc, ratio)
+            return b.MatchArrays(m.query_idx, m.train_idx, m.distance)
+
+    rng = np.random.default_rng(5)
+    xy = lambda n: [cv2.KeyPoint(float(x), float(y), 1.0) for x, y in rng.uniform(0, 900, size=(n, 2))]   # noqa: E731
+    a8, c8 = b.synth.binary_pair(seed=21, n=400, m=350, nbytes=32)
+    af, cf = b.synth.sift_pair(seed=22, n=300)
+    cases = [("ORB", a8, c8, {}), ("ORB", a8, c8, {"cross_check": True}), ("SIFT", af, cf, {"ratio_threshold": 0.8}),
+             ("SIFT", af, cf[:1], {"ratio_threshold": 0.8}), ("ORB", a8, c8, {"ratio_threshold": None})]
+    try:
+        assert len(b.install()) == 2
+        for method, d1, d2, params in cases:
+            f1 = cds.FeatureData(keypoints=xy(len(d1)), descriptors=d1, method=method)
+            f2 = cds.FeatureData(keypoints=xy(len(d2)), descriptors=d2, method=method)
+            ours = ref.matcher_factory.MatcherFactory()._create_bf_matcher(method, dict(params))
+            theirs_params = {"norm_type": ours.norm_type, "cross_check": ours.cross_check, "ratio_threshold": ours.ratio_threshold}
+            theirs = ref.matcher_factory._CV2_EnhancedBFMatcher(**theirs_params)
+            assert isinstance(ours, b.B200BFMatcher) and isinstance(ours, ref.base_classes.BaseFeatureMatcher)
+            ours._engine = OracleEngine()
+            got, want = ours.match(f1, f2), theirs.match(f1, f2)
+            assert type(got) is cds.MatchData and type(want) is cds.MatchData
+            assert got.method == want.method == "BF" and got.score_type == want.score_type
+            assert len(got.matches) == len(want.matches) and isinstance(got.matches, list)
+            for g, w in zip(got.matches, want.matches):
+                assert type(g) is cds.EnhancedDMatch
+                for field in ("queryIdx", "trainIdx", "score", "score_type", "imgIdx", "raw_distance", "confidence", "source_method"):
+                    assert getattr(g, field) == getattr(w, field), (method, params, field)
+                assert g.distance == w.distance and type(g.score) is float and type(g.queryIdx) is int
+                dm = g.to_cv2_dmatch()
+                assert (dm.queryIdx, dm.trainIdx) == (w.queryIdx, w.trainIdx) and dm.distance == np.float32(w.distance)
+            assert [m.queryIdx for m in got.get_best_matches()] == [m.queryIdx for m in want.get_best_matches()]
+            # the consumers of MatchData: the converter of the SfM hand-off and the per-pair pickle (result_types.py:173)
+            rg = conv._convert_method(rt.MethodResult(method_name=method, features1=f1, features2=f2, match_data=got))
+            rw = conv._convert_method(rt.MethodResult(method_name=method, features1=f1, features2=f2, match_data=want))
+            assert np.array_equal(rg.query_indices, rw.query_indices) and np.array_equal(rg.train_indices, rw.train_indices)
+            assert np.array_equal(rg.match_scores, rw.match_scores)
+            assert (rg.correspondences is None) == (rw.correspondences is None)
+            if rw.correspondences is not None:
+                assert np.array_equal(rg.correspondences, rw.correspondences)
+            back = pickle.loads(pickle.dumps(got))
+            assert type(back) is cds.MatchData and back.matches == got.matches
+            got.filtered_matches = got.matches[:3]            # callers mutate the result (pipeline.py:309-310)
+            assert len(got.get_best_matches()) == min(3, len(want.matches))
+    finally:
+        b.uninstall()

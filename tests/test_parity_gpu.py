@@ -55,18 +55,44 @@ def assert_exact(got, want, what=""):
     assert np.array_equal(got.distance.view(np.uint32), want.distance.view(np.uint32)), what
 
 
-def assert_close_float(got, want, what="", max_flip_frac=0.01):
-    """Non-integer float descriptors: compare as sets keyed by query; distances within RTOL; index
-    differences only allowed where the oracle's own distance gap is inside the tolerance."""
+def _flip_is_a_near_tie(q, g, w, a, c, mode):
+    """True iff the difference between the CUDA result `g` and the oracle's `w` for query row q ((train, dist) or None =
+    row not in the result) sits where the ORACLE's own decision margin, recomputed in float64, is inside RTOL."""
+    a64, c64 = a.astype(np.float64), c.astype(np.float64)
+    d = np.sqrt(((a64[q] - c64) ** 2).sum(axis=1))
+    if g is not None and w is not None:                       # another train row: the two must be equidistant within RTOL
+        return abs(d[g[0]] - d[w[0]]) <= RTOL * max(d[w[0]], 1e-6)
+    cc, ratio = mode
+    srt = np.sort(d)
+    if cc:                                                    # in / out of the mutual set: a tie in either direction
+        t = (g or w)[0]
+        fwd = len(srt) > 1 and srt[1] - srt[0] <= RTOL * max(srt[0], 1e-6)
+        e = np.sort(np.sqrt(((a64 - c64[t]) ** 2).sum(axis=1)))
+        bwd = len(e) > 1 and e[1] - e[0] <= RTOL * max(e[0], 1e-6)
+        return bool(fwd or bwd)
+    if ratio is not None:                                     # in / out of the ratio test: d1 ~ ratio * d2
+        return len(srt) > 1 and abs(srt[0] - ratio * srt[1]) <= RTOL * max(ratio * srt[1], 1e-6)
+    return False                                              # plain 1-NN keeps every row: membership cannot differ
+
+
+def assert_close_float(got, want, what="", max_flip_frac=0.01, descs=None, mode=None):
+    """Non-integer float descriptors: compare as sets keyed by query; distances within RTOL; differences of index or of
+    membership are counted, bounded, and -- with `descs` = (desc1, desc2) and `mode` = (cross_check, ratio) -- each one is
+    verified to sit where the oracle's own margin (float64) is inside RTOL: north_star's "near-tie index differences
+    counted and reported".  Returns the count."""
     g = {int(q): (int(t), float(d)) for q, t, d in zip(got.query_idx, got.train_idx, got.distance)}
     w = {int(q): (int(t), float(d)) for q, t, d in zip(want.query_idx, want.train_idx, want.distance)}
-    flips = len(set(g) ^ set(w))
+    flipped = sorted(set(g) ^ set(w))
     for q in set(g) & set(w):
         if g[q][0] != w[q][0]:
-            flips += 1
+            flipped.append(q)
         assert abs(g[q][1] - w[q][1]) <= RTOL * max(abs(w[q][1]), 1e-6) + 1e-7, f"{what}: q={q} {g[q]} vs {w[q]}"
-    assert flips <= max(1, int(max_flip_frac * max(len(w), 1))), f"{what}: {flips} near-tie flips of {len(w)}"
-    return flips
+    assert len(flipped) <= max(1, int(max_flip_frac * max(len(w), 1))), f"{what}: {len(flipped)} near-tie flips of {len(w)}"
+    if descs is not None:
+        for q in flipped:
+            assert _flip_is_a_near_tie(q, g.get(q), w.get(q), descs[0], descs[1], mode), \
+                f"{what}: q={q} differs ({g.get(q)} vs oracle {w.get(q)}) and the oracle's margin is NOT inside {RTOL}"
+    return len(flipped)
 
 
 MODES = [(False, None), (False, 0.7), (False, 0.75), (True, None)]
@@ -325,12 +351,13 @@ def test_l2_uint8_descriptors(eng):
 def test_l2_f32_vs_oracle(feng, mode):
     s = synth.superpoint_set(seed=21, images=2, n=1500, d=256, pool=2500)
     flips = assert_close_float(feng.match_arrays(s[0], s[1], b.NORM_L2, *mode),
-                               O.reference_match(s[0], s[1], O.NORM_L2, *mode), f"f32 {mode}")
+                               O.reference_match(s[0], s[1], O.NORM_L2, *mode), f"f32 {mode}", descs=(s[0], s[1]), mode=mode)
     print(f"f32 mode={mode}: near-tie flips={flips}")
     rng = np.random.default_rng(4)
     a = rng.normal(size=(333, 100)).astype(np.float32) * 3.0          # not unit norm, D not a multiple of 32
     c = (a[rng.permutation(333)[:290]] + rng.normal(size=(290, 100)).astype(np.float32) * 0.05).astype(np.float32)
-    assert_close_float(feng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"f32 generic {mode}")
+    assert_close_float(feng.match_arrays(a, c, b.NORM_L2, *mode), O.reference_match(a, c, O.NORM_L2, *mode), f"f32 generic {mode}",
+                       descs=(a, c), mode=mode)
 
 
 def assert_knn2_close(got, want, what=""):
@@ -419,7 +446,7 @@ def test_l2_f16c_kind_is_default_and_identical_to_tf32():
         for mode in [(False, 0.8), (True, None), (False, None)]:
             g16, g32 = e16.match_arrays(x, y, b.NORM_L2, *mode), e32.match_arrays(x, y, b.NORM_L2, *mode)
             assert_exact(g16, g32, f"f16 vs tf32 {name} {mode}")
-            assert_close_float(g16, O.reference_match(x, y, O.NORM_L2, *mode), f"f16 {name} {mode}")
+            assert_close_float(g16, O.reference_match(x, y, O.NORM_L2, *mode), f"f16 {name} {mode}", descs=(x, y), mode=mode)
         k16, k32 = e16.knn2_arrays(x, y, b.NORM_L2), e32.knn2_arrays(x, y, b.NORM_L2)
         for u, v in zip(k16, k32):
             assert np.array_equal(u, v), name
@@ -430,7 +457,7 @@ def test_l2_f32_config3_shape(eng):
     s = synth.superpoint_set(seed=2, images=2, n=4096, d=256)
     got = eng.match_arrays(s[0], s[1], b.NORM_L2, True, None)
     want = O.reference_match(s[0], s[1], O.NORM_L2, True, None)
-    flips = assert_close_float(got, want, "config3 pair", max_flip_frac=0.002)
+    flips = assert_close_float(got, want, "config3 pair", max_flip_frac=0.002, descs=(s[0], s[1]), mode=(True, None))
     assert len(got.query_idx) > 1000 and np.all(np.diff(got.distance) >= 0)
     print("config3 pair: matches", len(got.query_idx), "near-tie flips", flips)
 
@@ -486,7 +513,8 @@ def test_all_pairs_csr_equals_per_pair_oracle(eng, kind, mode):
             q, t, d = res.pair(p)
             want = O.reference_match(imgs[i], imgs[j], norm, *mode)
             if kind == "superpoint":
-                assert_close_float(O.Matches(q, t, d), want, f"{kind} pair {i},{j} chunk={chunk} mode={mode}", 0.02)
+                assert_close_float(O.Matches(q, t, d), want, f"{kind} pair {i},{j} chunk={chunk} mode={mode}", 0.02,
+                                   descs=(imgs[i], imgs[j]), mode=mode)
             else:
                 assert_exact(O.Matches(q, t, d), want, f"{kind} pair {i},{j} chunk={chunk} mode={mode}")
 

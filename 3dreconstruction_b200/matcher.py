@@ -26,10 +26,20 @@ def _materialise(c: contracts.Contracts, arr: MatchArrays) -> list:
     q = arr.query_idx.tolist()
     t = arr.train_idx.tolist()
     d = arr.distance.astype(np.float64).tolist()      # float32 widened to Python float, as cv2.DMatch.distance
-    if _positional_ok(EDM):                           # positional construction is ~3x cheaper than keywords (4096 objects per pair)
-        return [EDM(qi, ti, di, dist_t, 0, di) for qi, ti, di in zip(q, t, d)]
-    return [EDM(queryIdx=qi, trainIdx=ti, score=di, score_type=dist_t, raw_distance=di)
-            for qi, ti, di in zip(q, t, d)]
+    # Thousands of small objects per pair: the cyclic collector's generation-0 passes, triggered by the allocation count,
+    # cost 3x the construction itself (measured 4.8 -> 1.4 ms for 4096 matches); nothing here can form a cycle.
+    import gc
+    paused = gc.isenabled()
+    if paused:
+        gc.disable()
+    try:
+        if _positional_ok(EDM):                       # positional construction is ~3x cheaper than keywords
+            return [EDM(qi, ti, di, dist_t, 0, di) for qi, ti, di in zip(q, t, d)]
+        return [EDM(queryIdx=qi, trainIdx=ti, score=di, score_type=dist_t, raw_distance=di)
+                for qi, ti, di in zip(q, t, d)]
+    finally:
+        if paused:
+            gc.enable()
 
 
 _POSITIONAL: dict = {}

@@ -688,6 +688,42 @@ def test_plugin_raises_for_what_cv2_would_match_but_the_library_does_not(eng):
     assert md.matches == [] and md.method == "BF"
 
 
+def test_descriptor_cache_serves_only_live_unchanged_arrays():
+    """Engine's host-array -> prepared-store cache (the matcher is reused over all pairs of a run, pipeline.py:99-104): a hit
+    needs the same live array object and an unchanged fingerprint; results never depend on whether the cache was used."""
+    if not torch.cuda.is_available():
+        pytest.skip("needs a GPU")
+    e = b.Engine(cache_entries=4)
+    a, c = synth.sift_pair(seed=41, n=700)
+    want = O.reference_match(a, c, O.NORM_L2, False, 0.8)
+    assert_exact(e.match_arrays(a, c, b.NORM_L2, False, 0.8), want, "cold")
+    assert (e.cache.hits, e.cache.misses) == (0, 2)
+    assert_exact(e.match_arrays(a, c, b.NORM_L2, False, 0.8), want, "cached")
+    assert e.cache.hits == 2
+    assert_exact(e.match_arrays(c, a, b.NORM_L2, True, None), O.reference_match(c, a, O.NORM_L2, True, None), "cached, swapped, other mode")
+    assert e.cache.hits == 4
+    a[0] = np.clip(a[0] + 9, 0, 255)                              # in-place edit of a sampled row: the entry must not be served
+    assert_exact(e.match_arrays(a, c, b.NORM_L2, False, 0.8), O.reference_match(a, c, O.NORM_L2, False, 0.8), "after an edit")
+    assert e.cache.misses == 3
+    x, y = synth.binary_pair(seed=42, n=600, nbytes=32)
+    assert_exact(e.match_arrays(x, y, b.NORM_HAMMING, True, None), O.reference_match(x, y, O.NORM_HAMMING, True, None), "orb cold")
+    x2 = x.copy()
+    del x                                                         # the array dies: a new array (even at the same address) is a miss
+    h = e.cache.hits
+    assert_exact(e.match_arrays(x2, y, b.NORM_HAMMING, True, None), O.reference_match(x2, y, O.NORM_HAMMING, True, None), "orb new object")
+    assert e.cache.hits == h + 1                                  # y only
+    assert len(e.cache.d) <= 4                                    # bounded (least recently used evicted)
+    f = synth.superpoint_set(seed=43, images=2, n=512, d=256, pool=800)
+    g1 = e.match_arrays(f[0], f[1], b.NORM_L2, True, None)
+    g2 = e.match_arrays(f[0], f[1], b.NORM_L2, True, None)        # float stores from the cache: same bits
+    assert_exact(g2, g1, "float cached vs cold")
+    mixed = e.match_arrays(a, f[0][:, :128].copy(), b.NORM_L2, False, None)     # one side integer-valued, the other not
+    assert len(mixed.query_idx) == len(a)
+    e0 = b.Engine(cache_entries=0)
+    assert_exact(e0.match_arrays(a, c, b.NORM_L2, False, 0.8), O.reference_match(a, c, O.NORM_L2, False, 0.8), "cache off")
+    assert len(e0.cache.d) == 0
+
+
 # ------------------------------------------------------------------ SfM hand-off (feature cache -> all pairs -> correspondences)
 @pytest.mark.parametrize("name", ["orb_cross", "orb_ratio07", "sift_ratio075"])
 def test_sfm_handoff_equals_reference_converter(eng, name):

@@ -136,3 +136,30 @@ def homography_set(seed: int = 6, pairs: int = 64, n_lo: int = 50, n_hi: int = 2
     ptr = np.zeros(pairs + 1, np.int64)
     ptr[1:] = np.cumsum([len(s) for s in sets])
     return np.concatenate(sets, axis=0), ptr
+
+
+def two_view_pair(seed: int = 7, n: int = 1000, inlier_frac: float = 0.6, noise: float = 0.7, size=(1600, 1200),
+                  focal_ratio: float = 1.2):
+    """Correspondences of a rigid scene seen by two cameras, for the essential-matrix stage: float32 [n, 4] pixel
+    coordinates (x1, y1, x2, y2); `inlier_frac` of them follow the epipolar geometry (+ Gaussian pixel noise), the rest
+    are uniformly random in the second image.  Camera as the reference estimates it when none is given
+    (essential_estimation.py:36-60): f = focal_ratio * width, principal point at the image centre.  Returns (corr, K)."""
+    rng = np.random.default_rng(seed)
+    w, h = size
+    f = w * focal_ratio
+    K = np.array([[f, 0, w / 2.0], [0, f, h / 2.0], [0, 0, 1]], np.float64)
+    X = np.concatenate([rng.uniform(-2.5, 2.5, size=(n, 2)), rng.uniform(5, 12, size=(n, 1))], axis=1)
+    a = rng.uniform(-0.25, 0.25, size=3)
+    th = np.linalg.norm(a) + 1e-12
+    k = a / th
+    Kx = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+    R = np.eye(3) + np.sin(th) * Kx + (1 - np.cos(th)) * Kx @ Kx
+    t = rng.uniform(-1.0, 1.0, size=3)
+    Y = X @ R.T + t
+    p1 = X[:, :2] / X[:, 2:] * f + K[:2, 2]
+    p2 = Y[:, :2] / Y[:, 2:] * f + K[:2, 2]
+    p1 += rng.normal(size=p1.shape) * noise
+    p2 += rng.normal(size=p2.shape) * noise
+    bad = rng.permutation(n)[:n - int(round(n * inlier_frac))]
+    p2[bad] = np.stack([rng.uniform(0, w, len(bad)), rng.uniform(0, h, len(bad))], axis=1)
+    return np.concatenate([p1, p2], axis=1).astype(np.float32), K

@@ -24,7 +24,8 @@ EXPORTS = ["b200m_version", "b200m_error_string", "b200m_last_cuda_error", "b200
            "b200m_timing_enable", "b200m_timing_collect", "b200m_f32_stats", "b200m_l2_i8_aux_bytes",
            "b200m_l2_i8_aux_init", "b200m_prep_l2_i8_rows", "b200m_hamming_tc_width", "b200m_prep_hamming_tc",
            "b200m_gather_correspondences", "b200m_hamming_fp4_width", "b200m_prep_hamming_fp4", "b200m_ransac_homography", "b200m_l2_f16_aux_bytes", "b200m_prep_l2_f16",
-           "b200m_l2_i8_aux_rows", "b200m_rec_bytes", "b200m_match_pairs_rec", "b200m_match_pairs_static"]
+           "b200m_l2_i8_aux_rows", "b200m_rec_bytes", "b200m_match_pairs_rec", "b200m_match_pairs_static",
+           "b200m_ransac_essential"]
 
 
 class Pair(ctypes.Structure):
@@ -69,6 +70,7 @@ def load() -> ctypes.CDLL:
     lib.b200m_l2_f16_aux_bytes.argtypes = [i64, i32, ctypes.POINTER(ctypes.c_size_t)]
     lib.b200m_prep_l2_f16.argtypes = [vp, i64, i32, vp, vp]
     lib.b200m_ransac_homography.argtypes = [vp, vp, i32, dbl, dbl, i32, vp, vp, vp, vp, vp]
+    lib.b200m_ransac_essential.argtypes = [vp, vp, i32, vp, dbl, dbl, i32, vp, vp, vp, vp, vp]
     lib.b200m_workspace_bytes.argtypes = [i32, i32, i32, i64, i64, i32, i32, i32, ctypes.POINTER(ctypes.c_size_t)]
     lib.b200m_match_pairs.argtypes = [i32, vp, vp, i64, vp, vp, i64, i32, ctypes.POINTER(Pair), i32, i32, dbl,
                                       vp, vp, vp, vp, vp, ctypes.c_size_t, vp]

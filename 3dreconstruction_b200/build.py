@@ -13,9 +13,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libb200match.so")
-SOURCES = ["capi.cu", "hamming.cu", "hamming_tc.cu", "l2_i8.cu", "l2_f32.cu", "tail.cu", "prep.cu", "adapter.cu", "ransac.cu"]
+SOURCES = ["capi.cu", "hamming.cu", "hamming_tc.cu", "l2_i8.cu", "l2_f32.cu", "tail.cu", "prep.cu", "adapter.cu", "ransac.cu", "essential.cu"]
 # ransac.cu restates cv2's float32/fp64 arithmetic of findHomography: a*b+c must round twice there
-PER_SOURCE_FLAGS = {"ransac.cu": ["-fmad=false"]}
+PER_SOURCE_FLAGS = {"ransac.cu": ["-fmad=false"], "essential.cu": ["-fmad=false"]}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr"]
 

@@ -255,6 +255,27 @@ B200M_API int b200m_ransac_homography(const float* corr_xyxy, const int64_t* ptr
                      double confidence, int max_iters, double* H_out, uint8_t* mask_out, int32_t* inliers_out,
                      int32_t* iters_out, void* stream);
 
+/* Essential matrix of matched pairs: what, per image pair,
+ *     E, mask = cv2.findEssentialMat(pts1_norm, pts2_norm, focal=1.0, pp=(0, 0), method=cv2.RANSAC, prob=prob,
+ *                                    threshold=threshold, maxIters=max_iters)
+ * returns at /root/reference/CameraPoseEstimation/essential_estimation.py:118-126 on pts_norm = cv2.undistortPoints(pts, K, None)
+ * (:98-108), for every pair of a CSR in one launch (one CTA per pair; cv2's own random sequence and its order of the up to 10
+ * candidate models per sample, see csrc/essential.cu).
+ *   corr_xyxy   float32 [ptr[num_pairs], 4] PIXEL coordinates from b200m_gather_correspondences (device, 16-byte aligned)
+ *   ptr         int64 [num_pairs + 1] (device)
+ *   cam         float64 [num_pairs, 8] (device): fx1, fy1, cx1, cy1, fx2, fy2, cx2, cy2 of the pair's two cameras; the kernel
+ *               normalises x' = (x - cx) * (1 / fx) in float64, which is undistortPoints without distortion bit for bit.
+ *               NULL: the coordinates are already normalised.
+ *   threshold   in NORMALISED units (the reference passes focal = 1); prob in (0, 1)
+ *   E_out       float64 [num_pairs, 9] row-major 3x3, unit Frobenius norm; NaN where cv2 returns None
+ *   mask_out    uint8 [ptr[num_pairs]]: 1 = inlier of E (cv2's mask.ravel())
+ *   inliers_out int32 [num_pairs]: number of inliers, or -1 when there is no model (fewer than 5 points included)
+ *   iters_out   int32 [num_pairs] or NULL: RANSAC iterations run (diagnostic)
+ * No workspace. */
+B200M_API int b200m_ransac_essential(const float* corr_xyxy, const int64_t* ptr, int num_pairs, const double* cam,
+                     double threshold, double prob, int max_iters, double* E_out, uint8_t* mask_out, int32_t* inliers_out,
+                     int32_t* iters_out, void* stream);
+
 /* Measurement hooks for bench.py's roofline: when enabled, CUDA events are recorded on the
  * launching stream around every knn-stage kernel; collect() synchronises them and returns the summed
  * device time (ms) and the number of knn launches since the last collect/enable. */

@@ -19,24 +19,28 @@
 //     limit, the stop.  Hypotheses drawn past the stop are discarded, exactly as if they had never been drawn.
 // There is no refit: E is the winning model, the mask its inliers.  Compiled with -fmad=false (build.py).
 #include <float.h>
+#include <math.h>
+#include <string.h>
 #include <math_constants.h>
 #include "common.cuh"
 
 namespace {
 
 constexpr int ET = 128;          // threads per CTA
-constexpr int HYP = 64;          // hypotheses (5-tuples) per round = solver threads
-// per-thread workspace, element-major in shared memory: element e of thread t lives at ws[e * HYP + t]
-constexpr int OFF_V = 0;         // 81  V[9][9]: rows 0..4 an orthonormal basis of Q's row space, rows 5..8 the basis X, Y, Z, W
-constexpr int OFF_A = 81;        // 200 A[10][20]; after the elimination its free rows hold B, the polynomial, the roots, the models
-constexpr int OFF_T = 281;       // 10  tr(E E^T)
-constexpr int OFF_Q = 291;       // 10  quadratic temporary
-constexpr int SCR = 301;
+constexpr int HYP = 96;          // hypotheses (5-tuples) per round = solver threads (3 of the 4 warps)
+// per-thread workspace, element-major in shared memory: element e of thread t lives at ws[e * HYP + t].  256 doubles per
+// thread = 192 KiB for 96 threads: rows 0..4 of V (needed only while the basis is built) overlay A, which is zeroed later.
+constexpr int OFF_N = 0;         // 36  the basis X, Y, Z, W (rows 5..8 of V)
+constexpr int OFF_A = 36;        // 200 A[10][20]; before it is built: V rows 0..4; after the elimination: B, polynomial, roots, models
+constexpr int OFF_T = 236;       // 10  tr(E E^T)
+constexpr int OFF_Q = 246;       // 10  quadratic temporary
+constexpr int SCR = 256;
 constexpr int OFF_B = OFF_A;             // 39  B[3][13]          (rows 0, 1 of A)
 constexpr int OFF_C = OFF_A + 40;        // 11  c[0..10]          (row 2)
 constexpr int OFF_RE = OFF_A + 60;       // 10  roots, real parts  (row 3)
 constexpr int OFF_IM = OFF_A + 70;       // 10  roots, imaginary parts
 constexpr int OFF_M = OFF_A + 80;        // 90  models[10][9]     (rows 4..8, free once B is built)
+__device__ __forceinline__ int vidx(int i, int k) { return (i < 5 ? OFF_A + 9 * i : OFF_N + 9 * (i - 5)) + k; }   // V[i][k]
 
 __device__ const int8_t LLT[4][4] = {{0, 3, 4, 6}, {3, 1, 5, 7}, {4, 5, 2, 8}, {6, 7, 8, 9}};          // linear x linear -> quadratic
 __device__ const int8_t QLT[10][4] = {{0, 2, 4, 5}, {3, 1, 6, 7}, {10, 13, 16, 17}, {2, 3, 8, 9}, {4, 8, 10, 11},
@@ -58,41 +62,41 @@ __device__ bool null_basis(const WS& w) {
         for (int it = 0; it < 2; ++it)
             for (int j = 0; j < i; ++j) {
                 double sd = 0;
-                for (int k = 0; k < 9; ++k) sd += w(OFF_V + 9 * i + k) * w(OFF_V + 9 * j + k);
-                for (int k = 0; k < 9; ++k) w(OFF_V + 9 * i + k) -= sd * w(OFF_V + 9 * j + k);
+                for (int k = 0; k < 9; ++k) sd += w(vidx(i, k)) * w(vidx(j, k));
+                for (int k = 0; k < 9; ++k) w(vidx(i, k)) -= sd * w(vidx(j, k));
             }
         double nn = 0;
-        for (int k = 0; k < 9; ++k) nn += w(OFF_V + 9 * i + k) * w(OFF_V + 9 * i + k);
+        for (int k = 0; k < 9; ++k) nn += w(vidx(i, k)) * w(vidx(i, k));
         if (!(nn > 1e-300)) return false;
         nn = 1.0 / sqrt(nn);
-        for (int k = 0; k < 9; ++k) w(OFF_V + 9 * i + k) *= nn;
+        for (int k = 0; k < 9; ++k) w(vidx(i, k)) *= nn;
     }
     u64 st = 0x12345678ull;
     for (int i = 5; i < 9; ++i) {
-        for (int k = 0; k < 9; ++k) w(OFF_V + 9 * i + k) = (rng_next(st) & 256u) != 0 ? 1.0 / 9 : -1.0 / 9;
+        for (int k = 0; k < 9; ++k) w(vidx(i, k)) = (rng_next(st) & 256u) != 0 ? 1.0 / 9 : -1.0 / 9;
         for (int it = 0; it < 2; ++it)
             for (int j = 0; j < i; ++j) {
                 double sd = 0, asum = 0;
-                for (int k = 0; k < 9; ++k) sd += w(OFF_V + 9 * i + k) * w(OFF_V + 9 * j + k);
+                for (int k = 0; k < 9; ++k) sd += w(vidx(i, k)) * w(vidx(j, k));
                 for (int k = 0; k < 9; ++k) {
-                    const double t = w(OFF_V + 9 * i + k) - sd * w(OFF_V + 9 * j + k);
-                    w(OFF_V + 9 * i + k) = t;
+                    const double t = w(vidx(i, k)) - sd * w(vidx(j, k));
+                    w(vidx(i, k)) = t;
                     asum += fabs(t);
                 }
                 asum = asum > DBL_EPSILON * 100 ? 1 / asum : 0;
-                for (int k = 0; k < 9; ++k) w(OFF_V + 9 * i + k) *= asum;
+                for (int k = 0; k < 9; ++k) w(vidx(i, k)) *= asum;
             }
         double sd = 0;
-        for (int k = 0; k < 9; ++k) sd += w(OFF_V + 9 * i + k) * w(OFF_V + 9 * i + k);
+        for (int k = 0; k < 9; ++k) sd += w(vidx(i, k)) * w(vidx(i, k));
         sd = sqrt(sd);
         const double s = sd > DBL_MIN ? 1 / sd : 0;
-        for (int k = 0; k < 9; ++k) w(OFF_V + 9 * i + k) *= s;
+        for (int k = 0; k < 9; ++k) w(vidx(i, k)) *= s;
     }
     return true;
 }
 
 // linear polynomial of entry (r, c) of E = x X + y Y + z Z + W: coefficient k is basis vector k's element 3 r + c
-__device__ __forceinline__ double Elin(const WS& w, int r, int c, int k) { return w(OFF_V + 9 * (5 + k) + 3 * r + c); }
+__device__ __forceinline__ double Elin(const WS& w, int r, int c, int k) { return w(OFF_N + 9 * k + 3 * r + c); }
 
 // q (10 quadratic coefficients at offset oq) += s * E[r1][c1] * E[r2][c2]
 __device__ void mul_ll(const WS& w, int oq, int r1, int c1, int r2, int c2, double s) {
@@ -163,6 +167,60 @@ __device__ bool reduce(const WS& w) {
     return true;
 }
 
+// The same iteration for the common case n == 10 with the polynomial and the roots in REGISTERS (both inner loops fully
+// unrolled): in practice the roots never reach a fixed point -- they keep flipping in their last bits -- so all 300 sweeps run,
+// 300 x 10 x 20 complex multiplications per sample; with every operand in shared memory that was ~6 ms per round of 64
+// samples.  Same operations in the same order as solve_poly() below, hence the same bits.
+__device__ void solve_poly10(const WS& w) {
+    double c[11], re[10], im[10];
+#pragma unroll
+    for (int k = 0; k < 11; ++k) c[k] = w(OFF_C + k);
+    {
+        double pr = 1, pi = 0;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+            re[i] = pr; im[i] = pi;
+            const double t = pr - pi; pi = pr + pi; pr = t;
+        }
+    }
+#pragma unroll 1
+    for (int iter = 0; iter < 300; ++iter) {
+        bool changed = false;        // (cv's maxDiff <= 0 test implies "nothing changed", which ends the iteration here anyway)
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+            const double xr = re[i], xi = im[i];
+            double nr = c[10], ni = 0, dr = c[10], di = 0;
+            int same = 1;
+#pragma unroll
+            for (int j = 0; j < 10; ++j) {
+                const double t = nr * xr - ni * xi;
+                ni = nr * xi + ni * xr;
+                nr = t + c[9 - j];
+                if (j != i) {
+                    const double er = xr - re[j], ei = xi - im[j];
+                    if (er != 0 || ei != 0) { const double u = dr * er - di * ei; di = dr * ei + di * er; dr = u; }
+                    else ++same;
+                }
+            }
+            const double t = 1.0 / (dr * dr + di * di);
+            double qr = (nr * dr + ni * di) * t, qi = (-nr * di + ni * dr) * t;
+            if (same > 1) {
+                const double mag = pow(sqrt(qr * qr + qi * qi), 1.0 / same), ang = atan2(qi, qr) / same;
+                qr = mag * cos(ang); qi = mag * sin(ang);
+            }
+            const double yr = xr - qr, yi = xi - qi;
+            changed |= yr != xr || yi != xi;
+            re[i] = yr; im[i] = yi;
+        }
+        if (!changed) break;
+    }
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        w(OFF_RE + i) = re[i];
+        w(OFF_IM + i) = fabs(im[i]) < 1e-100 ? 0.0 : im[i];
+    }
+}
+
 // cv::solvePoly (Durand-Kerner, Gauss-Seidel updates, start values (1 + i)^k, 300 sweeps) on c[0..n] at OFF_C; roots to
 // OFF_RE / OFF_IM; returns their number.  A sweep that leaves every root unchanged ends the iteration: every later sweep
 // would recompute the same values.
@@ -170,6 +228,7 @@ __device__ int solve_poly(const WS& w) {
     int n = 10;
     for (; n > 1; --n)
         if (fabs(w(OFF_C + n)) > DBL_EPSILON) break;
+    if (n == 10) { solve_poly10(w); return 10; }
     double pr = 1, pi = 0;
     for (int i = 0; i < n; ++i) {
         w(OFF_RE + i) = pr; w(OFF_IM + i) = pi;
@@ -217,7 +276,7 @@ __device__ int five_point(const WS& w, const double (*m)[4]) {
     for (int i = 0; i < 5; ++i) {
         const double x1 = m[i][0], y1 = m[i][1], x2 = m[i][2], y2 = m[i][3];
         const double q[9] = {x1 * x2, y1 * x2, x2, x1 * y2, y1 * y2, y2, x1, y1, 1.0};     // = E row by row for x2^T E x1
-        for (int k = 0; k < 9; ++k) w(OFF_V + 9 * i + k) = q[k];
+        for (int k = 0; k < 9; ++k) w(vidx(i, k)) = q[k];
     }
     if (!null_basis(w)) return 0;
     coeff_matrix(w);
@@ -281,7 +340,7 @@ __device__ int five_point(const WS& w, const double (*m)[4]) {
         const double x = v[0] / v[2], y = v[1] / v[2];
         double nn = 0;
         for (int k = 0; k < 9; ++k) {
-            const double e = w(OFF_V + 45 + k) * x + w(OFF_V + 54 + k) * y + w(OFF_V + 63 + k) * z + w(OFF_V + 72 + k);
+            const double e = w(OFF_N + k) * x + w(OFF_N + 9 + k) * y + w(OFF_N + 18 + k) * z + w(OFF_N + 27 + k);
             w(OFF_M + 9 * count + k) = e;
             nn += e * e;
         }
@@ -292,12 +351,20 @@ __device__ int five_point(const WS& w, const double (*m)[4]) {
     return count;
 }
 
-// EMEstimatorCallback::computeError for one correspondence: Sampson distance in float64, stored as float32
-__device__ __forceinline__ float sampson(const double* E, double x1, double y1, double x2, double y2) {
+// EMEstimatorCallback::computeError + the threshold test for one correspondence: cv stores the Sampson distance
+// s^2 / d (float64) as float32 and keeps the point iff that float <= float32(threshold^2).  (float)q <= t  <=>  q <= M for the
+// double M the host derives from t (the midpoint to the next float, or the double below it, by the parity of t: round to
+// nearest even), and fl(s^2 / d) <= M is decided by one multiplication unless s^2 lies within 2^-50 of M d: only then is the
+// division carried out.  Same decisions, bit for bit; the division was a third of the counting loop.
+__device__ __forceinline__ bool sampson_inlier(const double* E, double x1, double y1, double x2, double y2, float thr2, double M) {
     const double a0 = E[0] * x1 + E[1] * y1 + E[2], a1 = E[3] * x1 + E[4] * y1 + E[5], a2 = E[6] * x1 + E[7] * y1 + E[8];
     const double b0 = E[0] * x2 + E[3] * y2 + E[6], b1 = E[1] * x2 + E[4] * y2 + E[7];
     const double s = x2 * a0 + y2 * a1 + a2;
-    return (float)(s * s / (a0 * a0 + a1 * a1 + b0 * b0 + b1 * b1));
+    const double num = s * s, den = a0 * a0 + a1 * a1 + b0 * b0 + b1 * b1;
+    const double p = M * den;
+    if (num < p * (1.0 - 0x1p-50)) return true;
+    if (num > p * (1.0 + 0x1p-50)) return false;
+    return (float)(num / den) <= thr2;            // the boundary, a zero or a non-finite denominator: exactly as cv computes it
 }
 
 __device__ int update_num_iters5(double p, double ep, int max_iters) {      // RANSACUpdateNumIters, modelPoints = 5
@@ -326,7 +393,7 @@ constexpr int SUB = 16;          // hypotheses whose inliers are counted between
 
 __global__ void __launch_bounds__(ET, 1)
 ransac_essential_kernel(const float4* __restrict__ corr, const long long* __restrict__ ptr, int num_pairs,
-                        const double* __restrict__ cam, float thr2, double prob, int max_iters, double* __restrict__ E_out,
+                        const double* __restrict__ cam, float thr2, double thrM, double prob, int max_iters, double* __restrict__ E_out,
                         uint8_t* __restrict__ mask_out, int32_t* __restrict__ inliers_out, int32_t* __restrict__ iters_out) {
     __shared__ ESmem sm;
     extern __shared__ double scratch[];          // [SCR][HYP]
@@ -424,7 +491,7 @@ ransac_essential_kernel(const float4* __restrict__ corr, const long long* __rest
                         double E[9];
 #pragma unroll
                         for (int k = 0; k < 9; ++k) E[k] = scratch[(OFF_M + 9 * m + k) * HYP + h];
-                        const bool good = in && sampson(E, x1, y1, x2, y2) <= thr2;
+                        const bool good = in && sampson_inlier(E, x1, y1, x2, y2, thr2, thrM);
                         const int c = __popc(__ballot_sync(0xffffffffu, good));
                         if (lane == 0 && c) atomicAdd(&sm.cnt[h][m], c);
                     }
@@ -461,7 +528,7 @@ ransac_essential_kernel(const float4* __restrict__ corr, const long long* __rest
     for (int i = tid; i < count; i += ET) {
         double x1, y1, x2, y2;
         norm_pt(__ldg(pts + i), x1, y1, x2, y2);
-        mask[i] = sampson(E, x1, y1, x2, y2) <= thr2;
+        mask[i] = sampson_inlier(E, x1, y1, x2, y2, thr2, thrM);
     }
     if (tid < 9) Eg[tid] = E[tid];
     if (tid == 0) { inliers_out[pair] = sm.best_cnt; if (iters_out) iters_out[pair] = sm.iters_run; }
@@ -488,8 +555,17 @@ int b200m_ransac_essential(const float* corr_xyxy, const int64_t* ptr, int num_p
                          "ransac_essential_kernel smem attribute");
         once.done[dev] = 1;
     }
+    // (float)q <= t  <=>  q <= M: M = the midpoint between t and the next float if t's mantissa is even (a tie rounds to t),
+    // else the double just below that midpoint
+    const float t = (float)(threshold * threshold);
+    if (!(t > 0.0f) || !isfinite(t)) return B200M_EINVAL;
+    const float tn = nextafterf(t, INFINITY);
+    uint32_t tbits;
+    memcpy(&tbits, &t, 4);
+    double M = 0.5 * ((double)t + (double)tn);
+    if (tbits & 1u) M = nextafter(M, 0.0);
     ransac_essential_kernel<<<(unsigned)num_pairs, ET, dyn, (cudaStream_t)stream>>>(
-        (const float4*)corr_xyxy, (const long long*)ptr, num_pairs, cam, (float)(threshold * threshold), prob, max_iters, E_out,
+        (const float4*)corr_xyxy, (const long long*)ptr, num_pairs, cam, t, M, prob, max_iters, E_out,
         mask_out, inliers_out, iters_out);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "ransac_essential_kernel launch");

@@ -311,6 +311,7 @@ def single_pair_extras(torch, b, eng, pk):
     out.update(allpairs_extras(torch, b, eng, pk))
     out.update(sfm_extras(torch, b, eng, pk))
     out.update(ransac_extras(torch, b, eng, pk))
+    out.update(essential_extras(torch, b, eng, pk))
     return out
 
 
@@ -482,6 +483,63 @@ def ransac_extras(torch, b, eng, pk):
     except ImportError:
         out["cpu_cv2_findHomography"] = None
     return {"ransac_homography_2048_pairs": out}
+
+
+def essential_extras(torch, b, eng, pk):
+    """SURVEY 8f N3, second half: essential-matrix RANSAC of 1024 pairs in one launch (csrc/essential.cu), device-resident pixel
+    correspondences; beside it cv2.findEssentialMat (what essential_estimation.py:118-126 calls) on a sample of the same pairs."""
+    import time
+    pose = importlib.import_module("3dreconstruction_b200.pose")
+    P = 1024
+    rng = np.random.default_rng(8)
+    parts, cams = [], []
+    for p in range(P):
+        n = int(rng.integers(150, 2500))
+        c, K = b.synth.two_view_pair(seed=20000 + p, n=n, inlier_frac=float(rng.uniform(0.35, 0.9)), noise=0.7)
+        parts.append(c)
+        cams.append([K[0, 0], K[1, 1], K[0, 2], K[1, 2]] * 2)
+    corr = np.concatenate(parts)
+    ptr = np.concatenate([[0], np.cumsum([len(x) for x in parts])]).astype(np.int64)
+    cams = np.asarray(cams, np.float64)
+    thr, prob, iters = 1.0 / 1920, 0.999, 5000            # ~1 pixel; the reference's confidence and iteration cap
+    dc, dp, dk = eng.to_device(corr), eng.to_device(ptr), eng.to_device(cams)
+    run = lambda: pose.estimate_pairs_device(eng, dc, dp, dk, thr, prob, iters)        # noqa: E731
+    for _ in range(2):
+        v = run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        v = run()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    its, inl, mask = v.iters.cpu().numpy(), v.inliers.cpu().numpy(), v.mask.cpu().numpy()
+    out = {"pairs": P, "matches": int(ptr[-1]), "ms_per_launch": ms, "pairs_per_s": P / (ms / 1e3),
+           "ransac_iterations_total": int(its.sum()), "hypotheses_per_s": float(its.sum()) / (ms / 1e3),
+           "pairs_with_model": int((inl >= 0).sum()),
+           "note": "one CTA per pair; cv2's own random sequence and model order replayed; per sample Nister's five-point solver in fp64 "
+                   "(null-space basis as cv's SVD completes it, 10 x 20 elimination, Durand-Kerner on the degree-10 polynomial), up to 10 "
+                   "models; Sampson error of every point for every model; threshold ~1 px, prob 0.999, maxIters 5000 (the reference's)"}
+    try:
+        import cv2
+        sample = list(range(0, P, P // 32))
+        same = 0
+        res = []
+        t0 = time.perf_counter()
+        for p in sample:
+            c = corr[ptr[p]:ptr[p + 1]].astype(np.float64)
+            K = cams[p]
+            m1 = np.stack([(c[:, 0] - K[2]) * (1.0 / K[0]), (c[:, 1] - K[3]) * (1.0 / K[1])], axis=1)
+            m2 = np.stack([(c[:, 2] - K[6]) * (1.0 / K[4]), (c[:, 3] - K[7]) * (1.0 / K[5])], axis=1)
+            res.append(cv2.findEssentialMat(m1, m2, focal=1.0, pp=(0.0, 0.0), method=cv2.RANSAC, prob=prob, threshold=thr, maxIters=iters))
+        t = time.perf_counter() - t0
+        for p, (Ec, mc) in zip(sample, res):
+            same += Ec is not None and np.array_equal(mc.ravel(), mask[ptr[p]:ptr[p + 1]])
+        out["cpu_cv2_findEssentialMat"] = {"sample_pairs": len(sample), "pairs_per_s": len(sample) / t, "threads": cv2.getNumThreads(),
+                                           "masks_identical_to_gpu": int(same), "speedup": out["pairs_per_s"] / (len(sample) / t)}
+    except ImportError:
+        out["cpu_cv2_findEssentialMat"] = None
+    return {"ransac_essential_1024_pairs": out}
 
 
 def superpoint_set_gpu(torch, device, images, n, d=256, seed=2, pool=8192, shared=0.5, sigma=0.05):

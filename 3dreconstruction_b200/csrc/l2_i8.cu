@@ -32,6 +32,19 @@
 #include "common.cuh"
 #include "sm100.cuh"
 
+// how the 16 epilogue warps of the fold kernel wait for their accumulator: 0 = spin on mbarrier.try_wait (default),
+// 1 = try_wait with a suspend-time hint, 2 = spin with __nanosleep(32) back-off.  Measured in profiles/r02_notes.md.
+#ifndef B200M_EPI_WAIT_MODE
+#define B200M_EPI_WAIT_MODE 0
+#endif
+#if B200M_EPI_WAIT_MODE == 1
+#define B200M_EPI_WAIT(bar, par) sm100::mbar_wait_suspend(bar, par)
+#elif B200M_EPI_WAIT_MODE == 2
+#define B200M_EPI_WAIT(bar, par) do { while (!sm100::mbar_try_wait(bar, par)) __nanosleep(32); } while (0)
+#else
+#define B200M_EPI_WAIT(bar, par) sm100::mbar_wait(bar, par)
+#endif
+
 namespace {
 
 constexpr int TM = 128;            // query rows per tile  (UMMA M)
@@ -585,7 +598,7 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 {   // accumulator ready == the ring stage of this tile's last K block has been released (see the MMA warp)
                     const uint32_t tc = 2 * k + g;                    // this CTA's tile counter
                     const uint32_t use = (tc * NKB + NKB - 1) / NBF, stage = (tc * NKB + NKB - 1) % NBF;
-                    sm100::mbar_wait(&sm.b_empty[stage], use & 1);
+                    B200M_EPI_WAIT(&sm.b_empty[stage], use & 1);
                 }
                 sm100::tc_fence_after();
                 uint32_t acc[2][32];

@@ -253,8 +253,10 @@ class DistributedAllPairs:
 
     # ------------------------------------------------------------------ ingest
     def _ingest(self, host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, ph):
-        """Enqueue, on the copy stream, upload + re-encoding + all-gather (+ local derivations) of every group.
-        Returns (Store, [event per group], not-integer flag tensor or None)."""
+        """Set up the store and return (Store, ingest_group, events, not-integer flag tensor or None): ingest_group(gi)
+        enqueues, on the copy stream, upload + re-encoding + all-gather (+ local derivations) of group gi and returns its
+        event.  Float descriptors are ingested here at once (one group + the store-wide re-encoding): then ingest_group is
+        None and `events` holds the event of every group."""
         import torch.distributed as dist
         eng, dev = self.engine, self.engine.device
         lib = eng.lib
@@ -300,6 +302,8 @@ class DistributedAllPairs:
                 aux = self._dbuf("i8aux", nb.value // 4, torch.int32)[:nb.value // 4]
                 flag = self._dbuf("flag", 1, torch.int32)
                 flag.zero_()
+                self._flag_pin = self._hbuf("flagpin", 4)[:4].view(torch.int32)
+                self._flag_pin.zero_()
                 with torch.cuda.device(dev):
                     L.check(lib.b200m_l2_i8_aux_init(aux.data_ptr(), rows, D, cs.cuda_stream), "b200m_l2_i8_aux_init")
                 dd = DeviceDescriptors(L.KIND_L2_I8, d8, aux, rows, Dp)
@@ -326,7 +330,10 @@ class DistributedAllPairs:
                     eng.prepare_l2_i8_rows(dd, flag, stage[a0:a1], a0)
                 ph.add("prep", e1, ph.mark(cs))
 
-            for j0, j1, _ in groups:
+        def ingest_group(gi: int):
+            """Enqueue group gi on the copy stream; returns the event that fires when its rows and aux data are resident."""
+            j0, j1, _ = groups[gi]
+            with torch.cuda.stream(cs):
                 r0, r1 = int(offsets[j0]), int(offsets[j1])
                 if world == 1:
                     upload_rows(r0, r1)
@@ -360,19 +367,23 @@ class DistributedAllPairs:
                             L.check(lib.b200m_l2_i8_aux_rows(d8.data_ptr(), r0, r1 - r0, rows, Dp, aux.data_ptr(),
                                                              cs.cuda_stream), "b200m_l2_i8_aux_rows")
                 ph.add("derive", e0, ph.mark(cs))
-                if flag is not None and world > 1 and not events:
+                if flag is not None:                             # host mirror of "a non-integer element was seen" (read without a sync)
+                    self._flag_pin.copy_(flag, non_blocking=True)
+                if flag is not None and world > 1 and gi == 0:
                     dist.all_reduce(flag, op=dist.ReduceOp.MAX)   # every rank must take the same branch on "integer-valued?"
                 ev = torch.cuda.Event()
                 ev.record(cs)
-                events.append(ev)
-            if float_path:
+            return ev
+        if float_path:                                   # one group: ingest it now, then the store-wide re-encoding
+            ev0 = ingest_group(0)
+            with torch.cuda.stream(cs):
                 e0 = ph.mark(cs)
                 dd = eng.prepare(f32, NORM_L2, force_kind=L.KIND_L2_F16C if eng.float_path == "f16" else L.KIND_L2_F32)
                 ph.add("prep", e0, ph.mark(cs))
                 ev = torch.cuda.Event()
                 ev.record(cs)
-                events = [ev] * len(groups)
-        return Store(dd, offsets, norm_type), events, flag
+            return Store(dd, offsets, norm_type), None, [ev] * len(groups), flag
+        return Store(dd, offsets, norm_type), ingest_group, None, flag
 
     # ------------------------------------------------------------------ one chunk of pairs -> packed records (device)
     def _enqueue_chunk(self, store: Store, chunk: np.ndarray, mode: int, ratio: float, fmt: int, slot: int, stream):
@@ -450,6 +461,17 @@ class DistributedAllPairs:
         if fmt is None:
             small = max(counts, default=0) <= 65536
             fmt = (L.REC_Q16T16D16 if norm_type == NORM_HAMMING and D <= 8191 else L.REC_Q16T16D32) if small else L.REC_Q32T32D32
+        # Integer-valued (OpenCV SIFT) or genuinely float?  A sample of the host rows decides which encoding to TRY without
+        # waiting for the device: non-integer samples go straight to the float path; integer samples take the int8 path, whose
+        # kernels still flag any non-integer element anywhere in the store (checked at the end of the call -> float path).
+        # Only where every rank sees the rows (same data, same decision); with rank-0 upload the device flag is awaited instead.
+        sampled_integer = False
+        if norm_type == NORM_L2 and not assume_float and host is not None and rows > 0 and (world == 1 or sharded):
+            smp = host[torch.linspace(0, rows - 1, min(rows, 64)).long()].numpy()
+            if bool(np.all((smp == np.rint(smp)) & (smp >= 0) & (smp <= 255))):
+                sampled_integer = True
+            else:
+                assume_float = True
         float_path = norm_type == NORM_L2 and assume_float
         G = max(1, self.group_images)
         if world > 1 and sharded:
@@ -465,14 +487,14 @@ class DistributedAllPairs:
                 raise ValueError("done_mask must have one entry per pair of itertools.combinations(range(I), 2)")
             groups = [(j0, j1, gp[~done_mask[pair_index(gp[:, 0], gp[:, 1], I)]] if len(gp) else gp) for j0, j1, gp in groups]
         res = self._run(host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, mode, ratio, fmt,
-                        consumer, keep, timing)
+                        consumer, keep, timing, sampled_integer)
         if res == "not-integer":                              # the int8 encoding is not exact for these rows: fp16/tf32 candidates
             return self.match_host(host, counts, norm_type, cross_check, ratio_threshold, D, dtype, consumer, keep, timing,
                                    assume_float=True, done_mask=done_mask)
         return res
 
     def _run(self, host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, mode, ratio, fmt,
-             consumer, keep, timing):
+             consumer, keep, timing, sampled_integer=False):
         import torch.distributed as dist
         eng, dev = self.engine, self.engine.device
         S = self._get_streams()
@@ -485,18 +507,23 @@ class DistributedAllPairs:
         if world > 1 and getattr(self, "_board", None) is None:   # collective: every rank gets here on its first call
             self._cpu_group = dist.new_group(backend="gloo")
             self._board = _HostBoard(world, rank, self._cpu_group)
-        store, events, flag = self._ingest(host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, ph)
+        slices = [partition_pairs(gp, offsets, world) if world > 1 else [gp] for _, _, gp in groups]
+        store, ingest_group, events, flag = self._ingest(host, offsets, D, dtype, norm_type, groups, world, rank, sharded, float_path, ph)
         rb = REC_DTYPES[fmt].itemsize
         to_rank0 = world > 1 and self.gather == "rank0"
         owner = rank == 0 or not to_rank0                       # this rank ends up with (its share of) the records
-        slices = [partition_pairs(gp, offsets, world) if world > 1 else [gp] for _, _, gp in groups]
-        if flag is not None and len(events):                    # integer-valued?  known once the first group is encoded
+        if events is None:
+            # Group 0 now; the other groups' ingest is enqueued AFTER group 0's chunks have been launched, so the GPU is
+            # already matching while the host enqueues the rest.  Every ingest collective is still issued before any
+            # collective of the return path, on every rank: the order NCCL needs is the same everywhere.
+            events = [ingest_group(0)] + [None] * (len(groups) - 1)
+        if flag is not None and not sampled_integer:            # integer-valued?  known once the first group is encoded
             events[0].synchronize()
             if int(flag.item()) != 0:
                 return "not-integer"
 
         blocks = []          # owner: (pairs[K, 2], counts int32[K] (host, valid after ev), rec byte offset, rec bytes, ev)
-        state = {"hoff": 0, "coff": 0, "consumed": 0, "next_group": 0, "enqueued": -1}
+        state = {"hoff": 0, "coff": 0, "consumed": 0, "next_group": 0, "enqueued": -1, "bad": False}
         chunks_left = [(len(sl[rank]) + self.chunk_pairs - 1) // self.chunk_pairs for sl in slices]
         gK = [0] * len(groups)                                   # to_rank0: records this rank produced per group
         gP = [0] * len(groups)
@@ -517,10 +544,15 @@ class DistributedAllPairs:
                 return carena[coff:coff + 4 * Pt].numpy().view(np.int32)
             return cn
 
+        def local_bad() -> bool:
+            return flag is not None and int(self._flag_pin[0]) != 0
+
         def consume_upto(n_blocks: int):
             if consumer is None:
                 return
             while state["consumed"] < n_blocks:
+                if state["bad"] or local_bad():                  # a non-integer element turned up: this int8 run will be redone on the
+                    return                                       # float path (match_host); nothing more of it reaches the consumer
                 pr, cn, arena, off, nb, ev = blocks[state["consumed"]]
                 ev.synchronize()
                 consumer(pr, counts_of(cn), arena[off:off + nb].numpy().view(REC_DTYPES[fmt]))
@@ -579,7 +611,10 @@ class DistributedAllPairs:
                 gs.wait_event(ev)
             # record counts travel on the HOST (_HostBoard); it doubles as the rendezvous: the NCCL messages below are
             # posted by all ranks at about the same time
-            K_all = self._board.exchange(gK[gi])
+            K_all = self._board.exchange(gK[gi] | (int(local_bad()) << 56))      # bit 56: this rank saw a non-integer element
+            if K_all is not None:
+                state["bad"] |= any(v >> 56 for v in K_all)
+                K_all = [v & ((1 << 56) - 1) for v in K_all]
             with torch.cuda.stream(gs):
                 e0 = ph.mark(gs)
                 hdr, snd = self._dev.get(f"shdr{gi & 1}"), self._dev.get(f"srec{gi & 1}")
@@ -660,6 +695,9 @@ class DistributedAllPairs:
                     finish(*pending)
                 pending = (gi, slot, chunk, *job)
             state["enqueued"] = gi
+            if gi == 0 and ingest_group is not None:
+                for g in range(1, len(groups)):
+                    events[g] = ingest_group(g)
             advance()
         if pending is not None:
             finish(*pending)
@@ -678,6 +716,8 @@ class DistributedAllPairs:
             return "not-integer"
         if not owner:
             return None
+        if state["bad"]:
+            return "not-integer"
         consume_upto(len(blocks))
         pairs_out, cnts = [], []
         for pr, cn, *_ in blocks:

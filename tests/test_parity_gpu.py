@@ -724,6 +724,34 @@ def test_descriptor_cache_serves_only_live_unchanged_arrays():
     assert len(e0.cache.d) == 0
 
 
+def test_late_non_integer_element_reroutes_the_job_and_the_consumer_gets_the_right_answer(eng, tmp_path):
+    """Host rows that pass the integer sample of match_host (64 evenly spaced rows) but hold one non-integer element in a
+    late image: the int8 kernels flag it, nothing of the int8 run reaches the consumer after that, the job is redone on the
+    float path, and what the consumer ends up with is what cv2 gives for these rows."""
+    import itertools
+    D, ckm = pkg("distributed"), pkg("checkpoint")
+    sizes = [300, 200, 256, 180, 220, 150, 260, 190, 240, 210]
+    imgs = [synth.sift_pair(seed=460 + i, n=s)[0] for i, s in enumerate(sizes)]
+    imgs[4][:100] = imgs[0][:100]
+    imgs[9][77, 5] += 0.5                                          # row 2073 of 2206: not one of the sampled rows
+    rows = sum(sizes)
+    assert 2073 not in torch.linspace(0, rows - 1, 64).long().tolist()
+    host = torch.from_numpy(np.concatenate(imgs)).pin_memory()
+    ck = ckm.AllPairsCheckpoint(tmp_path, len(sizes))
+    calls = []
+    r = D.DistributedAllPairs(eng, chunk_pairs=4, group_images=3).match_host(
+        host, sizes, b.NORM_L2, False, 0.8, keep=False, consumer=lambda p, c, rec: (calls.append(len(p)), ck.consumer(p, c, rec)))
+    combos = list(itertools.combinations(range(len(sizes)), 2))
+    assert len(r.pairs) == len(combos)
+    pairs, ptr, rec = ck.load()
+    assert [tuple(p) for p in pairs] == combos
+    for p, (i, j) in enumerate(combos):
+        want = O.reference_match(imgs[i], imgs[j], O.NORM_L2, False, 0.8)
+        got = O.Matches(rec["q"][ptr[p]:ptr[p + 1]].astype(np.int32), rec["t"][ptr[p]:ptr[p + 1]].astype(np.int32),
+                        rec["d"][ptr[p]:ptr[p + 1]].astype(np.float32))
+        assert_close_float(got, want, f"rerouted pair {i},{j}", 0.05, descs=(imgs[i], imgs[j]), mode=(False, 0.8))
+
+
 # ------------------------------------------------------------------ SfM hand-off (feature cache -> all pairs -> correspondences)
 @pytest.mark.parametrize("name", ["orb_cross", "orb_ratio07", "sift_ratio075"])
 def test_sfm_handoff_equals_reference_converter(eng, name):

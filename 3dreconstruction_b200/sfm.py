@@ -175,11 +175,16 @@ class SfMMatches:
 
 def match_feature_set(engine: Engine, fs: FeatureSet, pairs: Optional[np.ndarray] = None, cross_check: bool = False,
                       ratio_threshold: Optional[float] = None, chunk_pairs: int = 2048,
-                      matcher: Optional[AllPairsMatcher] = None, ransac: Optional[Tuple[float, float, int]] = None):
+                      matcher: Optional[AllPairsMatcher] = None, ransac: Optional[Tuple[float, float, int]] = None,
+                      essential: Optional[Tuple[float, float, int]] = None):
     """Match `pairs` (default: all i < j, the reference's pair_mode='all', image_manager.py:491-494) and gather the
     matched keypoint coordinates on the device; one D2H of the finished arrays.
     ransac = (threshold, confidence, max_iters): also verify every pair by RANSAC homography (N3) on the correspondences
-    while they are still in HBM; returns (SfMMatches, verify.Verification) instead of SfMMatches alone."""
+    while they are still in HBM; returns (SfMMatches, verify.Verification) instead of SfMMatches alone.
+    essential = (threshold, prob, max_iters): also estimate every pair's essential matrix (pose.estimate_pairs_device, what
+    EssentialMatrixEstimator.estimate's RANSAC branch computes, essential_estimation.py:118-126) with each image's camera
+    taken from its size as the reference does when none is given (:36-60; every image of `fs` needs a size); the result is
+    appended to the return value as a pose.PoseEstimates."""
     if pairs is None:
         pairs = all_pairs(len(fs.names))
     pairs = np.ascontiguousarray(pairs, np.int32).reshape(-1, 2)
@@ -201,14 +206,27 @@ def match_feature_set(engine: Engine, fs: FeatureSet, pairs: Optional[np.ndarray
     if ransac is not None:
         from . import verify
         ver = verify.verify_pairs_device(engine, corr[:K], csr.ptr, *ransac)
+    est = None
+    if essential is not None:
+        from . import pose
+        if any(sz is None for sz in fs.sizes):
+            raise ValueError("essential=...: every image needs its (width, height) to estimate a camera matrix")
+        cam4 = np.array([[1.2 * sz[0], 1.2 * sz[0], sz[0] / 2.0, sz[1] / 2.0] for sz in fs.sizes], np.float64)   # fx, fy, cx, cy
+        cams = np.concatenate([cam4[pairs[:, 0]], cam4[pairs[:, 1]]], axis=1) if len(pairs) else np.zeros((0, 8))
+        est = pose.estimate_pairs_device(engine, corr[:K], csr.ptr, torch.from_numpy(np.ascontiguousarray(cams)).to(dev), *essential)
     h = csr.to_host()
     res = SfMMatches(fs.names, fs.sizes, pairs, h.ptr, h.query_idx, h.train_idx, h.distance, corr[:K].cpu().numpy(),
                      method="BF", feature_type=fs.method)
-    if ver is None:
-        return res
-    from . import verify
-    return res, verify.Verification(h.ptr, ver.H.cpu().numpy().reshape(-1, 3, 3), ver.mask.cpu().numpy(),
-                                    ver.inliers.cpu().numpy(), ver.iters.cpu().numpy())
+    out = [res]
+    if ver is not None:
+        from . import verify
+        out.append(verify.Verification(h.ptr, ver.H.cpu().numpy().reshape(-1, 3, 3), ver.mask.cpu().numpy(),
+                                       ver.inliers.cpu().numpy(), ver.iters.cpu().numpy()))
+    if est is not None:
+        from . import pose
+        out.append(pose.PoseEstimates(h.ptr, est.E.cpu().numpy().reshape(-1, 3, 3), est.mask.cpu().numpy(),
+                                      est.inliers.cpu().numpy(), est.iters.cpu().numpy()))
+    return out[0] if len(out) == 1 else tuple(out)
 
 
 def match_all_pairs(features: Mapping[str, object], norm_type: int, cross_check: bool = False,

@@ -138,3 +138,28 @@ def test_against_live_cv2(eng):
         else:
             bad += not (np.array_equal(r.mask, mc.ravel()) and _same_E(r.E[0], Ec[:3], 1e-6))
     assert bad == 0
+
+
+def test_pipeline_match_gather_essential_on_the_device(eng):
+    """N1 -> N2 -> N3 without leaving the GPU: sfm.match_feature_set(..., essential=...) on a small image set; every pair's E
+    and mask equal cv2's route on the host (the oracle on the gathered correspondences with the camera from the image size)."""
+    sfm = pkg("sfm")
+    rng = np.random.default_rng(3)
+    n, size = 400, (1600, 1200)
+    corr, K = synth.two_view_pair(seed=77, n=n, inlier_frac=0.8, noise=0.5, size=size)
+    base = synth.binary_pair(seed=78, n=n, nbytes=32)[0]
+    F = b.contracts.FeatureData
+    feats = {}
+    for name, xy in (("a", corr[:, :2]), ("b", corr[:, 2:]), ("c", corr[rng.permutation(n), :2])):
+        feats[name] = F(keypoints=xy.copy(), descriptors=base.copy(), method="ORB")     # identical descriptors: match i <-> i
+    fs = sfm.build_feature_set(eng, feats, b.NORM_HAMMING, {k: size for k in feats})
+    res, est = sfm.match_feature_set(eng, fs, None, True, None, essential=(1.0 / 1920, 0.999, 1000))
+    assert len(res) == 3 and len(est.inliers) == 3
+    for p in range(3):
+        c = res.correspondences[res.pair_slice(p)]
+        Eo, mo, ito = _oracle(c, EO.camera_matrix_from_size(size), 1.0 / 1920, 0.999, 1000)
+        if Eo is None:
+            assert est.inliers[p] < 0
+        else:
+            assert np.array_equal(est.inlier_mask(p), mo) and _same_E(est.E[p], Eo) and int(est.iters[p]) == ito
+    assert est.inliers[0] > 250                                   # images a and b are the two views of one scene

@@ -357,12 +357,99 @@ static void run_sustained(int sms, double seconds) {
     cudaFree(dcyc);
 }
 
+// ---------------------------------------------------------------- cta_group::2: one MMA spans a CTA pair
+// Cluster of 2 CTAs; the leader's thread 32 issues M=256 (128 rows of A per CTA) x N (N/2 rows of B per CTA) MMAs.
+// Answers: does one M256 N256 K32 kind::i8 instruction take the 128 cycles of the M128 N256 one (2x per-SM-pair rate)
+// or 256 (no gain over two cta_group::1 streams)?
+#define MMA_KIND2(NAME, KINDSTR)                                                                         \
+    __device__ __forceinline__ void NAME(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { \
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"                                   \
+                     "tcgen05.mma.cta_group::2.kind::" KINDSTR " [%0], %1, %2, %3, p;\n\t}" ::"r"(d),    \
+                     "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");                                   \
+    }
+MMA_KIND2(mma2_k_i8, "i8")
+MMA_KIND2(mma2_k_f16, "f16")
+
+template <int KIND>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+pair_kernel(int iters, uint32_t idesc, int ncols, long long* cycles) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tptr;
+    const int warp = threadIdx.x >> 5;
+    const uint32_t rank = sm100::cluster_ctarank();
+    for (int i = threadIdx.x; i < (48 * 1024) / 4; i += blockDim.x) ((uint32_t*)smem)[i] = 0x01010101u;
+    if (threadIdx.x == 0) { sm100::mbar_init(&bar, 1); sm100::fence_barrier_init(); }
+    sm100::cluster_sync_all();
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sm100::smem_u32(&tptr)),
+                     "n"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    sm100::fence_proxy_async();
+    sm100::tc_fence_before(); sm100::cluster_sync_all(); sm100::tc_fence_after();
+    uint32_t tbase = tptr;
+    if (rank == 0 && threadIdx.x == 32) {
+        uint64_t ad = sm100::make_smem_desc_sw128(sm100::smem_u32(smem));
+        uint64_t bd = sm100::make_smem_desc_sw128(sm100::smem_u32(smem + 16384));
+        long long t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+            uint32_t d = tbase + ((it & 1) ? ncols : 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (KIND == 0) mma2_k_i8(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+                else mma2_k_f16(d, ad + 2 * k, bd + 2 * k, idesc, 1);
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     ::"r"(sm100::smem_u32(&bar)), "h"((uint16_t)3) : "memory");
+        sm100::mbar_wait(&bar, 0);
+        long long t1 = clock64();
+        if (blockIdx.x == 0) *cycles = t1 - t0;
+    } else if (threadIdx.x == 32) {
+        sm100::mbar_wait(&bar, 0);
+    }
+    sm100::tc_fence_before(); sm100::cluster_sync_all();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tbase), "n"(512) : "memory");
+}
+
+template <int KIND>
+static void run_pair(const char* name, int N, int k_elems_per_mma, int sms, uint32_t cfmt, uint32_t abfmt) {
+    const int iters = 20000;
+    long long* dcyc; cudaMalloc(&dcyc, 8); cudaMemset(dcyc, 0, 8);
+    cudaFuncSetAttribute(pair_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const uint32_t idesc = sm100::make_idesc(cfmt, abfmt, abfmt, 256, N);
+    const int grid = sms & ~1;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    pair_kernel<KIND><<<grid, 128, 64 * 1024>>>(200, idesc, N > 256 ? 256 : N, dcyc);
+    cudaEventRecord(e0);
+    pair_kernel<KIND><<<grid, 128, 64 * 1024>>>(iters, idesc, N > 256 ? 256 : N, dcyc);
+    cudaEventRecord(e1);
+    cudaError_t err = cudaDeviceSynchronize();
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    long long cyc = 0; cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+    double macs = (double)(grid / 2) * iters * 4.0 * 256 * N * k_elems_per_mma;
+    printf("pair %-5s %s: %.3f ms, %.1f TOP/s, %.1f cycles per MMA (cta_group::2 M256 N%d K=%d), %.0f MAC/clk/SM\n", name,
+           cudaGetErrorString(err), ms, 2 * macs / (ms * 1e-3) / 1e12, (double)cyc / (iters * 4.0), N, k_elems_per_mma,
+           256.0 * N * k_elems_per_mma / ((double)cyc / (iters * 4.0)) / 2);
+    cudaFree(dcyc);
+}
+
 int main(int argc, char** argv) {
     int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     printf("SMs: %d\n", sms);
     if (argc > 1 && !strcmp(argv[1], "mxf4")) {
         run_mxf4(256, sms, 0); run_mxf4(240, sms, 0); run_mxf4(128, sms, 0);
         run_mxf4(240, sms, argc > 2 ? atof(argv[2]) : 3.0);
+        return 0;
+    }
+    if (argc > 1 && !strcmp(argv[1], "pair")) {
+        run<0>("i8", sm100::make_idesc(2, 1, 1, 128, 256), 32, sms);
+        run_pair<0>("i8", 256, 32, sms, 2, 1); run_pair<0>("i8", 128, 32, sms, 2, 1); run_pair<0>("i8", 64, 32, sms, 2, 1);
+        run<1>("f16", sm100::make_idesc(1, 0, 0, 128, 256), 16, sms);
+        run_pair<1>("f16", 256, 16, sms, 1, 0); run_pair<1>("f16", 128, 16, sms, 1, 0);
         return 0;
     }
     if (argc > 1 && !strcmp(argv[1], "sustained")) { run_sustained(sms, argc > 2 ? atof(argv[2]) : 4.0); return 0; }

@@ -354,7 +354,6 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 if (lane == 0) sm100::mbar_arrive(&sm.cb_empty[slot]);       // constants consumed
                 insert(min(m0, m1), base + CHUNK);
             }
-            tc_base += (uint32_t)it.ntiles;
             // publish this warp's partial top-2 (Top2 slice = split * NSLICE + slice); finalize merges the slices
             const int row = it.r0 + quarter * 32 + lane;
             if (row < it.n) {
@@ -395,29 +394,35 @@ struct SmemFold {
     uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
     uint32_t* tmem_ptr;
 };
-__device__ __forceinline__ SmemFold carve_fold(uint8_t* base, int nkb) {
+// pair == true (cta_group::2): a CTA holds only ITS half of every train tile (128 rows), so a ring stage is half as
+// large and the ring twice as deep.
+__host__ __device__ constexpr int nbf_of(bool pair) { return pair ? 2 * NBF : NBF; }
+__device__ __forceinline__ SmemFold carve_fold(uint8_t* base, int nkb, bool pair = false) {
+    const int nbf = nbf_of(pair), bstage = pair ? B_KB_BYTES / 2 : B_KB_BYTES, xstage = pair ? X_BYTES / 2 : X_BYTES;
     SmemFold s;
     s.a = base;
     s.b = s.a + NABUF * nkb * A_KB_BYTES;
-    s.x = s.b + NBF * B_KB_BYTES;
-    s.ax = s.x + (NBF / nkb) * X_BYTES;
+    s.x = s.b + nbf * bstage;
+    s.ax = s.x + (nbf / nkb) * xstage;
     s.xch = (int4*)(s.ax + AX_BYTES);
     uint8_t* p = (uint8_t*)(s.xch + 2 * (EPI_WARPS - 4) * 32);
     s.a_full = (uint64_t*)p; p += NABUF * 8;
     s.a_empty = (uint64_t*)p; p += NABUF * 8;
-    s.b_full = (uint64_t*)p; p += NBF * 8;
-    s.b_empty = (uint64_t*)p; p += NBF * 8;
+    s.b_full = (uint64_t*)p; p += nbf * 8;
+    s.b_empty = (uint64_t*)p; p += nbf * 8;
     s.acc_full = (uint64_t*)p; p += 2 * 8;
     s.acc_empty = (uint64_t*)p; p += 2 * 8;
     s.tmem_ptr = (uint32_t*)p;
     return s;
 }
-__host__ __device__ constexpr size_t smem_bytes_fold(int nkb) {
-    return 1024 + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)NBF * B_KB_BYTES + (size_t)(NBF / nkb) * X_BYTES + AX_BYTES +
-           2 * (EPI_WARPS - 4) * 32 * sizeof(int4) + (2 * NABUF + 2 * NBF + 4) * 8 + 16;
+__host__ __device__ constexpr size_t smem_bytes_fold(int nkb, bool pair = false) {
+    return 1024 + (size_t)NABUF * nkb * A_KB_BYTES + (size_t)nbf_of(pair) * (pair ? B_KB_BYTES / 2 : B_KB_BYTES) +
+           (size_t)(nbf_of(pair) / nkb) * (pair ? X_BYTES / 2 : X_BYTES) + AX_BYTES +
+           2 * (EPI_WARPS - 4) * 32 * sizeof(int4) + (2 * NABUF + 2 * nbf_of(pair) + 4) * 8 + 16;
 }
 
-static_assert(smem_bytes_fold(1) <= 232448 && smem_bytes_fold(2) <= 232448, "fold kernel shared memory");
+static_assert(smem_bytes_fold(1) <= 232448 && smem_bytes_fold(2) <= 232448 && smem_bytes_fold(1, true) <= 232448 &&
+              smem_bytes_fold(2, true) <= 232448, "fold kernel shared memory");
 
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
 // maximum of 16 consecutive accumulator columns v[O .. O+15] = one fold chunk: 8 three-input max instructions
@@ -428,9 +433,16 @@ __device__ __forceinline__ int max16(const uint32_t (&v)[32]) {
     int a4 = max3((int)v[O + 12], (int)v[O + 13], (int)v[O + 14]);
     return max(max3(a0, a1, a2), max3(a3, a4, (int)v[O + 15]));
 }
+template <int FILL>
 __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // columns >= lim do not exist
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : 0x80000000u;
+    for (int i = 0; i < 32; ++i) v[i] = i < lim ? v[i] : (uint32_t)FILL;
+}
+// E * kmul + low on the FMA pipe (IMAD); kmul arrives as a kernel argument so that ptxas cannot turn it into an ALU-pipe LEA
+__device__ __forceinline__ int pack_key(int e, int kmul, int low) {
+    int r;
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(e), "r"(kmul), "r"(low));
+    return r;
 }
 
 // CS = CTAs per cluster (1 or 2).  With CS == 2 the two CTAs of a cluster work on two adjacent query row tiles of
@@ -439,16 +451,33 @@ __device__ __forceinline__ void mask32(uint32_t (&v)[32], int lim) {     // colu
 // halves.  A ring stage may be refilled only when BOTH CTAs' MMAs have consumed it: the stage's empty barrier counts
 // CS arrivals and every MMA issuer commits to the barrier of both CTAs (tcgen05.commit ... multicast::cluster).
 // Work items are (pair, split, tile pair) over clusters; the MMAs themselves stay single-CTA (cta_group::1).
-template <int NKB, int CS>
+//
+// PAIR (needs CS == 2) turns the cluster into a tcgen05 CTA pair: ONE cta_group::2 MMA of M = 256 covers both CTAs' query
+// row tiles, and each CTA supplies only its own 128 rows of the 256-row train tile -- nothing is multicast, a CTA's shared
+// memory sees half the TMA writes (20 instead of 40 KiB per tile) and two thirds of the operand reads (40 instead of
+// 60 KiB).  That traffic, 100 KiB per 640-cycle tile against 128 B/clk, was what held the multicast version at ~790
+// cycles per tile (sm__mem_tensor_cycles_active 82 %, profiles/r01_l2i8_v9_fold_cluster_ncu_full.md); the issue rate of
+// the pair instruction is the same 128 cycles (profiles/r02_mma_pair_issue_rate.txt).  The even CTA (leader) issues
+// every MMA; both CTAs' TMA loads report to the leader's "full" barriers, the leader's commits are multicast to both
+// CTAs' "empty" barriers, and both CTAs' epilogue warps hand TMEM stages back on the leader's acc_empty barriers.
+template <int NKB, int CS, bool PAIR = false>
 __global__ void __launch_bounds__(FOLD_THREADS, 1)
 l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const __grid_constant__ CUtensorMap tmap_x, const int32_t* __restrict__ fold_flag,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S,
-                  Top2* __restrict__ out, long long total_rows) {
+                  Top2* __restrict__ out, long long total_rows, int kmul) {
+    // packed running top-2 of the epilogue: index field wide enough for one window of train tiles, value field for |E|
+    // (|a'.b'| <= 2^21 per 128-byte K block, |h - bias| < 2^19: |E| < 2^22 for D = 128, < 2^23 for D = 256)
+    constexpr int IDX_BITS = NKB == 1 ? 9 : 8, IDX_MASK = (1 << IDX_BITS) - 1, EMIN = -(1 << (31 - IDX_BITS));
+    constexpr int WIN_SHIFT = IDX_BITS - 4, WIN_TILES = 1 << WIN_SHIFT;     // (2^IDX_BITS chunks) * 16 columns / TN
+    static_assert(TN / B200M_FOLD_CHUNK == 16, "window arithmetic assumes 16 chunks per tile");
     if (__ldg(fold_flag) == 0) return;             // digits do not cover this store (the call's snapshot): the keyed kernel runs instead
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const SmemFold sm = carve_fold(smem, NKB);
+    static_assert(!PAIR || CS == 2, "a CTA pair is a cluster of two");
+    const SmemFold sm = carve_fold(smem, NKB, PAIR);
+    constexpr int NBFK = nbf_of(PAIR);                                  // train K-block ring depth
+    constexpr int B_STAGE = PAIR ? B_KB_BYTES / 2 : B_KB_BYTES, X_STAGE = PAIR ? X_BYTES / 2 : X_BYTES;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int W_MMA = 0, W_PROD = 1, W_CONST = 2;
     constexpr int backward = 0;
@@ -470,8 +499,10 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         sm100::tma_prefetch_desc(&tmap_t);
         sm100::tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
-        for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], CS); }
-        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
+        // PAIR: one multicast commit of the leader frees a stage in both CTAs; a TMEM stage is free again once the 16
+        // epilogue warps of BOTH CTAs have drained it
+        for (int i = 0; i < NBFK; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], PAIR ? 1 : CS); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], (PAIR ? 2 : 1) * EPI_WARPS); }
         sm100::fence_barrier_init();
     }
     if (warp == W_CONST) {
@@ -481,7 +512,12 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         for (int w = lane; w < AX_BYTES / 4; w += 32) sm100::sts32(ax + 4 * w, (w & 3) == 3 ? (int)0xFF808080 : (int)0x80808080);
         sm100::fence_proxy_async();                // generic-proxy stores -> visible to tcgen05.mma (async proxy)
     }
-    if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    if constexpr (PAIR) {
+        sm100::cluster_sync_all();                         // both CTAs of the pair are running before the paired allocation
+        if (warp == W_MMA) sm100::tmem_alloc_2sm<512>(sm.tmem_ptr);
+    } else {
+        if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    }
     sm100::tc_fence_before();
     __syncthreads();
     if constexpr (CS > 1) sm100::cluster_sync_all();      // the peer's barriers exist before anything is multicast to them
@@ -496,11 +532,20 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_empty[ab], a_par);
             if (sm100::elect_one()) {
-                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+                if constexpr (PAIR) {                  // both CTAs' query tiles are counted on the leader's barrier
+                    if (crank == 0) sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(2 * NKB * A_KB_BYTES));
+                    const uint32_t lbar = sm100::mapa_u32(sm100::smem_u32(&sm.a_full[ab]), 0);
 #pragma unroll
-                for (int kb = 0; kb < NKB; ++kb)
-                    sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
-                                       kb * KB_BYTES, it.q_off + it.r0);
+                    for (int kb = 0; kb < NKB; ++kb)
+                        sm100::tma_load_2d_2sm(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, lbar,
+                                               kb * KB_BYTES, it.q_off + it.r0);
+                } else {
+                    sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+#pragma unroll
+                    for (int kb = 0; kb < NKB; ++kb)
+                        sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                           kb * KB_BYTES, it.q_off + it.r0);
+                }
             }
             __syncwarp();
             if (++ab == NABUF) { ab = 0; a_par ^= 1; }
@@ -511,24 +556,31 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     sm100::mbar_wait(&sm.b_empty[bs], b_par);          // CS arrivals: every CTA of the cluster is done with it
                     if (sm100::elect_one()) {
                         const bool last = kb == NKB - 1;       // the fold digits travel with the tile's last K block
-                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (last ? X_BYTES : 0)));
-                        uint8_t* bdst = sm.b + (size_t)bs * B_KB_BYTES + (size_t)crank * (B_KB_BYTES / CS);
-                        uint8_t* xdst = sm.x + (size_t)(bs / NKB) * X_BYTES + (size_t)crank * (X_BYTES / CS);
-                        if constexpr (CS > 1) {
+                        uint8_t* bdst = sm.b + (size_t)bs * B_STAGE + (PAIR ? 0 : (size_t)crank * (B_KB_BYTES / CS));
+                        uint8_t* xdst = sm.x + (size_t)(bs / NKB) * X_STAGE + (PAIR ? 0 : (size_t)crank * (X_BYTES / CS));
+                        if constexpr (PAIR) {          // this CTA's 128 train rows stay here; both halves count on the leader's barrier
+                            if (crank == 0)
+                                sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(2 * (B_STAGE + (last ? X_STAGE : 0))));
+                            const uint32_t lbar = sm100::mapa_u32(sm100::smem_u32(&sm.b_full[bs]), 0);
+                            sm100::tma_load_2d_2sm(bdst, &tmap_t, lbar, kb * KB_BYTES, row0 + j * TN);
+                            if (last) sm100::tma_load_2d_2sm(xdst, &tmap_x, lbar, 0, row0 + j * TN);
+                        } else if constexpr (CS > 1) {
+                            sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (last ? X_BYTES : 0)));
                             sm100::tma_load_2d_mc(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN, MC_MASK);
                             if (last) sm100::tma_load_2d_mc(xdst, &tmap_x, &sm.b_full[bs], 0, row0 + j * TN, MC_MASK);
                         } else {
+                            sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (last ? X_BYTES : 0)));
                             sm100::tma_load_2d(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN);
                             if (last) sm100::tma_load_2d(xdst, &tmap_x, &sm.b_full[bs], 0, row0 + j * TN);
                         }
                     }
                     __syncwarp();
-                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                    if (++bs == NBFK) { bs = 0; b_par ^= 1; }
                 }
             }
         }
-    } else if (warp == W_MMA) {
-        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, TN);
+    } else if (warp == W_MMA && (!PAIR || crank == 0)) {
+        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, PAIR ? 2 * TM : TM, TN);
         const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
         const uint32_t x_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.x));      // same low-word format
@@ -550,37 +602,56 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     sm100::mbar_wait(&sm.b_full[bs], b_par);
                     sm100::tc_fence_after();
                     if (sm100::elect_one()) {
-                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
+                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_STAGE >> 4);
+                        const uint64_t x_desc = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + (bs / NKB) * (X_STAGE >> 4));
 #pragma unroll
-                        for (int k = 0; k < KB_BYTES / 32; ++k)
-                            sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                          idesc, (kb | k) ? 1u : 0u);
-                        if (kb == NKB - 1)                      // + c . t = -(h - bias)
-                            sm100::mma_i8(d_tmem, ax_desc,
-                                          sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + (bs / NKB) * (X_BYTES >> 4)),
-                                          idesc, 1u);
+                        for (int k = 0; k < KB_BYTES / 32; ++k) {
+                            if constexpr (PAIR)
+                                sm100::mma_i8_2sm(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                                  idesc, (kb | k) ? 1u : 0u);
+                            else
+                                sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                              idesc, (kb | k) ? 1u : 0u);
+                        }
+                        if (kb == NKB - 1) {                    // + c . t = -(h - bias)
+                            if constexpr (PAIR) sm100::mma_i8_2sm(d_tmem, ax_desc, x_desc, idesc, 1u);
+                            else sm100::mma_i8(d_tmem, ax_desc, x_desc, idesc, 1u);
+                        }
                         // ONE commit per K block: it frees the ring stage (in both CTAs of a cluster) and, for the tile's last
                         // K block, is also what the epilogue waits on -- every tcgen05.commit drains the MMA pipe for ~40 cycles
                         // (tools/mma_peak), so a separate "accumulator full" commit per tile would cost ~5 % of the tensor time.
-                        if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
+                        if constexpr (PAIR) sm100::mma_commit_2sm_mc(&sm.b_empty[bs], MC_MASK);
+                        else if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
                         else sm100::mma_commit(&sm.b_empty[bs]);
                     }
                     __syncwarp();
-                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                    if (++bs == NBFK) { bs = 0; b_par ^= 1; }
                 }
                 as ^= 1;
             }
-            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            if (sm100::elect_one()) {
+                if constexpr (PAIR) sm100::mma_commit_2sm_mc(&sm.a_empty[ab], MC_MASK);   // both CTAs' query tiles are free
+                else sm100::mma_commit(&sm.a_empty[ab]);
+            }
             __syncwarp();
             if (++ab == NABUF) { ab = 0; a_par ^= 1; }
         }
     } else if (warp >= CTRL_WARPS) {
-        // epilogue: two groups of 8 warps on alternate tiles (group g owns TMEM stage g); inside a group a warp drains
-        // 128 columns (half) of its 32 TMEM lanes: 32-column tcgen05.ld, two in flight while it reduces the previous two.
+        // epilogue: ALL 16 warps drain EVERY tile -- warp (quarter, cb) reads its 32 TMEM lanes x 64 columns with two
+        // 32-column tcgen05.ld issued back to back, so no load waits for arithmetic and a TMEM stage is held only for the
+        // time its 128 KiB take to cross the 64 B/clk/SMSP read port (~512 cycles) plus the wake-up.  (Two groups of 8
+        // warps on alternate tiles, each warp re-using its registers for four loads per tile, held a stage ~960 cycles:
+        // with two stages the MMA of tile t+2 then starts 640 + 960 after the MMA of tile t -- 800 cycles per tile.)
         const int e = warp - CTRL_WARPS;
-        const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * TN + half * (TN / 2);
-        uint32_t k = 0, tc_base = 0, nitem = 0;
+        const int cb = e >> 2, quarter = warp & 3;                 // cb: 64-column block of the tile
+        constexpr int CBW = TN / 4, CB_CHUNKS = CBW / B200M_FOLD_CHUNK;
+        uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + cb * CBW;     // this tile's stage: toggles by TN columns
+        uint32_t acc_bar = PAIR ? sm100::mapa_u32(sm100::smem_u32(&sm.acc_empty[0]), 0) : sm100::smem_u32(&sm.acc_empty[0]);
+        uint32_t ready_bar = sm100::smem_u32(&sm.b_empty[0]);
+        uint32_t as8 = 0, rs = (NKB - 1) * 8, rp = 0, nitem = 0;   // acc_empty[as8 / 8]; "ready" = b_empty[rs / 8], parity rp
+        int lowc0 = IDX_MASK - cb * CB_CHUNKS, lowc1 = lowc0 - 1, lowc2 = lowc0 - 2, lowc3 = lowc0 - 3, m16 = -(TN / B200M_FOLD_CHUNK);
+        asm volatile("" : "+r"(taddr), "+r"(acc_bar), "+r"(ready_bar));
+        asm volatile("" : "+r"(lowc0), "+r"(lowc1), "+r"(lowc2), "+r"(lowc3), "+r"(m16));
         for (long long item = first_item; item < total_items; item += item_stride) {
             Item it = decode(item);
             if (!it.valid) continue;
@@ -592,40 +663,66 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 v1 = gt1 ? pm : v1;
                 i1 = gt1 ? base : i1;
             };
-            for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
-                const int base = it.c_begin + j * TN + half * (TN / 2);
-                const int lim = it.c_end - base;              // existing columns in this warp's 128 (tail tile: < 128)
-                {   // accumulator ready == the ring stage of this tile's last K block has been released (see the MMA warp)
-                    const uint32_t tc = 2 * k + g;                    // this CTA's tile counter
-                    const uint32_t use = (tc * NKB + NKB - 1) / NBF, stage = (tc * NKB + NKB - 1) % NBF;
-                    B200M_EPI_WAIT(&sm.b_empty[stage], use & 1);
+            // Inside a window of WIN_TILES train tiles the running top-2 lives in ONE word per entry:
+            //   key = E * 2^IDX_BITS + (2^IDX_BITS - 1 - chunk index in the window),   |E| < 2^(31 - IDX_BITS),
+            // so an update is min/max only (2.5 ALU-pipe instructions per chunk instead of 7; the packing is one IMAD on
+            // the otherwise idle FMA pipe).  At a window's end the two keys are unpacked into (value, column) and merged
+            // as before, so any m works.
+            int k1 = (int)0x80000000, k2 = (int)0x80000000;
+            int win = 0;
+            auto flush = [&]() {
+                auto put = [&](int key) {
+                    const int ev = key >> IDX_BITS;
+                    if (ev != EMIN) insert(ev, it.c_begin + win * (WIN_TILES * TN) + (IDX_MASK - (key & IDX_MASK)) * B200M_FOLD_CHUNK);
+                };
+                put(k1); put(k2);                              // k1 first: on equal values the earlier chunk stays ahead
+                k1 = k2 = (int)0x80000000;
+            };
+            auto push2 = [&](int ka, int kb) {               // top-2 of {k1, k2, ka, kb}: 5 min/max
+                const int mx = max(ka, kb), mn = min(ka, kb);
+                const int t = min(k1, mx);
+                k1 = max(k1, mx);
+                k2 = max3(t, k2, mn);
+            };
+            // Per tile the loop carries only: the TMEM address (toggling between the two stages), the "ready" barrier's
+            // address and parity, the columns left for this warp, and the tile's position in the window.  Everything
+            // thread-constant was made opaque above so that ptxas keeps it in a register instead of re-deriving it from
+            // %tid every tile (the ALU pipe is the epilogue's budget: 2 cycles per instruction per sub-partition).
+            int rem = it.c_end - it.c_begin - cb * CBW;          // existing columns from this warp's first one on
+            for (int j0 = 0; j0 < it.ntiles; j0 += WIN_TILES, ++win) {
+                const int jn = min(it.ntiles - j0, WIN_TILES);
+                for (int jw = 0; jw < jn; ++jw) {
+                    // accumulator ready == the ring stage of this tile's last K block has been released (see the MMA warp)
+                    sm100::mbar_wait_addr(ready_bar + rs, rp);
+                    rs += NKB * 8;
+                    if (rs >= (uint32_t)(NBFK * 8)) { rs -= NBFK * 8; rp ^= 1; }
+                    sm100::tc_fence_after();
+                    uint32_t acc[2][32];
+                    sm100::tmem_ld32(taddr, acc[0]);
+                    sm100::tmem_ld32(taddr + 32, acc[1]);
+                    sm100::tmem_ld_wait();                    // everything is in registers: hand the TMEM stage back first
+                    sm100::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if constexpr (PAIR) sm100::mbar_arrive_cluster(acc_bar + as8);
+                        else sm100::mbar_arrive_addr(acc_bar + as8);
+                    }
+                    taddr ^= TN; as8 ^= 8;
+                    if (rem < CBW) { mask32<EMIN>(acc[0], rem); mask32<EMIN>(acc[1], rem - 32); }     // tail tile
+                    rem -= TN;
+                    const int m0 = max16<0>(acc[0]), m1 = max16<16>(acc[0]);
+                    const int m2 = max16<0>(acc[1]), m3 = max16<16>(acc[1]);
+                    // chunk index inside the window, counted down from the top of the index field: (low_c) - 16 jw, on the FMA pipe
+                    push2(pack_key(m0, kmul, pack_key(jw, m16, lowc0)), pack_key(m1, kmul, pack_key(jw, m16, lowc1)));
+                    push2(pack_key(m2, kmul, pack_key(jw, m16, lowc2)), pack_key(m3, kmul, pack_key(jw, m16, lowc3)));
                 }
-                sm100::tc_fence_after();
-                uint32_t acc[2][32];
-                sm100::tmem_ld32(taddr, acc[0]);
-                sm100::tmem_ld32(taddr + 32, acc[1]);
-                sm100::tmem_ld_wait();
-                if (lim < TN / 2) { mask32(acc[0], lim); mask32(acc[1], lim - 32); }
-                int m0 = max16<0>(acc[0]), m1 = max16<16>(acc[0]);
-                sm100::tmem_ld32(taddr + 64, acc[0]);
-                int m2 = max16<0>(acc[1]), m3 = max16<16>(acc[1]);
-                sm100::tmem_ld32(taddr + 96, acc[1]);
-                insert(m0, base); insert(m1, base + 16); insert(m2, base + 32); insert(m3, base + 48);
-                sm100::tmem_ld_wait();                        // everything is in registers: hand the TMEM stage back first
-                sm100::tc_fence_before();
-                __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
-                if (lim < TN / 2) { mask32(acc[0], lim - 64); mask32(acc[1], lim - 96); }
-                m0 = max16<0>(acc[0]); m1 = max16<16>(acc[0]);
-                m2 = max16<0>(acc[1]); m3 = max16<16>(acc[1]);
-                insert(m0, base + 64); insert(m1, base + 80); insert(m2, base + 96); insert(m3, base + 112);
+                flush();
             }
-            tc_base += (uint32_t)it.ntiles;
-            // The four warps of a TMEM lane quarter hold partial top-2s of the same 32 query rows (2 groups x 2 column
-            // halves): merge them through shared memory so that ONE Top2 per row and split leaves the SM.
+            // The four warps of a TMEM lane quarter hold partial top-2s of the same 32 query rows (4 column blocks):
+            // merge them through shared memory so that ONE Top2 per row and split leaves the SM.
             int4* xbuf = sm.xch + (size_t)(nitem & 1) * (EPI_WARPS - 4) * 32;
             ++nitem;
-            const bool merger = e < 4;                      // g == 0, half == 0
+            const bool merger = e < 4;                      // cb == 0
             if (!merger) xbuf[(e - 4) * 32 + lane] = make_int4(v1, i1, v2, i2);
             asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");     // epilogue warps only
             if (merger) {
@@ -651,7 +748,10 @@ l2_i8_fold_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     sm100::tc_fence_before();
     __syncthreads();
     if constexpr (CS > 1) sm100::cluster_sync_all();      // the peer may still commit to this CTA's barriers until it is done too
-    if (warp == W_MMA) sm100::tmem_dealloc<512>(tmem_base);
+    if (warp == W_MMA) {
+        if constexpr (PAIR) sm100::tmem_dealloc_2sm<512>(tmem_base);
+        else sm100::tmem_dealloc<512>(tmem_base);
+    }
 }
 
 }  // namespace
@@ -726,15 +826,19 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
                                               (int)smem_bytes_fold(1)), "l2_i8 fold smem attr");
         B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem_bytes_fold(2)), "l2_i8 fold smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<1, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes_fold(1, true)), "l2_i8 fold smem attr");
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_i8_fold_kernel<2, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes_fold(2, true)), "l2_i8 fold smem attr");
         // How many 2-CTA clusters of the fold kernel can be resident at once?  Use them only if they cover every SM.
         cudaLaunchConfig_t qc = {};
         cudaLaunchAttribute qa[1];
         qa[0].id = cudaLaunchAttributeClusterDimension;
         qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
-        qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(FOLD_THREADS); qc.dynamicSmemBytes = smem_bytes_fold(1);
+        qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(FOLD_THREADS); qc.dynamicSmemBytes = smem_bytes_fold(1, true);
         qc.attrs = qa; qc.numAttrs = 1;
         int nc = 0;
-        if (cudaOccupancyMaxActiveClusters(&nc, l2_i8_fold_kernel<1, 2>, &qc) == cudaSuccess && nc * 2 >= sms &&
+        if (cudaOccupancyMaxActiveClusters(&nc, l2_i8_fold_kernel<1, 2, true>, &qc) == cudaSuccess && nc * 2 >= sms &&
             !getenv("B200M_NO_CLUSTER")) {
             fold_cs = 2;
             fold_clusters = nc;
@@ -743,6 +847,7 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
         }
         if (getenv("B200M_VERBOSE")) fprintf(stderr, "b200match: device %d: fold kernel clusters of %d (max active 2-CTA clusters %d, SMs %d)\n", dev, fold_cs, nc, sms);
         once.val[dev][0] = fold_cs; once.val[dev][1] = fold_clusters;
+        once.val[dev][2] = getenv("B200M_NO_PAIR") ? 0 : 1;          // A/B switch: multicast clusters of single-CTA MMAs instead of CTA pairs
         once.done[dev] = 1;
     }
     const int fold_cs = once.val[dev][0], fold_clusters = once.val[dev][1];
@@ -778,16 +883,21 @@ int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_row
         const long long max_units = cs == 2 ? fold_clusters : sms;
         cfg.gridDim = dim3((unsigned)((fitems < max_units ? fitems : max_units) * cs));
         cfg.blockDim = dim3(FOLD_THREADS);
-        cfg.dynamicSmemBytes = smem_bytes_fold(nkb);
+        const bool pair = cs == 2 && once.val[dev][2];
+        cfg.dynamicSmemBytes = smem_bytes_fold(nkb, pair);
         cfg.stream = st;
         cfg.attrs = at; cfg.numAttrs = 1;
+        const int kmul = nkb == 1 ? 512 : 256;        // 2^IDX_BITS of the kernel's packed top-2 keys
         cudaError_t e;
-        if (cs == 2)
-            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 2>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows)
-                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 2>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows);
+        if (pair)
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 2, true>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows, kmul)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 2, true>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows, kmul);
+        else if (cs == 2)
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 2>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows, kmul)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 2>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows, kmul);
         else
-            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 1>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows)
-                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 1>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows);
+            e = nkb == 1 ? cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<1, 1>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows, kmul)
+                         : cudaLaunchKernelEx(&cfg, l2_i8_fold_kernel<2, 1>, tq, tth, tx, fold_flag, pairs, fitems, groups, S, out, total_rows, kmul);
         b200m_count_launch();
         B200M_CUDA_CHECK(e, "l2_i8_fold_kernel launch");
     }

@@ -39,6 +39,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {}
 }
+// The same on raw shared::cta addresses (hot loops that keep the address in a register instead of re-deriving it).
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar_addr, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar_addr), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar_addr) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
 // Single-thread roles (TMA producer, MMA issuer): let the hardware suspend the thread until the
 // phase flips (suspend-time hint) instead of spinning on issue slots the epilogue warps need.
 __device__ __forceinline__ void mbar_wait_suspend(uint64_t* bar, uint32_t parity) {
@@ -167,6 +183,56 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
 // Same, arriving on the mbarrier at this shared-memory offset in every CTA of the cluster named by cta_mask.
 __device__ __forceinline__ void mma_commit_mc(uint64_t* bar, uint16_t cta_mask) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(cta_mask)
+                 : "memory");
+}
+
+// ---------------------------------------------------------------- CTA pairs (cta_group::2): one MMA spans two SMs
+// Shared-memory address of `local_smem_addr`'s twin in CTA `rank` of this cluster (shared::cluster window).
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(rank));
+    return r;
+}
+// Arrive on an mbarrier that may live in the peer CTA (address from mapa_u32).  Deliberately WITHOUT .release.cluster:
+// that form compiles to MEMBAR.ALL.GPU + ERRBAR + CGAERRBAR in front of the arrive (27 % of all stall samples of the
+// first CTA-pair kernel, profiles/r02_pair_v1_ncu.md).  The callers order tensor-memory reads, which
+// tcgen05.wait::ld + tcgen05.fence::before_thread_sync already do; no generic-proxy data is published here.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load into THIS CTA's shared memory whose completion bytes are counted on an mbarrier of either CTA of the pair
+// (cluster_bar from mapa_u32): both CTAs' halves of an operand stage report to the MMA-issuing CTA's barrier.
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* m, uint32_t cluster_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"((uint64_t)m), "r"(cluster_bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* dst_smem) {   // one whole warp in EACH CTA of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+                 "n"(kCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr) {     // the allocating warps, after a cluster barrier
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+// D[256 x N] (+)= A * B^T over the CTA pair: rows 0..127 of D and A live in the even CTA, 128..255 in the odd one; each
+// CTA supplies N/2 rows of B at the same shared-memory offset.  Issued by ONE thread of the even (leader) CTA.
+__device__ __forceinline__ void mma_i8_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// Arrive on the mbarrier at this shared-memory offset in every CTA of cta_mask once the pair's MMAs issued so far are done.
+__device__ __forceinline__ void mma_commit_2sm_mc(uint64_t* bar, uint16_t cta_mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                  ::"r"(smem_u32(bar)), "h"(cta_mask)
                  : "memory");
 }

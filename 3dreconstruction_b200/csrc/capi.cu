@@ -249,7 +249,7 @@ static int run_knn_stage(int kind, const void* q_desc, const void* q_norm, int64
                                         pl.pairs, num_pairs, max_n, max_m, S, back, out, rows, st);
             if (rc == B200M_OK)      // chunk-level top-2 -> exact (distance, column) top-2 in slice 0, the POPC kernel's format
                 rc = launch_hamming_tc_resolve((const uint8_t*)q_desc, (const uint8_t*)t_desc, D, pl.pairs, num_pairs,
-                                               max_n, max_m, S, back, out, rows, st);
+                                               max_n, max_m, S, back, !need2, out, rows, st);
         } else if (kind == B200M_KIND_L2_I8)
             rc = launch_l2_i8_top2((const int8_t*)q_desc, (const int32_t*)q_norm, q_rows, (const int8_t*)t_desc,
                                    (const int32_t*)t_norm, t_rows, D, pl.pairs, num_pairs, max_n, max_m, S,

@@ -123,7 +123,8 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
                            bool fp4, const DevPair* pairs, int num_pairs, int max_n, int max_m, int S, bool backward,
                            Top2* out, long long total_rows, cudaStream_t st);
 int launch_hamming_tc_resolve(const uint8_t* q_bits, const uint8_t* t_bits, int D, const DevPair* pairs, int num_pairs,
-                              int max_n, int max_m, int S, bool backward, Top2* arr, long long total_rows, cudaStream_t st);
+                              int max_n, int max_m, int S, bool backward, bool best_only, Top2* arr, long long total_rows,
+                              cudaStream_t st);
 #define B200M_HAMMING_IDX_BITS 19   // key32 = dist << 19 | index (hamming.cu); fused column minima need n <= 2^19
 int launch_l2_i8_top2(const int8_t* q_desc, const int32_t* q_norm, int64_t q_rows,
                       const int8_t* t_desc, const int32_t* t_norm, int64_t t_rows, int D,

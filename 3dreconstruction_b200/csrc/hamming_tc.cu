@@ -85,27 +85,34 @@ struct Smem {
     uint64_t *a_full, *a_empty, *b_full, *b_empty, *acc_full, *acc_empty;
     uint32_t* tmem_ptr;
 };
-__device__ __forceinline__ Smem carve(uint8_t* base, int nkb, bool fp4) {
+// pair == true (cta_group::2): a CTA keeps only its own half of every train tile, so a ring stage is half as large and
+// the ring twice as deep (see l2_i8_fold_kernel).
+__host__ __device__ constexpr int nbf_of(bool pair) { return pair ? 2 * NBF : NBF; }
+__device__ __forceinline__ Smem carve(uint8_t* base, int nkb, bool fp4, bool pair = false) {
+    const int nbf = nbf_of(pair);
     Smem s;
     s.a = base;
     s.b = s.a + nabuf_of(nkb) * nkb * A_KB_BYTES;
-    s.xch = (int2*)(s.b + NBF * b_kb_bytes(fp4));
+    s.xch = (int2*)(s.b + nbf * (b_kb_bytes(fp4) / (pair ? 2 : 1)));
     uint8_t* p = (uint8_t*)(s.xch + 2 * (EPI_WARPS - 4) * 32);
     s.a_full = (uint64_t*)p; p += 2 * 8;
     s.a_empty = (uint64_t*)p; p += 2 * 8;
-    s.b_full = (uint64_t*)p; p += NBF * 8;
-    s.b_empty = (uint64_t*)p; p += NBF * 8;
+    s.b_full = (uint64_t*)p; p += nbf * 8;
+    s.b_empty = (uint64_t*)p; p += nbf * 8;
     s.acc_full = (uint64_t*)p; p += 2 * 8;
     s.acc_empty = (uint64_t*)p; p += 2 * 8;
     s.tmem_ptr = (uint32_t*)p;
     return s;
 }
-__host__ __device__ constexpr size_t smem_bytes(int nkb, bool fp4 = false) {
-    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)NBF * b_kb_bytes(fp4) +
-           2 * (EPI_WARPS - 4) * 32 * sizeof(int2) + (4 + 2 * NBF + 4) * 8 + 16;
+__host__ __device__ constexpr size_t smem_bytes(int nkb, bool fp4 = false, bool pair = false) {
+    return 1024 + (size_t)nabuf_of(nkb) * nkb * A_KB_BYTES + (size_t)nbf_of(pair) * (b_kb_bytes(fp4) / (pair ? 2 : 1)) +
+           2 * (EPI_WARPS - 4) * 32 * sizeof(int2) + (4 + 2 * nbf_of(pair) + 4) * 8 + 16;
 }
 static_assert(smem_bytes(1) <= 232448 && smem_bytes(2) <= 232448 && smem_bytes(3) <= 232448 && smem_bytes(4) <= 232448,
               "shared memory (int8)");
+static_assert(smem_bytes(1, false, true) <= 232448 && smem_bytes(2, false, true) <= 232448 &&
+              smem_bytes(3, false, true) <= 232448 && smem_bytes(4, false, true) <= 232448 &&
+              smem_bytes(1, true, true) <= 232448 && smem_bytes(2, true, true) <= 232448, "shared memory (CTA pairs)");
 
 __device__ __forceinline__ int max3(int a, int b, int c) { return max(max(a, b), c); }
 template <int O>
@@ -144,19 +151,40 @@ __device__ __forceinline__ void mma_mxf4(uint32_t d_tmem, uint64_t a_desc, uint6
         : "memory");
 }
 
+__device__ __forceinline__ void mma_mxf4_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t sf,
+                                             uint32_t accumulate) {      // M = 256 over a CTA pair; issued by the even CTA
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%4], [%4], p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(sf), "r"(accumulate)
+        : "memory");
+}
+// m * kmul + low as ONE IMAD on the FMA pipe (kmul in a register so that ptxas cannot turn it into ALU-pipe shift + add)
+__device__ __forceinline__ int pack_key(int m, int kmul, int low) {
+    int r;
+    asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(m), "r"(kmul), "r"(low));
+    return r;
+}
+
 // CS = CTAs per cluster (1 or 2): the two CTAs of a cluster take adjacent query row tiles of the same pair, each fetches
 // half of every train tile and TMA-multicasts it to both (see l2_i8_fold_kernel for the protocol).
-template <int NKB, int CS, bool FP4>
+// PAIR (CS == 2): the cluster is a tcgen05 CTA pair instead -- one cta_group::2 MMA of M = 256 spans both CTAs' query
+// tiles and each CTA keeps only its own half of the train tile.  Per CTA and e2m1 tile that is 62 KiB of operand reads +
+// 30 KiB of TMA fill per 960 cycles (97 B/clk) instead of 92 + 60 KiB (160 B/clk against the 128 B/clk of shared memory,
+// which is what held the multicast version at 0.77 of the mxf4 issue rate: sm__mem_tensor_cycles_active 92 %).
+template <int NKB, int CS, bool FP4, bool PAIR = false>
 __global__ void __launch_bounds__(THREADS, 1)
 hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                   const DevPair* __restrict__ pairs, long long total_items, int tiles_max, int S, int backward,
-                  int dbits, Top2* __restrict__ out, long long total_rows) {
+                  int dbits, Top2* __restrict__ out, long long total_rows, int kmul) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const Smem sm = carve(smem, NKB, FP4);
+    static_assert(!PAIR || CS == 2, "a CTA pair is a cluster of two");
+    const Smem sm = carve(smem, NKB, FP4, PAIR);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int W_MMA = 0, W_PROD = 1;
     constexpr int TN = tn_of(FP4), B_KB_BYTES = b_kb_bytes(FP4);
+    constexpr int NBFK = nbf_of(PAIR), B_STAGE = PAIR ? B_KB_BYTES / 2 : B_KB_BYTES;
     static_assert(!FP4 || NKB <= 2, "e2m1: 256 bits per K block, |a.b| <= 512");
     constexpr int NABUF = nabuf_of(NKB);
     constexpr bool SEP_ACC = sep_acc_of(NKB);
@@ -175,11 +203,18 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         sm100::tma_prefetch_desc(&tmap_q);
         sm100::tma_prefetch_desc(&tmap_t);
         for (int i = 0; i < NABUF; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
-        for (int i = 0; i < NBF; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], CS); }
-        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_WARPS / 2); }
+        // PAIR: one multicast commit of the leader frees a stage in both CTAs; a TMEM stage is free once the 16 epilogue
+        // warps of BOTH CTAs have drained it (they arrive on the leader's barrier)
+        for (int i = 0; i < NBFK; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], PAIR ? 1 : CS); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], (PAIR ? 2 : 1) * EPI_WARPS); }
         sm100::fence_barrier_init();
     }
-    if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    if constexpr (PAIR) {
+        sm100::cluster_sync_all();                         // both CTAs of the pair are running before the paired allocation
+        if (warp == W_MMA) sm100::tmem_alloc_2sm<512>(sm.tmem_ptr);
+    } else {
+        if (warp == W_MMA) sm100::tmem_alloc<512>(sm.tmem_ptr);
+    }
     sm100::tc_fence_before();
     __syncthreads();
     if constexpr (CS > 1) sm100::cluster_sync_all();
@@ -206,11 +241,20 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_empty[ab], a_par);
             if (sm100::elect_one()) {
-                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+                if constexpr (PAIR) {                  // both CTAs' query tiles are counted on the leader's barrier
+                    if (crank == 0) sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(2 * NKB * A_KB_BYTES));
+                    const uint32_t lbar = sm100::mapa_u32(sm100::smem_u32(&sm.a_full[ab]), 0);
 #pragma unroll
-                for (int kb = 0; kb < NKB; ++kb)
-                    sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
-                                       kb * KB_BYTES, it.q_off + it.r0);
+                    for (int kb = 0; kb < NKB; ++kb)
+                        sm100::tma_load_2d_2sm(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, lbar,
+                                               kb * KB_BYTES, it.q_off + it.r0);
+                } else {
+                    sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(NKB * A_KB_BYTES));
+#pragma unroll
+                    for (int kb = 0; kb < NKB; ++kb)
+                        sm100::tma_load_2d(sm.a + (size_t)(ab * NKB + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                           kb * KB_BYTES, it.q_off + it.r0);
+                }
             }
             __syncwarp();
             if (++ab == NABUF) { ab = 0; a_par ^= 1; }
@@ -220,18 +264,25 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 for (int kb = 0; kb < NKB; ++kb) {
                     sm100::mbar_wait(&sm.b_empty[bs], b_par);
                     if (sm100::elect_one()) {
-                        sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
-                        uint8_t* bdst = sm.b + (size_t)bs * B_KB_BYTES + (size_t)crank * (B_KB_BYTES / CS);
-                        if constexpr (CS > 1) sm100::tma_load_2d_mc(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN, MC_MASK);
-                        else sm100::tma_load_2d(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN);
+                        if constexpr (PAIR) {          // this CTA's half of the tile stays here; both halves count on the leader's barrier
+                            if (crank == 0) sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(2 * B_STAGE));
+                            sm100::tma_load_2d_2sm(sm.b + (size_t)bs * B_STAGE, &tmap_t, sm100::mapa_u32(sm100::smem_u32(&sm.b_full[bs]), 0),
+                                                   kb * KB_BYTES, row0 + j * TN);
+                        } else {
+                            sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)B_KB_BYTES);
+                            uint8_t* bdst = sm.b + (size_t)bs * B_KB_BYTES + (size_t)crank * (B_KB_BYTES / CS);
+                            if constexpr (CS > 1) sm100::tma_load_2d_mc(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN, MC_MASK);
+                            else sm100::tma_load_2d(bdst, &tmap_t, &sm.b_full[bs], kb * KB_BYTES, row0 + j * TN);
+                        }
                     }
                     __syncwarp();
-                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                    if (++bs == NBFK) { bs = 0; b_par ^= 1; }
                 }
             }
         }
-    } else if (warp == W_MMA) {
-        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, TM, 256);
+    } else if (warp == W_MMA && (!PAIR || crank == 0)) {
+        constexpr uint32_t idesc = sm100::make_idesc(/*S32*/ 2, /*s8*/ 1, /*s8*/ 1, PAIR ? 2 * TM : TM, 256);
+        constexpr uint32_t idesc4 = PAIR ? (IDESC_MXF4 & ~(0x1Fu << 24)) | ((uint32_t)(2 * TM >> 4) << 24) : IDESC_MXF4;
         const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
@@ -250,38 +301,53 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     sm100::mbar_wait(&sm.b_full[bs], b_par);
                     sm100::tc_fence_after();
                     if (sm100::elect_one()) {
-                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_KB_BYTES >> 4);
+                        const uint32_t al = a_lo + kb * (A_KB_BYTES >> 4), bl = b_lo0 + bs * (B_STAGE >> 4);
 #pragma unroll
                         for (int k = 0; k < KB_BYTES / 32; ++k) {
-                            if constexpr (FP4)
-                                mma_mxf4(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k), IDESC_MXF4,
-                                         tmem_base + SF_COL, (kb | k) ? 1u : 0u);
-                            else
-                                sm100::mma_i8(d_tmem, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                              idesc, (kb | k) ? 1u : 0u);
+                            const uint64_t ad = sm100::smem_desc_join(al + 2 * k), bd = sm100::smem_desc_join(bl + 2 * k);
+                            const uint32_t accf = (kb | k) ? 1u : 0u;
+                            if constexpr (FP4 && PAIR) mma_mxf4_2sm(d_tmem, ad, bd, idesc4, tmem_base + SF_COL, accf);
+                            else if constexpr (FP4) mma_mxf4(d_tmem, ad, bd, idesc4, tmem_base + SF_COL, accf);
+                            else if constexpr (PAIR) sm100::mma_i8_2sm(d_tmem, ad, bd, idesc, accf);
+                            else sm100::mma_i8(d_tmem, ad, bd, idesc, accf);
                         }
-                        if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
+                        if constexpr (PAIR) sm100::mma_commit_2sm_mc(&sm.b_empty[bs], MC_MASK);
+                        else if constexpr (CS > 1) sm100::mma_commit_mc(&sm.b_empty[bs], MC_MASK);
                         else sm100::mma_commit(&sm.b_empty[bs]);
-                        if (SEP_ACC && kb == NKB - 1) sm100::mma_commit(&sm.acc_full[as]);
+                        if (SEP_ACC && kb == NKB - 1) {
+                            if constexpr (PAIR) sm100::mma_commit_2sm_mc(&sm.acc_full[as], MC_MASK);
+                            else sm100::mma_commit(&sm.acc_full[as]);
+                        }
                     }
                     __syncwarp();
-                    if (++bs == NBF) { bs = 0; b_par ^= 1; }
+                    if (++bs == NBFK) { bs = 0; b_par ^= 1; }
                 }
                 as ^= 1;
             }
-            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            if (sm100::elect_one()) {
+                if constexpr (PAIR) sm100::mma_commit_2sm_mc(&sm.a_empty[ab], MC_MASK);   // both CTAs' query tiles are free
+                else sm100::mma_commit(&sm.a_empty[ab]);
+            }
             __syncwarp();
             if (++ab == NABUF) { ab = 0; a_par ^= 1; }
         }
     } else if (warp >= CTRL_WARPS) {
-        // epilogue: two groups of 8 warps on alternate tiles (group g owns TMEM stage g); a warp drains 128 columns
-        // (half a tile) of its 32 TMEM lanes
+        // epilogue: ALL 16 warps drain EVERY tile -- warp (quarter, cb) reads its 32 TMEM lanes x 64 columns with two
+        // 32-column tcgen05.ld issued back to back and hands the stage back before any arithmetic (l2_i8_fold_kernel has
+        // the measurements behind this shape).  Column block 3 of an e2m1 tile ends at column 240: its last chunk would be
+        // the scale factors and is skipped.
         const int e = warp - CTRL_WARPS;
-        const int g = e >> 3, half = (e >> 2) & 1, quarter = warp & 3;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + g * 256 + half * 128;
-        const int width = FP4 && half ? TN - 128 : 128;      // e2m1 tiles: the upper half has 112 columns = 7 chunks
+        const int cb = e >> 2, quarter = warp & 3;
+        constexpr int CBW = 64, CB_CHUNKS = CBW / CHUNK;
+        const int width = FP4 && cb == 3 ? TN - 3 * CBW : CBW;
         constexpr int KOFF = (512 << KEY_SHIFT) + KEY_LOW;
-        uint32_t k = 0, tc_base = 0, nitem = 0;
+        uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + cb * CBW;     // this tile's stage: toggles by 256 columns
+        uint32_t acc_bar = PAIR ? sm100::mapa_u32(sm100::smem_u32(&sm.acc_empty[0]), 0) : sm100::smem_u32(&sm.acc_empty[0]);
+        uint32_t ready_bar = sm100::smem_u32(SEP_ACC ? &sm.acc_full[0] : &sm.b_empty[0]);
+        // "accumulator ready": SEP_ACC -> acc_full[tile & 1], parity (tile >> 1) & 1; else the ring stage of the tile's last K block
+        uint32_t as8 = 0, rs = SEP_ACC ? 0 : (NKB - 1) * 8, rp = 0, nitem = 0;
+        int mtn = -(TN / CHUNK);
+        asm volatile("" : "+r"(taddr), "+r"(acc_bar), "+r"(ready_bar), "+r"(mtn));
         for (long long item = first_item; item < total_items; item += item_stride) {
             Item it = decode(item);
             if (!it.valid) continue;
@@ -290,44 +356,48 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 v2 = max(v2, min(v1, key));
                 v1 = max(v1, key);
             };
-            for (int j = (int)((g - tc_base) & 1); j < it.ntiles; j += 2, ++k) {
-                const int base = it.c_begin + j * TN + half * 128;
-                const int lim = it.c_end - base;
-                const int kc = KOFF - (base >> 4);        // key of chunk c of this warp's 8 = (max << 20) + kc - c
+            auto push2 = [&](int ka, int kb) {             // top-2 of {v1, v2, ka, kb}: 5 min/max instead of 6
+                const int mx = max(ka, kb), mn = min(ka, kb);
+                const int t = min(v1, mx);
+                v1 = max(v1, mx);
+                v2 = max3(t, v2, mn);
+            };
+            // key of chunk c of this warp's 4 in tile j = (max << 20) + lowc_c - j * (TN / 16)
+            int lowc0 = KOFF - ((it.c_begin + cb * CBW) >> 4), lowc1 = lowc0 - 1, lowc2 = lowc0 - 2, lowc3 = lowc0 - 3;
+            asm volatile("" : "+r"(lowc0), "+r"(lowc1), "+r"(lowc2), "+r"(lowc3));
+            int rem = it.c_end - it.c_begin - cb * CBW;      // existing columns from this warp's first one on
+            for (int j = 0; j < it.ntiles; ++j) {
+                sm100::mbar_wait_addr(ready_bar + rs, rp);
                 if constexpr (SEP_ACC) {
-                    sm100::mbar_wait(&sm.acc_full[g], k & 1);
-                } else {   // accumulator ready == the ring stage of this tile's last K block has been released
-                    const uint32_t tc = 2 * k + g;
-                    const uint32_t use = (tc * NKB + NKB - 1) / NBF, stage = (tc * NKB + NKB - 1) % NBF;
-                    sm100::mbar_wait(&sm.b_empty[stage], use & 1);
+                    rs ^= 8; rp ^= (rs == 0);
+                } else {
+                    rs += NKB * 8;
+                    if (rs >= (uint32_t)(NBFK * 8)) { rs -= NBFK * 8; rp ^= 1; }
                 }
                 sm100::tc_fence_after();
                 uint32_t acc[2][32];
                 sm100::tmem_ld32(taddr, acc[0]);
                 sm100::tmem_ld32(taddr + 32, acc[1]);
-                sm100::tmem_ld_wait();
-                if (lim < width) { mask32<FP4>(acc[0], lim); mask32<FP4>(acc[1], lim - 32); }
-                int m0 = chunk_max<0, FP4>(acc[0]), m1 = chunk_max<16, FP4>(acc[0]);
-                sm100::tmem_ld32(taddr + 64, acc[0]);
-                int m2 = chunk_max<0, FP4>(acc[1]), m3 = chunk_max<16, FP4>(acc[1]);
-                sm100::tmem_ld32(taddr + 96, acc[1]);
-                insert((m0 << KEY_SHIFT) + kc); insert((m1 << KEY_SHIFT) + kc - 1);
-                insert((m2 << KEY_SHIFT) + kc - 2); insert((m3 << KEY_SHIFT) + kc - 3);
-                sm100::tmem_ld_wait();
+                sm100::tmem_ld_wait();                        // everything is in registers: hand the TMEM stage back first
                 sm100::tc_fence_before();
                 __syncwarp();
-                if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[g]);
-                if (lim < width) { mask32<FP4>(acc[0], lim - 64); mask32<FP4>(acc[1], lim - 96); }
-                m0 = chunk_max<0, FP4>(acc[0]); m1 = chunk_max<16, FP4>(acc[0]);
-                m2 = chunk_max<0, FP4>(acc[1]);
-                insert((m0 << KEY_SHIFT) + kc - 4); insert((m1 << KEY_SHIFT) + kc - 5);
-                insert((m2 << KEY_SHIFT) + kc - 6);
-                if (!(FP4 && half)) {          // columns 240..255 of an e2m1 tile are the scale factors, not distances
-                    m3 = chunk_max<16, FP4>(acc[1]);
-                    insert((m3 << KEY_SHIFT) + kc - 7);
+                if (lane == 0) {
+                    if constexpr (PAIR) sm100::mbar_arrive_cluster(acc_bar + as8);
+                    else sm100::mbar_arrive_addr(acc_bar + as8);
+                }
+                taddr ^= 256; as8 ^= 8;
+                if (rem < width) { mask32<FP4>(acc[0], rem); mask32<FP4>(acc[1], rem - 32); }     // tail tile
+                rem -= TN;
+                const int m0 = chunk_max<0, FP4>(acc[0]), m1 = chunk_max<16, FP4>(acc[0]);
+                const int m2 = chunk_max<0, FP4>(acc[1]);
+                push2(pack_key(m0, kmul, pack_key(j, mtn, lowc0)), pack_key(m1, kmul, pack_key(j, mtn, lowc1)));
+                if (FP4 && cb == 3) {          // columns 240..255 of an e2m1 tile are the scale factors, not distances
+                    insert(pack_key(m2, kmul, pack_key(j, mtn, lowc2)));
+                } else {
+                    const int m3 = chunk_max<16, FP4>(acc[1]);
+                    push2(pack_key(m2, kmul, pack_key(j, mtn, lowc2)), pack_key(m3, kmul, pack_key(j, mtn, lowc3)));
                 }
             }
-            tc_base += (uint32_t)it.ntiles;
             // the four warps of a TMEM lane quarter hold partial top-2s of the same 32 query rows: merge in shared memory
             int2* xbuf = sm.xch + (size_t)(nitem & 1) * (EPI_WARPS - 4) * 32;
             ++nitem;
@@ -358,7 +428,10 @@ hamming_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     sm100::tc_fence_before();
     __syncthreads();
     if constexpr (CS > 1) sm100::cluster_sync_all();
-    if (warp == W_MMA) sm100::tmem_dealloc<512>(tmem_base);
+    if (warp == W_MMA) {
+        if constexpr (PAIR) sm100::tmem_dealloc_2sm<512>(tmem_base);
+        else sm100::tmem_dealloc<512>(tmem_base);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -381,18 +454,43 @@ __device__ __forceinline__ int popc_row(const uint8_t* __restrict__ a, const uin
 
 // One warp per query row: merge the column splits' chunk-level top-2, recompute both chunks (lane = chunk x column)
 // with POPC on the packed bits, write the exact (distance << 32 | column) top-2 into slice 0.
+// BEST_ONLY (cross-check and plain 1-NN consume only the nearest neighbour): half a warp per row recomputes the best
+// chunk alone -- half the gathered train rows (the kernel is bound by those 64-byte gathers from L2) and a single-key
+// min reduction instead of the top-2 butterfly.
+template <bool BEST_ONLY>
 __global__ void __launch_bounds__(256)
 hamming_tc_resolve_kernel(const uint8_t* __restrict__ q_bits, const uint8_t* __restrict__ t_bits, int D, int vec,
                           const DevPair* __restrict__ pairs, int blocks_per_pair, Top2* __restrict__ arr,
                           long long total_rows, int S, int backward) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int p = blockIdx.x / blocks_per_pair;
-    const int i = (blockIdx.x - p * blocks_per_pair) * 8 + warp;
+    const int i = BEST_ONLY ? (blockIdx.x - p * blocks_per_pair) * 16 + warp * 2 + (lane >> 4)
+                            : (blockIdx.x - p * blocks_per_pair) * 8 + warp;
     const DevPair pr = pairs[p];
     int q_off = pr.q_off, n = pr.n, t_off = pr.t_off, m = pr.m;
     long long row_base = pr.fwd_off;
     const uint8_t *qb = q_bits, *tb = t_bits;
     if (backward) { q_off = pr.t_off; n = pr.m; t_off = pr.q_off; m = pr.n; row_base = pr.bwd_off; qb = t_bits; tb = q_bits; }
+    if constexpr (BEST_ONLY) {
+        static_assert(CHUNK == 16, "half a warp per chunk");
+        const bool live = i < n;                     // the other half-warp of this warp may still have a row
+        const long long row = row_base + (live ? i : 0);
+        u64 ck = B200M_SENTINEL;
+        if (live) {
+            ck = arr[row].k1;
+            for (int s = 1; s < S; ++s) { const u64 o = arr[(long long)s * total_rows + row].k1; ck = o < ck ? o : ck; }
+        }
+        const int col = (int)(u32)ck + (lane & (CHUNK - 1));
+        u64 k1 = B200M_SENTINEL;
+        if (ck != B200M_SENTINEL && col < m) {
+            const int d = popc_row(qb + (long long)(q_off + i) * D, tb + (long long)(t_off + col) * D, D, vec);
+            k1 = ((u64)(u32)d << 32) | (u64)(u32)col;
+        }
+#pragma unroll
+        for (int off = 8; off > 0; off >>= 1) { const u64 o = __shfl_xor_sync(0xffffffffu, k1, off); k1 = o < k1 ? o : k1; }
+        if (live && (lane & 15) == 0) { Top2 r; r.k1 = k1; r.k2 = B200M_SENTINEL; arr[row] = r; }
+        return;
+    }
     if (i >= n) return;
     const long long row = row_base + i;
     Top2 t = arr[row];
@@ -482,7 +580,15 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
     int dev = 0, sms = 0;
     if (!b200m_current_device(&dev, &sms)) return B200M_ENODEVICE;
     int (&cs_ok)[12] = once.val[dev];
+    // cs_ == 3 names the CTA-pair (cta_group::2) instantiation of the 2-CTA cluster
     auto kern = [](int nkb_, int cs_, bool f4) -> const void* {
+        if (cs_ == 3) {
+            if (f4) return nkb_ == 1 ? (const void*)hamming_tc_kernel<1, 2, true, true> : (const void*)hamming_tc_kernel<2, 2, true, true>;
+            switch (nkb_) {
+                case 1: return (const void*)hamming_tc_kernel<1, 2, false, true>; case 2: return (const void*)hamming_tc_kernel<2, 2, false, true>;
+                case 3: return (const void*)hamming_tc_kernel<3, 2, false, true>; default: return (const void*)hamming_tc_kernel<4, 2, false, true>;
+            }
+        }
         if (f4) {
             switch (nkb_ * 2 + cs_ - 1) {
                 case 2: return (const void*)hamming_tc_kernel<1, 1, true>; case 3: return (const void*)hamming_tc_kernel<1, 2, true>;
@@ -499,25 +605,27 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
     if (!once.done[dev]) {
         for (int f4 = 0; f4 < 2; ++f4)
             for (int nk = 1; nk <= (f4 ? 2 : 4); ++nk) {
-                for (int cs = 1; cs <= 2; ++cs)
+                for (int cs = 1; cs <= 3; ++cs)
                     B200M_CUDA_CHECK(cudaFuncSetAttribute(kern(nk, cs, f4), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                          (int)smem_bytes(nk, f4)), "hamming_tc smem attr");
+                                                          (int)smem_bytes(nk, f4, cs == 3)), "hamming_tc smem attr");
                 cudaLaunchConfig_t qc = {};
                 cudaLaunchAttribute qa[1];
                 qa[0].id = cudaLaunchAttributeClusterDimension;
                 qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
-                qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(THREADS); qc.dynamicSmemBytes = smem_bytes(nk, f4);
+                qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(THREADS); qc.dynamicSmemBytes = smem_bytes(nk, f4, true);
                 qc.attrs = qa; qc.numAttrs = 1;
                 int nc = 0;
-                if (cudaOccupancyMaxActiveClusters(&nc, kern(nk, 2, f4), &qc) == cudaSuccess && nc * 2 >= sms && !getenv("B200M_NO_CLUSTER"))
+                if (cudaOccupancyMaxActiveClusters(&nc, kern(nk, 3, f4), &qc) == cudaSuccess && nc * 2 >= sms && !getenv("B200M_NO_CLUSTER"))
                     cs_ok[f4 * 5 + nk] = nc;
                 else
                     cudaGetLastError();
             }
+        cs_ok[11] = getenv("B200M_NO_PAIR") ? 0 : 1;       // A/B switch: multicast clusters of single-CTA MMAs instead of CTA pairs
         once.done[dev] = 1;
     }
     CUtensorMap tq, tt;
     const int cs = cs_ok[(fp4 ? 5 : 0) + nkb] > 0 ? 2 : 1;
+    const bool pair = cs == 2 && cs_ok[11];
     int rc = b200m_make_tmap_2d(&tq, q_store, (uint64_t)q_rows, (uint64_t)Dpad, TM, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
     if (rc != B200M_OK) return rc;
     rc = b200m_make_tmap_2d(&tt, t_store, (uint64_t)t_rows, (uint64_t)Dpad, TN / cs, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1);
@@ -533,29 +641,35 @@ int launch_hamming_tc_top2(const void* q_store, int64_t q_rows, const void* t_st
     const long long max_units = cs == 2 ? cs_ok[(fp4 ? 5 : 0) + nkb] : sms;
     cfg.gridDim = dim3((unsigned)((items < max_units ? items : max_units) * cs));
     cfg.blockDim = dim3(THREADS);
-    cfg.dynamicSmemBytes = smem_bytes(nkb, fp4);
+    cfg.dynamicSmemBytes = smem_bytes(nkb, fp4, pair);
     cfg.stream = st;
     cfg.attrs = at; cfg.numAttrs = 1;
-    int bw = backward ? 1 : 0;
+    int bw = backward ? 1 : 0, kmul = 1 << KEY_SHIFT;
     void* args[] = {(void*)&tq, (void*)&tt, (void*)&pairs, (void*)&items, (void*)&groups, (void*)&S, (void*)&bw,
-                    (void*)&dbits, (void*)&out, (void*)&total_rows};
-    cudaError_t e = cudaLaunchKernelExC(&cfg, kern(nkb, cs, fp4), args);
+                    (void*)&dbits, (void*)&out, (void*)&total_rows, (void*)&kmul};
+    cudaError_t e = cudaLaunchKernelExC(&cfg, kern(nkb, pair ? 3 : cs, fp4), args);
     b200m_count_launch();
     B200M_CUDA_CHECK(e, "hamming_tc_kernel launch");
     return B200M_OK;
 }
 
 int launch_hamming_tc_resolve(const uint8_t* q_bits, const uint8_t* t_bits, int D, const DevPair* pairs, int num_pairs,
-                              int max_n, int max_m, int S, bool backward, Top2* arr, long long total_rows, cudaStream_t st) {
+                              int max_n, int max_m, int S, bool backward, bool best_only, Top2* arr, long long total_rows,
+                              cudaStream_t st) {
     const int max_rows = backward ? max_m : max_n;
-    const int bpp = (max_rows + 7) / 8;
+    const int rpb = best_only ? 16 : 8;            // rows per 256-thread block
+    const int bpp = (max_rows + rpb - 1) / rpb;
     const long long grid = (long long)num_pairs * bpp;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
     const uintptr_t al = (uintptr_t)q_bits | (uintptr_t)t_bits | (uintptr_t)D;
     const int vec = (al & 15) == 0 ? 16 : ((al & 3) == 0 ? 4 : 1);
-    hamming_tc_resolve_kernel<<<(unsigned)grid, 256, 0, st>>>(q_bits, t_bits, D, vec, pairs, bpp, arr, total_rows, S,
-                                                              backward ? 1 : 0);
+    if (best_only)
+        hamming_tc_resolve_kernel<true><<<(unsigned)grid, 256, 0, st>>>(q_bits, t_bits, D, vec, pairs, bpp, arr, total_rows, S,
+                                                                        backward ? 1 : 0);
+    else
+        hamming_tc_resolve_kernel<false><<<(unsigned)grid, 256, 0, st>>>(q_bits, t_bits, D, vec, pairs, bpp, arr, total_rows, S,
+                                                                         backward ? 1 : 0);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "hamming_tc_resolve_kernel launch");
     return B200M_OK;

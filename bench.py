@@ -33,7 +33,7 @@ RATIO = 0.75
 HW_INT8_TOPS = 4590.0                 # burst issue-rate peak of tcgen05.mma kind::i8 at 1965 MHz (tools/mma_peak.cu, profiles/r01_mma_peak_microbench.txt)
 HW_INT8_TOPS_SUSTAINED = 3730.0       # the same instruction stream back to back for 6 s: the chip settles at its 1000 W cap,
                                       # SM clock ~1540 MHz (profiles/r01_mma_int8_sustained.txt) -- SURVEY 8(d)'s "measured int8 peak"
-NCU_DRAM_BYTES_PER_PAIR = (191.9e6 + 111.4e6) / 1128.0     # ncu --set full of the shipped fold kernel (profiles/r01_l2i8_v9_fold_cluster_ncu_full.md)
+NCU_DRAM_BYTES_PER_PAIR = (2700.3e6 + 269.0e6) / 2048.0    # ncu --set full of the shipped fold kernel, a 2048-pair launch of this workload (profiles/r02_l2i8_pair_v3_ncu_full.md)
 
 
 def parse_args():
@@ -859,7 +859,7 @@ def run_b200(args):
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "int8", "data": "synthetic", "config": workload_config(args),
                 "matches_per_step": matches_all,
-                "roofline": {"bound": "tensor", "kernel": "l2_i8_fold_kernel (tcgen05 kind::i8 M128 N256; 4 descriptor K-steps + 1 folded-norm K-step, "
+                "roofline": {"bound": "tensor", "kernel": "l2_i8_fold_kernel (tcgen05 cta_group::2 kind::i8 M256 N256 over a CTA pair; 4 descriptor K-steps + 1 folded-norm K-step, "
                                                         "achieved counts the 4 algorithmic ones)", "achieved": achieved,
                              "peak": peak, "unit": "TOP/s int8 (TFLOP/s-equivalent)", "frac": achieved / peak if achieved else None,
                              "peak_source": "measured int8 tensor peak of this pool's B200, sustained under the 1000 W power cap: tools/mma_peak.cu, "
@@ -881,9 +881,10 @@ def run_b200(args):
                              "algorithmic_ops_per_pair": 2.0 * n * n * D,
                              "algorithmic_hbm_bytes_per_pair": 2 * n * (D + 36) + 64 * n,
                              "traffic": NCU_DRAM_BYTES_PER_PAIR * my_pairs * args.steps / max(knn_launches.value, 1),
-                             "traffic_source": "ncu --set full of the shipped l2_i8_fold_kernel, 1128-pair launch: dram read 191.9 MB + write 111.4 MB "
-                                               "(profiles/r01_l2i8_v9_fold_cluster_ncu_full.md) = 0.269 MB/pair, scaled to this run's pairs per launch; "
-                                               "below the algorithmic bytes because the store's rows are re-read from L2 (hit rate 99 %)"},
+                             "traffic_source": "ncu --set full of the shipped l2_i8_fold_kernel (CTA pairs), one 2048-pair launch of this workload: dram read "
+                                               "2700.3 MB + write 269.0 MB (profiles/r02_l2i8_pair_v3_ncu_full.md) = 1.45 MB/pair, scaled to this run's "
+                                               "pairs per launch; below the 3.2 MB/pair of algorithmic bytes because the store's rows are re-read from L2 "
+                                               "(hit rate 93 %)"},
                 "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel() * 4),
                         "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": 1e3 * float(t_e2e.item()) / e2e_steps,
                         "record_bytes_per_match": 8,

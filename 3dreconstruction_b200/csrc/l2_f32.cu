@@ -545,8 +545,13 @@ refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, in
     }
 }
 
-// Exhaustive fp32 re-scan of the queued rows (candidate list overflowed): one CTA per row, each warp takes
-// an eighth of the columns, 8 columns per step so that 16 independent 512-byte loads are in flight per warp.
+// Exhaustive fp32 re-scan of the queued rows (candidate list overflowed): FB_SLICES CTAs per row (a handful of rows per
+// launch is the normal case -- one CTA per row left the launch as long as one CTA needs for m kilobyte-sized gathers,
+// 0.22 ms for 8 rows of 4096 columns, 7 % of the float knn stage), each warp takes a strided share of the columns,
+// 8 columns per step so that 16 independent 512-byte loads are in flight per warp.  The slices merge into the row's
+// Top2 (which refine_f32_kernel left at the sentinel) with two 64-bit atomicMin: k1 keeps the minimum, every key that
+// loses there -- each key except the final minimum loses exactly once -- competes for k2.
+constexpr int FB_SLICES = 16;
 __global__ void __launch_bounds__(256)
 fallback_f32_kernel(int backward, const DevPair* __restrict__ pairs, const u64* __restrict__ fbq,
                     const int* __restrict__ fb_count, const float* __restrict__ q_desc,
@@ -555,7 +560,8 @@ fallback_f32_kernel(int backward, const DevPair* __restrict__ pairs, const u64* 
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int count = *fb_count;
     const int nf4 = D >> 2;
-    for (int q = blockIdx.x; q < count; q += gridDim.x) {
+    for (int item = blockIdx.x; item < count * FB_SLICES; item += gridDim.x) {
+        const int q = item / FB_SLICES, g = item - q * FB_SLICES;
         const u64 ent = fbq[q];
         const int p = (int)(ent >> 32), i = (int)(u32)ent;
         DevPair pr = pairs[p];
@@ -567,7 +573,7 @@ fallback_f32_kernel(int backward, const DevPair* __restrict__ pairs, const u64* 
         ar[0] = lane < nf4 ? __ldg(a4 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
         ar[1] = lane + 32 < nf4 ? __ldg(a4 + lane + 32) : make_float4(0.f, 0.f, 0.f, 0.f);
         u64 k1 = B200M_SENTINEL, k2 = B200M_SENTINEL;
-        for (int c0 = w * 8; c0 < m; c0 += 64) {
+        for (int c0 = (g * 8 + w) * 8; c0 < m; c0 += 64 * FB_SLICES) {
             float s[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
@@ -596,8 +602,14 @@ fallback_f32_kernel(int backward, const DevPair* __restrict__ pairs, const u64* 
         __syncthreads();
         if (threadIdx.x == 0) {
             for (int ww = 1; ww < 8; ++ww) { top2_insert(k1, k2, red[ww][0]); top2_insert(k1, k2, red[ww][1]); }
-            Top2 t; t.k1 = k1; t.k2 = k2;
-            out[row_base + i] = t;
+            unsigned long long* o = reinterpret_cast<unsigned long long*>(out + row_base + i);      // {k1, k2}
+            static_assert(sizeof(Top2) == 16, "Top2 is two 64-bit keys");
+            for (int r = 0; r < 2; ++r) {
+                const u64 key = r ? k2 : k1;
+                if (key == B200M_SENTINEL) break;
+                const u64 old = atomicMin(o, (unsigned long long)key);
+                atomicMin(o + 1, (unsigned long long)(old > key ? old : key));
+            }
         }
         __syncthreads();
     }

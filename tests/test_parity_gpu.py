@@ -318,6 +318,30 @@ def test_l2_i8_fold_small_and_ragged(eng):
 
 
 
+@pytest.mark.parametrize("D,m", [(128, 20000), (256, 9500)])
+def test_l2_i8_fold_long_rows_cross_key_windows(eng, D, m):
+    """The fold kernel keeps its running top-2 as packed (value, chunk) words inside a window of 8192 (D = 128) or 4096
+    (D = 256) train columns and unpacks at window ends (l2_i8.cu): one column split longer than several windows, best and
+    second-best neighbours planted in different windows, exact duplicates across windows (ties -> lowest column)."""
+    rng = np.random.default_rng(D + m)
+    n = 300                                                   # 3 row tiles of one pair: a single column split
+    def rows(k):           # D = 256: values away from 128, or the rows' norms fall below the range the fold digits cover
+        x = rng.integers(0, 256 if D == 128 else 48, size=(k, D))
+        return np.where(rng.integers(0, 2, size=(k, D)) == 1, 255 - x, x).astype(np.float32) if D == 256 else x.astype(np.float32)
+    a, c = rows(n), rows(m)
+    win = 8192 if D == 128 else 4096
+    for i in range(0, n, 3):                                  # near copies of query rows, one per window, increasingly far
+        for w, col in enumerate(range(17 + 5 * i, m, win)):
+            c[col] = np.clip(a[i] + rng.integers(-w - 1, w + 2, size=D), 0, 255)
+    for i in range(1, n, 7):                                  # exact duplicates of one another in the first and the last window
+        c[40 + i] = a[i]
+        c[m - 40 - i] = a[i]
+    assert _fold_flag(eng.prepare(c, b.NORM_L2)) == 1
+    for ratio in (0.75, 1.5):
+        assert_exact(eng.match_arrays(a, c, b.NORM_L2, False, ratio), O.reference_match(a, c, O.NORM_L2, False, ratio),
+                     f"fold windows D={D} m={m} ratio={ratio}")
+
+
 def test_l2_i8_knn2_raw(eng):
     a, c = synth.sift_pair(seed=6, n=900, m=800)
     got = eng.knn2_arrays(a, c, b.NORM_L2)

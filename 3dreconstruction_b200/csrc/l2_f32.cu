@@ -71,7 +71,7 @@ struct Item {
 };
 
 __device__ __forceinline__ Item decode_item(long long item, const DevPair* __restrict__ pairs, int tiles_max, int S,
-                                            int backward, int rows_per_item = TM) {
+                                            int backward, int rows_per_item = TM, int tn = TN) {
     Item it;
     int tile = (int)(item % tiles_max); item /= tiles_max;
     it.split = (int)(item % S);
@@ -81,7 +81,7 @@ __device__ __forceinline__ Item decode_item(long long item, const DevPair* __res
     if (!backward) { it.q_off = pr.q_off; it.n = pr.n; it.t_off = pr.t_off; it.m = pr.m; it.row_base = pr.fwd_off; }
     else           { it.q_off = pr.t_off; it.n = pr.m; it.t_off = pr.q_off; it.m = pr.n; it.row_base = pr.bwd_off; }
     it.r0 = tile * rows_per_item;
-    int cols_per = ((it.m + S - 1) / S + TN - 1) / TN * TN;
+    int cols_per = ((it.m + S - 1) / S + tn - 1) / tn * tn;
     it.c_begin = it.split * cols_per;
     it.c_end = min(it.m, it.c_begin + cols_per);
     it.valid = it.r0 < it.n;
@@ -142,7 +142,13 @@ __host__ __device__ constexpr size_t smem_bytes(int nkb, bool fold = false) {
 // with no per-column constant: no shared-memory norm staging, no barrier per tile, one FMNMX instead of FMA + LDS + FMNMX
 // per element.  fold_mode: 0 = run; 1 = run only if r = s_q / s_t is a small power of two (the FOLD kernel's own gate);
 // 2 = return if it is (the plain kernel launched right behind a FOLD kernel: device-side dispatch, no host sync).
-template <bool H16, int MT, bool FOLD>
+// PAIR (fp16 FOLD kernel, launched as clusters of two): the cluster is a tcgen05 CTA pair.  An item is still two query row
+// tiles, but each CTA holds ONE of them and its own 128 rows of a 256-column train tile; one cta_group::2 MMA of M = 256,
+// N = 256 covers both.  Why: an M128 x N128 instruction reads 8 KiB of operands in 64 cycles -- the whole 128 B/clk of shared
+// memory -- so with the TMA fill on top the MT = 2 kernel sat at 0.76 of the f16 issue rate (156 B/clk demanded); per CTA of
+// a pair it is 8 KiB per 128 cycles + 16 KiB of fill per 512 = 96 B/clk.  Protocol as in l2_i8_fold_kernel: leader-issued
+// MMAs, both CTAs' TMA bytes on the leader's "full" barriers, multicast commits, remote TMEM-release arrives.
+template <bool H16, int MT, bool FOLD, bool PAIR = false>
 __global__ void __launch_bounds__(THREADS, 1)
 l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_t,
                    const __grid_constant__ CUtensorMap tmap_x, int fold_mode,
@@ -150,8 +156,14 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                    int tiles_max, int S, int backward, int nkb, const float* __restrict__ q_norm,
                    const float* __restrict__ pmax, float2* __restrict__ cand, int* __restrict__ cand_cnt,
                    long long total_rows, const float* __restrict__ q_info, const float* __restrict__ t_info) {
+    static_assert(!PAIR || (H16 && FOLD && MT == 1), "the CTA-pair variant exists for the fp16 FOLD kernel");
     constexpr int KB_ELEMS = H16 ? KB_BYTES / 2 : KB_BYTES / 4;
     constexpr int NBK = FOLD ? NB_FOLD : NB;            // train K-block ring depth
+    constexpr int TNK = PAIR ? 2 * TN : TN;             // train columns per tile (a CTA of a pair supplies TN of them)
+    constexpr uint16_t MC_MASK = 3;
+    const uint32_t crank = PAIR ? sm100::cluster_ctarank() : 0;
+    const long long first_item = PAIR ? (long long)sm100::cluster_id_x() : (long long)blockIdx.x;
+    const long long item_stride = PAIR ? (long long)sm100::cluster_count_x() : (long long)gridDim.x;
     if (fold_mode) {
         const float r = __ldg(q_info) * __ldg(t_info + 1);          // s_q / s_t, a power of two
         const bool foldable = r >= 0.00390625f && r <= 256.0f;
@@ -162,15 +174,15 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
     const SmemLayout sm = carve(smem, nkb, FOLD);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nabuf = MT == 2 ? 1 : nabuf_of(nkb);      // MT == 2: both buffers hold the item's two row tiles
-    constexpr int ROWS_ITEM = TM * MT;
-    constexpr uint32_t ACC_COLS = TN * MT;              // TMEM columns of one stage (MT accumulators side by side)
+    constexpr int ROWS_ITEM = PAIR ? 2 * TM : TM * MT;  // PAIR: one row tile per CTA
+    constexpr uint32_t ACC_COLS = PAIR ? TNK : TN * MT; // TMEM columns of one stage (MT accumulators side by side)
 
     if (warp == 8 && lane == 0) {
         sm100::tma_prefetch_desc(&tmap_q);
         sm100::tma_prefetch_desc(&tmap_t);
         for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.a_full[i], 1); sm100::mbar_init(&sm.a_empty[i], 1); }
         for (int i = 0; i < NBK; ++i) { sm100::mbar_init(&sm.b_full[i], 1); sm100::mbar_init(&sm.b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], EPI_THREADS / 32); }
+        for (int i = 0; i < 2; ++i) { sm100::mbar_init(&sm.acc_full[i], 1); sm100::mbar_init(&sm.acc_empty[i], (PAIR ? 2 : 1) * (EPI_THREADS / 32)); }
         sm100::fence_barrier_init();
         if constexpr (FOLD) sm100::tma_prefetch_desc(&tmap_x);
     }
@@ -185,9 +197,15 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             sm100::fence_proxy_async();            // generic-proxy stores -> visible to tcgen05.mma (async proxy)
         }
     }
-    if (warp == 9) sm100::tmem_alloc<2 * ACC_COLS>(sm.tmem_ptr);
+    if constexpr (PAIR) {
+        sm100::cluster_sync_all();                          // both CTAs of the pair are running before the paired allocation
+        if (warp == 9) sm100::tmem_alloc_2sm<2 * ACC_COLS>(sm.tmem_ptr);
+    } else {
+        if (warp == 9) sm100::tmem_alloc<2 * ACC_COLS>(sm.tmem_ptr);
+    }
     sm100::tc_fence_before();
     __syncthreads();
+    if constexpr (PAIR) sm100::cluster_sync_all();         // the peer's barriers exist before anything signals them
     sm100::tc_fence_after();
     const uint32_t tmem_base = *sm.tmem_ptr;
 
@@ -195,28 +213,44 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
         // ===================== TMA producer: lockstep warp, one elected lane issues =====================
         uint32_t ab = 0, a_par = 1, bs = 0, b_par = 1;     // parities to wait for on a_empty / b_empty
         uint32_t xs = 0;                                   // folded-norm slot = tile parity (the MMA warp's `as`)
-        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM, TNK);
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_empty[ab], a_par);
             if (sm100::elect_one()) {
-                sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(MT * nkb * A_KB_BYTES));
-                for (int t = 0; t < MT; ++t)
+                if constexpr (PAIR) {                   // this CTA's row tile; both tiles are counted on the leader's barrier
+                    if (crank == 0) sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(2 * nkb * A_KB_BYTES));
+                    const uint32_t lbar = sm100::mapa_u32(sm100::smem_u32(&sm.a_full[ab]), 0);
                     for (int kb = 0; kb < nkb; ++kb)
-                        sm100::tma_load_2d(sm.a + (size_t)((ab * MT + t) * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
-                                           kb * KB_ELEMS, it.q_off + it.r0 + t * TM);
+                        sm100::tma_load_2d_2sm(sm.a + (size_t)(ab * nkb + kb) * A_KB_BYTES, &tmap_q, lbar, kb * KB_ELEMS,
+                                               it.q_off + it.r0 + (int)crank * TM);
+                } else {
+                    sm100::mbar_arrive_expect_tx(&sm.a_full[ab], (uint32_t)(MT * nkb * A_KB_BYTES));
+                    for (int t = 0; t < MT; ++t)
+                        for (int kb = 0; kb < nkb; ++kb)
+                            sm100::tma_load_2d(sm.a + (size_t)((ab * MT + t) * nkb + kb) * A_KB_BYTES, &tmap_q, &sm.a_full[ab],
+                                               kb * KB_ELEMS, it.q_off + it.r0 + t * TM);
+                }
             }
             __syncwarp();
             if (++ab == (uint32_t)nabuf) { ab = 0; a_par ^= 1; }
-            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TNK) {
                 for (int kb = 0; kb < nkb; ++kb) {
                     sm100::mbar_wait(&sm.b_empty[bs], b_par);
                     if (sm100::elect_one()) {
                         const bool withx = FOLD && kb == nkb - 1;      // the tile's folded-norm rows travel with its last K block
+                        if constexpr (PAIR) {          // this CTA's TN train rows of the 2 TN-column tile stay here
+                            if (crank == 0) sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(2 * (B_KB_BYTES + (withx ? X_BYTES : 0))));
+                            const uint32_t lbar = sm100::mapa_u32(sm100::smem_u32(&sm.b_full[bs]), 0);
+                            const int trow = it.t_off + c0 + (int)crank * TN;
+                            sm100::tma_load_2d_2sm(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, lbar, kb * KB_ELEMS, trow);
+                            if (withx) sm100::tma_load_2d_2sm(sm.x + (size_t)xs * X_BYTES, &tmap_x, lbar, 0, trow);
+                        } else {
                         sm100::mbar_arrive_expect_tx(&sm.b_full[bs], (uint32_t)(B_KB_BYTES + (withx ? X_BYTES : 0)));
                         sm100::tma_load_2d(sm.b + (size_t)bs * B_KB_BYTES, &tmap_t, &sm.b_full[bs], kb * KB_ELEMS,
                                            it.t_off + c0);
                         if (withx) sm100::tma_load_2d(sm.x + (size_t)xs * X_BYTES, &tmap_x, &sm.b_full[bs], 0, it.t_off + c0);
+                        }
                     }
                     __syncwarp();
                     if (++bs == NBK) { bs = 0; b_par ^= 1; }
@@ -224,23 +258,33 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 xs ^= 1;
             }
         }
-    } else if (warp == 9) {
-        // ===================== MMA issuer: lockstep warp, one elected lane issues =====================
+    } else if (warp == 9 && (!PAIR || crank == 0)) {
+        // ===================== MMA issuer: lockstep warp, one elected lane issues (PAIR: the even CTA only) =====================
         // (a single thread with per-tile modulo arithmetic and 64-bit descriptor maths was the bottleneck of
         // the int8 kernel; descriptors here are a constant high word and a running 32-bit low word)
-        constexpr uint32_t idesc = H16 ? sm100::make_idesc(/*F32*/ 1, /*f16*/ 0, /*f16*/ 0, TM, TN)
+        constexpr uint32_t idesc = H16 ? sm100::make_idesc(/*F32*/ 1, /*f16*/ 0, /*f16*/ 0, PAIR ? 2 * TM : TM, TNK)
                                        : sm100::make_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, TM, TN);
+        auto mma16 = [](uint32_t d, uint64_t a, uint64_t b, uint32_t id, uint32_t acc) {
+            if constexpr (PAIR) {
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                    ::"r"(d), "l"(a), "l"(b), "r"(id), "r"(acc) : "memory");
+            } else {
+                sm100::mma_f16(d, a, b, id, acc);
+            }
+        };
         const uint32_t a_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.a));
         const uint32_t b_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.b));
         const uint32_t x_lo0 = sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.x));      // same low-word format
         const uint64_t ax_desc = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, sm100::smem_desc_lo_sw128(sm100::smem_u32(sm.ax)));
         uint32_t ab = 0, a_par = 0, bs = 0, b_par = 0, as = 0, acc_par = 3;
-        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM, TNK);
             if (!it.valid) continue;
             sm100::mbar_wait(&sm.a_full[ab], a_par);
             const uint32_t a_lo = a_lo0 + ab * (uint32_t)(MT * nkb * (A_KB_BYTES >> 4));
-            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+            for (int c0 = it.c_begin; c0 < it.c_end; c0 += TNK) {
                 sm100::mbar_wait(&sm.acc_empty[as], (acc_par >> as) & 1);
                 acc_par ^= 1u << as;
                 sm100::tc_fence_after();
@@ -256,8 +300,8 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 #pragma unroll
                             for (int k = 0; k < KB_BYTES / 32; ++k) {    // UMMA K = 8 tf32 or 16 halves = 32 bytes; +2 = 32 B >> 4
                                 if constexpr (H16)
-                                    sm100::mma_f16(d_tmem + t * TN, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
-                                                   idesc, (kb | k) ? 1u : 0u);
+                                    mma16(d_tmem + t * TN, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
+                                          idesc, (kb | k) ? 1u : 0u);
                                 else
                                     sm100::mma_tf32(d_tmem + t * TN, sm100::smem_desc_join(al + 2 * k), sm100::smem_desc_join(bl + 2 * k),
                                                     idesc, (kb | k) ? 1u : 0u);
@@ -267,32 +311,41 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                             if (kb == nkb - 1) {                     // + r (hi + mid + lo) = -(s_q s_t / 2) ||b||^2, into every accumulator
                                 const uint64_t xd = sm100::smem_desc_join_hi(sm100::SMEM_DESC_HI_SW32, x_lo0 + as * (X_BYTES >> 4));
 #pragma unroll
-                                for (int t = 0; t < MT; ++t) sm100::mma_f16(d_tmem + t * TN, ax_desc, xd, idesc, 1u);
+                                for (int t = 0; t < MT; ++t) mma16(d_tmem + t * TN, ax_desc, xd, idesc, 1u);
                             }
                         }
-                        sm100::mma_commit(&sm.b_empty[bs]);
-                        if (kb == nkb - 1) sm100::mma_commit(&sm.acc_full[as]);
+                        if constexpr (PAIR) {
+                            sm100::mma_commit_2sm_mc(&sm.b_empty[bs], MC_MASK);
+                            if (kb == nkb - 1) sm100::mma_commit_2sm_mc(&sm.acc_full[as], MC_MASK);
+                        } else {
+                            sm100::mma_commit(&sm.b_empty[bs]);
+                            if (kb == nkb - 1) sm100::mma_commit(&sm.acc_full[as]);
+                        }
                     }
                     __syncwarp();
                     if (++bs == NBK) { bs = 0; b_par ^= 1; }
                 }
                 as ^= 1;
             }
-            if (sm100::elect_one()) sm100::mma_commit(&sm.a_empty[ab]);
+            if (sm100::elect_one()) {
+                if constexpr (PAIR) sm100::mma_commit_2sm_mc(&sm.a_empty[ab], MC_MASK);
+                else sm100::mma_commit(&sm.a_empty[ab]);
+            }
             __syncwarp();
             if (++ab == (uint32_t)nabuf) { ab = 0; a_par ^= 1; }
         }
-    } else {
+    } else if (warp < 8) {
         // ===================== epilogue: 8 warps, TMEM lane quarter = warp % 4, column half = warp / 4 =====================
         const int e = threadIdx.x;                 // 0..255
         const int quarter = warp & 3, half = warp >> 2;
         const int row_in_tile = quarter * 32 + lane;
-        constexpr int HC = TN / 2;                 // columns per half
+        constexpr int HC = TNK / 2;                // columns per half
+        constexpr int NCH = HC / 32;               // 32-column tcgen05.ld per warp and tile (PAIR: 4, all issued before any arithmetic)
         uint32_t acc_cnt = 0;
         const Window window = make_window(H16 ? q_info : nullptr, t_info, nkb * KB_ELEMS);
         const float neg2 = H16 ? -2.0f * __ldg(q_info + 1) * __ldg(t_info + 1) : -2.0f;     // -2 / (s_q s_t), exact
-        for (long long item = blockIdx.x; item < total_items; item += gridDim.x) {
-            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM);
+        for (long long item = first_item; item < total_items; item += item_stride) {
+            Item it = decode_item(item, pairs, tiles_max, S, backward, ROWS_ITEM, TNK);
             if (!it.valid) continue;
             // per-row state (one set per resident row tile): running top-2 of 16-column minima, append window, list cursor
             bool row_ok[MT];
@@ -302,7 +355,7 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
             int cnt[MT];
 #pragma unroll
             for (int t = 0; t < MT; ++t) {
-                const int row = it.r0 + t * TM + row_in_tile;
+                const int row = it.r0 + (PAIR ? (int)crank : t) * TM + row_in_tile;
                 row_ok[t] = row < it.n;
                 v1[t] = CUDART_INF_F; v2[t] = CUDART_INF_F;
                 win[t] = row_ok[t] ? window(__ldg(q_norm + it.q_off + row), __ldg(pmax + it.pair)) : -CUDART_INF_F;
@@ -316,25 +369,28 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                 const float half_ss = -1.0f / neg2;                  // s_q s_t / 2: the window in accumulator units
 #pragma unroll
                 for (int t = 0; t < MT; ++t) { v1[t] = NEG_BIG; v2[t] = NEG_BIG; win[t] *= half_ss; }
-                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TN) {
+                for (int c0 = it.c_begin; c0 < it.c_end; c0 += TNK) {
                     const uint32_t as = acc_cnt & 1;
-                    const bool tail = c0 + TN > it.c_end;            // columns past the pair's last train row: other images' rows
+                    const bool tail = c0 + TNK > it.c_end;           // columns past the pair's last train row: other images' rows
                     sm100::mbar_wait(&sm.acc_full[as], (acc_cnt >> 1) & 1);
                     sm100::tc_fence_after();
 #pragma unroll
                     for (int t = 0; t < MT; ++t) {
                         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * ACC_COLS + t * TN + half * HC;
-                        uint32_t acc[2][32];
-                        sm100::tmem_ld32(taddr, acc[0]);
-                        sm100::tmem_ld32(taddr + 32, acc[1]);
+                        uint32_t acc[NCH][32];
+#pragma unroll
+                        for (int ch = 0; ch < NCH; ++ch) sm100::tmem_ld32(taddr + 32 * ch, acc[ch]);
                         sm100::tmem_ld_wait();
                         if (t == MT - 1) {
                             sm100::tc_fence_before();
                             __syncwarp();
-                            if (lane == 0) sm100::mbar_arrive(&sm.acc_empty[as]);
+                            if (lane == 0) {
+                                if constexpr (PAIR) sm100::mbar_arrive_cluster(sm100::mapa_u32(sm100::smem_u32(&sm.acc_empty[as]), 0));
+                                else sm100::mbar_arrive(&sm.acc_empty[as]);
+                            }
                         }
 #pragma unroll
-                        for (int ch = 0; ch < 2; ++ch) {
+                        for (int ch = 0; ch < NCH; ++ch) {
                             const int colb = c0 + half * HC + ch * 32;
                             float y[32];
 #pragma unroll
@@ -434,7 +490,11 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
 
     sm100::tc_fence_before();
     __syncthreads();
-    if (warp == 9) sm100::tmem_dealloc<2 * ACC_COLS>(tmem_base);
+    if constexpr (PAIR) sm100::cluster_sync_all();         // the leader may still commit to this CTA's barriers until it is done too
+    if (warp == 9) {
+        if constexpr (PAIR) sm100::tmem_dealloc_2sm<2 * ACC_COLS>(tmem_base);
+        else sm100::tmem_dealloc<2 * ACC_COLS>(tmem_base);
+    }
 }
 
 // max ||b|| over the train rows of each pair (for the TF32 error window)
@@ -680,8 +740,24 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
         B200M_CAND_ATTR(false, 1, false); B200M_CAND_ATTR(false, 2, false); B200M_CAND_ATTR(true, 1, false);
         B200M_CAND_ATTR(true, 2, false); B200M_CAND_ATTR(true, 1, true); B200M_CAND_ATTR(true, 2, true);
 #undef B200M_CAND_ATTR
+        B200M_CUDA_CHECK(cudaFuncSetAttribute(l2_f32_cand_kernel<true, 1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem_bytes(MAX_NKB)), "l2_f32 smem attr");
+        // CTA pairs for the fp16 FOLD kernel: only if 2-CTA clusters of it cover every SM
+        cudaLaunchConfig_t qc = {};
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+        qc.gridDim = dim3((unsigned)(sms & ~1)); qc.blockDim = dim3(THREADS); qc.dynamicSmemBytes = smem_bytes(MAX_NKB / 2, true);
+        qc.attrs = qa; qc.numAttrs = 1;
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, l2_f32_cand_kernel<true, 1, true, true>, &qc) == cudaSuccess && nc * 2 >= sms &&
+            !getenv("B200M_NO_CLUSTER") && !getenv("B200M_NO_PAIR"))
+            once.val[dev][0] = nc;
+        else
+            cudaGetLastError();
         once.done[dev] = 1;
     }
+    const int pair_clusters = once.val[dev][0];
     // two resident row tiles per work item when both fit (nkb <= 4) and the pairs are tall enough to fill the SMs that way
     static const int mt_env = getenv("B200M_F32_MT") ? atoi(getenv("B200M_F32_MT")) : 0;
     const int MTr = mt_env ? mt_env : 2;
@@ -712,6 +788,22 @@ int launch_l2_f32_top2(const float* q_desc, const float* q_norm, int64_t q_rows,
     l2_f32_cand_kernel<H, M, F><<<grid, THREADS, smem_bytes(nkb, F), st>>>(tq, tt, tx, MODE, t_norm, pairs, total_items, tiles_max, S, \
                                                                           backward ? 1 : 0, nkb, q_norm, pmax, cand, cand_cnt, total_rows, QI, TI)
     if (h16) {
+        if (fold && MT == 2 && pair_clusters > 0) {
+            // the two row tiles of an item go to the two CTAs of a pair (same item count as MT == 2)
+            cudaLaunchConfig_t cfg = {};
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.gridDim = dim3((unsigned)((total_items < pair_clusters ? total_items : pair_clusters) * 2));
+            cfg.blockDim = dim3(THREADS);
+            cfg.dynamicSmemBytes = smem_bytes(nkb, true);
+            cfg.stream = st;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            const int fmode = 1, bw = backward ? 1 : 0;
+            cudaError_t e = cudaLaunchKernelEx(&cfg, l2_f32_cand_kernel<true, 1, true, true>, tq, tt, tx, fmode, t_norm, pairs, total_items,
+                                               tiles_max, S, bw, nkb, q_norm, pmax, cand, cand_cnt, total_rows, q_info, t_info);
+            B200M_CUDA_CHECK(e, "l2_f32_cand_kernel (CTA pairs) launch");
+        } else
         if (fold) { if (MT == 2) B200M_LAUNCH_CAND(true, 2, true, 1, q_info, t_info); else B200M_LAUNCH_CAND(true, 1, true, 1, q_info, t_info); }
         const int mode = fold ? 2 : 0;
         if (MT == 2) B200M_LAUNCH_CAND(true, 2, false, mode, q_info, t_info); else B200M_LAUNCH_CAND(true, 1, false, mode, q_info, t_info);

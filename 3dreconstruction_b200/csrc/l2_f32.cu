@@ -390,31 +390,52 @@ l2_f32_cand_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_cons
                             }
                         }
 #pragma unroll
+                        // (1) all 16-column group maxima of this warp's share of the tile FIRST, and the running top-2 over all
+                        //     of them, so that the tile's groups are tested against the tightest threshold available (any subset
+                        //     of groups gives a valid bound; the first tiles of a scan used to append most of their columns);
+                        // (2) a group that passes is walked in four 4-column steps, each behind its own maximum: one lane's
+                        //     row passing makes the whole warp walk, ~30 instructions now instead of ~50.
+                        if (tail) {
+#pragma unroll
+                            for (int ch = 0; ch < NCH; ++ch)
+#pragma unroll
+                                for (int i = 0; i < 32; ++i)
+                                    acc[ch][i] = c0 + half * HC + ch * 32 + i < it.c_end ? acc[ch][i] : __float_as_uint(NEG_BIG);
+                        }
+                        float hm[2 * NCH];
+#pragma unroll
                         for (int ch = 0; ch < NCH; ++ch) {
-                            const int colb = c0 + half * HC + ch * 32;
-                            float y[32];
+                            float h0 = __uint_as_float(acc[ch][0]), h1 = __uint_as_float(acc[ch][16]);
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) y[i] = __uint_as_float(acc[ch][i]);
-                            if (tail) {
-#pragma unroll
-                                for (int i = 0; i < 32; ++i) y[i] = colb + i < it.c_end ? y[i] : NEG_BIG;
+                            for (int i = 1; i < 16; ++i) {
+                                h0 = fmaxf(h0, __uint_as_float(acc[ch][i]));
+                                h1 = fmaxf(h1, __uint_as_float(acc[ch][16 + i]));
                             }
-                            float h0 = y[0], h1 = y[16];
-#pragma unroll
-                            for (int i = 1; i < 16; ++i) { h0 = fmaxf(h0, y[i]); h1 = fmaxf(h1, y[16 + i]); }
+                            hm[2 * ch] = h0; hm[2 * ch + 1] = h1;
                             v2[t] = fmaxf(v2[t], fminf(v1[t], h0)); v1[t] = fmaxf(v1[t], h0);
                             v2[t] = fmaxf(v2[t], fminf(v1[t], h1)); v1[t] = fmaxf(v1[t], h1);
-                            // rows past the pair (window -inf) never append; masked columns (NEG_BIG) never pass
-                            const float tau = row_ok[t] ? fmaxf(v2[t] - win[t], 0.5f * NEG_BIG) : CUDART_INF_F;
+                        }
+                        // rows past the pair (window -inf) never append; masked columns (NEG_BIG) never pass
+                        const float tau = row_ok[t] ? fmaxf(v2[t] - win[t], 0.5f * NEG_BIG) : CUDART_INF_F;
+#pragma unroll
+                        for (int ch = 0; ch < NCH; ++ch) {
 #pragma unroll
                             for (int g = 0; g < 2; ++g) {
-                                if ((g ? h1 : h0) >= tau) {
+                                if (hm[2 * ch + g] >= tau) {
+                                    const int colg = c0 + half * HC + ch * 32 + g * 16;
 #pragma unroll
-                                    for (int i = 0; i < 16; ++i) {
-                                        const float x = y[g * 16 + i];
-                                        const bool pass = x >= tau;
-                                        if (pass & (cnt[t] < KC)) list[t][cnt[t]] = make_float2(neg2 * x, __int_as_float(colb + g * 16 + i));
-                                        cnt[t] += pass;
+                                    for (int q = 0; q < 4; ++q) {
+                                        const float x0 = __uint_as_float(acc[ch][g * 16 + 4 * q]), x1 = __uint_as_float(acc[ch][g * 16 + 4 * q + 1]);
+                                        const float x2 = __uint_as_float(acc[ch][g * 16 + 4 * q + 2]), x3 = __uint_as_float(acc[ch][g * 16 + 4 * q + 3]);
+                                        if (fmaxf(fmaxf(x0, x1), fmaxf(x2, x3)) >= tau) {
+#pragma unroll
+                                            for (int i = 0; i < 4; ++i) {
+                                                const float x = i == 0 ? x0 : i == 1 ? x1 : i == 2 ? x2 : x3;
+                                                const bool pass = x >= tau;
+                                                if (pass & (cnt[t] < KC)) list[t][cnt[t]] = make_float2(neg2 * x, __int_as_float(colg + 4 * q + i));
+                                                cnt[t] += pass;
+                                            }
+                                        }
                                     }
                                 }
                             }
@@ -559,14 +580,29 @@ refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, in
     const int nlist = 2 * S;
     float m1 = CUDART_INF_F, m2 = CUDART_INF_F;
     bool overflow = false;
-    for (int l = 0; l < nlist; ++l) {
-        const long long lrow = (long long)l * total_rows + row;
-        const int c = __ldg(cand_cnt + lrow);
-        overflow |= c > KC;
-        float e = lane < min(c, KC) ? cand[lrow * KC + lane].x : CUDART_INF_F;
-        float hi = fmaxf(m1, e);
-        m1 = fminf(m1, e);
-        m2 = fminf(m2, hi);
+    // One column split (the usual case): both lists are fetched whole and unconditionally, together with the counts and the
+    // row's norm, so the warp's dependent global loads are two deep (lists, then the survivors' rows) instead of four
+    // (count -> entries -> entries again -> rows); this kernel is bound by that latency chain, not by bytes.
+    const bool two = nlist == 2;
+    float2 v0 = make_float2(CUDART_INF_F, 0.0f), v1 = v0;
+    int c0 = 0, c1 = 0;
+    if (two) {
+        c0 = __ldg(cand_cnt + row); c1 = __ldg(cand_cnt + total_rows + row);
+        const float2 w0 = cand[row * KC + lane], w1 = cand[(total_rows + row) * KC + lane];
+        overflow = c0 > KC || c1 > KC;
+        if (lane < min(c0, KC)) v0 = w0;
+        if (lane < min(c1, KC)) v1 = w1;
+        m1 = fminf(v0.x, v1.x); m2 = fmaxf(v0.x, v1.x);
+    } else {
+        for (int l = 0; l < nlist; ++l) {
+            const long long lrow = (long long)l * total_rows + row;
+            const int c = __ldg(cand_cnt + lrow);
+            overflow |= c > KC;
+            float e = lane < min(c, KC) ? cand[lrow * KC + lane].x : CUDART_INF_F;
+            float hi = fmaxf(m1, e);
+            m1 = fminf(m1, e);
+            m2 = fminf(m2, hi);
+        }
     }
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {
@@ -581,9 +617,15 @@ refine_f32_kernel(int backward, int need2, const DevPair* __restrict__ pairs, in
         const float win = make_window(q_info, t_info, Dh)(__ldg(q_norm + q_off + i), __ldg(pmax + p));
         const float bound = (need2 ? m2 : m1) + win;       // m2 == +inf with a single column: everything passes
         for (int l = 0; l < nlist; ++l) {
-            const long long lrow = (long long)l * total_rows + row;
-            const int c = min(__ldg(cand_cnt + lrow), KC);
-            float2 v = lane < c ? cand[lrow * KC + lane] : make_float2(CUDART_INF_F, 0.0f);
+            float2 v;
+            int c;
+            if (two) {
+                v = l ? v1 : v0; c = min(l ? c1 : c0, KC);   // (bound is +inf when the pair has a single train row)
+            } else {
+                const long long lrow = (long long)l * total_rows + row;
+                c = min(__ldg(cand_cnt + lrow), KC);
+                v = lane < c ? cand[lrow * KC + lane] : make_float2(CUDART_INF_F, 0.0f);
+            }
             unsigned mask = __ballot_sync(0xffffffffu, lane < c && v.x <= bound);
             while (mask) {
                 int src = __ffs(mask) - 1;

@@ -33,7 +33,7 @@ RATIO = 0.75
 HW_INT8_TOPS = 4590.0                 # burst issue-rate peak of tcgen05.mma kind::i8 at 1965 MHz (tools/mma_peak.cu, profiles/r01_mma_peak_microbench.txt)
 HW_INT8_TOPS_SUSTAINED = 3730.0       # the same instruction stream back to back for 6 s: the chip settles at its 1000 W cap,
                                       # SM clock ~1540 MHz (profiles/r01_mma_int8_sustained.txt) -- SURVEY 8(d)'s "measured int8 peak"
-NCU_DRAM_BYTES_PER_PAIR = (2700.3e6 + 269.0e6) / 2048.0    # ncu --set full of the shipped fold kernel, a 2048-pair launch of this workload (profiles/r02_l2i8_pair_v3_ncu_full.md)
+NCU_DRAM_BYTES_PER_PAIR = (2716.6e6 + 268.5e6) / 2048.0    # ncu --set full of the shipped fold kernel, a 2048-pair launch of this workload (profiles/r02_l2i8_pair_final_ncu_full.md)
 
 
 def parse_args():
@@ -882,7 +882,7 @@ def run_b200(args):
                              "algorithmic_hbm_bytes_per_pair": 2 * n * (D + 36) + 64 * n,
                              "traffic": NCU_DRAM_BYTES_PER_PAIR * my_pairs * args.steps / max(knn_launches.value, 1),
                              "traffic_source": "ncu --set full of the shipped l2_i8_fold_kernel (CTA pairs), one 2048-pair launch of this workload: dram read "
-                                               "2700.3 MB + write 269.0 MB (profiles/r02_l2i8_pair_v3_ncu_full.md) = 1.45 MB/pair, scaled to this run's "
+                                               "2716.6 MB + write 268.5 MB (profiles/r02_l2i8_pair_final_ncu_full.md) = 1.46 MB/pair, scaled to this run's "
                                                "pairs per launch; below the 3.2 MB/pair of algorithmic bytes because the store's rows are re-read from L2 "
                                                "(hit rate 93 %)"},
                 "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": int(host_pinned.numel() * 4),

@@ -9,8 +9,9 @@
 // same clock -- 16x the POPC bound, at the price of an 8x larger operand stream (256 B instead of 32 B per row).
 //
 // Kernel = the pipeline of l2_i8_fold_kernel (l2_i8.cu) without the norm: persistent warp-specialised CTAs in
-// clusters of two that share the train stream by TMA multicast, M128 x N256 tiles, NKB = Dbits / 128 K-blocks of
-// 128 int8, int32 accumulators double-buffered in TMEM.  All rows have the same norm, so the epilogue is a bare
+// clusters of two -- CTA pairs issuing cta_group::2 MMAs of M = 256 where the device co-schedules them everywhere (each
+// CTA keeps its half of the train tile), else TMA-multicast clusters or single CTAs with M = 128 -- N = 256 (240 for
+// e2m1) tiles, NKB = Dbits / 128 K-blocks of 128 int8, int32 accumulators double-buffered in TMEM.  All rows have the same norm, so the epilogue is a bare
 // 3-input MAX tree over the raw accumulators (larger a.b == closer).  Per 16-column chunk only the maximum
 // survives, packed with the chunk index into ONE int32 key ((a.b + 512) << 20 | ~chunk): the running top-2 of chunk
 // keys is two integer max/min instructions and orders chunks by (distance asc, first column asc) -- cv2's tie rule.

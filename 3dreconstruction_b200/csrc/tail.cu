@@ -347,6 +347,28 @@ __device__ __forceinline__ void bitonic(u64* a, int npad) {
     }
 }
 
+// one match (key = distance bits << 32 | query row) to output position o, in the caller's record format
+__device__ __forceinline__ void emit_match(u64 k, long long o, const int32_t* __restrict__ tbest_pair, int32_t* __restrict__ out_q,
+                                           int32_t* __restrict__ out_t, float* __restrict__ out_d, int rec_format,
+                                           void* __restrict__ out_rec) {
+    const int q = (int)(u32)k;
+    const int tr = tbest_pair[q];
+    const u32 dbits = (u32)(k >> 32);
+    if (rec_format == 0) {                               // three arrays (b200m_match_pairs / _csr)
+        out_q[o] = q;
+        out_t[o] = tr;
+        out_d[o] = __uint_as_float(dbits);
+    } else if (rec_format == B200M_REC_Q32T32D32) {      // one record per match (b200m_match_pairs_rec)
+        int32_t* r = (int32_t*)out_rec + 3 * o;
+        r[0] = q; r[1] = tr; r[2] = (int32_t)dbits;
+    } else if (rec_format == B200M_REC_Q16T16D32) {
+        ((uint2*)out_rec)[o] = make_uint2((u32)q | ((u32)tr << 16), dbits);
+    } else {                                             // B200M_REC_Q16T16D16: Hamming bit counts are small integers
+        unsigned short* r = (unsigned short*)out_rec + 3 * o;
+        r[0] = (unsigned short)q; r[1] = (unsigned short)tr; r[2] = (unsigned short)(int)__uint_as_float(dbits);
+    }
+}
+
 __global__ void __launch_bounds__(1024)
 sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
                  const int32_t* __restrict__ tbest, int smem_keys, int32_t* __restrict__ out_q,
@@ -393,27 +415,82 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
     if (sort_n > 1) bitonic(a, sort_n);
     __syncthreads();
     const int cnt = s_count;
-    for (int t = threadIdx.x; t < cnt; t += blockDim.x) {
-        u64 k = a[t];
-        int q = (int)(u32)k;
-        const int tr = tbest[pr.fwd_off + q];
-        const u32 dbits = (u32)(k >> 32);
-        const long long o = pr.out_off + t;
-        if (rec_format == 0) {                               // three arrays (b200m_match_pairs / _csr)
-            out_q[o] = q;
-            out_t[o] = tr;
-            out_d[o] = __uint_as_float(dbits);
-        } else if (rec_format == B200M_REC_Q32T32D32) {      // one record per match (b200m_match_pairs_rec)
-            int32_t* r = (int32_t*)out_rec + 3 * o;
-            r[0] = q; r[1] = tr; r[2] = (int32_t)dbits;
-        } else if (rec_format == B200M_REC_Q16T16D32) {
-            ((uint2*)out_rec)[o] = make_uint2((u32)q | ((u32)tr << 16), dbits);
-        } else {                                             // B200M_REC_Q16T16D16: Hamming bit counts are small integers
-            unsigned short* r = (unsigned short*)out_rec + 3 * o;
-            r[0] = (unsigned short)q; r[1] = (unsigned short)tr; r[2] = (unsigned short)(int)__uint_as_float(dbits);
-        }
-    }
+    for (int t = threadIdx.x; t < cnt; t += blockDim.x)
+        emit_match(a[t], pr.out_off + t, tbest + pr.fwd_off, out_q, out_t, out_d, rec_format, out_rec);
     if (threadIdx.x == 0) out_count[blockIdx.x] = cnt;
+}
+
+// ---- a handful of pairs (the plugin's one-pair call): one CTA per pair leaves the sort to a single SM -- 84 us of a
+// 150 us ORB 10k x 10k call (tools/orb_pair_probe.py), more than both tensor passes.  SPLIT_G CTAs per pair instead:
+// each compacts and sorts one segment of the pair's keys (sort_segments_kernel), then every CTA stages all SPLIT_G sorted
+// runs in shared memory and places ITS run's keys by rank: position = index in its own run + sum over the other runs of
+// the number of smaller keys (keys are unique: distance bits << 32 | query row), found by binary search.
+constexpr int SPLIT_G = 8;
+
+__global__ void __launch_bounds__(1024)
+sort_segments_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf, int32_t* __restrict__ segcnt) {
+    extern __shared__ u64 skeys[];
+    __shared__ int s_count;
+    const int p = blockIdx.x / SPLIT_G, sg = blockIdx.x - p * SPLIT_G;
+    const DevPair pr = pairs[p];
+    const int L = max(pr.npad / SPLIT_G, 1);                 // segment length (npad is a power of two)
+    u64* g = sortbuf + pr.sort_off + (size_t)sg * L;
+    const int lim = min(L, pr.n - sg * L);                   // rows of the pair inside this segment (may be <= 0)
+    if (threadIdx.x == 0) s_count = 0;
+    __syncthreads();
+    for (int t = threadIdx.x; t < lim; t += blockDim.x) {
+        const u64 k = g[t];
+        if (k != B200M_SENTINEL) skeys[atomicAdd(&s_count, 1)] = k;
+    }
+    __syncthreads();
+    const int c = s_count;
+    int sort_n = 1;
+    while (sort_n < c) sort_n <<= 1;
+    for (int t = c + threadIdx.x; t < sort_n; t += blockDim.x) skeys[t] = B200M_SENTINEL;
+    __syncthreads();
+    if (sort_n > 1) bitonic(skeys, sort_n);
+    __syncthreads();
+    for (int t = threadIdx.x; t < c; t += blockDim.x) g[t] = skeys[t];      // the sorted run, in place
+    if (threadIdx.x == 0) segcnt[blockIdx.x] = c;
+}
+
+__global__ void __launch_bounds__(1024)
+merge_emit_kernel(const DevPair* __restrict__ pairs, const u64* __restrict__ sortbuf, const int32_t* __restrict__ segcnt,
+                  const int32_t* __restrict__ tbest, int32_t* __restrict__ out_q, int32_t* __restrict__ out_t,
+                  float* __restrict__ out_d, int32_t* __restrict__ out_count, int rec_format, void* __restrict__ out_rec) {
+    extern __shared__ u64 skeys[];                           // the pair's SPLIT_G runs, run r at r * L
+    __shared__ int cnts[SPLIT_G];
+    const int p = blockIdx.x / SPLIT_G, sg = blockIdx.x - p * SPLIT_G;
+    const DevPair pr = pairs[p];
+    const int L = max(pr.npad / SPLIT_G, 1);
+    const u64* g = sortbuf + pr.sort_off;
+    if (threadIdx.x < SPLIT_G) cnts[threadIdx.x] = segcnt[p * SPLIT_G + threadIdx.x];
+    __syncthreads();
+    for (int r = 0; r < SPLIT_G; ++r)
+        for (int t = threadIdx.x; t < cnts[r]; t += blockDim.x) skeys[r * L + t] = g[(size_t)r * L + t];
+    __syncthreads();
+    const int mine = cnts[sg];
+    for (int x = threadIdx.x; x < mine; x += blockDim.x) {
+        const u64 k = skeys[sg * L + x];
+        int rank = x;
+#pragma unroll
+        for (int r = 0; r < SPLIT_G; ++r) {
+            if (r == sg) continue;
+            const u64* run = skeys + r * L;
+            int lo = 0, hi = cnts[r];                        // number of keys < k in run r
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (run[mid] < k) lo = mid + 1; else hi = mid;
+            }
+            rank += lo;
+        }
+        emit_match(k, pr.out_off + rank, tbest + pr.fwd_off, out_q, out_t, out_d, rec_format, out_rec);
+    }
+    if (sg == 0 && threadIdx.x == 0) {
+        int total = 0;
+        for (int r = 0; r < SPLIT_G; ++r) total += cnts[r];
+        out_count[p] = total;
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -478,6 +555,26 @@ int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npa
     // MODE_RATIO usually keeps a few percent of the rows: a 16 KiB slice (2048 keys) and 256 threads are enough, and such
     // a block fits beside a resident knn CTA of the next chunk.  Pairs that keep more (and the other modes, which keep
     // most rows) take the big shape: 128 KiB slice, 1024 threads.  A handful of pairs has nothing to overlap with: big only.
+    if (num_pairs <= 4 && max_npad >= 2048 && max_npad <= kMaxSmemKeys && !getenv("B200M_NO_SPLIT_SORT")) {
+        // a handful of pairs: SPLIT_G CTAs per pair (segment sorts, then placement by rank); segment counts live in the
+        // call's flag words [8, 8 + 4 SPLIT_G)
+        static_assert(8 + 4 * SPLIT_G <= 64, "segment counts fit the plan's flag words");
+        int32_t* segcnt = plan.flags + 8;
+        const int seg_keys = max_npad / SPLIT_G;
+        const int seg_threads = seg_keys >= 1024 ? 1024 : (seg_keys >= 256 ? 256 : 64);
+        if (!once.val[dev][0]) {
+            B200M_CUDA_CHECK(cudaFuncSetAttribute(merge_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  kMaxSmemKeys * (int)sizeof(u64)), "merge_emit smem attr");
+            once.val[dev][0] = 1;
+        }
+        sort_segments_kernel<<<num_pairs * SPLIT_G, seg_threads, (size_t)seg_keys * sizeof(u64), st>>>(plan.pairs, plan.sortbuf, segcnt);
+        B200M_CUDA_CHECK(cudaGetLastError(), "sort_segments_kernel launch");
+        merge_emit_kernel<<<num_pairs * SPLIT_G, seg_threads, (size_t)max_npad * sizeof(u64), st>>>(
+            plan.pairs, plan.sortbuf, segcnt, plan.tbest, out_q, out_t, out_d, out_count, rec_format, out_rec);
+        B200M_CUDA_CHECK(cudaGetLastError(), "merge_emit_kernel launch");
+        b200m_count_launch(2);
+        return B200M_OK;
+    }
     const bool few = mode == B200M_MODE_RATIO && num_pairs >= 64 && max_npad > 2048;
     const int big_keys = max_npad <= kMaxSmemKeys ? max_npad : kMaxSmemKeys;
     const int big_threads = max_npad >= 2048 ? 1024 : (max_npad >= 512 ? 256 : 64);

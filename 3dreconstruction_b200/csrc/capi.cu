@@ -21,17 +21,44 @@ int b200m_set_cuda_error(cudaError_t e, const char* where) {
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int pow2ceil(int n) { int p = 1; while (p < n) p <<= 1; return p; }
 
-static int choose_splits(int kind, int num_pairs, int max_n, int max_m, int mode, int sm_count) {
+// Column splits per pair.  `bound` (workspace sizing, no device at hand): an upper limit of what any device would pick.
+static int choose_splits(int kind, int num_pairs, int max_n, int max_m, int mode, int sm_count, bool bound = false) {
     // Enough CTAs for ~2 per SM; a single image pair has only ceil(n/128) row tiles.
     long long tiles = (long long)num_pairs * ((max_n + 127) / 128);
     if (mode == B200M_MODE_CROSS) tiles += (long long)num_pairs * ((max_m + 127) / 128);
-    long long want = 2LL * sm_count;
-    int S = (int)((want + tiles - 1) / (tiles > 0 ? tiles : 1));
     // keep >= 256 columns per split (>= 512 for L2_I8: four 128-column tiles, one per epilogue group)
     const int min_cols = kind == B200M_KIND_L2_I8 || kind == B200M_KIND_HAMMING_TC || kind == B200M_KIND_HAMMING_FP4 ? 512 : 256;
     int max_split = (((max_n < max_m ? max_n : max_m) + min_cols - 1) / min_cols);
+    if (max_split > 8) max_split = 8;
+    if (max_split < 1) max_split = 1;
+    if (bound) return tiles >= 2LL * 256 ? 1 : max_split;              // no device has more than 256 SMs
+    if (tiles >= 2LL * sm_count) return 1;
+    const bool paired = (kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO) || kind == B200M_KIND_HAMMING_TC ||
+                        kind == B200M_KIND_HAMMING_FP4;
+    if (paired) {
+        // The tensor kernels of these kinds are persistent: a cluster of two CTAs takes (pair, split, two row tiles) items in
+        // turn, so a small call takes rounds x (train tiles per item + ~2 tiles of per-item work).  A few more or fewer splits
+        // change the number of rounds: ORB 10k x 10k, 40 row-tile pairs on 74 clusters -- 2 splits are 2 rounds of 21 tiles,
+        // 3 splits 2 rounds of 14.  Each direction of a cross-check is its own launch.
+        const int units = sm_count / 2 > 0 ? sm_count / 2 : 1;
+        const int tn = kind == B200M_KIND_HAMMING_FP4 ? 240 : 256;
+        long long best_cost = -1;
+        int best = 1;
+        for (int S = 1; S <= max_split; ++S) {
+            long long cost = 0;
+            for (int dir = 0; dir < (mode == B200M_MODE_CROSS ? 2 : 1); ++dir) {
+                const int rows = dir ? max_m : max_n, cols = dir ? max_n : max_m;
+                const long long items = (long long)num_pairs * S * ((rows + 255) / 256);
+                const long long rounds = (items + units - 1) / units;
+                cost += rounds * (((cols + S - 1) / S + tn - 1) / tn + 2);
+            }
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = S; }
+        }
+        return best;
+    }
+    long long want = 2LL * sm_count;
+    int S = (int)((want + tiles - 1) / (tiles > 0 ? tiles : 1));
     if (S > max_split) S = max_split;
-    if (S > 8) S = 8;
     if (S < 1) S = 1;
     return S;
 }
@@ -157,11 +184,11 @@ int b200m_workspace_bytes(int kind, int mode, int num_pairs, int64_t total_n, in
                           int max_n, int max_m, int D, size_t* bytes) {
     (void)D;
     if (!bytes || num_pairs < 0 || total_n < 0 || total_m < 0) return B200M_EINVAL;
-    // Upper bounds that do not depend on the device: choose_splits is monotone in the SM count (<= 256
-    // assumed), sum pow2ceil(n) <= 2 * total_n + P.
+    // Upper bounds that do not depend on the device: choose_splits(..., bound = true) is an upper limit of the split count
+    // on any device (<= 256 SMs assumed), sum pow2ceil(n) <= 2 * total_n + P.
     MatchPlan pl;
     make_plan(pl, nullptr, kind, mode, num_pairs, total_n, total_m, 2 * total_n + num_pairs,
-              choose_splits(kind, num_pairs, max_n, max_m, mode, 256), mode == B200M_MODE_CROSS);
+              choose_splits(kind, num_pairs, max_n, max_m, mode, 256, true), mode == B200M_MODE_CROSS);
     *bytes = pl.bytes;
     return B200M_OK;
 }

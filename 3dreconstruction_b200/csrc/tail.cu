@@ -347,6 +347,17 @@ __device__ __forceinline__ void bitonic(u64* a, int npad) {
     }
 }
 
+// Slot of this lane's element in a block-wide compaction: one atomicAdd per warp on the shared counter (thousands of
+// single-lane atomics on one shared-memory word serialise).  Every lane of the warp must call.
+__device__ __forceinline__ int warp_compact_slot(bool live, int* counter) {
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
 // one match (key = distance bits << 32 | query row) to output position o, in the caller's record format
 __device__ __forceinline__ void emit_match(u64 k, long long o, const int32_t* __restrict__ tbest_pair, int32_t* __restrict__ out_q,
                                            int32_t* __restrict__ out_t, float* __restrict__ out_d, int rec_format,
@@ -391,12 +402,11 @@ sort_emit_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbuf,
     int sort_n;
     // compact the survivors into shared memory (order is irrelevant before the sort): the bitonic network then runs
     // over pow2ceil(#survivors) keys instead of pow2ceil(n), and the block needs only a small shared-memory slice
-    for (int t = threadIdx.x; t < n; t += blockDim.x) {
-        u64 k = g[t];
-        if (k != B200M_SENTINEL) {
-            int slot = atomicAdd(&s_count, 1);
-            if (slot < smem_keys) skeys[slot] = k;
-        }
+    for (int t0 = 0; t0 < n; t0 += blockDim.x) {
+        const int t = t0 + threadIdx.x;
+        const u64 k = t < n ? g[t] : B200M_SENTINEL;
+        const int slot = warp_compact_slot(k != B200M_SENTINEL, &s_count);
+        if (k != B200M_SENTINEL && slot < smem_keys) skeys[slot] = k;
     }
     __syncthreads();
     if (s_count <= lo_count || s_count > hi_count) return;
@@ -438,9 +448,11 @@ sort_segments_kernel(const DevPair* __restrict__ pairs, u64* __restrict__ sortbu
     const int lim = min(L, pr.n - sg * L);                   // rows of the pair inside this segment (may be <= 0)
     if (threadIdx.x == 0) s_count = 0;
     __syncthreads();
-    for (int t = threadIdx.x; t < lim; t += blockDim.x) {
-        const u64 k = g[t];
-        if (k != B200M_SENTINEL) skeys[atomicAdd(&s_count, 1)] = k;
+    for (int t0 = 0; t0 < lim; t0 += blockDim.x) {            // whole warps iterate together: one shared-memory atomic per warp
+        const int t = t0 + threadIdx.x;
+        const u64 k = t < lim ? g[t] : B200M_SENTINEL;
+        const int slot = warp_compact_slot(k != B200M_SENTINEL, &s_count);
+        if (k != B200M_SENTINEL) skeys[slot] = k;
     }
     __syncthreads();
     const int c = s_count;

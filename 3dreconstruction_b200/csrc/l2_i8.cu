@@ -32,18 +32,8 @@
 #include "common.cuh"
 #include "sm100.cuh"
 
-// how the 16 epilogue warps of the fold kernel wait for their accumulator: 0 = spin on mbarrier.try_wait (default),
-// 1 = try_wait with a suspend-time hint, 2 = spin with __nanosleep(32) back-off.  Measured in profiles/r02_notes.md.
-#ifndef B200M_EPI_WAIT_MODE
-#define B200M_EPI_WAIT_MODE 0
-#endif
-#if B200M_EPI_WAIT_MODE == 1
-#define B200M_EPI_WAIT(bar, par) sm100::mbar_wait_suspend(bar, par)
-#elif B200M_EPI_WAIT_MODE == 2
-#define B200M_EPI_WAIT(bar, par) do { while (!sm100::mbar_try_wait(bar, par)) __nanosleep(32); } while (0)
-#else
-#define B200M_EPI_WAIT(bar, par) sm100::mbar_wait(bar, par)
-#endif
+// (The fold kernel's epilogue warps spin on mbarrier.try_wait; a suspend-time hint and a __nanosleep back-off were measured
+// equal, profiles/r02_notes.md.)
 
 namespace {
 

@@ -233,11 +233,16 @@ __global__ void __launch_bounds__(256)
 finalize_kernel(int kind, int mode, double ratio, const DevPair* __restrict__ pairs, int blocks_per_pair,
                 const Top2* __restrict__ fwd, long long total_n, const Top2* __restrict__ bwd,
                 long long total_m, int S, u64* __restrict__ sortbuf, int32_t* __restrict__ tbest,
-                int32_t* __restrict__ counts, RefineI8 rf, const u32* __restrict__ colmin) {
+                int32_t* __restrict__ counts, RefineI8 rf, const u32* __restrict__ colmin, int rpw) {
+    // rpw = rows per warp: 32 (one per lane), or fewer for calls with a handful of pairs -- the exact recomputations of the
+    // fold path are whole-warp work done one row after the other (a memory round trip each), so a warp owning 32 rows of
+    // which half need one is a 16-deep latency chain while most SMs have nothing to run: lanes >= rpw own no row and only
+    // help (one SIFT 8192 x 8192 call: 34 -> ~10 us).
     int p = blockIdx.x / blocks_per_pair;
-    int i = (blockIdx.x - p * blocks_per_pair) * blockDim.x + threadIdx.x;
+    const int lane_ = threadIdx.x & 31;
+    int i = ((blockIdx.x - p * blocks_per_pair) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * rpw + lane_;
     DevPair pr = pairs[p];
-    const bool active = i < pr.n;
+    const bool active = lane_ < rpw && i < pr.n;
     Top2 t; t.k1 = B200M_SENTINEL; t.k2 = B200M_SENTINEL;
     const bool fold = kind == B200M_KIND_L2_I8 && mode == B200M_MODE_RATIO && rf.fold_flag && __ldg(rf.fold_flag);
     // S counts Top2 slices: splits x B200M_I8_GROUPS for the keyed L2_I8 kernel, splits x B200M_FOLD_SLICES when the fold kernel ran
@@ -540,12 +545,18 @@ int launch_finalize(int kind, int mode, double ratio, const MatchPlan& plan, int
                     int32_t* counts, const RefineI8& rf, cudaStream_t st) {
     // 128-thread blocks: small enough to share an SM with the persistent knn kernel of the next chunk
     const int threads = 128;
-    int bpp = (max_n + threads - 1) / threads;
+    int dev = 0, sms = 0;
+    if (!b200m_current_device(&dev, &sms)) return B200M_ENODEVICE;
+    // few rows in the whole call: spread them over more warps (see the kernel)
+    const long long warps32 = (long long)num_pairs * ((max_n + 31) / 32);
+    const int rpw = warps32 >= 16LL * sms ? 32 : (warps32 >= 4LL * sms ? 16 : 8);
+    const int rows_per_block = (threads / 32) * rpw;
+    int bpp = (max_n + rows_per_block - 1) / rows_per_block;
     long long grid = (long long)num_pairs * bpp;
     if (grid <= 0) return B200M_OK;
     if (grid > 0x7fffffffLL) return B200M_EUNSUPPORTED;
     finalize_kernel<<<(unsigned)grid, threads, 0, st>>>(kind, mode, ratio, plan.pairs, bpp, plan.fwd, plan.total_n,
-                                                    plan.bwd, plan.total_m, plan.slices, plan.sortbuf, plan.tbest, counts, rf, plan.colmin);
+                                                    plan.bwd, plan.total_m, plan.slices, plan.sortbuf, plan.tbest, counts, rf, plan.colmin, rpw);
     b200m_count_launch();
     B200M_CUDA_CHECK(cudaGetLastError(), "finalize_kernel launch");
     return B200M_OK;

@@ -344,6 +344,7 @@ l2_i8_top2_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 if (lane == 0) sm100::mbar_arrive(&sm.cb_empty[slot]);       // constants consumed
                 insert(min(m0, m1), base + CHUNK);
             }
+            tc_base += (uint32_t)it.ntiles;
             // publish this warp's partial top-2 (Top2 slice = split * NSLICE + slice); finalize merges the slices
             const int row = it.r0 + quarter * 32 + lane;
             if (row < it.n) {

@@ -578,9 +578,9 @@ int launch_sort_emit(int mode, const MatchPlan& plan, int num_pairs, int max_npa
     // MODE_RATIO usually keeps a few percent of the rows: a 16 KiB slice (2048 keys) and 256 threads are enough, and such
     // a block fits beside a resident knn CTA of the next chunk.  Pairs that keep more (and the other modes, which keep
     // most rows) take the big shape: 128 KiB slice, 1024 threads.  A handful of pairs has nothing to overlap with: big only.
-    if (num_pairs <= 4 && max_npad >= 2048 && max_npad <= kMaxSmemKeys && !getenv("B200M_NO_SPLIT_SORT")) {
-        // a handful of pairs: SPLIT_G CTAs per pair (segment sorts, then placement by rank); segment counts live in the
-        // call's flag words [8, 8 + 4 SPLIT_G)
+    if (num_pairs == 1 && max_npad >= 2048 && max_npad <= kMaxSmemKeys && !getenv("B200M_NO_SPLIT_SORT")) {
+        // the one-pair call (the only shape this path has been validated on): SPLIT_G CTAs for the pair (segment sorts, then
+        // placement by rank); segment counts live in the call's flag words [8, 8 + SPLIT_G)
         static_assert(8 + 4 * SPLIT_G <= 64, "segment counts fit the plan's flag words");
         int32_t* segcnt = plan.flags + 8;
         const int seg_keys = max_npad / SPLIT_G;
